@@ -1,0 +1,194 @@
+/* include/mcpt.h -- C ABI of libmcpt.so, the B200 (sm_100a) drop-in for the render loop of
+ * luotong96/Monte_Carlo_Path_Tracing.
+ *
+ * The reference has no plugin/FFI interface: its "API" is the pixel/sample loop of main()
+ * (main.cpp:557-588) calling RadianceRGB shade*(intersec_result, vec) (main.cpp:269,348,402)
+ * on two file-scope globals, `Myobj veach` and `Mylight lights` (main.cpp:23-24).  The seam cut
+ * here is that whole loop: inputs = what Myobj / Mylight hold after read() + gather_light_triangles()
+ * (main.cpp:500-504) flattened to plain arrays + the camera literals (main.cpp:507-553) + the
+ * loop constants (resolution, spp, which shade*), output = the film `buffer[i][j]` (main.cpp:496,582)
+ * as linear radiance.  Plain pointers and sizes only; no C++ or torch types.  Every entry point
+ * returns 0 on success or a negative McptError and never calls exit() (the reference exit(1)s on
+ * loader failure, Myobj.cpp:15-20, Mylight.cpp:16-20); mcpt_last_error() gives the message.
+ *
+ * One host thread per McptScene.  All pointers are HOST pointers unless named d_*.
+ */
+#ifndef MCPT_H
+#define MCPT_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MCPT_VERSION 100
+
+typedef enum McptError {
+    MCPT_OK = 0,
+    MCPT_ERR_INVALID = -1,        /* bad argument / malformed scene */
+    MCPT_ERR_CUDA = -2,           /* CUDA runtime error (message in mcpt_last_error) */
+    MCPT_ERR_NO_DEVICE = -3,      /* no CUDA device: there is NO CPU fallback */
+    MCPT_ERR_IO = -4,             /* file not found / parse error (host loaders) */
+    MCPT_ERR_QUEUE_OVERFLOW = -5, /* MIS path-tree outgrew the ray queue; retry with smaller batch_spp */
+    MCPT_ERR_OOM = -6
+} McptError;
+
+/* Which shade* body runs (main.cpp:269 / 348 / 402).  Same numbering as oracle/mcpt_oracle.h. */
+typedef enum McptStrategy {
+    MCPT_NEE_SPHERICAL = 0, /* shade(): 1 spherical-triangle light sample + 1 BRDF sample (main.cpp:298) */
+    MCPT_BRDF_ONLY = 1,     /* shade_with_brdf() */
+    MCPT_MIS = 2,           /* shade_with_mis(): both samples recursed, balance heuristic (path tree, F6) */
+    MCPT_NEE_UNIFORM = 3    /* shade() with the uniform-area sampler of the commented line main.cpp:297 */
+} McptStrategy;
+
+/* flags: 0 == the reference's estimators as written (F8, F9 reproduced).  The stale-MIS-state bug
+ * F10 (Mylight scratch overwritten by recursion #1, main.cpp:443/464/487) is never reproduced: the
+ * light pdf is always evaluated for the current vertex (== oracle flag ORACLE_FIX_STALE_MIS). */
+enum {
+    MCPT_FIX_NEE_MEASURE = 2,  /* F9: NEE_SPHERICAL uses the solid-angle estimator Le f cos / pdf */
+    MCPT_FIX_MIXTURE_PDF = 4,  /* F8: BRDF-sampled directions are weighted with the mixture pdf */
+    MCPT_JITTER = 16,          /* uniform sub-pixel jitter (the reference has none, F4) */
+    MCPT_ACCUMULATE = 64       /* mcpt_render_device: add into d_out instead of overwriting */
+};
+
+/* Flattened Myobj + Mylight.  prim = shape_offset[s] + f for the reference's (s,f) (Myobj.h:44-66). */
+typedef struct McptSceneDesc {
+    uint32_t num_prims;       /* P  triangles (tinyobj triangulates, tiny_obj_loader.h:509-531) */
+    uint32_t num_shapes;      /* S */
+    uint32_t num_materials;   /* M */
+    uint32_t num_lights;      /* L  emissive triangles (Mylight::lightsTriangles, Mylight.h:108) */
+    uint32_t num_classes;     /* C  <light> nodes (Mylight::lightsRadiance, Mylight.h:106) */
+    const float* positions;   /* [P][3][3] get_vertexes_of_facet (Myobj.cpp:626-650); tinyobj real_t = float */
+    const float* normals;     /* [P][3][3] get_normals_of_facet (Myobj.cpp:653-678) */
+    const int32_t* material_id;   /* [P] mesh.material_ids[f] (main.cpp:292) */
+    const uint32_t* shape_offset; /* [S+1] */
+    const float* mat_kd;      /* [M][3] material_t::diffuse */
+    const float* mat_ks;      /* [M][3] material_t::specular */
+    const float* mat_ns;      /* [M]    material_t::shininess */
+    const int32_t* light_prim;    /* [L] in the reference's iteration order: class (mtlname ascending,
+                                     std::map), then gather order (s,f ascending) (Mylight.cpp:41-86,169-173) */
+    const int32_t* light_class;   /* [L] non-decreasing */
+    const double* class_radiance; /* [C][3] RadianceRGB(std::string) = stod (RadianceRGB.cpp:17-27) */
+} McptSceneDesc;
+
+/* Camera exactly as main.cpp:546-553 parametrises it: dir(i,j) = normalize(T * (-pl*(i-(H-1)/2),
+ * pl*(j-(W-1)/2), |w|)), T = [U V N], N = w/|w|, V = normalize(N x up), U = normalize(V x N). */
+typedef struct McptCamera {
+    double eye[3];
+    double w[3];      /* lookat - eye, NOT normalised (|w| enters the formula) */
+    double up[3];
+    double pixellen;  /* tan(fovy/2) * |w| / (H/2); the reference's literal is F7 */
+} McptCamera;
+
+typedef struct McptRenderParams {
+    int32_t width, height;
+    int32_t spp;         /* samples per pixel rendered by THIS call */
+    int32_t spp_offset;  /* global index of the first sample (spp sharding across GPUs) */
+    int32_t spp_total;   /* normalisation: out = sum / spp_total (main.cpp:575 `* 0.1` at 10 spp); 0 -> spp */
+    int32_t max_depth;   /* RR forced to fail at vertices of depth >= max_depth; <=0 unlimited (F5) */
+    int32_t strategy;    /* McptStrategy */
+    uint32_t flags;
+    uint64_t seed;
+    float p_rr;          /* 0 -> 0.6 (main.cpp:321,375,429) */
+    int32_t batch_spp;   /* samples per pixel in flight per wavefront pass; 0 -> auto */
+} McptRenderParams;
+
+typedef struct McptStats {
+    uint64_t paths;          /* primary samples = W*H*spp */
+    uint64_t primary_hits;
+    uint64_t vertices;       /* sample-bounces: non-emissive vertices shaded (RR draws) */
+    uint64_t rays_closest;   /* closest-hit rays traced (primary rays counted once per pixel if no jitter) */
+    uint64_t rays_shadow;    /* NEE visibility rays */
+    uint64_t rays_light;     /* light-only rays (MIS light pdf, main.cpp:484) */
+    uint32_t passes;         /* wavefront passes (batches) */
+    uint32_t bounces;        /* kernel bounce iterations summed over passes */
+    uint32_t kernel_launches;
+    uint32_t queue_peak;     /* largest ray-queue length seen */
+    float ms_total;          /* device time of the call, CUDA events on the launch stream */
+    float ms_bounce;         /* time in the bounce (extend+shade) kernels */
+    float ms_other;
+} McptStats;
+
+typedef struct McptScene McptScene;
+
+/* ---- scene --------------------------------------------------------------------------------- */
+/* Copies the arrays, computes geometric normals (get_unique_normal_of_facet, Myobj.cpp:680-709) and
+ * light areas/CDFs (Mylight.cpp:66-69,112-135), builds the SAH BVHs (replacing cal_scene_boundingbox +
+ * meshing, Myobj.cpp:78-162) and uploads everything to `device`.  Caller keeps its arrays. */
+int mcpt_scene_create(const McptSceneDesc* desc, int device, McptScene** out);
+void mcpt_scene_destroy(McptScene* scene);
+/* bytes of scene data resident on the device / re-upload them (used by the e2e timing) */
+size_t mcpt_scene_device_bytes(const McptScene* scene);
+int mcpt_scene_upload(McptScene* scene);
+
+/* ---- render: the replacement for main.cpp:557-588 ----------------------------------------------
+ * out_rgb: W*H*3 floats, row-major like buffer[i][j] (i = row), linear radiance (no tone mapping). */
+int mcpt_render(McptScene* scene, const McptCamera* cam, const McptRenderParams* params, float* out_rgb,
+                McptStats* stats);
+/* Same, output left on the device (d_out_rgb: W*H*3 floats) and launched on `stream` (a cudaStream_t,
+ * NULL = default) so callers can chain an NCCL reduce; returns after the work is enqueued AND complete. */
+int mcpt_render_device(McptScene* scene, const McptCamera* cam, const McptRenderParams* params, float* d_out_rgb,
+                       void* stream, McptStats* stats);
+/* RadianceRGB::tone_mapping (RadianceRGB.cpp:51-67) on the device: rgb8 = clamp(floor(255*(L/Lmax)^g+.5)) */
+int mcpt_tonemap(McptScene* scene, const float* rgb, size_t num_pixels, double max_radiance, double gamma,
+                 uint8_t* out_rgb8);
+
+/* ---- deterministic parity entry points (explicit uniforms in, values out) ------------------------
+ * precision: 0 = FP64 device code in the reference's expression order, 1 = the FP32 code the renderer runs. */
+/* Myobj::intersect_with_triangle (Myobj.cpp:165-192) */
+int mcpt_intersect_tri_batch(McptScene*, size_t n, const double* ro, const double* rd, const int32_t* prim,
+                             int precision, int32_t* hit, double* bgt);
+/* closest hit over all prims except `exclude` (Myobj::closet_ray_intersect, Myobj.cpp:334-474) or, with
+ * light_only, over emissive prims (closet_ray_intersect_light_triangle, :476-622); semantics = exhaustive
+ * search with strict < on t and ascending prim order (Myobj.cpp:194-213).  prim = -1 on miss. */
+int mcpt_intersect_batch(McptScene*, size_t n, const double* ro, const double* rd, const int32_t* exclude,
+                         int light_only, int precision, int32_t* prim, double* bgt);
+/* BRDF::get_brdf_phong / sample_from_phong / eval_sample_from_phong_pdf (BRDF.cpp:17-132) */
+int mcpt_phong_eval_batch(McptScene*, size_t n, const double* N, const double* wi, const double* wr,
+                          const double* kd, const double* ks, const double* ns, int precision, double* rgb);
+int mcpt_phong_sample_batch(McptScene*, size_t n, const double* N, const double* wr, const double* kd,
+                            const double* ks, const double* ns, const double* u3, int precision, double* dir,
+                            double* pdf);
+int mcpt_phong_pdf_batch(McptScene*, size_t n, const double* N, const double* wi, const double* wr,
+                         const double* kd, const double* ks, const double* ns, int precision, double* pdf);
+/* Mylight::select_a_point_from_lights (Mylight.cpp:102-160); u4 = (u_class, u_tri, xi1, xi2) consumed in the
+ * reference's order (u_class / u_tri skipped when there is one class / one triangle) */
+int mcpt_light_sample_uniform_batch(McptScene*, size_t n, const double* u4, int precision, int32_t* prim,
+                                    double* point, double* Le, double* pdf);
+/* prepared_for_lights_spherical_triangle_sampling + lights_spherical_triangle_sampling +
+ * eval_spherical_triangle_sampling_pdf(query) (Mylight.cpp:322-493; one-shot variant :163-318 is the same
+ * arithmetic).  u3 = (u_tri, xi1, xi2); out: chosen prim, point on the light, Le, pdf (solid angle),
+ * weights_sum, number of surviving spherical triangles, pdf of `query` prim at this vertex. */
+int mcpt_light_sample_spherical_batch(McptScene*, size_t n, const double* x1, const double* N, const double* u3,
+                                      const int32_t* query, int precision, int32_t* prim, double* point, double* Le,
+                                      double* pdf, double* wsum, int32_t* nsurv, double* query_pdf);
+
+/* ---- introspection ---------------------------------------------------------------------------- */
+/* geometric normals [P][3] and light areas [L] as computed at scene_create (FP64) */
+int mcpt_scene_geom_normals(const McptScene*, double* out_P3);
+int mcpt_scene_light_areas(const McptScene*, double* out_L);
+/* BVH summary: nodes, leaves, max depth, SAH cost (for tests and DESIGN.md) */
+int mcpt_scene_bvh_info(const McptScene*, int which /*0 scene, 1 lights*/, uint32_t* nodes, uint32_t* leaves,
+                        uint32_t* max_depth, double* sah_cost);
+/* Host-only (no GPU needed): build the SAH BVH for `desc` (all prims, or the emissive ones) and validate it:
+ * every prim appears in exactly one leaf, every triangle lies inside its leaf box, every child box inside its
+ * parent's.  out4 = {nodes, leaves, max_depth, errors}. */
+int mcpt_host_bvh_check(const McptSceneDesc* desc, int lights_only, uint32_t out4[4], double* sah_cost);
+const char* mcpt_last_error(void);
+int mcpt_version(void);
+int mcpt_device_count(void);
+
+/* ---- host loaders: the host-side mirror of Myobj / Mylight (csrc/host_scene.h) -------------------
+ * Parses <stem>.obj (+ its mtllib) and <stem>.xml like Myobj::read / Mylight::read +
+ * gather_light_triangles (Myobj.cpp:10-28, Mylight.cpp:11-100) and hands back a flat desc whose arrays
+ * live until mcpt_host_scene_free.  has_camera = 0 if the XML has no <camera> node (README.md:339-343). */
+typedef struct McptHostScene McptHostScene;
+int mcpt_host_scene_load(const char* obj_path, const char* xml_path, McptHostScene** out);
+const McptSceneDesc* mcpt_host_scene_desc(const McptHostScene*);
+int mcpt_host_scene_camera(const McptHostScene*, McptCamera* cam, int32_t* width, int32_t* height, double* fovy_deg);
+void mcpt_host_scene_free(McptHostScene*);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MCPT_H */

@@ -1,0 +1,410 @@
+// csrc/api.cu -- C ABI: scene lifetime, upload, introspection, host loaders, render entry points.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <numeric>
+#include "mcpt_internal.h"
+
+namespace mcpt {
+static thread_local std::string g_last_error;
+void set_last_error(const std::string& msg) { g_last_error = msg; }
+
+namespace {
+struct BlobLayout {
+    size_t off_nodes, off_tris, off_lnodes, off_ltris, off_pverts, off_pnorms, off_mats, off_lights, off_lng64, off_larea64,
+        off_crad64, off_class_begin, off_class_cdf, off_tri_cdf, total;
+};
+size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
+
+void validate(const McptSceneDesc* d)
+{
+    if (!d) throw Error(MCPT_ERR_INVALID, "null scene description");
+    if (d->num_prims == 0) throw Error(MCPT_ERR_INVALID, "scene has no triangles");
+    if (!d->positions || !d->normals || !d->material_id || !d->mat_kd || !d->mat_ks || !d->mat_ns)
+        throw Error(MCPT_ERR_INVALID, "scene description has null geometry/material arrays");
+    if (d->num_lights && (!d->light_prim || !d->light_class || !d->class_radiance))
+        throw Error(MCPT_ERR_INVALID, "scene description has null light arrays");
+    for (uint32_t p = 0; p < d->num_prims; p++)
+        if (d->material_id[p] < 0 || (uint32_t)d->material_id[p] >= d->num_materials)
+            throw Error(MCPT_ERR_INVALID, "material_id out of range (the reference's materials.at() would throw, main.cpp:292)");
+    int prev = 0;
+    std::vector<int> per_class(d->num_classes, 0);
+    for (uint32_t l = 0; l < d->num_lights; l++) {
+        if (d->light_prim[l] < 0 || (uint32_t)d->light_prim[l] >= d->num_prims) throw Error(MCPT_ERR_INVALID, "light_prim out of range");
+        int c = d->light_class[l];
+        if (c < 0 || (uint32_t)c >= d->num_classes || c < prev) throw Error(MCPT_ERR_INVALID, "light_class must be non-decreasing and < num_classes");
+        prev = c;
+        per_class[c]++;
+    }
+    for (uint32_t c = 0; c < d->num_classes; c++)
+        if (per_class[c] == 0)
+            throw Error(MCPT_ERR_INVALID, "a <light> class has no triangles (lightsTriangles.at() throws in the reference, Mylight.cpp:126)");
+}
+}  // namespace
+}  // namespace mcpt
+
+using namespace mcpt;
+
+extern "C" {
+
+const char* mcpt_last_error(void) { return g_last_error.c_str(); }
+int mcpt_version(void) { return MCPT_VERSION; }
+int mcpt_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int mcpt_scene_upload(McptScene* s)
+{
+    return guarded([&] {
+        if (!s) throw Error(MCPT_ERR_INVALID, "null scene");
+        MCPT_CUDA(cudaSetDevice(s->device));
+        MCPT_CUDA(cudaMemcpy(s->d_blob, s->h_blob, s->blob_bytes, cudaMemcpyHostToDevice));
+    });
+}
+
+size_t mcpt_scene_device_bytes(const McptScene* s) { return s ? s->blob_bytes : 0; }
+
+int mcpt_scene_create(const McptSceneDesc* desc, int device, McptScene** out)
+{
+    if (out) *out = nullptr;
+    McptScene* s = nullptr;
+    int rc = guarded([&] {
+        if (!out) throw Error(MCPT_ERR_INVALID, "null output pointer");
+        validate(desc);
+        int ndev = 0;
+        if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+            cudaGetLastError();
+            throw Error(MCPT_ERR_NO_DEVICE, "no CUDA device available: libmcpt has no CPU fallback");
+        }
+        if (device < 0 || device >= ndev) throw Error(MCPT_ERR_INVALID, "device index out of range");
+        MCPT_CUDA(cudaSetDevice(device));
+        s = new McptScene();
+        s->device = device;
+        const uint32_t P = desc->num_prims, L = desc->num_lights, C = desc->num_classes, Mn = desc->num_materials;
+        s->P = P; s->S = desc->num_shapes; s->Mn = Mn; s->L = L; s->C = C;
+        s->positions.assign(desc->positions, desc->positions + (size_t)P * 9);
+        s->normals.assign(desc->normals, desc->normals + (size_t)P * 9);
+        s->material_id.assign(desc->material_id, desc->material_id + P);
+        if (L) {
+            s->light_prim.assign(desc->light_prim, desc->light_prim + L);
+            s->light_class.assign(desc->light_class, desc->light_class + L);
+            s->class_radiance.assign(desc->class_radiance, desc->class_radiance + (size_t)C * 3);
+        }
+        // geometric normals (Myobj.cpp:680-709) and light areas (Mylight.cpp:66-69), FP64
+        s->geom_normals.resize((size_t)P * 3);
+        for (uint32_t p = 0; p < P; p++) {
+            dvec g = unique_normal(&s->positions[(size_t)p * 9], &s->normals[(size_t)p * 9]);
+            for (int c = 0; c < 3; c++) s->geom_normals[(size_t)p * 3 + c] = g[c];
+        }
+        s->light_area.resize(L);
+        for (uint32_t l = 0; l < L; l++) {
+            const float* v = &s->positions[(size_t)s->light_prim[l] * 9];
+            double e1[3], e2[3], n[3];
+            for (int c = 0; c < 3; c++) { e1[c] = (double)v[3 + c] - (double)v[c]; e2[c] = (double)v[6 + c] - (double)v[c]; }
+            n[0] = e1[1] * e2[2] - e1[2] * e2[1]; n[1] = e1[2] * e2[0] - e1[0] * e2[2]; n[2] = e1[0] * e2[1] - e1[1] * e2[0];
+            double len = std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+            double inv = 1.0 / len;
+            double u[3] = {n[0] * inv, n[1] * inv, n[2] * inv};
+            double ans = 0;
+            for (int c = 0; c < 3; c++) ans += n[c] * u[c];
+            s->light_area[l] = 0.5 * ans;
+        }
+        // BVHs
+        std::vector<int32_t> all(P);
+        std::iota(all.begin(), all.end(), 0);
+        s->bvh = build_bvh(s->positions.data(), all.data(), P);
+        std::vector<int32_t> lp(s->light_prim);
+        std::sort(lp.begin(), lp.end());
+        s->lbvh = build_bvh(s->positions.data(), lp.data(), lp.size());
+        s->extent = std::max({s->bvh.hi[0] - s->bvh.lo[0], s->bvh.hi[1] - s->bvh.lo[1], s->bvh.hi[2] - s->bvh.lo[2], 1e-30f});
+
+        // pack the blob
+        BlobLayout B;
+        size_t o = 0;
+        auto place = [&](size_t bytes) { size_t at = o; o = align_up(o + std::max<size_t>(bytes, 16)); return at; };
+        B.off_nodes = place(s->bvh.nodes.size() * sizeof(BvhNode));
+        B.off_tris = place(s->bvh.tris.size() * sizeof(f4));
+        B.off_lnodes = place(s->lbvh.nodes.size() * sizeof(BvhNode));
+        B.off_ltris = place(s->lbvh.tris.size() * sizeof(f4));
+        B.off_pverts = place((size_t)P * 3 * 16);
+        B.off_pnorms = place((size_t)P * 3 * 16);
+        B.off_mats = place((size_t)Mn * 2 * 16);
+        B.off_lights = place((size_t)L * 5 * 16);
+        B.off_lng64 = place((size_t)L * 3 * 8);
+        B.off_larea64 = place((size_t)L * 8);
+        B.off_crad64 = place((size_t)C * 3 * 8);
+        B.off_class_begin = place((size_t)(C + 1) * 4);
+        B.off_class_cdf = place((size_t)C * 4);
+        B.off_tri_cdf = place((size_t)L * 4);
+        B.total = o;
+        s->blob_bytes = B.total;
+        MCPT_CUDA(cudaMallocHost(&s->h_blob, B.total));
+        std::memset(s->h_blob, 0, B.total);
+        char* hb = (char*)s->h_blob;
+        std::memcpy(hb + B.off_nodes, s->bvh.nodes.data(), s->bvh.nodes.size() * sizeof(BvhNode));
+        std::memcpy(hb + B.off_tris, s->bvh.tris.data(), s->bvh.tris.size() * sizeof(f4));
+        std::memcpy(hb + B.off_lnodes, s->lbvh.nodes.data(), s->lbvh.nodes.size() * sizeof(BvhNode));
+        std::memcpy(hb + B.off_ltris, s->lbvh.tris.data(), s->lbvh.tris.size() * sizeof(f4));
+        std::vector<int32_t> light_of_prim(P, -1);
+        for (uint32_t l = 0; l < L; l++) light_of_prim[s->light_prim[l]] = (int32_t)l;
+        f4* pv = (f4*)(hb + B.off_pverts);
+        f4* pn = (f4*)(hb + B.off_pnorms);
+        for (uint32_t p = 0; p < P; p++) {
+            const float* v = &s->positions[(size_t)p * 9];
+            const float* n = &s->normals[(size_t)p * 9];
+            for (int k = 0; k < 3; k++) {
+                pv[3 * p + k] = f4{v[3 * k], v[3 * k + 1], v[3 * k + 2], 0.f};
+                pn[3 * p + k] = f4{n[3 * k], n[3 * k + 1], n[3 * k + 2], 0.f};
+            }
+            std::memcpy(&pv[3 * p + 0].w, &s->material_id[p], 4);
+            std::memcpy(&pv[3 * p + 1].w, &light_of_prim[p], 4);
+        }
+        f4* mt = (f4*)(hb + B.off_mats);
+        for (uint32_t m = 0; m < Mn; m++) {
+            mt[2 * m + 0] = f4{desc->mat_kd[3 * m], desc->mat_kd[3 * m + 1], desc->mat_kd[3 * m + 2], desc->mat_ns[m]};
+            mt[2 * m + 1] = f4{desc->mat_ks[3 * m], desc->mat_ks[3 * m + 1], desc->mat_ks[3 * m + 2], 0.f};
+        }
+        f4* lt = (f4*)(hb + B.off_lights);
+        double* lng = (double*)(hb + B.off_lng64);
+        double* lar = (double*)(hb + B.off_larea64);
+        double* crd = (double*)(hb + B.off_crad64);
+        int32_t* cb = (int32_t*)(hb + B.off_class_begin);
+        float* ccdf = (float*)(hb + B.off_class_cdf);
+        float* tcdf = (float*)(hb + B.off_tri_cdf);
+        for (uint32_t c = 0; c < C * 3; c++) crd[c] = s->class_radiance[c];
+        for (uint32_t l = 0; l < L; l++) {
+            int32_t prim = s->light_prim[l], cls = s->light_class[l];
+            const float* v = &s->positions[(size_t)prim * 9];
+            const double* g = &s->geom_normals[(size_t)prim * 3];
+            const double* r = &s->class_radiance[(size_t)cls * 3];
+            lt[5 * l + 0] = f4{v[0], v[1], v[2], 0.f};
+            lt[5 * l + 1] = f4{v[3], v[4], v[5], 0.f};
+            lt[5 * l + 2] = f4{v[6], v[7], v[8], (float)s->light_area[l]};
+            lt[5 * l + 3] = f4{(float)g[0], (float)g[1], (float)g[2], (float)(r[0] + r[1] + r[2])};
+            lt[5 * l + 4] = f4{(float)r[0], (float)r[1], (float)r[2], 0.f};
+            std::memcpy(&lt[5 * l + 0].w, &prim, 4);
+            std::memcpy(&lt[5 * l + 1].w, &cls, 4);
+            for (int c = 0; c < 3; c++) lng[3 * l + c] = g[c];
+            lar[l] = s->light_area[l];
+        }
+        // class ranges + the two discrete distributions of Mylight.cpp:112-135 as cumulative tables
+        for (uint32_t c = 0; c <= C; c++) cb[c] = 0;
+        for (uint32_t l = 0; l < L; l++) cb[s->light_class[l] + 1] = (int32_t)l + 1;
+        for (uint32_t c = 1; c <= C; c++) cb[c] = std::max(cb[c], cb[c - 1]);
+        double csum = 0;
+        for (uint32_t c = 0; c < C; c++) csum += crd[3 * c] + crd[3 * c + 1] + crd[3 * c + 2];
+        double acc = 0;
+        for (uint32_t c = 0; c < C; c++) {
+            acc += (crd[3 * c] + crd[3 * c + 1] + crd[3 * c + 2]) / csum;
+            ccdf[c] = (c + 1 == C) ? 1.0f : (float)acc;
+            double asum = 0, a2 = 0;
+            for (int32_t l = cb[c]; l < cb[c + 1]; l++) asum += s->light_area[l];
+            for (int32_t l = cb[c]; l < cb[c + 1]; l++) {
+                a2 += s->light_area[l] / asum;
+                tcdf[l] = (l + 1 == cb[c + 1]) ? 1.0f : (float)a2;
+            }
+        }
+        MCPT_CUDA(cudaMalloc(&s->d_blob, B.total));
+        char* db = (char*)s->d_blob;
+        DScene& d = s->d;
+        d.nodes = (const float4*)(db + B.off_nodes); d.tris = (const float4*)(db + B.off_tris);
+        d.lnodes = (const float4*)(db + B.off_lnodes); d.ltris = (const float4*)(db + B.off_ltris);
+        d.pverts = (const float4*)(db + B.off_pverts); d.pnorms = (const float4*)(db + B.off_pnorms);
+        d.mats = (const float4*)(db + B.off_mats); d.lights = (const float4*)(db + B.off_lights);
+        d.lng64 = (const double*)(db + B.off_lng64); d.larea64 = (const double*)(db + B.off_larea64);
+        d.crad64 = (const double*)(db + B.off_crad64); d.class_begin = (const int32_t*)(db + B.off_class_begin);
+        d.class_cdf = (const float*)(db + B.off_class_cdf); d.tri_cdf = (const float*)(db + B.off_tri_cdf);
+        d.P = (int32_t)P; d.L = (int32_t)L; d.C = (int32_t)C; d.M = (int32_t)Mn;
+        d.tmin = s->extent * 1e-6f;
+        MCPT_CUDA(cudaMemcpy(s->d_blob, s->h_blob, B.total, cudaMemcpyHostToDevice));
+        for (int i = 0; i < 4; i++) MCPT_CUDA(cudaEventCreate(&s->ev[i]));
+        *out = s;
+    });
+    if (rc != MCPT_OK && s) { mcpt_scene_destroy(s); }
+    return rc;
+}
+
+void mcpt_scene_destroy(McptScene* s)
+{
+    if (!s) return;
+    cudaSetDevice(s->device);
+    workspace_free(s->ws);
+    if (s->d_blob) cudaFree(s->d_blob);
+    if (s->h_blob) cudaFreeHost(s->h_blob);
+    for (int i = 0; i < 4; i++)
+        if (s->ev[i]) cudaEventDestroy(s->ev[i]);
+    delete s;
+}
+
+int mcpt_scene_geom_normals(const McptScene* s, double* out)
+{
+    return guarded([&] {
+        if (!s || !out) throw Error(MCPT_ERR_INVALID, "null argument");
+        std::memcpy(out, s->geom_normals.data(), s->geom_normals.size() * sizeof(double));
+    });
+}
+int mcpt_scene_light_areas(const McptScene* s, double* out)
+{
+    return guarded([&] {
+        if (!s || !out) throw Error(MCPT_ERR_INVALID, "null argument");
+        std::memcpy(out, s->light_area.data(), s->light_area.size() * sizeof(double));
+    });
+}
+int mcpt_scene_bvh_info(const McptScene* s, int which, uint32_t* nodes, uint32_t* leaves, uint32_t* max_depth, double* sah)
+{
+    return guarded([&] {
+        if (!s) throw Error(MCPT_ERR_INVALID, "null scene");
+        const Bvh& b = which ? s->lbvh : s->bvh;
+        if (nodes) *nodes = (uint32_t)b.nodes.size();
+        if (leaves) *leaves = b.num_leaves;
+        if (max_depth) *max_depth = b.max_depth;
+        if (sah) *sah = b.sah_cost;
+    });
+}
+
+int mcpt_host_bvh_check(const McptSceneDesc* desc, int lights_only, uint32_t out4[4], double* sah_cost)
+{
+    return guarded([&] {
+        validate(desc);
+        std::vector<int32_t> ids;
+        if (lights_only) { ids.assign(desc->light_prim, desc->light_prim + desc->num_lights); std::sort(ids.begin(), ids.end()); }
+        else { ids.resize(desc->num_prims); std::iota(ids.begin(), ids.end(), 0); }
+        Bvh b = build_bvh(desc->positions, ids.data(), ids.size());
+        uint32_t errors = 0;
+        std::vector<uint32_t> seen(desc->num_prims, 0);
+        struct Item { int32_t code; float lo[3], hi[3]; };
+        std::vector<Item> stack;
+        const float inf = std::numeric_limits<float>::infinity();
+        stack.push_back(Item{0, {-inf, -inf, -inf}, {inf, inf, inf}});
+        while (!stack.empty()) {
+            Item it = stack.back();
+            stack.pop_back();
+            if (it.code >= 0) {
+                if ((size_t)it.code >= b.nodes.size()) { errors++; continue; }
+                const BvhNode& n = b.nodes[it.code];
+                Item c0{n.c0, {n.n0.x, n.n0.z, n.n2.x}, {n.n0.y, n.n0.w, n.n2.y}};
+                Item c1{n.c1, {n.n1.x, n.n1.z, n.n2.z}, {n.n1.y, n.n1.w, n.n2.w}};
+                for (Item* c : {&c0, &c1}) {
+                    if (c->lo[0] > c->hi[0]) continue;  // empty child
+                    for (int k = 0; k < 3; k++)
+                        if (c->lo[k] < it.lo[k] - 1e-3f * std::fabs(it.lo[k]) - 1e-6f || c->hi[k] > it.hi[k] + 1e-3f * std::fabs(it.hi[k]) + 1e-6f) errors++;
+                    stack.push_back(*c);
+                }
+            } else {
+                int code = ~it.code, first = code >> 3, cnt = (code & 7) + 1;
+                for (int i = 0; i < cnt; i++) {
+                    if ((size_t)(first + i) * 3 + 2 >= b.tris.size()) { errors++; continue; }
+                    int32_t prim;
+                    std::memcpy(&prim, &b.tris[3 * (first + i)].w, 4);
+                    if (prim < 0 || (uint32_t)prim >= desc->num_prims) { errors++; continue; }
+                    seen[prim]++;
+                    for (int v = 0; v < 3; v++) {
+                        const f4& p = b.tris[3 * (first + i) + v];
+                        const float* q = desc->positions + (size_t)prim * 9 + 3 * v;
+                        if (p.x != q[0] || p.y != q[1] || p.z != q[2]) errors++;
+                        float c[3] = {p.x, p.y, p.z};
+                        for (int k = 0; k < 3; k++)
+                            if (c[k] < it.lo[k] || c[k] > it.hi[k]) errors++;
+                    }
+                }
+            }
+        }
+        for (int32_t id : ids) if (seen[id] != 1) errors++;
+        uint32_t total = 0;
+        for (uint32_t v : seen) total += v;
+        if (total != ids.size()) errors++;
+        if (out4) { out4[0] = (uint32_t)b.nodes.size(); out4[1] = b.num_leaves; out4[2] = b.max_depth; out4[3] = errors; }
+        if (sah_cost) *sah_cost = b.sah_cost;
+    });
+}
+
+// ---- render ------------------------------------------------------------------------------------------
+int mcpt_render_device(McptScene* scene, const McptCamera* cam, const McptRenderParams* params, float* d_out, void* stream,
+                       McptStats* stats)
+{
+    return guarded([&] {
+        if (!scene || !cam || !params || !d_out) throw Error(MCPT_ERR_INVALID, "null argument");
+        MCPT_CUDA(cudaSetDevice(scene->device));
+        render_device(scene, cam, params, d_out, (cudaStream_t)stream, stats);
+    });
+}
+
+int mcpt_render(McptScene* scene, const McptCamera* cam, const McptRenderParams* params, float* out_rgb, McptStats* stats)
+{
+    return guarded([&] {
+        if (!scene || !cam || !params || !out_rgb) throw Error(MCPT_ERR_INVALID, "null argument");
+        if (params->width <= 0 || params->height <= 0) throw Error(MCPT_ERR_INVALID, "bad resolution");
+        MCPT_CUDA(cudaSetDevice(scene->device));
+        size_t bytes = (size_t)params->width * params->height * 3 * sizeof(float);
+        Workspace& ws = scene->ws;
+        if (ws.image_bytes < bytes) {
+            if (ws.d_image) MCPT_CUDA(cudaFree(ws.d_image));
+            ws.d_image = nullptr; ws.image_bytes = 0;
+            MCPT_CUDA(cudaMalloc((void**)&ws.d_image, bytes));
+            ws.image_bytes = bytes;
+        }
+        McptRenderParams p = *params;
+        p.flags &= ~(uint32_t)MCPT_ACCUMULATE;
+        render_device(scene, cam, &p, ws.d_image, nullptr, stats);
+        MCPT_CUDA(cudaMemcpy(out_rgb, ws.d_image, bytes, cudaMemcpyDeviceToHost));
+    });
+}
+
+int mcpt_tonemap(McptScene* scene, const float* rgb, size_t n, double max_radiance, double gamma, uint8_t* out)
+{
+    return guarded([&] {
+        if (!scene || !rgb || !out) throw Error(MCPT_ERR_INVALID, "null argument");
+        MCPT_CUDA(cudaSetDevice(scene->device));
+        tonemap_device(scene, rgb, n, max_radiance, gamma, out);
+    });
+}
+
+// ---- host loaders --------------------------------------------------------------------------------------
+struct McptHostScene {
+    FlatScene flat;
+    McptSceneDesc desc;
+    CameraDesc cam;
+};
+
+int mcpt_host_scene_load(const char* obj_path, const char* xml_path, McptHostScene** out)
+{
+    if (out) *out = nullptr;
+    return guarded([&] {
+        if (!obj_path || !xml_path || !out) throw Error(MCPT_ERR_INVALID, "null argument");
+        Myobj obj(obj_path);
+        Mylight lights(xml_path);
+        obj.read();                           // main.cpp:500
+        lights.read();                        // main.cpp:503
+        lights.gather_light_triangles(obj);   // main.cpp:504
+        McptHostScene* h = new McptHostScene();
+        h->flat = flatten(obj, lights);
+        h->desc = h->flat.desc();
+        h->cam = lights.camera;
+        *out = h;
+    });
+}
+const McptSceneDesc* mcpt_host_scene_desc(const McptHostScene* h) { return h ? &h->desc : nullptr; }
+int mcpt_host_scene_camera(const McptHostScene* h, McptCamera* cam, int32_t* width, int32_t* height, double* fovy)
+{
+    if (!h || !h->cam.present) return 0;
+    const CameraDesc& c = h->cam;
+    if (cam) {
+        double wl = 0;
+        for (int k = 0; k < 3; k++) {
+            cam->eye[k] = c.eye[k]; cam->w[k] = c.lookat[k] - c.eye[k]; cam->up[k] = c.up[k];
+            wl += cam->w[k] * cam->w[k];
+        }
+        cam->pixellen = std::tan(c.fovy * (M_PI / 180.0) * 0.5) * std::sqrt(wl) / (c.height * 0.5);
+    }
+    if (width) *width = c.width;
+    if (height) *height = c.height;
+    if (fovy) *fovy = c.fovy;
+    return 1;
+}
+void mcpt_host_scene_free(McptHostScene* h) { delete h; }
+
+}  // extern "C"

@@ -1,0 +1,212 @@
+// csrc/bvh_build.cpp -- binned-SAH top-down BVH builder (host), emitting the layout of bvh.h.
+#include "bvh.h"
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+#include <limits>
+
+namespace mcpt {
+namespace {
+
+struct Box {
+    float lo[3], hi[3];
+    void reset() { for (int a = 0; a < 3; a++) { lo[a] = FLT_MAX; hi[a] = -FLT_MAX; } }
+    void grow(const float* p) { for (int a = 0; a < 3; a++) { lo[a] = std::min(lo[a], p[a]); hi[a] = std::max(hi[a], p[a]); } }
+    void grow(const Box& b) { for (int a = 0; a < 3; a++) { lo[a] = std::min(lo[a], b.lo[a]); hi[a] = std::max(hi[a], b.hi[a]); } }
+    float half_area() const
+    {
+        float d[3] = {hi[0] - lo[0], hi[1] - lo[1], hi[2] - lo[2]};
+        if (d[0] < 0 || d[1] < 0 || d[2] < 0) return 0.f;
+        return d[0] * d[1] + d[1] * d[2] + d[2] * d[0];
+    }
+};
+
+struct Ref { Box box; float c[3]; int32_t prim; };
+
+struct TmpNode {
+    Box box;
+    int32_t left = -1, right = -1;  // children (tmp indices) or -1
+    uint32_t first = 0, count = 0;  // leaf range into refs
+};
+
+constexpr int kBins = 16;
+constexpr float kCostTrav = 1.0f, kCostTri = 1.0f;
+
+struct Builder {
+    std::vector<Ref> refs;
+    std::vector<TmpNode> tmp;
+    uint32_t max_depth = 0;
+
+    int32_t build(uint32_t lo, uint32_t hi, uint32_t depth)
+    {
+        int32_t idx = (int32_t)tmp.size();
+        tmp.emplace_back();
+        Box box, cbox;
+        box.reset(); cbox.reset();
+        for (uint32_t i = lo; i < hi; i++) { box.grow(refs[i].box); cbox.grow(refs[i].c); }
+        tmp[idx].box = box;
+        max_depth = std::max(max_depth, depth);
+        uint32_t n = hi - lo;
+        auto make_leaf = [&]() { tmp[idx].first = lo; tmp[idx].count = n; return idx; };
+        if (n <= 1) return make_leaf();
+
+        uint32_t mid = 0;
+        bool split_found = false;
+        if (depth < (uint32_t)kBvhStackDepth - 24) {
+            // binned SAH over the three axes
+            float best = std::numeric_limits<float>::infinity();
+            int best_axis = -1, best_bin = -1;
+            for (int a = 0; a < 3; a++) {
+                float ext = cbox.hi[a] - cbox.lo[a];
+                if (!(ext > 0)) continue;
+                Box bb[kBins]; uint32_t bc[kBins];
+                for (int b = 0; b < kBins; b++) { bb[b].reset(); bc[b] = 0; }
+                float scale = kBins / ext;
+                for (uint32_t i = lo; i < hi; i++) {
+                    int b = std::min(kBins - 1, std::max(0, (int)((refs[i].c[a] - cbox.lo[a]) * scale)));
+                    bb[b].grow(refs[i].box); bc[b]++;
+                }
+                float la[kBins]; uint32_t lc[kBins];
+                Box acc; acc.reset(); uint32_t cnt = 0;
+                for (int b = 0; b < kBins - 1; b++) { acc.grow(bb[b]); cnt += bc[b]; la[b] = acc.half_area(); lc[b] = cnt; }
+                acc.reset(); cnt = 0;
+                for (int b = kBins - 1; b > 0; b--) {
+                    acc.grow(bb[b]); cnt += bc[b];
+                    if (lc[b - 1] == 0 || cnt == 0) continue;
+                    float cost = la[b - 1] * lc[b - 1] + acc.half_area() * cnt;
+                    if (cost < best) { best = cost; best_axis = a; best_bin = b; }
+                }
+            }
+            if (best_axis >= 0) {
+                float pa = box.half_area();
+                float split_cost = kCostTrav + (pa > 0 ? best / pa : 0.f) * kCostTri;
+                if (n <= (uint32_t)kBvhMaxLeaf && split_cost >= n * kCostTri) return make_leaf();
+                float ext = cbox.hi[best_axis] - cbox.lo[best_axis];
+                float scale = kBins / ext, base = cbox.lo[best_axis];
+                int a = best_axis, bsplit = best_bin;
+                auto it = std::partition(refs.begin() + lo, refs.begin() + hi, [&](const Ref& r) {
+                    int b = std::min(kBins - 1, std::max(0, (int)((r.c[a] - base) * scale)));
+                    return b < bsplit;
+                });
+                mid = (uint32_t)(it - refs.begin());
+                split_found = mid > lo && mid < hi;
+            }
+        }
+        if (!split_found) {
+            if (n <= (uint32_t)kBvhMaxLeaf) return make_leaf();
+            // object median on the widest centroid axis (also the depth guard)
+            int a = 0;
+            float e[3] = {cbox.hi[0] - cbox.lo[0], cbox.hi[1] - cbox.lo[1], cbox.hi[2] - cbox.lo[2]};
+            if (e[1] > e[a]) a = 1;
+            if (e[2] > e[a]) a = 2;
+            mid = lo + n / 2;
+            std::nth_element(refs.begin() + lo, refs.begin() + mid, refs.begin() + hi,
+                             [a](const Ref& x, const Ref& y) { return x.c[a] < y.c[a]; });
+        }
+        int32_t l = build(lo, mid, depth + 1);
+        int32_t r = build(mid, hi, depth + 1);
+        tmp[idx].left = l; tmp[idx].right = r;
+        return idx;
+    }
+};
+
+inline void pad_box(const Box& b, float tiny, float lo[3], float hi[3])
+{
+    for (int a = 0; a < 3; a++) {
+        lo[a] = b.lo[a] - (std::fabs(b.lo[a]) * 2e-7f + tiny);
+        hi[a] = b.hi[a] + (std::fabs(b.hi[a]) * 2e-7f + tiny);
+    }
+}
+
+}  // namespace
+
+Bvh build_bvh(const float* positions, const int32_t* prims, size_t count)
+{
+    Bvh out;
+    Builder B;
+    B.refs.resize(count);
+    Box all; all.reset();
+    for (size_t i = 0; i < count; i++) {
+        Ref& r = B.refs[i];
+        r.prim = prims[i];
+        const float* v = positions + (size_t)prims[i] * 9;
+        r.box.reset();
+        for (int k = 0; k < 3; k++) r.box.grow(v + 3 * k);
+        for (int a = 0; a < 3; a++) r.c[a] = 0.5f * (r.box.lo[a] + r.box.hi[a]);
+        all.grow(r.box);
+    }
+    const float inf = std::numeric_limits<float>::infinity();
+    if (count == 0) {
+        BvhNode n; std::memset(&n, 0, sizeof n);
+        n.n0 = {inf, -inf, inf, -inf}; n.n1 = n.n0; n.n2 = {inf, -inf, inf, -inf};
+        n.c0 = n.c1 = ~0;
+        out.nodes.push_back(n);
+        for (int k = 0; k < 3; k++) out.tris.push_back(f4{0, 0, 0, 0});
+        return out;
+    }
+    for (int a = 0; a < 3; a++) { out.lo[a] = all.lo[a]; out.hi[a] = all.hi[a]; }
+    float ext = std::max(std::max(all.hi[0] - all.lo[0], all.hi[1] - all.lo[1]), all.hi[2] - all.lo[2]);
+    float tiny = std::max(ext, 1e-30f) * 1e-7f;
+    B.tmp.reserve(count * 2);
+    int32_t root = B.build(0, (uint32_t)count, 0);
+    out.max_depth = B.max_depth;
+
+    // triangles in leaf order == refs order (leaves own contiguous ranges)
+    out.tris.resize(count * 3);
+    for (size_t i = 0; i < count; i++) {
+        const float* v = positions + (size_t)B.refs[i].prim * 9;
+        f4 a = {v[0], v[1], v[2], 0.f};
+        std::memcpy(&a.w, &B.refs[i].prim, 4);
+        out.tris[3 * i + 0] = a;
+        out.tris[3 * i + 1] = f4{v[3], v[4], v[5], 0.f};
+        out.tris[3 * i + 2] = f4{v[6], v[7], v[8], 0.f};
+    }
+
+    // emit: every tmp inner node becomes one output node; a lone root leaf gets a wrapper node
+    auto leaf_code = [](const TmpNode& t) { return (int32_t)~((t.first << 3) | (t.count - 1)); };
+    double root_area = std::max(B.tmp[root].box.half_area(), 1e-30f);
+    double sah = 0;
+    std::vector<int32_t> out_index(B.tmp.size(), -1);
+    uint32_t n_inner = 0;
+    for (size_t i = 0; i < B.tmp.size(); i++)
+        if (B.tmp[i].left >= 0) out_index[i] = (int32_t)n_inner++;
+    auto split_leaf = [&](TmpNode t, std::vector<TmpNode>& parts) {
+        // leaves larger than 8 cannot be encoded; cannot happen (kBvhMaxLeaf = 4) but keep it safe
+        while (t.count > 8) { TmpNode h = t; h.count = 8; parts.push_back(h); t.first += 8; t.count -= 8; }
+        parts.push_back(t);
+    };
+    (void)split_leaf;
+    auto set_child = [&](BvhNode& n, int which, const TmpNode& c, int32_t code) {
+        float lo[3], hi[3];
+        pad_box(c.box, tiny, lo, hi);
+        if (which == 0) { n.n0 = {lo[0], hi[0], lo[1], hi[1]}; n.n2.x = lo[2]; n.n2.y = hi[2]; n.c0 = code; }
+        else { n.n1 = {lo[0], hi[0], lo[1], hi[1]}; n.n2.z = lo[2]; n.n2.w = hi[2]; n.c1 = code; }
+    };
+    if (B.tmp[root].left < 0) {
+        BvhNode n; std::memset(&n, 0, sizeof n);
+        set_child(n, 0, B.tmp[root], leaf_code(B.tmp[root]));
+        n.n1 = {inf, -inf, inf, -inf}; n.n2.z = inf; n.n2.w = -inf; n.c1 = ~0;
+        out.nodes.push_back(n);
+        out.num_leaves = 1;
+        out.sah_cost = kCostTrav + B.tmp[root].count * kCostTri;
+        return out;
+    }
+    out.nodes.resize(n_inner);
+    for (size_t i = 0; i < B.tmp.size(); i++) {
+        const TmpNode& t = B.tmp[i];
+        double rel = t.box.half_area() / root_area;
+        if (t.left < 0) { out.num_leaves++; sah += rel * t.count * kCostTri; continue; }
+        sah += rel * kCostTrav;
+        BvhNode n; std::memset(&n, 0, sizeof n);
+        const TmpNode& l = B.tmp[t.left];
+        const TmpNode& r = B.tmp[t.right];
+        set_child(n, 0, l, l.left >= 0 ? out_index[t.left] : leaf_code(l));
+        set_child(n, 1, r, r.left >= 0 ? out_index[t.right] : leaf_code(r));
+        out.nodes[out_index[i]] = n;
+    }
+    out.sah_cost = sah;
+    return out;
+}
+
+}  // namespace mcpt

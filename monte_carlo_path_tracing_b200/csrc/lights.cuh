@@ -1,0 +1,147 @@
+// csrc/lights.cuh -- area-triangle light sampling: uniform-area and Arvo spherical-triangle.
+// Device restatement of Mylight.cpp:102-160 (select_a_point_from_lights) and :163-493 (spherical
+// triangle sampling, one-shot and staged), templated on the real type like brdf.cuh.
+#pragma once
+#include "device_math.cuh"
+#include "scene_dev.cuh"
+
+namespace mcpt {
+
+template <class T> struct LightTri { V3<T> v0, v1, v2, ng, Le; T lsum, area; int prim, cls; };
+
+template <class T> __device__ __forceinline__ LightTri<T> load_light(const DScene& s, int l);
+template <> __device__ __forceinline__ LightTri<float> load_light<float>(const DScene& s, int l)
+{
+    const float4 a = __ldg(s.lights + 5 * l + 0), b = __ldg(s.lights + 5 * l + 1), c = __ldg(s.lights + 5 * l + 2);
+    const float4 n = __ldg(s.lights + 5 * l + 3), e = __ldg(s.lights + 5 * l + 4);
+    LightTri<float> t;
+    t.v0 = to_f3(a); t.v1 = to_f3(b); t.v2 = to_f3(c); t.ng = to_f3(n); t.Le = to_f3(e);
+    t.lsum = n.w; t.area = c.w; t.prim = __float_as_int(a.w); t.cls = __float_as_int(b.w);
+    return t;
+}
+template <> __device__ __forceinline__ LightTri<double> load_light<double>(const DScene& s, int l)
+{
+    const float4 a = __ldg(s.lights + 5 * l + 0), b = __ldg(s.lights + 5 * l + 1), c = __ldg(s.lights + 5 * l + 2);
+    LightTri<double> t;
+    t.v0 = to_d3(a); t.v1 = to_d3(b); t.v2 = to_d3(c);
+    t.ng = mk<double>(s.lng64[3 * l], s.lng64[3 * l + 1], s.lng64[3 * l + 2]);
+    t.prim = __float_as_int(a.w); t.cls = __float_as_int(b.w);
+    t.Le = mk<double>(s.crad64[3 * t.cls], s.crad64[3 * t.cls + 1], s.crad64[3 * t.cls + 2]);
+    t.lsum = t.Le.x + t.Le.y + t.Le.z;  // RadianceRGB::sum, RadianceRGB.cpp:70-73
+    t.area = s.larea64[l];
+    return t;
+}
+
+// ---- spherical triangle of one light as seen from x1 (Mylight.cpp:175-253 == :335-413) ----------
+template <class T> struct SphTri { bool ok; V3<T> A, B, C; T alpha, c, sA, w; };
+
+template <class T>
+__device__ __forceinline__ SphTri<T> spherical_project(const LightTri<T>& lt, V3<T> x1, V3<T> n)
+{
+    const T eps = M<T>::eps;
+    SphTri<T> r;
+    r.ok = false; r.w = T(0); r.sA = T(0); r.alpha = T(0); r.c = T(0);
+    T tmp = dot(lt.ng, x1 - lt.v0);
+    if (tmp < T(0) || M<T>::abs_(tmp) < eps) return r;  // :180-185 x1 behind the light
+    T t0 = dot(n, lt.v0 - x1), t1 = dot(n, lt.v1 - x1), t2 = dot(n, lt.v2 - x1);
+    if ((t0 < T(0) || M<T>::abs_(t0) < eps) && (t1 < T(0) || M<T>::abs_(t1) < eps) && (t2 < T(0) || M<T>::abs_(t2) < eps))
+        return r;  // :194 light entirely below the horizon
+    V3<T> A = normalized(lt.v0 - x1), B = normalized(lt.v1 - x1), C = normalized(lt.v2 - x1);
+    if (dot(cross(normalized(C - A), normalized(B - A)), n) < T(0)) { V3<T> t = B; B = C; C = t; }  // :206-211
+    T a = M<T>::acos_(clamp1(dot(B, C)));
+    T b = M<T>::acos_(clamp1(dot(A, C)));
+    T c = M<T>::acos_(clamp1(dot(A, B)));
+    if (a < eps || b < eps || c < eps) return r;  // :219
+    T alpha = M<T>::acos_(clamp1(dot(-normalized(cross(B, A)), normalized(cross(A, C)))));
+    T beta = M<T>::acos_(clamp1(dot(-normalized(cross(C, B)), normalized(cross(B, A)))));
+    T gamma = M<T>::acos_(clamp1(dot(-normalized(cross(A, C)), normalized(cross(C, B)))));
+    if (alpha < eps || beta < eps || gamma < eps) return r;  // :230
+    T sA = alpha + beta + gamma - M<T>::pi;                   // :236
+    if (sA < T(0)) return r;
+    T w = sA * lt.lsum;                                       // :244
+    if (w < T(0) || M<T>::bad_(w)) return r;
+    r.ok = true; r.A = A; r.B = B; r.C = C; r.alpha = alpha; r.c = c; r.sA = sA; r.w = w;
+    return r;
+}
+
+// Arvo SampleTriangle(xi1, xi2), Mylight.cpp:289-297: direction uniformly distributed in the
+// spherical triangle (A,B,C).
+template <class T>
+__device__ __forceinline__ V3<T> arvo_sample(const SphTri<T>& st, T xi1, T xi2)
+{
+    T sA1 = xi1 * st.sA;
+    T s, t, sa, ca;
+    M<T>::sincos_(sA1 - st.alpha, &s, &t);
+    M<T>::sincos_(st.alpha, &sa, &ca);
+    T u = t - ca;
+    T v = s + sa * M<T>::cos_(st.c);
+    T q = ((v * t - u * s) * ca - v) / ((v * s + u * t) * sa);
+    V3<T> C1 = normalized(st.A * q + normalized(st.C - st.A * dot(st.C, st.A)) * M<T>::sqrt_(T(1) - q * q));
+    T z = T(1) - xi2 * (T(1) - dot(C1, st.B));
+    return normalized(st.B * z + normalized(C1 - st.B * dot(C1, st.B)) * M<T>::sqrt_(T(1) - z * z));
+}
+
+// ---- FP32 weight of one light for the renderer's O(L) loop -------------------------------------------
+// Same culls (:180-197) and the same quantity sA * (R+G+B), with the solid angle from the
+// Van Oosterom-Strackee form  tan(sA/2) = |a.(b x c)| / (|a||b||c| + (a.b)|c| + (a.c)|b| + (b.c)|a|)
+// where a,b,c = vertices - x1.  a.(b x c) = (v0-x1).((v1-v0) x (v2-v0)) = 2 area * ng.(v0-x1) has no
+// cancellation, so tiny lights keep full FP32 relative accuracy where alpha+beta+gamma-pi has none.
+__device__ __forceinline__ float light_weight_fast(const DScene& s, int l, f3 x1, f3 n)
+{
+    const float4 p0 = __ldg(s.lights + 5 * l + 0), p1 = __ldg(s.lights + 5 * l + 1), p2 = __ldg(s.lights + 5 * l + 2);
+    const float4 ng = __ldg(s.lights + 5 * l + 3);
+    f3 a = to_f3(p0) - x1, b = to_f3(p1) - x1, c = to_f3(p2) - x1;
+    float tmp = -dot(to_f3(ng), a);
+    if (tmp < 1e-8f) return 0.f;
+    float ha = dot(n, a), hb = dot(n, b), hc = dot(n, c);
+    if (ha < 1e-8f && hb < 1e-8f && hc < 1e-8f) return 0.f;
+    float la = sqrtf(dot(a, a)), lb = sqrtf(dot(b, b)), lc = sqrtf(dot(c, c));
+    float num = tmp * (2.0f * p2.w);
+    float den = la * lb * lc + dot(a, b) * lc + dot(a, c) * lb + dot(b, c) * la;
+    float sA = 2.0f * atan2f(num, den);
+    float w = sA * ng.w;
+    return (w > 0.f && !isinf(w)) ? w : 0.f;
+}
+
+// ---- uniform-area sampling, Mylight.cpp:102-160 --------------------------------------------------------
+template <class T> struct LightPoint { int prim; int light; V3<T> coord, Le; T prob; };
+
+// barycentric point of :141-154 on light l
+template <class T>
+__device__ __forceinline__ V3<T> uniform_point(const LightTri<T>& lt, T xi1, T xi2)
+{
+    T beta = T(1) - M<T>::sqrt_(T(1) - xi1);
+    T gamma = (T(1) - beta) * xi2;
+    T alpha = T(1) - beta - gamma;
+    return lt.v0 * alpha + lt.v1 * beta + lt.v2 * gamma;
+}
+
+// FP32 renderer: inverse-CDF lookups in the prebuilt tables (pdf in AREA measure)
+__device__ __forceinline__ LightPoint<float> light_sample_uniform_fast(const DScene& s, float u_class, float u_tri, float xi1, float xi2)
+{
+    int c = 0;
+    float pc = 1.f;
+    if (s.C > 1) {
+        while (c < s.C - 1 && __ldg(s.class_cdf + c) < u_class) c++;
+        pc = __ldg(s.class_cdf + c) - (c ? __ldg(s.class_cdf + c - 1) : 0.f);
+    }
+    int b = __ldg(s.class_begin + c), e = __ldg(s.class_begin + c + 1);
+    int l = b;
+    float pt = 1.f;
+    if (e - b > 1) {
+        int lo = b, hi = e - 1;  // first l with tri_cdf[l] >= u
+        while (lo < hi) {
+            int mid = (lo + hi) >> 1;
+            if (__ldg(s.tri_cdf + mid) < u_tri) lo = mid + 1; else hi = mid;
+        }
+        l = lo;
+        pt = __ldg(s.tri_cdf + l) - (l > b ? __ldg(s.tri_cdf + l - 1) : 0.f);
+    }
+    LightTri<float> lt = load_light<float>(s, l);
+    LightPoint<float> r;
+    r.prim = lt.prim; r.light = l; r.coord = uniform_point<float>(lt, xi1, xi2); r.Le = lt.Le;
+    r.prob = pc * pt / lt.area;
+    return r;
+}
+
+}  // namespace mcpt

@@ -1,0 +1,78 @@
+// csrc/mcpt_internal.h -- McptScene, error plumbing, shared between api.cu / batch.cu / render.cu.
+#pragma once
+#include <cuda_runtime.h>
+#include <string>
+#include <vector>
+#include "../../include/mcpt.h"
+#include "bvh.h"
+#include "host_scene.h"
+#include "scene_dev.cuh"
+
+namespace mcpt {
+
+void set_last_error(const std::string& msg);
+
+#define MCPT_CUDA(expr)                                                                                      \
+    do {                                                                                                     \
+        cudaError_t e__ = (expr);                                                                            \
+        if (e__ != cudaSuccess)                                                                              \
+            throw ::mcpt::Error(MCPT_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e__) + " (" +  \
+                                                   __FILE__ + ":" + std::to_string(__LINE__) + ")");         \
+    } while (0)
+
+// Runs `body`, mapping exceptions to McptError codes (the C ABI never throws and never exits).
+template <class F> int guarded(F&& body)
+{
+    try {
+        body();
+        return MCPT_OK;
+    } catch (const Error& e) {
+        set_last_error(e.what());
+        return e.code;
+    } catch (const std::bad_alloc&) {
+        set_last_error("out of host memory");
+        return MCPT_ERR_OOM;
+    } catch (const std::exception& e) {
+        set_last_error(e.what());
+        return MCPT_ERR_INVALID;
+    }
+}
+
+// Device buffers of the wavefront renderer, grown on demand and reused across calls.
+struct Workspace {
+    void* base = nullptr;
+    size_t bytes = 0;
+    void* pinned = nullptr;  // small pinned staging area for counters
+    float* d_image = nullptr;  // W*H*3 output staging for mcpt_render
+    size_t image_bytes = 0;
+};
+
+}  // namespace mcpt
+
+struct McptScene {
+    int device = 0;
+    uint32_t P = 0, S = 0, Mn = 0, L = 0, C = 0;
+    // host copies of the description (the caller keeps ownership of its own arrays)
+    std::vector<float> positions, normals;
+    std::vector<int32_t> material_id, light_prim, light_class;
+    std::vector<double> class_radiance;
+    std::vector<double> geom_normals;  // [P][3]  get_unique_normal_of_facet
+    std::vector<double> light_area;    // [L]
+    mcpt::Bvh bvh, lbvh;
+    // one packed, pinned host image of everything the kernels read + its device twin
+    void* h_blob = nullptr;
+    void* d_blob = nullptr;
+    size_t blob_bytes = 0;
+    mcpt::DScene d{};      // device pointers into d_blob
+    float extent = 1.f;    // largest scene dimension
+    mcpt::Workspace ws;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+};
+
+namespace mcpt {
+// render.cu
+void render_device(McptScene* scene, const McptCamera* cam, const McptRenderParams* params, float* d_out_rgb,
+                   cudaStream_t stream, McptStats* stats);
+void tonemap_device(McptScene* scene, const float* rgb, size_t n, double max_radiance, double gamma, uint8_t* out);
+void workspace_free(Workspace& ws);
+}  // namespace mcpt

@@ -1,0 +1,716 @@
+// csrc/render.cu -- the wavefront path tracer: replacement for the pixel/sample loop of main()
+// (main.cpp:557-588) and the three recursive estimators shade / shade_with_brdf / shade_with_mis
+// (main.cpp:269-494), as bounce-synchronous kernels over a queue of rays.
+//
+// One pass renders `batch_spp` samples of every pixel:  slot = sample_in_batch * npix + pixel.
+//   k_primary   camera rays (main.cpp:563-564) + closest hit, once per pixel (no jitter: every sample of a
+//               pixel shoots the same ray, F4) -> primary_hit[pixel]
+//   k_bounce    per queued ray: closest-hit traversal of the SAH BVH (extend), shade prologue
+//               (main.cpp:273-288), next-event estimation incl. its visibility ray, Russian roulette, BRDF /
+//               light sampling, and emission of 0..2 child rays into the next queue through an
+//               ORDER-PRESERVING compaction (warp ballot/prefix sums inside the block, one decoupled
+//               look-back word per 128-ray chunk across blocks -- no per-element atomics)
+//   k_runsum    MIS path tree only: children of one path are adjacent in the queue, so the head of each
+//               run of equal slots sums the run's emission contributions into that slot
+//   k_accumulate / k_finalize   per-pixel owner sums its slots (atomic-free), scales by 1/spp
+// Depth is implied by the bounce index: the vertex shaded at bounce b has depth b+1, because every
+// earlier vertex of its path was a non-emissive, front-facing vertex that passed RR.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include "brdf.cuh"
+#include "lights.cuh"
+#include "mcpt_internal.h"
+#include "rng.cuh"
+#include "traverse.cuh"
+
+namespace mcpt {
+namespace {
+
+constexpr int kBlk = 128;             // threads per block == rays per chunk
+constexpr unsigned kFull = 0xffffffffu;
+constexpr size_t kTargetSlots = 4u << 20;  // auto batch: ~4M path slots in flight per pass
+
+enum { CNT_VERTICES = 0, CNT_RAYS, CNT_SHADOW, CNT_LIGHTRAYS, CNT_PRIMARY_HITS, CNT_OVERFLOW, CNT_N };
+
+struct Queue {
+    float4* org;   // o.xyz | exclude prim (int bits)          (Myobj.cpp:417 rotri)
+    float4* dir;   // d.xyz | slot (int bits)
+    float4* thr;   // throughput rgb | unused
+    uint2* node;   // path-tree node code (MIS only)
+};
+
+struct BounceArgs {
+    DScene s;
+    DCamera cam;
+    Queue in, out;
+    float4* Lacc;              // [slots] per-slot radiance accumulator (owner-exclusive)
+    float4* contrib;           // [capacity] MIS: per-element emission contribution | slot
+    const float4* primary_hit; // [npix] prim | beta | gamma | t
+    unsigned long long* status;  // [chunks] look-back words: flag(2) | count(62)
+    int* ticket;               // chunk ticket counter
+    int* out_count;            // final size of the out queue
+    unsigned long long* counters;
+    uint64_t seed;
+    int in_count, capacity, npix, batch_spp, sample_base, bounce, max_depth;
+    uint32_t flags;
+    float p_rr;
+};
+
+// ---- small helpers --------------------------------------------------------------------------------------
+__device__ __forceinline__ PhongMat<float> load_mat(const DScene& s, int m)
+{
+    const float4 a = __ldg(s.mats + 2 * m), b = __ldg(s.mats + 2 * m + 1);
+    PhongMat<float> r;
+    r.kd = to_f3(a); r.ns = a.w; r.ks = to_f3(b);
+    return r;
+}
+
+// camera ray of pixel (i,j), main.cpp:563-564; (di,dj) = optional sub-pixel jitter in [-0.5,0.5)
+__device__ __forceinline__ f3 camera_dir(const DCamera& c, int pixel, float di, float dj)
+{
+    int i = pixel / c.W, j = pixel - i * c.W;
+    float dx = -c.pixellen * ((float)i + di - c.ci);
+    float dy = c.pixellen * ((float)j + dj - c.cj);
+    f3 d = mk<float>(c.U[0] * dx + c.V[0] * dy + c.N[0] * c.wlen, c.U[1] * dx + c.V[1] * dy + c.N[1] * c.wlen,
+                     c.U[2] * dx + c.V[2] * dy + c.N[2] * c.wlen);
+    return normalize_fast(d);
+}
+
+// ---- warp-cooperative spherical-triangle light selection --------------------------------------------------
+// The reference loops over ALL light triangles at every vertex (Mylight.cpp:169-259 / :329-421) and then
+// draws one with probability weight/weights_sum (:271-276).  Here a warp serves its lanes' vertices one at a
+// time: lanes stride over the lights (coalesced float4 loads), a shuffle scan gives weights_sum and the lane
+// whose partial interval contains u*weights_sum, and a second short pass over that lane's lights resolves the
+// triangle.  Same distribution, O(L/32) per lane per vertex, and no lane idles while others loop.
+// Must be called by all 32 lanes; lanes with need == false only help.
+__device__ __forceinline__ void warp_light_select(const DScene& s, bool need, f3 x, f3 n, float u, int* chosen, float* wsum_out,
+                                                  float* w_chosen)
+{
+    const int lane = threadIdx.x & 31;
+    unsigned todo = __ballot_sync(kFull, need);
+    *chosen = -1; *wsum_out = 0.f; *w_chosen = 0.f;
+    while (todo) {
+        const int src = __ffs(todo) - 1;
+        todo &= todo - 1;
+        f3 X = mk<float>(__shfl_sync(kFull, x.x, src), __shfl_sync(kFull, x.y, src), __shfl_sync(kFull, x.z, src));
+        f3 Nn = mk<float>(__shfl_sync(kFull, n.x, src), __shfl_sync(kFull, n.y, src), __shfl_sync(kFull, n.z, src));
+        const float uu = __shfl_sync(kFull, u, src);
+        float part = 0.f;
+        for (int l = lane; l < s.L; l += 32) part += light_weight_fast(s, l, X, Nn);
+        float incl = part;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            float t = __shfl_up_sync(kFull, incl, o);
+            if (lane >= o) incl += t;
+        }
+        const float total = __shfl_sync(kFull, incl, 31);
+        int found = -1;
+        float wfound = 0.f;
+        if (total > 0.f) {
+            const float target = uu * total;
+            const unsigned nz = __ballot_sync(kFull, part > 0.f);
+            unsigned ge = __ballot_sync(kFull, incl >= target && part > 0.f);
+            const int j = ge ? (__ffs(ge) - 1) : (31 - __clz(nz));
+            const float rem = target - (__shfl_sync(kFull, incl, j) - __shfl_sync(kFull, part, j));
+            float running = 0.f;
+            int last_l = -1;
+            float last_w = 0.f;
+            for (int k0 = 0; j + 32 * k0 < s.L && found < 0; k0 += 32) {
+                const int l = j + 32 * (k0 + lane);
+                const float w = (l < s.L) ? light_weight_fast(s, l, X, Nn) : 0.f;
+                float wi = w;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    float t = __shfl_up_sync(kFull, wi, o);
+                    if (lane >= o) wi += t;
+                }
+                const unsigned pos = __ballot_sync(kFull, w > 0.f);
+                const unsigned hit = __ballot_sync(kFull, w > 0.f && running + wi >= rem);
+                if (hit) {
+                    const int f = __ffs(hit) - 1;
+                    found = j + 32 * (k0 + f);
+                    wfound = __shfl_sync(kFull, w, f);
+                } else if (pos) {
+                    const int f = 31 - __clz(pos);
+                    last_l = j + 32 * (k0 + f);
+                    last_w = __shfl_sync(kFull, w, f);
+                }
+                running += __shfl_sync(kFull, wi, 31);
+            }
+            if (found < 0) { found = last_l; wfound = last_w; }  // rounding: fall back to the lane's last survivor
+        }
+        if (lane == src) { *chosen = found; *wsum_out = total; *w_chosen = wfound; }
+    }
+}
+
+// ---- order-preserving compaction --------------------------------------------------------------------------
+// Block-exclusive offsets of `n_out` (0..2) per thread via __ballot_sync / shuffle prefix sums, then the
+// chunk's global base from a decoupled look-back over the per-chunk status words.  Chunks are handed out by
+// a ticket counter in increasing order, so every predecessor of a waiting chunk is already running.
+constexpr unsigned long long kFlagAgg = 1ull << 62, kFlagIncl = 2ull << 62, kValMask = (1ull << 62) - 1;
+
+__device__ __forceinline__ int block_compact_offset(int n_out, int chunk, unsigned long long* status, int* base_out, int* smem_i)
+{
+    // smem_i: kBlk/32 + 2 ints
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int incl = n_out;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(kFull, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) smem_i[warp] = incl;
+    __syncthreads();
+    int wbase = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kBlk / 32; w++) {
+        int c = smem_i[w];
+        if (w < warp) wbase += c;
+        total += c;
+    }
+    if (threadIdx.x == 0) {
+        unsigned long long excl = 0;
+        volatile unsigned long long* st = status;
+        if (chunk == 0) {
+            st[0] = kFlagIncl | (unsigned long long)total;
+        } else {
+            st[chunk] = kFlagAgg | (unsigned long long)total;
+            __threadfence();
+            int j = chunk - 1;
+            for (;;) {
+                unsigned long long v = st[j];
+                if ((v >> 62) == 0) continue;  // predecessor not published yet
+                excl += v & kValMask;
+                if ((v >> 62) == 2) break;
+                j--;
+            }
+            st[chunk] = kFlagIncl | (excl + (unsigned long long)total);
+        }
+        __threadfence();
+        smem_i[kBlk / 32] = (int)excl;
+    }
+    __syncthreads();
+    *base_out = smem_i[kBlk / 32];
+    int r = wbase + incl - n_out;
+    __syncthreads();  // smem_i reused by the next chunk
+    return r;
+}
+
+
+// ---- primary rays ----------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlk) k_primary(DScene s, DCamera cam, int npix, float4* primary_hit)
+{
+    __shared__ int stack[kStackSm * kBlk];
+    int pixel = blockIdx.x * kBlk + threadIdx.x;
+    if (pixel >= npix) return;
+    f3 o = mk<float>(cam.eye[0], cam.eye[1], cam.eye[2]);
+    f3 d = camera_dir(cam, pixel, 0.f, 0.f);
+    Hit h = trace_fast<false>(s.nodes, s.tris, o, d, -1, s.tmin, 3.0e38f, stack + threadIdx.x, kBlk);
+    primary_hit[pixel] = make_float4(__int_as_float(h.prim), h.b, h.g, h.t);
+}
+
+// ---- one bounce --------------------------------------------------------------------------------------------
+struct Child { f3 o, d, thr; int exclude; uint64_t node; };
+
+template <int STRAT, bool FIRST>
+__global__ void __launch_bounds__(kBlk) k_bounce(const BounceArgs a)
+{
+    constexpr bool kTree = (STRAT == MCPT_MIS);
+    constexpr bool kNee = (STRAT == MCPT_NEE_SPHERICAL || STRAT == MCPT_NEE_UNIFORM);
+    constexpr bool kSph = (STRAT == MCPT_NEE_SPHERICAL || STRAT == MCPT_MIS);
+    __shared__ int stack[kStackSm * kBlk];
+    __shared__ int sm_i[kBlk / 32 + 2];
+    __shared__ int sm_chunk;
+    __shared__ unsigned long long sm_cnt[CNT_N];
+    const DScene& s = a.s;
+    if (threadIdx.x < CNT_N) sm_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    unsigned long long c_vert = 0, c_rays = 0, c_shadow = 0, c_lrays = 0, c_phits = 0, c_ovf = 0;
+    const int nchunks = (a.in_count + kBlk - 1) / kBlk;
+
+    for (;;) {
+        if (threadIdx.x == 0) sm_chunk = atomicAdd(a.ticket, 1);
+        __syncthreads();
+        const int chunk = sm_chunk;
+        if (chunk >= nchunks) break;
+        const int i = chunk * kBlk + threadIdx.x;
+        const bool valid = i < a.in_count;
+
+        // -- A. ray + path state, closest hit (extend) ------------------------------------------------
+        f3 o = mk<float>(0.f, 0.f, 0.f), d = mk<float>(0.f, 0.f, 1.f), thr = mk<float>(1.f, 1.f, 1.f);
+        int slot = 0, exclude = -1;
+        uint64_t node = 1;
+        Hit h;
+        h.prim = -1; h.b = h.g = h.t = 0.f;
+        uint32_t pixel = 0, sample = 0;
+        if (valid) {
+            if (FIRST) {
+                slot = i;
+                pixel = (uint32_t)(i % a.npix);
+                sample = (uint32_t)(a.sample_base + i / a.npix);
+                o = mk<float>(a.cam.eye[0], a.cam.eye[1], a.cam.eye[2]);
+                if (a.flags & MCPT_JITTER) {
+                    Rng4 r = rng_draw4(a.seed, pixel, sample, 1, 2);
+                    d = camera_dir(a.cam, (int)pixel, r.u[0] - 0.5f, r.u[1] - 0.5f);
+                    h = trace_fast<false>(s.nodes, s.tris, o, d, -1, s.tmin, 3.0e38f, stack + threadIdx.x, kBlk);
+                    c_rays++;
+                } else {
+                    d = camera_dir(a.cam, (int)pixel, 0.f, 0.f);
+                    const float4 ph = __ldg(a.primary_hit + pixel);
+                    h.prim = __float_as_int(ph.x); h.b = ph.y; h.g = ph.z; h.t = ph.w;
+                }
+                if (h.prim >= 0) c_phits++;
+            } else {
+                const float4 qo = a.in.org[i], qd = a.in.dir[i], qt = a.in.thr[i];
+                o = to_f3(qo); d = to_f3(qd); thr = to_f3(qt);
+                exclude = __float_as_int(qo.w);
+                slot = __float_as_int(qd.w);
+                pixel = (uint32_t)(slot % a.npix);
+                sample = (uint32_t)(a.sample_base + slot / a.npix);
+                if (kTree) { const uint2 nd = a.in.node[i]; node = ((uint64_t)nd.y << 32) | nd.x; }
+                else node = (uint64_t)a.bounce + 1;
+                h = trace_fast<false>(s.nodes, s.tris, o, d, exclude, s.tmin, 3.0e38f, stack + threadIdx.x, kBlk);
+                c_rays++;
+            }
+        }
+
+        // -- B. shade prologue: p, N, back-face, emission (main.cpp:273-288 / 351-366 / 406-421) -----------
+        f3 contrib = mk<float>(0.f, 0.f, 0.f);
+        bool alive = valid && h.prim >= 0;
+        f3 p = o, N = d, wo = -d;
+        PhongMat<float> mat;
+        mat.kd = mat.ks = mk<float>(0.f, 0.f, 0.f); mat.ns = 1.f;
+        if (alive) {
+            const float4 v0 = __ldg(s.pverts + 3 * h.prim), v1 = __ldg(s.pverts + 3 * h.prim + 1), v2 = __ldg(s.pverts + 3 * h.prim + 2);
+            const float4 n0 = __ldg(s.pnorms + 3 * h.prim), n1 = __ldg(s.pnorms + 3 * h.prim + 1), n2 = __ldg(s.pnorms + 3 * h.prim + 2);
+            const float al = 1.0f - h.b - h.g;
+            p = to_f3(v0) * al + to_f3(v1) * h.b + to_f3(v2) * h.g;
+            N = normalize_fast(to_f3(n0) * al + to_f3(n1) * h.b + to_f3(n2) * h.g);
+            if (dot(N, wo) < 0.f) alive = false;  // hit from behind -> 0
+            else {
+                const int li = __float_as_int(v1.w);
+                if (li >= 0) {  // emissive: self-emission only
+                    // shade(): an indirect ray that lands on a light contributes 0 (main.cpp:338); the emission
+                    // return of main.cpp:284-288 is only reachable from the camera ray.
+                    if (!kNee || FIRST) contrib = thr * to_f3(__ldg(s.lights + 5 * li + 4));
+                    alive = false;
+                } else mat = load_mat(s, __float_as_int(v0.w));
+            }
+        }
+        const int depth = a.bounce + 1;
+        const bool rr_forced = a.max_depth > 0 && depth >= a.max_depth;
+        Rng4 r0, r1;
+        r0.u[0] = r0.u[1] = r0.u[2] = r0.u[3] = 0.5f;
+        r1 = r0;
+        if (alive) { r0 = rng_draw4(a.seed, pixel, sample, node, 0); if (STRAT != MCPT_BRDF_ONLY) r1 = rng_draw4(a.seed, pixel, sample, node, 1); }
+        if (alive) c_vert++;
+
+        // MIS / BRDF-only: roulette before any sampling (main.cpp:375-383 / 429-437)
+        bool rr_ok = alive && !rr_forced && !(r0.u[0] > a.p_rr);
+        if (!kNee && !rr_ok) alive = false;
+
+        // -- C. light sampling ---------------------------------------------------------------------------
+        Child ch[2];
+        int n_out = 0;
+        float wsum = 0.f;
+        if (kSph) {
+            int chosen; float wch;
+            warp_light_select(s, alive, p, N, r1.u[0], &chosen, &wsum, &wch);
+            if (alive && chosen >= 0) {
+                // Arvo sample of the chosen triangle (Mylight.cpp:285-317): FP32 for comfortably large solid angles,
+                // FP64 below (alpha+beta+gamma-pi and the edge-angle algebra lose all FP32 digits on tiny lights)
+                const float lsum_f = __ldg(s.lights + 5 * chosen + 3).w;
+                f3 wl; bool ok;
+                int lprim;
+                f3 Le, ngl, lv0;
+                if (wch > 1e-2f * lsum_f) {
+                    LightTri<float> lt = load_light<float>(s, chosen);
+                    SphTri<float> st = spherical_project<float>(lt, p, N);
+                    ok = st.ok;
+                    wl = ok ? arvo_sample<float>(st, r1.u[1], r1.u[2]) : N;
+                    lprim = lt.prim; Le = lt.Le; ngl = lt.ng; lv0 = lt.v0;
+                } else {
+                    LightTri<double> lt = load_light<double>(s, chosen);
+                    SphTri<double> st = spherical_project<double>(lt, to_d3(p), to_d3(N));
+                    ok = st.ok;
+                    wl = ok ? to_f3(arvo_sample<double>(st, (double)r1.u[1], (double)r1.u[2])) : N;
+                    lprim = lt.prim; Le = to_f3(lt.Le); ngl = to_f3(lt.ng); lv0 = to_f3(lt.v0);
+                }
+                const float pl = lsum_f / wsum;  // solid-angle pdf, Mylight.cpp:317
+                const float cosN = dot(wl, N);
+                if (ok && cosN > 0.f) {
+                    if (STRAT == MCPT_MIS) {
+                        // light-sample branch (main.cpp:453-466): the ray continues into whatever it hits
+                        const float pp = phong_pdf<float>(N, wl, wo, mat);
+                        const f3 f = phong_eval<float>(N, wl, wo, mat);
+                        Child& c = ch[n_out++];
+                        c.o = p; c.d = wl; c.exclude = h.prim; c.node = node * 2;
+                        c.thr = thr * f * (cosN / (pl + pp) / a.p_rr);
+                    } else {
+                        // NEE (main.cpp:300-316): visible iff the closest hit along wl IS the sampled triangle
+                        const float cosL = -dot(wl, ngl);
+                        if (cosL > 0.f) {
+                            const float4 q1 = __ldg(s.lights + 5 * chosen + 1), q2 = __ldg(s.lights + 5 * chosen + 2);
+                            float be, ga, tl;
+                            if (tri_test_fast(p, wl, lv0, to_f3(q1), to_f3(q2), s.tmin, &be, &ga, &tl)) {
+                                Hit sh = trace_fast<true>(s.nodes, s.tris, p, wl, h.prim, s.tmin, tl, stack + threadIdx.x, kBlk, lprim);
+                                c_shadow++;
+                                if (sh.prim == lprim) {
+                                    const f3 f = phong_eval<float>(N, wl, wo, mat);
+                                    const float g = (a.flags & MCPT_FIX_NEE_MEASURE) ? cosN / pl : cosN * cosL / (tl * tl) / pl;  // F9
+                                    contrib = contrib + thr * Le * f * g;
+                                }
+                            }
+                        }
+                    }
+                }
+            }
+        } else if (STRAT == MCPT_NEE_UNIFORM) {
+            if (alive) {
+                LightPoint<float> lp = light_sample_uniform_fast(s, r1.u[0], r1.u[1], r1.u[2], r1.u[3]);
+                const f3 dl = lp.coord - p;
+                const float d2 = dot(dl, dl);
+                const f3 wl = dl * rsqrtf(d2);
+                const f3 ngl = to_f3(__ldg(s.lights + 5 * lp.light + 3));
+                const float cosN = dot(wl, N), cosL = -dot(wl, ngl);
+                if (cosN > 0.f && cosL > 0.f) {
+                    const float4 q0 = __ldg(s.lights + 5 * lp.light), q1 = __ldg(s.lights + 5 * lp.light + 1), q2 = __ldg(s.lights + 5 * lp.light + 2);
+                    float be, ga, tl;
+                    if (tri_test_fast(p, wl, to_f3(q0), to_f3(q1), to_f3(q2), s.tmin, &be, &ga, &tl)) {
+                        Hit sh = trace_fast<true>(s.nodes, s.tris, p, wl, h.prim, s.tmin, tl, stack + threadIdx.x, kBlk, lp.prim);
+                        c_shadow++;
+                        if (sh.prim == lp.prim) {
+                            const f3 f = phong_eval<float>(N, wl, wo, mat);
+                            contrib = contrib + thr * lp.Le * f * (cosN * cosL / d2 / lp.prob);  // main.cpp:314
+                        }
+                    }
+                }
+            }
+        }
+
+        // NEE: roulette after the direct term (main.cpp:321-329)
+        if (kNee && !rr_ok) alive = false;
+
+        // -- D. BRDF sample (main.cpp:331-341 / 385-395 / 471-491) ---------------------------------------
+        if (alive) {
+            float pdf;
+            const f3 wi = phong_sample_fast(N, wo, mat, r0.u[1], r0.u[2], r0.u[3], &pdf);
+            const float cosN = dot(wi, N);
+            if (!(cosN < 0.f) && pdf > 0.f) {
+                if (a.flags & MCPT_FIX_MIXTURE_PDF) pdf = phong_pdf<float>(N, wi, wo, mat);  // F8
+                float lpdf = 0.f;
+                if (STRAT == MCPT_MIS && wsum > 0.f) {
+                    // pdf of wi under light sampling (main.cpp:484-489): nearest EMISSIVE triangle along wi, occluders
+                    // ignored; it counts iff it survived this vertex's culls (Mylight.cpp:484-493, evaluated for the
+                    // current vertex -- F10 not reproduced)
+                    Hit lh = trace_fast<false>(s.lnodes, s.ltris, p, wi, h.prim, s.tmin, 3.0e38f, stack + threadIdx.x, kBlk);
+                    c_lrays++;
+                    if (lh.prim >= 0) {
+                        const int li = __float_as_int(__ldg(s.pverts + 3 * lh.prim + 1).w);
+                        if (light_weight_fast(s, li, p, N) > 0.f) lpdf = __ldg(s.lights + 5 * li + 3).w / wsum;
+                    }
+                }
+                const f3 f = phong_eval<float>(N, wi, wo, mat);
+                Child& c = ch[n_out++];
+                c.o = p; c.d = wi; c.exclude = h.prim; c.node = kTree ? node * 2 + 1 : 0;
+                c.thr = thr * f * (cosN / (pdf + lpdf) / a.p_rr);
+            }
+        }
+
+        // -- E. accumulate + emit children --------------------------------------------------------------
+        if (valid) {
+            if (FIRST) a.Lacc[slot] = make_float4(contrib.x, contrib.y, contrib.z, 0.f);
+            else if (kTree) a.contrib[i] = make_float4(contrib.x, contrib.y, contrib.z, __int_as_float(slot));
+            else if (contrib.x != 0.f || contrib.y != 0.f || contrib.z != 0.f) {
+                float4 L = a.Lacc[slot];
+                L.x += contrib.x; L.y += contrib.y; L.z += contrib.z;
+                a.Lacc[slot] = L;
+            }
+        }
+        int base;
+        int off = block_compact_offset(n_out, chunk, a.status, &base, sm_i);
+        for (int k = 0; k < n_out; k++) {
+            const int dst = base + off + k;
+            if (dst < a.capacity) {
+                const Child& c = ch[k];
+                a.out.org[dst] = make_float4(c.o.x, c.o.y, c.o.z, __int_as_float(c.exclude));
+                a.out.dir[dst] = make_float4(c.d.x, c.d.y, c.d.z, __int_as_float(slot));
+                a.out.thr[dst] = make_float4(c.thr.x, c.thr.y, c.thr.z, 0.f);
+                if (kTree) a.out.node[dst] = make_uint2((uint32_t)c.node, (uint32_t)(c.node >> 32));
+            } else c_ovf++;
+        }
+        if (chunk == nchunks - 1 && threadIdx.x == 0) {
+            // the last chunk's inclusive prefix is the size of the out queue
+            volatile unsigned long long* st = a.status;
+            unsigned long long v = st[chunk];
+            int total = (int)(v & kValMask);
+            *a.out_count = total < a.capacity ? total : a.capacity;
+        }
+    }
+    // block-level counter reduction: one atomic per counter per block
+    atomicAdd(&sm_cnt[CNT_VERTICES], c_vert); atomicAdd(&sm_cnt[CNT_RAYS], c_rays); atomicAdd(&sm_cnt[CNT_SHADOW], c_shadow);
+    atomicAdd(&sm_cnt[CNT_LIGHTRAYS], c_lrays); atomicAdd(&sm_cnt[CNT_PRIMARY_HITS], c_phits); atomicAdd(&sm_cnt[CNT_OVERFLOW], c_ovf);
+    __syncthreads();
+    if (threadIdx.x < CNT_N && sm_cnt[threadIdx.x]) atomicAdd(a.counters + threadIdx.x, sm_cnt[threadIdx.x]);
+}
+
+
+// ---- MIS path tree: per-slot sums of per-element contributions ----------------------------------------------
+// The compaction is order preserving and the initial queue is sorted by slot, so all elements of one slot
+// are adjacent.  The head of each run owns the run: no two threads ever write the same slot.
+__global__ void k_runsum(const float4* __restrict__ contrib, int n, float4* Lacc)
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 c = contrib[i];
+    const int slot = __float_as_int(c.w);
+    if (i > 0 && __float_as_int(contrib[i - 1].w) == slot) return;  // not a run head
+    float sx = c.x, sy = c.y, sz = c.z;
+    for (int k = i + 1; k < n; k++) {
+        const float4 e = contrib[k];
+        if (__float_as_int(e.w) != slot) break;
+        sx += e.x; sy += e.y; sz += e.z;
+    }
+    if (sx != 0.f || sy != 0.f || sz != 0.f) {
+        float4 L = Lacc[slot];
+        L.x += sx; L.y += sy; L.z += sz;
+        Lacc[slot] = L;
+    }
+}
+
+// film accumulation (main.cpp:566,575-576,582): the pixel's owner thread sums its slots of this pass
+__global__ void k_accumulate(const float4* __restrict__ Lacc, int npix, int batch_spp, float4* image, int first_pass)
+{
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npix) return;
+    float sx = 0.f, sy = 0.f, sz = 0.f;
+    for (int k = 0; k < batch_spp; k++) {
+        const float4 v = Lacc[(size_t)k * npix + p];
+        sx += v.x; sy += v.y; sz += v.z;
+    }
+    float4 o = first_pass ? make_float4(0.f, 0.f, 0.f, 0.f) : image[p];
+    o.x += sx; o.y += sy; o.z += sz;
+    image[p] = o;
+}
+
+__global__ void k_finalize(const float4* __restrict__ image, int npix, float inv_spp, int accumulate, float* out_rgb)
+{
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npix) return;
+    const float4 v = image[p];
+    float r = v.x * inv_spp, g = v.y * inv_spp, b = v.z * inv_spp;
+    if (accumulate) { r += out_rgb[3 * p]; g += out_rgb[3 * p + 1]; b += out_rgb[3 * p + 2]; }
+    out_rgb[3 * p] = r; out_rgb[3 * p + 1] = g; out_rgb[3 * p + 2] = b;
+}
+
+// RadianceRGB::tone_mapping, RadianceRGB.cpp:51-67
+__global__ void k_tonemap(const float* __restrict__ rgb, size_t n3, double A, double gamma, uint8_t* out)
+{
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n3) return;
+    double r = A * pow((double)rgb[i], gamma);
+    int v = (int)floor(r * 255 + 0.5);
+    out[i] = (uint8_t)(v > 255 ? 255 : (v < 0 ? 0 : v));
+}
+
+template <int STRAT>
+void launch_bounce(bool first, const BounceArgs& a, int grid, cudaStream_t st)
+{
+    if (first) k_bounce<STRAT, true><<<grid, kBlk, 0, st>>>(a);
+    else k_bounce<STRAT, false><<<grid, kBlk, 0, st>>>(a);
+}
+
+template <int STRAT> int bounce_blocks_per_sm()
+{
+    int a = 0, b = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, k_bounce<STRAT, true>, kBlk, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, k_bounce<STRAT, false>, kBlk, 0);
+    return std::max(1, std::min(a, b));
+}
+
+}  // namespace
+
+void workspace_free(Workspace& ws)
+{
+    if (ws.base) cudaFree(ws.base);
+    if (ws.pinned) cudaFreeHost(ws.pinned);
+    if (ws.d_image) cudaFree(ws.d_image);
+    ws = Workspace();
+}
+
+void tonemap_device(McptScene* scene, const float* rgb, size_t n, double max_radiance, double gamma, uint8_t* out)
+{
+    (void)scene;
+    float* d_in = nullptr;
+    uint8_t* d_out = nullptr;
+    size_t n3 = n * 3;
+    MCPT_CUDA(cudaMalloc((void**)&d_in, n3 * sizeof(float)));
+    MCPT_CUDA(cudaMalloc((void**)&d_out, n3));
+    MCPT_CUDA(cudaMemcpy(d_in, rgb, n3 * sizeof(float), cudaMemcpyHostToDevice));
+    if (n3) k_tonemap<<<(unsigned)((n3 + 255) / 256), 256>>>(d_in, n3, std::pow(max_radiance, -gamma), gamma, d_out);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = cudaMemcpy(out, d_out, n3, cudaMemcpyDeviceToHost);
+    cudaFree(d_in); cudaFree(d_out);
+    MCPT_CUDA(e);
+}
+
+void render_device(McptScene* scene, const McptCamera* cam, const McptRenderParams* prm, float* d_out_rgb, cudaStream_t st,
+                   McptStats* stats)
+{
+    const int W = prm->width, H = prm->height;
+    if (W <= 0 || H <= 0 || prm->spp <= 0) throw Error(MCPT_ERR_INVALID, "width, height and spp must be positive");
+    if (prm->strategy < 0 || prm->strategy > 3) throw Error(MCPT_ERR_INVALID, "unknown strategy");
+    if (prm->strategy != MCPT_BRDF_ONLY && scene->L == 0) throw Error(MCPT_ERR_INVALID, "light sampling needs at least one light");
+    const size_t npix = (size_t)W * H;
+    if (npix > (1u << 30)) throw Error(MCPT_ERR_INVALID, "image too large");
+    const bool tree = prm->strategy == MCPT_MIS;
+    const int spp_total = prm->spp_total > 0 ? prm->spp_total : prm->spp;
+    const float p_rr = prm->p_rr > 0.f ? prm->p_rr : 0.6f;
+    int batch = prm->batch_spp > 0 ? prm->batch_spp : (int)std::max<size_t>(1, kTargetSlots / npix);
+    batch = std::min(batch, prm->spp);
+    const size_t slots = npix * (size_t)batch;
+    if (slots > (1u << 30)) throw Error(MCPT_ERR_INVALID, "batch_spp * pixels too large");
+    const size_t cap = tree ? slots * 3 : slots;
+    const size_t chunks = (cap + kBlk - 1) / kBlk + 1;
+
+    // workspace carve-up
+    size_t off = 0;
+    auto place = [&](size_t bytes) { size_t at = off; off = (off + bytes + 255) & ~(size_t)255; return at; };
+    size_t o_q[2][4];
+    for (int q = 0; q < 2; q++) {
+        o_q[q][0] = place(cap * 16); o_q[q][1] = place(cap * 16); o_q[q][2] = place(cap * 16);
+        o_q[q][3] = place(tree ? cap * 8 : 16);
+    }
+    const size_t o_lacc = place(slots * 16), o_contrib = place(tree ? cap * 16 : 16), o_ph = place(npix * 16), o_img = place(npix * 16);
+    const size_t o_status = place(chunks * 8), o_small = place(256);
+    Workspace& ws = scene->ws;
+    if (ws.bytes < off) {
+        if (ws.base) MCPT_CUDA(cudaFree(ws.base));
+        ws.base = nullptr; ws.bytes = 0;
+        if (cudaMalloc(&ws.base, off) != cudaSuccess) { cudaGetLastError(); throw Error(MCPT_ERR_OOM, "cannot allocate render workspace; lower batch_spp"); }
+        ws.bytes = off;
+    }
+    if (!ws.pinned) MCPT_CUDA(cudaMallocHost(&ws.pinned, 256));
+    char* base = (char*)ws.base;
+    Queue Q[2];
+    for (int q = 0; q < 2; q++) {
+        Q[q].org = (float4*)(base + o_q[q][0]); Q[q].dir = (float4*)(base + o_q[q][1]); Q[q].thr = (float4*)(base + o_q[q][2]);
+        Q[q].node = (uint2*)(base + o_q[q][3]);
+    }
+    float4* Lacc = (float4*)(base + o_lacc);
+    float4* contrib = (float4*)(base + o_contrib);
+    float4* primary = (float4*)(base + o_ph);
+    float4* image = (float4*)(base + o_img);
+    unsigned long long* status = (unsigned long long*)(base + o_status);
+    // small block: [0] ticket (int), [1] out_count (int), [8..] counters (u64 x CNT_N)
+    int* d_ticket = (int*)(base + o_small);
+    int* d_count = d_ticket + 1;
+    unsigned long long* d_counters = (unsigned long long*)(base + o_small + 64);
+    volatile int* h_count = (volatile int*)ws.pinned;
+    unsigned long long* h_counters = (unsigned long long*)((char*)ws.pinned + 64);
+
+    // camera (main.cpp:546-553), basis in FP64 on the host
+    DCamera dc;
+    {
+        auto nrm = [](double* v) { double l = std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]); v[0] /= l; v[1] /= l; v[2] /= l; };
+        auto crs = [](const double* a, const double* b, double* o) { o[0] = a[1] * b[2] - a[2] * b[1]; o[1] = a[2] * b[0] - a[0] * b[2]; o[2] = a[0] * b[1] - a[1] * b[0]; };
+        double N[3] = {cam->w[0], cam->w[1], cam->w[2]}, V[3], U[3];
+        double wl = std::sqrt(N[0] * N[0] + N[1] * N[1] + N[2] * N[2]);
+        if (!(wl > 0)) throw Error(MCPT_ERR_INVALID, "camera w must be non-zero");
+        nrm(N); crs(N, cam->up, V); nrm(V); crs(V, N, U); nrm(U);
+        for (int k = 0; k < 3; k++) { dc.eye[k] = (float)cam->eye[k]; dc.U[k] = (float)U[k]; dc.V[k] = (float)V[k]; dc.N[k] = (float)N[k]; }
+        dc.pixellen = (float)cam->pixellen; dc.wlen = (float)wl;
+        dc.ci = (float)((H - 1) * 0.5); dc.cj = (float)((W - 1) * 0.5);
+        dc.W = W; dc.H = H;
+    }
+
+    int dev = scene->device, sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    int bps = prm->strategy == MCPT_NEE_SPHERICAL ? bounce_blocks_per_sm<MCPT_NEE_SPHERICAL>()
+              : prm->strategy == MCPT_BRDF_ONLY   ? bounce_blocks_per_sm<MCPT_BRDF_ONLY>()
+              : prm->strategy == MCPT_MIS         ? bounce_blocks_per_sm<MCPT_MIS>()
+                                                  : bounce_blocks_per_sm<MCPT_NEE_UNIFORM>();
+    const int max_grid = sms * bps;
+
+    McptStats S;
+    std::memset(&S, 0, sizeof S);
+    S.paths = (uint64_t)npix * (uint64_t)prm->spp;
+    MCPT_CUDA(cudaEventRecord(scene->ev[0], st));
+    MCPT_CUDA(cudaMemsetAsync(d_counters, 0, CNT_N * 8, st));
+    const bool jitter = (prm->flags & MCPT_JITTER) != 0;
+    if (!jitter) {
+        k_primary<<<(unsigned)((npix + kBlk - 1) / kBlk), kBlk, 0, st>>>(scene->d, dc, (int)npix, primary);
+        S.kernel_launches++;
+        S.rays_closest += npix;
+    }
+    float ms_bounce = 0.f;
+    bool overflow = false;
+    int done = 0, pass = 0;
+    while (done < prm->spp) {
+        const int b = std::min(batch, prm->spp - done);
+        BounceArgs a;
+        a.s = scene->d; a.cam = dc;
+        a.Lacc = Lacc; a.contrib = contrib; a.primary_hit = primary; a.status = status; a.ticket = d_ticket; a.out_count = d_count;
+        a.counters = d_counters; a.seed = prm->seed; a.capacity = (int)cap; a.npix = (int)npix; a.batch_spp = b;
+        a.sample_base = prm->spp_offset + done; a.max_depth = prm->max_depth; a.flags = prm->flags; a.p_rr = p_rr;
+        int count = (int)(npix * (size_t)b);
+        int cur = 0;
+        for (int bounce = 0; count > 0; bounce++) {
+            if (prm->max_depth <= 0 && bounce >= 256) break;  // unlimited depth: RR has long emptied the queue
+            a.in = Q[cur]; a.out = Q[cur ^ 1]; a.in_count = count; a.bounce = bounce;
+            const int nch = (count + kBlk - 1) / kBlk;
+            MCPT_CUDA(cudaMemsetAsync(status, 0, (size_t)nch * 8, st));
+            MCPT_CUDA(cudaMemsetAsync(d_ticket, 0, 8, st));
+            MCPT_CUDA(cudaEventRecord(scene->ev[2], st));
+            const int grid = std::min(nch, max_grid);
+            switch (prm->strategy) {
+                case MCPT_NEE_SPHERICAL: launch_bounce<MCPT_NEE_SPHERICAL>(bounce == 0, a, grid, st); break;
+                case MCPT_BRDF_ONLY: launch_bounce<MCPT_BRDF_ONLY>(bounce == 0, a, grid, st); break;
+                case MCPT_MIS: launch_bounce<MCPT_MIS>(bounce == 0, a, grid, st); break;
+                default: launch_bounce<MCPT_NEE_UNIFORM>(bounce == 0, a, grid, st); break;
+            }
+            MCPT_CUDA(cudaGetLastError());
+            MCPT_CUDA(cudaEventRecord(scene->ev[3], st));
+            S.kernel_launches++;
+            if (tree && bounce > 0) {
+                k_runsum<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(contrib, count, Lacc);
+                S.kernel_launches++;
+            }
+            MCPT_CUDA(cudaMemcpyAsync((void*)h_count, d_count, 4, cudaMemcpyDeviceToHost, st));
+            MCPT_CUDA(cudaStreamSynchronize(st));
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, scene->ev[2], scene->ev[3]);
+            ms_bounce += ms;
+            S.queue_peak = std::max<uint32_t>(S.queue_peak, (uint32_t)count);
+            S.bounces++;
+            count = *h_count;
+            cur ^= 1;
+            if (prm->max_depth > 0 && bounce + 1 >= prm->max_depth + 1) break;  // vertices deeper than max_depth never spawn
+        }
+        k_accumulate<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(Lacc, (int)npix, b, image, pass == 0);
+        S.kernel_launches++;
+        done += b;
+        pass++;
+    }
+    k_finalize<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(image, (int)npix, 1.0f / (float)spp_total, (prm->flags & MCPT_ACCUMULATE) ? 1 : 0, d_out_rgb);
+    S.kernel_launches++;
+    MCPT_CUDA(cudaMemcpyAsync(h_counters, d_counters, CNT_N * 8, cudaMemcpyDeviceToHost, st));
+    MCPT_CUDA(cudaEventRecord(scene->ev[1], st));
+    MCPT_CUDA(cudaStreamSynchronize(st));
+    MCPT_CUDA(cudaGetLastError());
+    float ms_total = 0.f;
+    cudaEventElapsedTime(&ms_total, scene->ev[0], scene->ev[1]);
+    S.passes = (uint32_t)pass;
+    S.vertices = h_counters[CNT_VERTICES];
+    S.rays_closest += h_counters[CNT_RAYS];
+    S.rays_shadow = h_counters[CNT_SHADOW];
+    S.rays_light = h_counters[CNT_LIGHTRAYS];
+    S.primary_hits = h_counters[CNT_PRIMARY_HITS];
+    overflow = h_counters[CNT_OVERFLOW] != 0;
+    S.ms_total = ms_total; S.ms_bounce = ms_bounce; S.ms_other = ms_total - ms_bounce;
+    if (stats) *stats = S;
+    if (overflow) throw Error(MCPT_ERR_QUEUE_OVERFLOW, "MIS path tree outgrew the ray queue; retry with a smaller batch_spp");
+}
+
+}  // namespace mcpt

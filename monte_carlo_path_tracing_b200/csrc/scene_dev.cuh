@@ -1,0 +1,47 @@
+// csrc/scene_dev.cuh -- the scene as the kernels see it: plain device pointers, passed by value.
+//
+// HBM layout (everything 16-byte vectors, read through the read-only path):
+//   nodes / tris, lnodes / ltris : the two BVHs of bvh.h (whole scene; emissive triangles only)
+//   pverts [P][3] float4 : prim-order vertices; v0.w = material id bits, v1.w = light index bits (-1 = not a light)
+//   pnorms [P][3] float4 : prim-order vertex normals (shading normal = normalised barycentric blend,
+//                          main.cpp:273-274)
+//   mats   [M][2] float4 : (kd.rgb, ns), (ks.rgb, 0)              (main.cpp:292,313)
+//   lights [L][5] float4 : v0|prim bits, v1|class bits, v2|area, ng|Lsum (R+G+B), Le|0 -- in the
+//                          reference's light order (Mylight.cpp:169-173); FP32 copy for the renderer
+//   lng64 [L][3], larea64 [L], crad64 [C][3] : FP64 originals for the parity entry points
+//   class_begin [C+1], class_cdf [C], tri_cdf [L] : the two discrete distributions of
+//                          select_a_point_from_lights (Mylight.cpp:112-135) as normalised cumulative tables
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace mcpt {
+
+struct DScene {
+    const float4* nodes;
+    const float4* tris;
+    const float4* lnodes;
+    const float4* ltris;
+    const float4* pverts;
+    const float4* pnorms;
+    const float4* mats;
+    const float4* lights;
+    const double* lng64;
+    const double* larea64;
+    const double* crad64;
+    const int32_t* class_begin;
+    const float* class_cdf;
+    const float* tri_cdf;
+    int32_t P, L, C, M;
+    float tmin;  // FP32 leaf test: reject t < tmin (scene-scale aware stand-in for the reference's 1e-8)
+};
+
+struct DCamera {
+    float eye[3];
+    float U[3], V[3], N[3];  // T = [U V N], main.cpp:549-553
+    float pixellen, wlen;    // main.cpp:547, |w|
+    float ci, cj;            // (H-1)/2, (W-1)/2 (359.5 / 639.5 at 720x1280, main.cpp:563)
+    int32_t W, H;
+};
+
+}  // namespace mcpt

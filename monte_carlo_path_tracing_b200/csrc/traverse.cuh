@@ -1,0 +1,225 @@
+// csrc/traverse.cuh -- ray/triangle tests and BVH traversal (closest hit, any hit).
+//
+// Replaces Myobj::intersect_with_triangle (Myobj.cpp:165-192), closet_ray_intersect (:334-474) and
+// closet_ray_intersect_light_triangle (:476-622).  Result semantics = the exhaustive search the grid
+// approximates (Myobj.cpp:194-213): minimum t, strict <, ascending prim on ties, origin triangle
+// excluded by id (:417), a hit needs |detA| >= 1e-8, beta,gamma >= 0, beta+gamma <= 1, t >= 1e-8.
+//
+// Two leaf tests:
+//   EXACT : FP64, the reference's Cramer's-rule expression tree evaluated with round-to-nearest
+//           intrinsics so nothing is contracted into FMAs -> beta, gamma, t and therefore the winning
+//           prim are bit-identical to the g++ x86-64 build of the reference.
+//   FAST  : FP32 Moeller-Trumbore, what the renderer runs by default.
+// Traversal stack: per-thread, first kStackSm entries in shared memory ([entry][thread] so a warp's
+// pushes hit 32 different banks), deeper entries spill to a local array.
+#pragma once
+#include "bvh.h"
+#include "device_math.cuh"
+#include "scene_dev.cuh"
+
+namespace mcpt {
+
+constexpr int kStackSm = 24;
+constexpr int kStackLocal = kBvhStackDepth - kStackSm;
+
+struct Hit { int prim; float b, g, t; };       // a2: intersec_result as one float4 (prim = -1: miss)
+struct HitD { int prim; double b, g, t; };
+
+// ---- exact FP64 leaf test -----------------------------------------------------------------------
+__device__ __forceinline__ double rn_dot(d3 a, d3 b)  // vec.cpp:73-81: ((0 + a0 b0) + a1 b1) + a2 b2
+{
+    return __dadd_rn(__dadd_rn(__dmul_rn(a.x, b.x), __dmul_rn(a.y, b.y)), __dmul_rn(a.z, b.z));
+}
+__device__ __forceinline__ d3 rn_cross(d3 a, d3 b)    // vec.cpp:67-70
+{
+    return mk<double>(__dsub_rn(__dmul_rn(a.y, b.z), __dmul_rn(a.z, b.y)), __dsub_rn(__dmul_rn(a.z, b.x), __dmul_rn(a.x, b.z)),
+                      __dsub_rn(__dmul_rn(a.x, b.y), __dmul_rn(a.y, b.x)));
+}
+__device__ __forceinline__ d3 rn_sub(d3 a, d3 b) { return mk<double>(__dsub_rn(a.x, b.x), __dsub_rn(a.y, b.y), __dsub_rn(a.z, b.z)); }
+__device__ __forceinline__ double rn_det(d3 a, d3 b, d3 c) { return rn_dot(rn_cross(a, b), c); }  // vec.cpp:84-87
+
+__device__ __forceinline__ bool tri_test_exact(d3 ro, d3 rd, d3 a, d3 b, d3 c, double* beta, double* gamma, double* t)
+{
+    d3 ab = rn_sub(a, b), ac = rn_sub(a, c), ao = rn_sub(a, ro);
+    double detA = rn_det(ab, ac, rd);                    // Myobj.cpp:172
+    if (fabs(detA) < 1e-8) return false;                 // :175
+    double be = __ddiv_rn(rn_det(ao, ac, rd), detA);     // :180
+    double ga = __ddiv_rn(rn_det(ab, ao, rd), detA);     // :181
+    double tt = __ddiv_rn(rn_det(ab, ac, ao), detA);     // :182
+    if (be < 0 || ga < 0 || __dadd_rn(be, ga) > 1 || tt < 0 || fabs(tt) < 1e-8) return false;  // :185
+    *beta = be; *gamma = ga; *t = tt;
+    return true;
+}
+
+// ---- fast FP32 leaf test --------------------------------------------------------------------------
+__device__ __forceinline__ bool tri_test_fast(f3 ro, f3 rd, f3 a, f3 b, f3 c, float tmin, float* beta, float* gamma, float* t)
+{
+    f3 e1 = b - a, e2 = c - a;
+    f3 pv = cross(rd, e2);
+    float det = dot(e1, pv);
+    if (fabsf(det) < 1e-8f) return false;
+    float inv = 1.0f / det;
+    f3 tv = ro - a;
+    float u = dot(tv, pv) * inv;
+    f3 qv = cross(tv, e1);
+    float v = dot(rd, qv) * inv;
+    float tt = dot(e2, qv) * inv;
+    if (u < 0.f || v < 0.f || u + v > 1.f || tt < tmin) return false;
+    *beta = u; *gamma = v; *t = tt;
+    return true;
+}
+
+// ---- traversal stack --------------------------------------------------------------------------------
+struct TStack {
+    int* sm;      // &smem[threadIdx] ; entry k at sm[k * stride]
+    int stride;
+    int sp;
+    int local[kStackLocal];
+    __device__ __forceinline__ void init(int* base, int stride_) { sm = base; stride = stride_; sp = 0; }
+    __device__ __forceinline__ void push(int v)
+    {
+        if (sp < kStackSm) sm[sp * stride] = v;
+        else if (sp < kBvhStackDepth) local[sp - kStackSm] = v;
+        sp++;
+    }
+    __device__ __forceinline__ int pop()
+    {
+        sp--;
+        return sp < kStackSm ? sm[sp * stride] : (sp < kBvhStackDepth ? local[sp - kStackSm] : 0);
+    }
+};
+
+__device__ __forceinline__ float safe_rcp(float d)
+{
+    return 1.0f / (fabsf(d) > 1e-30f ? d : copysignf(1e-30f, d));
+}
+
+// Closest hit (ANY = false) or first hit with t < tmax (ANY = true), FP32.
+// Ties on t resolve to the lowest prim id (the exhaustive loop's strict <).
+template <bool ANY>
+__device__ __forceinline__ Hit trace_fast(const float4* __restrict__ nodes, const float4* __restrict__ tris, f3 o, f3 d,
+                                          int exclude, float tmin, float tmax, int* stack_sm, int stack_stride, int init_prim = -1)
+{
+    TStack st;
+    st.init(stack_sm, stack_stride);
+    f3 id = mk<float>(safe_rcp(d.x), safe_rcp(d.y), safe_rcp(d.z));
+    f3 ood = mk<float>(o.x * id.x, o.y * id.y, o.z * id.z);
+    // init_prim >= 0: the caller already holds a hit (init_prim at t = tmax); only something that beats it
+    // under the closest-hit order (smaller t, or equal t and lower prim) replaces it -- the visibility test
+    // "closest hit IS the sampled light triangle" of main.cpp:309-311 with an any-hit early out.
+    Hit best;
+    best.prim = init_prim; best.b = 0.f; best.g = 0.f; best.t = tmax;
+    int node = 0;
+    for (;;) {
+        if (node >= 0) {
+            const float4 n0 = __ldg(nodes + 4 * node + 0);
+            const float4 n1 = __ldg(nodes + 4 * node + 1);
+            const float4 n2 = __ldg(nodes + 4 * node + 2);
+            const float4 n3 = __ldg(nodes + 4 * node + 3);
+            float ax = n0.x * id.x - ood.x, bx = n0.y * id.x - ood.x;
+            float ay = n0.z * id.y - ood.y, by = n0.w * id.y - ood.y;
+            float az = n2.x * id.z - ood.z, bz = n2.y * id.z - ood.z;
+            float t0n = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.f));
+            float t0f = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best.t));
+            ax = n1.x * id.x - ood.x; bx = n1.y * id.x - ood.x;
+            ay = n1.z * id.y - ood.y; by = n1.w * id.y - ood.y;
+            az = n2.z * id.z - ood.z; bz = n2.w * id.z - ood.z;
+            float t1n = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.f));
+            float t1f = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best.t));
+            bool h0 = t0n <= t0f, h1 = t1n <= t1f;
+            int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
+            if (h0 && h1) {
+                bool swap = t1n < t0n;
+                st.push(swap ? c0 : c1);
+                node = swap ? c1 : c0;
+                continue;
+            }
+            if (h0) { node = c0; continue; }
+            if (h1) { node = c1; continue; }
+        } else {
+            int code = ~node;
+            int first = code >> 3, cnt = (code & 7) + 1;
+            for (int i = 0; i < cnt; i++) {
+                const float4 v0 = __ldg(tris + 3 * (first + i) + 0);
+                int prim = __float_as_int(v0.w);
+                if (prim == exclude) continue;
+                const float4 v1 = __ldg(tris + 3 * (first + i) + 1);
+                const float4 v2 = __ldg(tris + 3 * (first + i) + 2);
+                float be, ga, tt;
+                if (tri_test_fast(o, d, to_f3(v0), to_f3(v1), to_f3(v2), tmin, &be, &ga, &tt)) {
+                    if (tt < best.t || (tt == best.t && (unsigned)prim < (unsigned)best.prim)) {
+                        best.prim = prim; best.b = be; best.g = ga; best.t = tt;
+                        if (ANY) return best;
+                    }
+                }
+            }
+        }
+        if (st.sp == 0) break;
+        node = st.pop();
+    }
+    return best;
+}
+
+// Closest hit, FP64 boxes + exact leaf test (parity mode).  `ANY`/tmax as above.
+template <bool ANY>
+__device__ __forceinline__ HitD trace_exact(const float4* __restrict__ nodes, const float4* __restrict__ tris, d3 o, d3 d,
+                                            int exclude, double tmax, int* stack_sm, int stack_stride)
+{
+    TStack st;
+    st.init(stack_sm, stack_stride);
+    auto rcp = [](double x) { return 1.0 / (fabs(x) > 1e-300 ? x : copysign(1e-300, x)); };
+    d3 id = mk<double>(rcp(d.x), rcp(d.y), rcp(d.z));
+    HitD best;
+    best.prim = -1; best.b = 0; best.g = 0; best.t = tmax;
+    int node = 0;
+    for (;;) {
+        if (node >= 0) {
+            const float4 n0 = __ldg(nodes + 4 * node + 0);
+            const float4 n1 = __ldg(nodes + 4 * node + 1);
+            const float4 n2 = __ldg(nodes + 4 * node + 2);
+            const float4 n3 = __ldg(nodes + 4 * node + 3);
+            double ax = ((double)n0.x - o.x) * id.x, bx = ((double)n0.y - o.x) * id.x;
+            double ay = ((double)n0.z - o.y) * id.y, by = ((double)n0.w - o.y) * id.y;
+            double az = ((double)n2.x - o.z) * id.z, bz = ((double)n2.y - o.z) * id.z;
+            double t0n = fmax(fmax(fmin(ax, bx), fmin(ay, by)), fmax(fmin(az, bz), 0.0));
+            double t0f = fmin(fmin(fmax(ax, bx), fmax(ay, by)), fmin(fmax(az, bz), best.t));
+            ax = ((double)n1.x - o.x) * id.x; bx = ((double)n1.y - o.x) * id.x;
+            ay = ((double)n1.z - o.y) * id.y; by = ((double)n1.w - o.y) * id.y;
+            az = ((double)n2.z - o.z) * id.z; bz = ((double)n2.w - o.z) * id.z;
+            double t1n = fmax(fmax(fmin(ax, bx), fmin(ay, by)), fmax(fmin(az, bz), 0.0));
+            double t1f = fmin(fmin(fmax(ax, bx), fmax(ay, by)), fmin(fmax(az, bz), best.t));
+            bool h0 = t0n <= t0f, h1 = t1n <= t1f;
+            int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
+            if (h0 && h1) {
+                bool swap = t1n < t0n;
+                st.push(swap ? c0 : c1);
+                node = swap ? c1 : c0;
+                continue;
+            }
+            if (h0) { node = c0; continue; }
+            if (h1) { node = c1; continue; }
+        } else {
+            int code = ~node;
+            int first = code >> 3, cnt = (code & 7) + 1;
+            for (int i = 0; i < cnt; i++) {
+                const float4 v0 = __ldg(tris + 3 * (first + i) + 0);
+                int prim = __float_as_int(v0.w);
+                if (prim == exclude) continue;
+                const float4 v1 = __ldg(tris + 3 * (first + i) + 1);
+                const float4 v2 = __ldg(tris + 3 * (first + i) + 2);
+                double be, ga, tt;
+                if (tri_test_exact(o, d, to_d3(v0), to_d3(v1), to_d3(v2), &be, &ga, &tt)) {
+                    if (tt < best.t || (tt == best.t && (unsigned)prim < (unsigned)best.prim)) {
+                        best.prim = prim; best.b = be; best.g = ga; best.t = tt;
+                        if (ANY) return best;
+                    }
+                }
+            }
+        }
+        if (st.sp == 0) break;
+        node = st.pop();
+    }
+    return best;
+}
+
+}  // namespace mcpt

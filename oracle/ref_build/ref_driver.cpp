@@ -183,7 +183,8 @@ void ref_closest(int n, const double* ro, const double* rd, const int* exclude, 
             r = ans;
         }
         prim[i] = r.isIntersec ? (int)tri_to_prim(r.s, r.f) : -1;
-        bgt[3 * i] = r.beta; bgt[3 * i + 1] = r.gamma; bgt[3 * i + 2] = r.t;
+        // misses report zeros (the reference leaves t = DBL_MAX in `ans`, Myobj.cpp:397)
+        bgt[3 * i] = r.isIntersec ? r.beta : 0; bgt[3 * i + 1] = r.isIntersec ? r.gamma : 0; bgt[3 * i + 2] = r.isIntersec ? r.t : 0;
     }
 }
 

@@ -1,0 +1,127 @@
+"""Shared helpers for the tests: seeded input generators and scene construction.
+
+Everything is seeded and pure numpy so the same inputs can be regenerated on the GPU box
+(where /root/reference does not exist) and compared with tests/golden/*.npz.
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from monte_carlo_path_tracing_b200 import scenes  # noqa: E402
+
+GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
+
+# small scene variants used by the parity tests (same generator parameters as golden/make_golden.py)
+SCENE_KW = {
+    "cornell-box": dict(width=48, height=36),
+    "veach-mis": dict(width=40, height=24, sphere_subdiv=1, plate_tess=(4, 2)),
+}
+
+
+def scene_text(name):
+    return scenes.SCENES[name](**SCENE_KW[name])
+
+
+def u53(rng, shape):
+    """Uniforms that are exact multiples of 2^-53 (what oracle/stream.h delivers)."""
+    m = rng.integers(0, 1 << 53, size=shape, dtype=np.uint64)
+    return m.astype(np.float64) * (1.0 / 9007199254740992.0)
+
+
+def unit(v):
+    return v / np.linalg.norm(v, axis=-1, keepdims=True)
+
+
+def random_rays(arrays, n, seed, inside=True):
+    """Rays with origins inside the scene bounds (or on a shell around it) and random directions."""
+    rng = np.random.default_rng(seed)
+    lo = arrays.positions.reshape(-1, 3).min(0).astype(np.float64)
+    hi = arrays.positions.reshape(-1, 3).max(0).astype(np.float64)
+    if inside:
+        ro = lo + (hi - lo) * rng.random((n, 3))
+    else:
+        c = 0.5 * (lo + hi)
+        ro = c + unit(rng.normal(size=(n, 3))) * np.linalg.norm(hi - lo)
+    rd = unit(rng.normal(size=(n, 3)))
+    # rd need not be unit for intersect_with_triangle (Myobj.cpp:165): scale a quarter of them
+    rd[: n // 4] *= rng.uniform(0.25, 4.0, size=(n // 4, 1))
+    return ro, rd
+
+
+def aimed_rays(arrays, prim, seed):
+    """Rays from random origins aimed at (or just beside) triangle prim[i]: exercises the accept/reject
+    rules of intersect_with_triangle (Myobj.cpp:185) with a healthy hit rate on any scene."""
+    rng = np.random.default_rng(seed)
+    n = len(prim)
+    ro, _ = random_rays(arrays, n, seed + 1)
+    b = rng.uniform(-0.2, 1.0, n); g = rng.uniform(-0.2, 1.0, n) * (1 - np.clip(b, 0, 1))
+    v = arrays.positions[prim].astype(np.float64)
+    tgt = v[:, 0] * (1 - b - g)[:, None] + v[:, 1] * b[:, None] + v[:, 2] * g[:, None]
+    rd = tgt - ro
+    rd[: n // 2] = unit(rd[: n // 2])  # half unit-length, half unnormalised (t ~ 1)
+    return ro, rd
+
+
+def surface_rays(arrays, n, seed):
+    """Rays leaving random points ON triangles, excluding the origin triangle (the renderer's case)."""
+    rng = np.random.default_rng(seed)
+    P = len(arrays.material_id)
+    prim = rng.integers(0, P, size=n).astype(np.int32)
+    b = rng.random(n); g = rng.random(n) * (1 - b)
+    v = arrays.positions[prim].astype(np.float64)
+    ro = v[:, 0] * (1 - b - g)[:, None] + v[:, 1] * b[:, None] + v[:, 2] * g[:, None]
+    rd = unit(rng.normal(size=(n, 3)))
+    return ro, rd, prim
+
+
+def brdf_inputs(n, seed):
+    """Randomised (n, wi, wo, kd, ks, ns in {1,10,100,1000,10000})."""
+    rng = np.random.default_rng(seed)
+    N = unit(rng.normal(size=(n, 3)))
+    # directions in the upper hemisphere of N (mostly), some below to exercise the clamps
+    def hemi():
+        d = unit(rng.normal(size=(n, 3)))
+        s = np.sign(np.sum(d * N, axis=1, keepdims=True))
+        flip = rng.random((n, 1)) < 0.9
+        return np.where(flip, d * s, d)
+    wi, wo = hemi(), hemi()
+    kd = rng.uniform(0.05, 0.6, size=(n, 3))
+    ks = rng.uniform(0.0, 0.4, size=(n, 3))
+    ks[rng.random(n) < 0.2] = 0.0  # purely diffuse materials (discrete_distribution(d, 0))
+    ns = rng.choice([1.0, 10.0, 100.0, 1000.0, 10000.0], size=n)
+    u3 = u53(rng, (n, 3))
+    return N, wi, wo, kd, ks, ns, u3
+
+
+def shading_points(arrays, n, seed):
+    """Random non-emissive surface points with their interpolated shading normal."""
+    rng = np.random.default_rng(seed)
+    is_light = np.zeros(len(arrays.material_id), bool)
+    is_light[arrays.light_prim] = True
+    cand = np.nonzero(~is_light)[0]
+    prim = rng.choice(cand, size=n)
+    b = rng.random(n); g = rng.random(n) * (1 - b)
+    v = arrays.positions[prim].astype(np.float64)
+    nn = arrays.normals[prim].astype(np.float64)
+    w = np.stack([1 - b - g, b, g], axis=1)[:, :, None]
+    x = (v * w).sum(1)
+    N = unit((nn * w).sum(1))
+    u3 = u53(rng, (n, 3))
+    return x, N, u3, prim.astype(np.int32)
+
+
+def rel_err(a, b, floor=1e-300):
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    return np.abs(a - b) / np.maximum(np.abs(b), floor)
+
+
+def rmse(a, b):
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    return float(np.sqrt(np.mean((a - b) ** 2)))
