@@ -1,0 +1,329 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the path-tracing hot path (BASELINE.json).
+
+  python bench.py --gpus N --steps K --warmup W            our CUDA path (one rank per GPU under torchrun)
+  python bench.py --impl reference --gpus N --steps K ...  the reference's own CPU code (oracle/_ref) on the
+                                                           host cores, same workload/metric
+
+Workload (BASELINE.json configs[1]): veach-mis look-alike, 1280x720, shade_with_mis (spherical-triangle +
+BRDF sampling, balance heuristic), no depth cap (the reference has none; Russian roulette p = 0.6 ends
+paths).  One "step" = `--spp-per-step` samples of every pixel on every rank (weak scaling: per-GPU work is
+fixed) followed, for N > 1, by the NCCL reduce of the W*H*3 float film onto rank 0.
+metric = primary Msamples/s = W*H*spp_per_step*N / step time.  Inputs (scene, BVH) are resident in HBM
+for `value`; `e2e` times mcpt_scene_upload (pinned H2D) + mcpt_render (+ film D2H) per step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+from monte_carlo_path_tracing_b200 import scenes  # noqa: E402
+
+WORKLOADS = {
+    # name: (scene generator kwargs, strategy name, max_depth)
+    "veach-mis": dict(scene="veach-mis", kw=dict(width=1280, height=720), strategy="MIS", max_depth=0),
+    "cornell-box": dict(scene="cornell-box", kw=dict(width=512, height=512), strategy="NEE_UNIFORM", max_depth=5),
+}
+STRAT = {"NEE_SPHERICAL": 0, "BRDF_ONLY": 1, "MIS": 2, "NEE_UNIFORM": 3}
+# compulsory wavefront state traffic per sample-bounce (rays, hit, path state, queue words)
+ALGO_BYTES_PER_VERTEX = {"MIS": 384, "NEE_UNIFORM": 256, "NEE_SPHERICAL": 256, "BRDF_ONLY": 160}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)), "measured"
+        except Exception:
+            pass
+    return {"hbm_gbs": 6650.0}, "fallback"
+
+
+# ---- clocks during the timed region ------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.rows, self.stop_flag, self.gpu = [], False, gpu_index
+        self.thread = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self.stop_flag:
+            try:
+                o = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                                   capture_output=True, text=True, timeout=5).stdout.strip()
+                if o:
+                    self.rows.append([x.strip() for x in o.splitlines()[0].split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def start(self):
+        self.thread.start()
+
+    def stop(self):
+        self.stop_flag = True
+        self.thread.join(timeout=6)
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[k] for r in self.rows for k in range(4) if len(r) > 2 + k and r[2 + k].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ---- the reference's CPU code on the host cores ----------------------------------------------------------------
+def _cpu_worker(args):
+    """One process = one copy of the reference (it is not thread-safe: global caches and Mylight scratch,
+    SURVEY.md 8b).  Renders interleaved rows of the workload at 1 spp until the deadline; returns samples done."""
+    stem, cam_d, strategy, max_depth, wid, nw, budget_s, seed, use_ref = args
+    sys.path.insert(0, ROOT)
+    import oracle
+    from monte_carlo_path_tracing_b200.scenes import Camera
+    cam = Camera(**cam_d)
+    if use_ref:
+        lib = oracle.RefLib(stem + ".obj", stem + ".xml")
+        lib.build_grid(cam.eye, 100000)
+        strat = {"NEE_SPHERICAL": 0, "BRDF_ONLY": 1, "MIS": 2}[strategy]
+        render = lambda r0, r1, k: lib.render(cam, strat, 1, max_depth=max_depth, seed=seed, rows=(r0, r1), spp_offset=k, spp_total=1)
+    else:
+        from monte_carlo_path_tracing_b200 import api
+        arrays, _ = api.load_scene_files(stem + ".obj", stem + ".xml")
+        lib = oracle.OracleLib(arrays)
+        lib.build_grid(cam.eye, 100000)
+        render = lambda r0, r1, k: lib.render(cam, STRAT[strategy], 1, max_depth=max_depth, seed=seed, rows=(r0, r1), spp_offset=k, spp_total=1)
+    t0 = time.time()
+    samples = vertices = 0
+    k = 0
+    rows = list(range(wid, cam.height, nw))
+    # spread the rows this worker visits over the whole frame
+    rng = np.random.default_rng(1234 + wid)
+    rng.shuffle(rows)
+    while True:
+        for r in rows:
+            _, cnt = render(r, r + 1, k)
+            samples += cam.width
+            vertices += cnt["vertices"]
+            if time.time() - t0 >= budget_s:
+                return samples, vertices, time.time() - t0
+        k += 1
+
+
+def cpu_reference_run(stem, cam, strategy, max_depth, budget_s, seed=1, procs=None):
+    """All host cores, one reference process each, for ~budget_s seconds.  Returns dict(value Msamples/s, ...)."""
+    import multiprocessing as mp
+    import oracle
+    use_ref = oracle.ref_available() and strategy in ("NEE_SPHERICAL", "BRDF_ONLY", "MIS")
+    if not os.path.exists(oracle.ORACLE_SO):
+        oracle.build(ref=False)
+    nproc = procs or os.cpu_count() or 1
+    cam_d = dict(eye=cam.eye, lookat=cam.lookat, up=cam.up, fovy_deg=cam.fovy_deg, width=cam.width, height=cam.height)
+    ctx = mp.get_context("spawn")
+    t0 = time.time()
+    with ctx.Pool(nproc) as pool:
+        res = pool.map(_cpu_worker, [(stem, cam_d, strategy, max_depth, w, nproc, budget_s, seed, use_ref) for w in range(nproc)])
+    wall = time.time() - t0
+    samples = sum(r[0] for r in res)
+    vertices = sum(r[1] for r in res)
+    busy = max(r[2] for r in res)
+    return {"value": samples / busy / 1e6, "unit": "Msamples/s", "cores": nproc, "kind": "reference" if use_ref else "port",
+            "sample": "%d primary samples (interleaved full-width rows at 1 spp, %.1f s on %d processes; wall incl. load %.1f s)" % (samples, busy, nproc, wall),
+            "sample_bounces_per_s": vertices / busy, "samples": samples, "seconds": busy}
+
+
+# ---- arms -------------------------------------------------------------------------------------------------------
+def write_scene(wl, td):
+    sc = scenes.SCENES[wl["scene"]](**wl["kw"])
+    return sc, sc.write(td)
+
+
+def base_line(args, wl_name, wl, cam, spp_per_step):
+    return {"metric": "primary Msamples/s", "unit": "Msamples/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": "%s %dx%d %s max_depth=%s spp_per_step=%d per GPU" % (
+                wl_name, cam.width, cam.height, wl["strategy"], wl["max_depth"] or "none(RR 0.6)", spp_per_step),
+                "scene": wl["scene"], "width": cam.width, "height": cam.height, "strategy": wl["strategy"],
+                "max_depth": wl["max_depth"], "spp_per_step": spp_per_step, "parallelism": "spp-shard x%d + 1 NCCL reduce" % args.gpus,
+                "l2_policy": "per-step working set (ray queues + film, >400 MB) exceeds the 126 MB L2"}}
+
+
+def run_reference(args, wl_name, wl):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return  # the CPU reference runs once, on rank 0's host cores
+    with tempfile.TemporaryDirectory() as td:
+        sc, stem = write_scene(wl, td)
+        cam = sc.camera
+        for _ in range(min(args.warmup, 1)):
+            cpu_reference_run(stem, cam, wl["strategy"], wl["max_depth"], 1.0)
+        per = max(2.0, min(20.0, 60.0 / max(args.steps, 1)))
+        runs = [cpu_reference_run(stem, cam, wl["strategy"], wl["max_depth"], per, seed=1 + k) for k in range(args.steps)]
+    samples = sum(r["samples"] for r in runs)
+    secs = sum(r["seconds"] for r in runs)
+    v = samples / secs / 1e6
+    line = base_line(args, wl_name, wl, cam, args.spp_per_step)
+    line.update({"impl": "reference", "value": v, "ms_per_step": 1e3 * secs / max(args.steps, 1), "n_gpus": args.gpus,
+                 "dtype": "f64", "gpu_launches": 0,
+                 "cpu_baseline": {"value": v, "unit": "Msamples/s", "cores": runs[0]["cores"], "kind": runs[0]["kind"],
+                                  "sample": "%d steps x %s" % (args.steps, runs[0]["sample"])},
+                 "e2e": {"value": v, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args, wl_name, wl):
+    import torch
+    import torch.distributed as dist
+    from monte_carlo_path_tracing_b200 import api
+    from monte_carlo_path_tracing_b200 import dist as mdist
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    strategy = STRAT[wl["strategy"]]
+    S = args.spp_per_step
+    td = tempfile.mkdtemp(prefix="mcpt_bench_")
+    sc, stem = write_scene(wl, td)
+    cam = sc.camera
+    arrays, _ = api.load_scene_files(stem + ".obj", stem + ".xml")
+    scene = api.Scene(arrays, local)
+    npix = cam.width * cam.height
+    film = torch.zeros(npix * 3, dtype=torch.float32, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    kw = dict(max_depth=wl["max_depth"], seed=args.seed, batch_spp=args.batch_spp)
+
+    def step(k):
+        # global sample range of this step: [k*world*S, (k+1)*world*S), rank r owns S of them
+        st = scene.render_device(cam, strategy, S, film.data_ptr(), stream=stream, spp_offset=(k * world + rank) * S,
+                                 spp_total=S * world, **kw)
+        mdist.reduce_film(film, 0)
+        return st
+
+    def sync():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for k in range(args.warmup):
+        step(k)
+    sync()
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    stats = []
+    sync()
+    e0.record()
+    for k in range(args.steps):
+        stats.append(step(args.warmup + k))
+    e1.record()
+    sync()
+    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    clocks = sampler.stop() if sampler else None
+
+    # ---- e2e through the host-buffer C ABI: scene upload (pinned H2D) + render + film D2H, every step
+    host_out = np.zeros((cam.height, cam.width, 3), np.float32)
+    scene.upload(); scene.render(cam, strategy, min(S, 2), **kw)
+    sync()
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        scene.upload()
+        img, _ = scene.render(cam, strategy, S, spp_offset=(k * world + rank) * S, spp_total=S * world, **kw)
+        if world > 1:
+            film.copy_(torch.from_numpy(img.reshape(-1)), non_blocking=False)
+            mdist.reduce_film(film, 0)
+            if rank == 0:
+                host_out[...] = film.cpu().numpy().reshape(host_out.shape)
+    sync()
+    e2e_s = torch.tensor([time.perf_counter() - t0], device="cuda")
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_s = float(e2e_s.item())
+
+    tot = {k: sum(s[k] for s in stats) for k in ("paths", "vertices", "rays_closest", "rays_shadow", "rays_light", "kernel_launches", "bounces")}
+    ms_bounce = sum(s["ms_bounce"] for s in stats)
+    if rank == 0:
+        samples = npix * S * world * args.steps
+        value = samples / ms / 1e3
+        peaks, which = measured_peaks()
+        algo_b = ALGO_BYTES_PER_VERTEX[wl["strategy"]]
+        launches_bounce = max(tot["bounces"], 1)
+        achieved = algo_b * tot["vertices"] / (ms_bounce * 1e-3) / 1e9  # rank 0's kernels, CUDA events on the launch stream
+        L = len(arrays.light_prim)
+        flops_per_vertex = 320 + (70 * L if wl["strategy"] in ("MIS", "NEE_SPHERICAL") else 0)
+        fp32_peak = 148 * 128 * 2 * 1.965e9
+        line = base_line(args, wl_name, wl, cam, S)
+        line.update({
+            "value": value, "ms_per_step": ms / args.steps,
+            "gpu_launches": int(tot["kernel_launches"]),
+            "clocks": clocks,
+            "e2e": {"value": samples / e2e_s / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": scene.device_bytes(),
+                    "d2h_bytes_per_step": npix * 12},
+            "roofline": {"bound": "hbm", "kernel": "k_bounce<%s>" % wl["strategy"], "achieved": achieved, "peak": peaks["hbm_gbs"],
+                         "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": which,
+                         "algorithmic_bytes_per_sample_bounce": algo_b,
+                         "sample_bounces_per_launch": tot["vertices"] / launches_bounce,
+                         "avg_launch_ms": ms_bounce / launches_bounce, "kernel_share_of_step": ms_bounce / ms * (1.0 if world == 1 else 1.0),
+                         "note": "latency/issue-bound by design (SURVEY.md 8d): HBM fraction shown for completeness, fp32 below"},
+            "fp32": {"achieved_tflops": flops_per_vertex * tot["vertices"] / (ms_bounce * 1e-3) / 1e12, "peak_tflops": fp32_peak / 1e12,
+                     "frac": flops_per_vertex * tot["vertices"] / (ms_bounce * 1e-3) / fp32_peak,
+                     "algorithmic_flops_per_sample_bounce": flops_per_vertex, "lights": L},
+            "extra": {"Msample_bounces_per_s": tot["vertices"] * world / ms / 1e3,
+                      "Mrays_per_s": (tot["rays_closest"] + tot["rays_shadow"] + tot["rays_light"]) * world / ms / 1e3,
+                      "sample_bounces_per_path": tot["vertices"] / max(tot["paths"], 1),
+                      "time_to_1024spp_s": 1024.0 / (S * world) * (ms / args.steps) / 1e3},
+        })
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_reference_run(stem, cam, wl["strategy"], wl["max_depth"], args.cpu_seconds)
+            for k in ("samples", "seconds"):
+                line["cpu_baseline"].pop(k, None)
+        print(json.dumps(line), flush=True)
+    scene.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="veach-mis", choices=sorted(WORKLOADS))
+    ap.add_argument("--spp-per-step", type=int, default=16)
+    ap.add_argument("--batch-spp", type=int, default=0)
+    ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, args.workload, wl)
+    else:
+        run_ours(args, args.workload, wl)
+
+
+if __name__ == "__main__":
+    main()

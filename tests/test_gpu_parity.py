@@ -1,0 +1,178 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (include/mcpt.h), against the oracle
+restatement and the golden vectors of the compiled reference, on identical seeded inputs.
+
+Bars (BASELINE.json north_star): intersection hit / triangle ids bit-exact; BRDF values, pdfs and
+sample directions within 1e-5 relative for fixed uniform inputs (tolerances written at each assert).
+"""
+import numpy as np
+import pytest
+
+import util
+from monte_carlo_path_tracing_b200 import api
+
+pytestmark = pytest.mark.gpu
+
+
+def test_extension_is_loaded_and_native():
+    lib = api.load()
+    assert lib.mcpt_device_count() >= 1, "no CUDA device: the product has no CPU fallback"
+    assert lib.mcpt_version() == 100
+
+
+def test_scene_precompute(scene_name, golden, gpu_scene_of):
+    g = golden(scene_name)
+    s = gpu_scene_of(scene_name)
+    assert np.array_equal(s.geom_normals(), g["geom_normals"])  # get_unique_normal_of_facet, bit-exact
+    assert np.array_equal(s.light_areas(), g["light_area"])
+    info = s.bvh_info()
+    assert info["nodes"] >= 1 and info["max_depth"] < 64
+
+
+def test_intersect_tri_bit_exact(scene_name, golden, gpu_scene_of, arrays_of):
+    g = golden(scene_name)
+    a, _ = arrays_of(scene_name)
+    prim = np.random.default_rng(103).integers(0, len(a.material_id), size=3000).astype(np.int32)
+    ro, rd = util.aimed_rays(a, prim, 104)
+    hit, bgt = gpu_scene_of(scene_name).intersect_tri(ro, rd, prim, api.FP64)
+    assert np.array_equal(hit, g["tri_hit"])
+    assert np.array_equal(bgt, g["tri_bgt"])  # beta, gamma, t bit-identical (Myobj.cpp:172-185)
+
+
+def test_closest_hit_bit_exact(scene_name, golden, gpu_scene_of, arrays_of, oracle_of):
+    """FP64 traversal: same prim AND same (beta, gamma, t) bits as the exhaustive search over
+    intersect_with_triangle (Myobj.cpp:194-213) -- golden vectors and, on fresh rays, the oracle."""
+    g = golden(scene_name)
+    a, _ = arrays_of(scene_name)
+    s = gpu_scene_of(scene_name)
+    ro, rd = util.random_rays(a, 3000, 101)
+    prim, bgt = s.closest(ro, rd, None, False, api.FP64)
+    assert np.array_equal(prim, g["closest_brute_prim"]) and np.array_equal(bgt, g["closest_brute_bgt"])
+    prim, bgt = s.closest(ro, rd, None, True, api.FP64)
+    assert np.array_equal(prim, g["closest_lbrute_prim"]) and np.array_equal(bgt, g["closest_lbrute_bgt"])
+    ro, rd, ex = util.surface_rays(a, 3000, 102)
+    prim, bgt = s.closest(ro, rd, ex, False, api.FP64)
+    assert np.array_equal(prim, g["surf_brute_prim"]) and np.array_equal(bgt, g["surf_brute_bgt"])
+    prim, bgt = s.closest(ro, rd, ex, True, api.FP64)
+    assert np.array_equal(prim, g["surf_lbrute_prim"]) and np.array_equal(bgt, g["surf_lbrute_bgt"])
+    # fresh rays from outside the scene + the oracle (not in the golden file)
+    ro, rd = util.random_rays(a, 20000, 777, inside=False)
+    rd = util.unit(a.positions.reshape(-1, 3)[np.random.default_rng(778).integers(0, a.positions.size // 3, 20000)] - ro)
+    p1, b1 = s.closest(ro, rd, None, False, api.FP64)
+    p0, b0 = oracle_of(scene_name).closest(ro, rd, None, 2)
+    assert np.array_equal(p1, p0) and np.array_equal(b1, b0)
+    assert (p0 >= 0).mean() > 0.5
+
+
+def test_closest_hit_fp32_mismatch_rate(scene_name, golden, gpu_scene_of, arrays_of):
+    """The renderer's FP32 leaf test is not bit-exact; its id mismatch rate vs the reference stays tiny."""
+    g = golden(scene_name)
+    a, _ = arrays_of(scene_name)
+    ro, rd = util.random_rays(a, 3000, 101)
+    prim, bgt = gpu_scene_of(scene_name).closest(ro, rd, None, False, api.FP32)
+    mism = np.mean(prim != g["closest_brute_prim"])
+    assert mism < 5e-3, mism
+    same = prim == g["closest_brute_prim"]
+    hit = same & (prim >= 0)
+    assert np.max(util.rel_err(bgt[hit, 2], g["closest_brute_bgt"][hit, 2])) < 1e-3
+
+
+def test_phong_fp64(scene_name, golden, gpu_scene_of):
+    g = golden(scene_name)
+    s = gpu_scene_of(scene_name)
+    N, wi, wo, kd, ks, ns, u3 = util.brdf_inputs(3000, 105)
+    # tolerance 1e-9 relative: same FP64 expression order, only libm (CUDA vs glibc pow/acos/sincos) differs
+    assert np.max(util.rel_err(s.brdf_eval(N, wi, wo, kd, ks, ns, api.FP64), g["brdf_eval"], 1e-12)) < 1e-9
+    assert np.max(util.rel_err(s.brdf_pdf(N, wi, wo, kd, ks, ns, api.FP64), g["brdf_pdf"], 1e-12)) < 1e-9
+    d, pdf = s.brdf_sample(N, wo, kd, ks, ns, u3, api.FP64)
+    assert np.max(np.abs(d - g["brdf_sample_dir"])) < 1e-9
+    assert np.max(util.rel_err(pdf, g["brdf_sample_pdf"], 1e-12)) < 1e-9
+
+
+def test_phong_fp32_renderer_variant(scene_name, golden, gpu_scene_of):
+    """What the renderer runs.  FP32 cannot hold 1e-5 everywhere: (a) rounding the lobe cosine x (a few ulp,
+    ~5e-7 relative) is amplified by ns in x^ns, so the relative bound is 1e-5 + 1e-6 * ns; (b) a grazing
+    cosine carries ~1e-7 ABSOLUTE error from the dot product, so there is an absolute floor of 3e-7 times the
+    lobe's peak value.  The 1e-5 bar itself is met by the FP64 instantiation above (DESIGN.md 'precision')."""
+    g = golden(scene_name)
+    s = gpu_scene_of(scene_name)
+    N, wi, wo, kd, ks, ns, u3 = util.brdf_inputs(3000, 105)
+    rtol = 1e-5 + 1e-6 * ns
+    atol = 3e-7 * (1.0 + (ns + 1.0) / (2 * np.pi))
+
+    def close(a, b, k=1.0):
+        a = np.asarray(a); b = np.asarray(b)
+        r, t = (rtol, atol) if a.ndim == 1 else (rtol[:, None], atol[:, None])
+        return np.all(np.abs(a - b) <= k * (r * np.abs(b) + t))
+    assert close(s.brdf_eval(N, wi, wo, kd, ks, ns, api.FP32), g["brdf_eval"])
+    assert close(s.brdf_pdf(N, wi, wo, kd, ks, ns, api.FP32), g["brdf_pdf"])
+    d, pdf = s.brdf_sample(N, wo, kd, ks, ns, u3, api.FP32)  # phong_sample_fast
+    # the lobe choice compares u with P(diffuse): skip the few inputs where FP32 rounding of u flips it
+    dsum = kd.sum(1) / 3; ssum = ks.sum(1) / 3
+    safe = np.abs(dsum / (dsum + ssum) - u3[:, 0]) > 1e-6
+    assert np.max(np.abs(d[safe] - g["brdf_sample_dir"][safe])) < 2e-5  # sample directions: 1e-5-level absolute
+    ok = np.abs(pdf - g["brdf_sample_pdf"]) <= 2 * (rtol * np.abs(g["brdf_sample_pdf"]) + atol)
+    assert np.all(ok[safe])
+
+
+def test_light_uniform(scene_name, golden, gpu_scene_of):
+    g = golden(scene_name)
+    u4 = util.u53(np.random.default_rng(106), (2000, 4))
+    prim, pt, Le, pdf = gpu_scene_of(scene_name).light_sample_uniform(u4, api.FP64)
+    assert np.array_equal(prim, g["lu_prim"])
+    assert np.max(np.abs(pt - g["lu_point"])) < 1e-9 * max(1.0, np.abs(g["lu_point"]).max())
+    assert np.array_equal(Le, g["lu_Le"])
+    assert np.max(util.rel_err(pdf, g["lu_pdf"])) < 1e-12
+    prim, pt, Le, pdf = gpu_scene_of(scene_name).light_sample_uniform(u4, api.FP32)
+    assert np.mean(prim != g["lu_prim"]) < 2e-3
+    ok = prim == g["lu_prim"]
+    assert np.max(util.rel_err(pdf[ok], g["lu_pdf"][ok])) < 1e-5
+
+
+def test_light_spherical(scene_name, golden, gpu_scene_of, arrays_of):
+    g = golden(scene_name)
+    a, _ = arrays_of(scene_name)
+    s = gpu_scene_of(scene_name)
+    x, Nn, u3, _ = util.shading_points(a, 600, 107)
+    query = a.light_prim[np.random.default_rng(108).integers(0, len(a.light_prim), size=600)]
+    r = s.light_sample_spherical(x, Nn, u3, query, api.FP64)
+    assert np.array_equal(r["nsurv"], g["ls_nsurv"])
+    # sA = alpha+beta+gamma-pi (Mylight.cpp:236) cancels: a 1-ulp libm difference in one acos (CUDA vs glibc) is
+    # amplified by pi/sA, ~1e8 on the small sphere lights -> 1e-6 relative on weights_sum and the pdfs
+    assert np.max(util.rel_err(r["wsum"], g["ls_wsum"], 1e-30)) < 1e-6
+    assert np.mean(r["prim"] != g["ls_prim"]) < 0.005  # a tie in the discrete pick can flip on that rounding
+    has = g["ls_nsurv"] > 0
+    assert np.max(util.rel_err(r["pdf"][has], g["ls_pdf"][has])) < 1e-6
+    assert np.max(util.rel_err(r["query_pdf"], g["ls_query_pdf"], 1e-30)) < 1e-6
+    # sampled point on the light == x1 + P t: direction within 1e-5 relative is the north-star bar;
+    # the FP64 path gives ~1e-9 of the scene scale
+    scale = np.abs(g["ls_point"][has]).max()
+    fin = has & np.isfinite(g["ls_point"]).all(1) & (r["prim"] == g["ls_prim"])
+    assert np.max(np.abs(r["point"][fin] - g["ls_point"][fin])) < 1e-7 * scale
+    dir_g = util.unit(g["ls_point"][fin] - x[fin]); dir_r = util.unit(r["point"][fin] - x[fin])
+    moved = np.linalg.norm(g["ls_point"][fin] - x[fin], axis=1) > 0
+    assert np.max(np.abs(dir_g[moved] - dir_r[moved])) < 1e-5
+    # the renderer's FP32 weights (Van Oosterom-Strackee): weights_sum within 1e-4, same survivors
+    f = s.light_sample_spherical(x, Nn, u3, query, 2)
+    big = g["ls_wsum"] > 0
+    assert np.mean(f["nsurv"] != g["ls_nsurv"]) < 0.02
+    same = big & (f["nsurv"] == g["ls_nsurv"])
+    assert np.max(util.rel_err(f["wsum"][same], g["ls_wsum"][same])) < 1e-4
+
+
+def test_tonemap(gpu_scene_of, golden):
+    vals = np.abs(np.random.default_rng(109).normal(size=(200, 3))) * 200
+    out = gpu_scene_of("cornell-box").tonemap(vals.astype(np.float32))
+    ref = golden("cornell-box")["tonemap"]
+    assert np.max(np.abs(out.astype(int) - ref)) <= 1  # inputs rounded to float32 on the way in
+
+
+def test_error_paths(arrays_of):
+    a, _ = arrays_of("cornell-box")
+    import copy
+    bad = copy.copy(a)
+    bad.material_id = a.material_id.copy(); bad.material_id[0] = 99
+    with pytest.raises(api.McptError) as e:
+        api.Scene(bad)
+    assert e.value.code == -1
+    with pytest.raises(api.McptError):
+        api.Scene(a, device=1000)
