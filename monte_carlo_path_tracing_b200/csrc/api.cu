@@ -12,7 +12,7 @@ void set_last_error(const std::string& msg) { g_last_error = msg; }
 
 namespace {
 struct BlobLayout {
-    size_t off_nodes, off_tris, off_lnodes, off_ltris, off_pverts, off_pnorms, off_mats, off_lights, off_lng64, off_larea64,
+    size_t off_nodes, off_tris, off_lnodes, off_ltris, off_pverts, off_pnorms, off_mats, off_lights, off_lsoa, off_lng64, off_larea64,
         off_crad64, off_class_begin, off_class_cdf, off_tri_cdf, total;
 };
 size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -134,6 +134,8 @@ int mcpt_scene_create(const McptSceneDesc* desc, int device, McptScene** out)
         B.off_pnorms = place((size_t)P * 3 * 16);
         B.off_mats = place((size_t)Mn * 2 * 16);
         B.off_lights = place((size_t)L * 5 * 16);
+        const uint32_t Lpad = (L + 63) / 64 * 64;
+        B.off_lsoa = place((size_t)Lpad * 4 * 16);
         B.off_lng64 = place((size_t)L * 3 * 8);
         B.off_larea64 = place((size_t)L * 8);
         B.off_crad64 = place((size_t)C * 3 * 8);
@@ -176,6 +178,8 @@ int mcpt_scene_create(const McptSceneDesc* desc, int device, McptScene** out)
         float* ccdf = (float*)(hb + B.off_class_cdf);
         float* tcdf = (float*)(hb + B.off_tri_cdf);
         for (uint32_t c = 0; c < C * 3; c++) crd[c] = s->class_radiance[c];
+        f4* so = (f4*)(hb + B.off_lsoa);
+        for (uint32_t l = L; l < Lpad; l++) so[2 * Lpad + l].w = std::numeric_limits<float>::infinity();  // padding: always culled
         for (uint32_t l = 0; l < L; l++) {
             int32_t prim = s->light_prim[l], cls = s->light_class[l];
             const float* v = &s->positions[(size_t)prim * 9];
@@ -188,6 +192,11 @@ int mcpt_scene_create(const McptSceneDesc* desc, int device, McptScene** out)
             lt[5 * l + 4] = f4{(float)r[0], (float)r[1], (float)r[2], 0.f};
             std::memcpy(&lt[5 * l + 0].w, &prim, 4);
             std::memcpy(&lt[5 * l + 1].w, &cls, 4);
+            const double a2 = 2.0 * s->light_area[l];
+            so[l] = f4{v[0], v[1], v[2], 0.f};
+            so[Lpad + l] = f4{v[3], v[4], v[5], 0.f};
+            so[2 * Lpad + l] = f4{v[6], v[7], v[8], (float)(1e-8 * a2)};
+            so[3 * Lpad + l] = f4{(float)(g[0] * a2), (float)(g[1] * a2), (float)(g[2] * a2), (float)(r[0] + r[1] + r[2])};
             for (int c = 0; c < 3; c++) lng[3 * l + c] = g[c];
             lar[l] = s->light_area[l];
         }
@@ -215,6 +224,7 @@ int mcpt_scene_create(const McptSceneDesc* desc, int device, McptScene** out)
         d.lnodes = (const float4*)(db + B.off_lnodes); d.ltris = (const float4*)(db + B.off_ltris);
         d.pverts = (const float4*)(db + B.off_pverts); d.pnorms = (const float4*)(db + B.off_pnorms);
         d.mats = (const float4*)(db + B.off_mats); d.lights = (const float4*)(db + B.off_lights);
+        d.lsoa = (const float4*)(db + B.off_lsoa); d.Lpad = (int32_t)Lpad;
         d.lng64 = (const double*)(db + B.off_lng64); d.larea64 = (const double*)(db + B.off_larea64);
         d.crad64 = (const double*)(db + B.off_crad64); d.class_begin = (const int32_t*)(db + B.off_class_begin);
         d.class_cdf = (const float*)(db + B.off_class_cdf); d.tri_cdf = (const float*)(db + B.off_tri_cdf);

@@ -86,21 +86,72 @@ __device__ __forceinline__ V3<T> arvo_sample(const SphTri<T>& st, T xi1, T xi2)
 // Van Oosterom-Strackee form  tan(sA/2) = |a.(b x c)| / (|a||b||c| + (a.b)|c| + (a.c)|b| + (b.c)|a|)
 // where a,b,c = vertices - x1.  a.(b x c) = (v0-x1).((v1-v0) x (v2-v0)) = 2 area * ng.(v0-x1) has no
 // cancellation, so tiny lights keep full FP32 relative accuracy where alpha+beta+gamma-pi has none.
+//
+// The loop reads the SoA table `lsoa` (scene_dev.cuh): four float4 planes of Lpad entries, so a warp's 32
+// lanes fetch 32 consecutive 16-byte vectors per plane (4 x 512 B, fully coalesced):
+//   plane0 = v0 | -, plane1 = v1 | -, plane2 = v2 | cull threshold 1e-8 * 2 area,
+//   plane3 = Ns = 2 area * ng | Lsum;  padding entries have threshold = +inf and evaluate to 0.
+// Branch-free on purpose: two evaluations are interleaved per loop trip and every load is hoisted.
+
+// atan(q) for q in [0,1]: Abramowitz & Stegun 4.4.49, |error| <= 2e-8; exact to first order as q -> 0
+__device__ __forceinline__ float atan_unit(float q)
+{
+    const float s = q * q;
+    float p = 0.0028662257f;
+    p = fmaf(p, s, -0.0161657367f);
+    p = fmaf(p, s, 0.0429096138f);
+    p = fmaf(p, s, -0.0752896400f);
+    p = fmaf(p, s, 0.1065626393f);
+    p = fmaf(p, s, -0.1420889944f);
+    p = fmaf(p, s, 0.1999355085f);
+    p = fmaf(p, s, -0.3333314528f);
+    return fmaf(q, p * s, q);
+}
+// atan2(y, x) for y > 0, result in (0, pi)
+__device__ __forceinline__ float atan2_pos(float y, float x)
+{
+    const float ax = fabsf(x);
+    const float mx = fmaxf(ax, y), mn = fminf(ax, y);
+    float r = atan_unit(__fdividef(mn, mx));
+    r = (y > ax) ? 1.57079632679489662f - r : r;
+    return (x < 0.f) ? 3.14159265358979324f - r : r;
+}
+
+__device__ __forceinline__ float light_weight_soa(float4 p0, float4 p1, float4 p2, float4 p3, f3 x1, f3 n)
+{
+    const f3 a = to_f3(p0) - x1, b = to_f3(p1) - x1, c = to_f3(p2) - x1;
+    const float num = -(p3.x * a.x + p3.y * a.y + p3.z * a.z);         // 2 area * (ng . (x1 - v0)), :178-185
+    const float hmax = fmaxf(dot(n, a), fmaxf(dot(n, b), dot(n, c)));  // :187-197
+    const float aa = dot(a, a), bb = dot(b, b), cc = dot(c, c);
+    const float la = aa * rsqrtf(aa), lb = bb * rsqrtf(bb), lc = cc * rsqrtf(cc);
+    const float den = la * lb * lc + dot(a, b) * lc + dot(a, c) * lb + dot(b, c) * la;
+    const float w = 2.0f * atan2_pos(num, den) * p3.w;
+    const bool ok = num >= p2.w && hmax >= 1e-8f && w > 0.f && w < CUDART_INF_F;
+    return ok ? w : 0.f;
+}
+
 __device__ __forceinline__ float light_weight_fast(const DScene& s, int l, f3 x1, f3 n)
 {
-    const float4 p0 = __ldg(s.lights + 5 * l + 0), p1 = __ldg(s.lights + 5 * l + 1), p2 = __ldg(s.lights + 5 * l + 2);
-    const float4 ng = __ldg(s.lights + 5 * l + 3);
-    f3 a = to_f3(p0) - x1, b = to_f3(p1) - x1, c = to_f3(p2) - x1;
-    float tmp = -dot(to_f3(ng), a);
-    if (tmp < 1e-8f) return 0.f;
-    float ha = dot(n, a), hb = dot(n, b), hc = dot(n, c);
-    if (ha < 1e-8f && hb < 1e-8f && hc < 1e-8f) return 0.f;
-    float la = sqrtf(dot(a, a)), lb = sqrtf(dot(b, b)), lc = sqrtf(dot(c, c));
-    float num = tmp * (2.0f * p2.w);
-    float den = la * lb * lc + dot(a, b) * lc + dot(a, c) * lb + dot(b, c) * la;
-    float sA = 2.0f * atan2f(num, den);
-    float w = sA * ng.w;
-    return (w > 0.f && !isinf(w)) ? w : 0.f;
+    const float4* P = s.lsoa + l;
+    return light_weight_soa(__ldg(P), __ldg(P + s.Lpad), __ldg(P + 2 * s.Lpad), __ldg(P + 3 * s.Lpad), x1, n);
+}
+
+// Sum over this lane's lights (l = lane, lane + 32, ...) of the weights seen from (x1, n).  All 32 lanes call.
+__device__ __forceinline__ float warp_light_partial(const DScene& s, f3 x1, f3 n)
+{
+    const int lane = threadIdx.x & 31;
+    const float4* __restrict__ P0 = s.lsoa;
+    const float4* __restrict__ P1 = P0 + s.Lpad;
+    const float4* __restrict__ P2 = P1 + s.Lpad;
+    const float4* __restrict__ P3 = P2 + s.Lpad;
+    float s0 = 0.f, s1 = 0.f;
+    for (int l = lane; l < s.Lpad; l += 64) {  // Lpad is a multiple of 64
+        const float4 a0 = __ldg(P0 + l), a1 = __ldg(P1 + l), a2 = __ldg(P2 + l), a3 = __ldg(P3 + l);
+        const float4 b0 = __ldg(P0 + l + 32), b1 = __ldg(P1 + l + 32), b2 = __ldg(P2 + l + 32), b3 = __ldg(P3 + l + 32);
+        s0 += light_weight_soa(a0, a1, a2, a3, x1, n);
+        s1 += light_weight_soa(b0, b1, b2, b3, x1, n);
+    }
+    return s0 + s1;
 }
 
 // ---- uniform-area sampling, Mylight.cpp:102-160 --------------------------------------------------------

@@ -27,9 +27,9 @@
 namespace mcpt {
 namespace {
 
-constexpr int kBlk = 128;             // threads per block == rays per chunk
+constexpr int kBlk = 128;             // threads per block (4 warps; a warp owns one 32-ray chunk at a time)
 constexpr unsigned kFull = 0xffffffffu;
-constexpr size_t kTargetSlots = 4u << 20;  // auto batch: ~4M path slots in flight per pass
+constexpr size_t kTargetSlots = 16u << 20;  // auto batch: ~16M path slots in flight per pass
 
 enum { CNT_VERTICES = 0, CNT_RAYS, CNT_SHADOW, CNT_LIGHTRAYS, CNT_PRIMARY_HITS, CNT_OVERFLOW, CNT_N };
 
@@ -47,9 +47,11 @@ struct BounceArgs {
     float4* Lacc;              // [slots] per-slot radiance accumulator (owner-exclusive)
     float4* contrib;           // [capacity] MIS: per-element emission contribution | slot
     const float4* primary_hit; // [npix] prim | beta | gamma | t
-    unsigned long long* status;  // [chunks] look-back words: flag(2) | count(62)
+    const int2* sel;           // [slots] first-vertex light drawn by k_lightprep: index | weight bits
+    const float* wsum_pix;     // [npix] first-vertex weights_sum
+    int* counts;               // [chunks] children staged by each chunk
+    int* groupsum;             // [chunks / kGroup] sums of counts, filled with one integer atomic per chunk
     int* ticket;               // chunk ticket counter
-    int* out_count;            // final size of the out queue
     unsigned long long* counters;
     uint64_t seed;
     int in_count, capacity, npix, batch_spp, sample_base, bounce, max_depth;
@@ -79,10 +81,64 @@ __device__ __forceinline__ f3 camera_dir(const DCamera& c, int pixel, float di, 
 
 // ---- warp-cooperative spherical-triangle light selection --------------------------------------------------
 // The reference loops over ALL light triangles at every vertex (Mylight.cpp:169-259 / :329-421) and then
-// draws one with probability weight/weights_sum (:271-276).  Here a warp serves its lanes' vertices one at a
-// time: lanes stride over the lights (coalesced float4 loads), a shuffle scan gives weights_sum and the lane
-// whose partial interval contains u*weights_sum, and a second short pass over that lane's lights resolves the
-// triangle.  Same distribution, O(L/32) per lane per vertex, and no lane idles while others loop.
+// draws one with probability weight/weights_sum (:271-276).  Here a warp serves one vertex at a time: lanes
+// stride over the SoA light table (warp_light_partial, lights.cuh), a shuffle scan gives weights_sum and the
+// lane whose partial interval contains u*weights_sum, and a second short pass over that lane's lights resolves
+// the triangle.  Same distribution, O(L/32) per lane per vertex, and no lane idles while others loop.
+struct LightPick { int light; float w; };
+
+// `part` = this lane's partial sum, `incl` its inclusive scan over lanes, `total` the sum over all lanes.
+__device__ __forceinline__ LightPick warp_light_pick(const DScene& s, f3 X, f3 Nn, float part, float incl, float total, float uu)
+{
+    const int lane = threadIdx.x & 31;
+    LightPick r;
+    r.light = -1; r.w = 0.f;
+    if (!(total > 0.f)) return r;
+    const float target = uu * total;
+    const unsigned nz = __ballot_sync(kFull, part > 0.f);
+    const unsigned ge = __ballot_sync(kFull, incl >= target && part > 0.f);
+    const int j = ge ? (__ffs(ge) - 1) : (31 - __clz(nz));
+    const float rem = target - (__shfl_sync(kFull, incl, j) - __shfl_sync(kFull, part, j));
+    float running = 0.f;
+    int last_l = -1;
+    float last_w = 0.f;
+    for (int k0 = 0; j + 32 * k0 < s.L && r.light < 0; k0 += 32) {
+        const int l = j + 32 * (k0 + lane);
+        const float w = (l < s.L) ? light_weight_fast(s, l, X, Nn) : 0.f;
+        float wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            float t = __shfl_up_sync(kFull, wi, o);
+            if (lane >= o) wi += t;
+        }
+        const unsigned pos = __ballot_sync(kFull, w > 0.f);
+        const unsigned hit = __ballot_sync(kFull, w > 0.f && running + wi >= rem);
+        if (hit) {
+            const int f = __ffs(hit) - 1;
+            r.light = j + 32 * (k0 + f);
+            r.w = __shfl_sync(kFull, w, f);
+        } else if (pos) {
+            const int f = 31 - __clz(pos);
+            last_l = j + 32 * (k0 + f);
+            last_w = __shfl_sync(kFull, w, f);
+        }
+        running += __shfl_sync(kFull, wi, 31);
+    }
+    if (r.light < 0) { r.light = last_l; r.w = last_w; }  // rounding: fall back to the lane's last survivor
+    return r;
+}
+
+__device__ __forceinline__ float warp_scan_incl(float v)
+{
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        float t = __shfl_up_sync(kFull, v, o);
+        if (lane >= o) v += t;
+    }
+    return v;
+}
+
 // Must be called by all 32 lanes; lanes with need == false only help.
 __device__ __forceinline__ void warp_light_select(const DScene& s, bool need, f3 x, f3 n, float u, int* chosen, float* wsum_out,
                                                   float* w_chosen)
@@ -96,107 +152,101 @@ __device__ __forceinline__ void warp_light_select(const DScene& s, bool need, f3
         f3 X = mk<float>(__shfl_sync(kFull, x.x, src), __shfl_sync(kFull, x.y, src), __shfl_sync(kFull, x.z, src));
         f3 Nn = mk<float>(__shfl_sync(kFull, n.x, src), __shfl_sync(kFull, n.y, src), __shfl_sync(kFull, n.z, src));
         const float uu = __shfl_sync(kFull, u, src);
-        float part = 0.f;
-        for (int l = lane; l < s.L; l += 32) part += light_weight_fast(s, l, X, Nn);
-        float incl = part;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            float t = __shfl_up_sync(kFull, incl, o);
-            if (lane >= o) incl += t;
-        }
+        const float part = warp_light_partial(s, X, Nn);
+        const float incl = warp_scan_incl(part);
         const float total = __shfl_sync(kFull, incl, 31);
-        int found = -1;
-        float wfound = 0.f;
-        if (total > 0.f) {
-            const float target = uu * total;
-            const unsigned nz = __ballot_sync(kFull, part > 0.f);
-            unsigned ge = __ballot_sync(kFull, incl >= target && part > 0.f);
-            const int j = ge ? (__ffs(ge) - 1) : (31 - __clz(nz));
-            const float rem = target - (__shfl_sync(kFull, incl, j) - __shfl_sync(kFull, part, j));
-            float running = 0.f;
-            int last_l = -1;
-            float last_w = 0.f;
-            for (int k0 = 0; j + 32 * k0 < s.L && found < 0; k0 += 32) {
-                const int l = j + 32 * (k0 + lane);
-                const float w = (l < s.L) ? light_weight_fast(s, l, X, Nn) : 0.f;
-                float wi = w;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    float t = __shfl_up_sync(kFull, wi, o);
-                    if (lane >= o) wi += t;
-                }
-                const unsigned pos = __ballot_sync(kFull, w > 0.f);
-                const unsigned hit = __ballot_sync(kFull, w > 0.f && running + wi >= rem);
-                if (hit) {
-                    const int f = __ffs(hit) - 1;
-                    found = j + 32 * (k0 + f);
-                    wfound = __shfl_sync(kFull, w, f);
-                } else if (pos) {
-                    const int f = 31 - __clz(pos);
-                    last_l = j + 32 * (k0 + f);
-                    last_w = __shfl_sync(kFull, w, f);
-                }
-                running += __shfl_sync(kFull, wi, 31);
-            }
-            if (found < 0) { found = last_l; wfound = last_w; }  // rounding: fall back to the lane's last survivor
-        }
-        if (lane == src) { *chosen = found; *wsum_out = total; *w_chosen = wfound; }
+        const LightPick pk = warp_light_pick(s, X, Nn, part, incl, total, uu);
+        if (lane == src) { *chosen = pk.light; *wsum_out = total; *w_chosen = pk.w; }
     }
 }
 
-// ---- order-preserving compaction --------------------------------------------------------------------------
-// Block-exclusive offsets of `n_out` (0..2) per thread via __ballot_sync / shuffle prefix sums, then the
-// chunk's global base from a decoupled look-back over the per-chunk status words.  Chunks are handed out by
-// a ticket counter in increasing order, so every predecessor of a waiting chunk is already running.
-constexpr unsigned long long kFlagAgg = 1ull << 62, kFlagIncl = 2ull << 62, kValMask = (1ull << 62) - 1;
+// ---- order-preserving queue compaction, wait-free ------------------------------------------------------------
+// A chunk is the 32 rays one warp processes.  The warp packs its 0..2 children per lane with __ballot_sync /
+// popc prefix sums into the chunk's own window of a STAGING queue (stage[chunk * stride + k], stride = 32 or,
+// for the MIS path tree, 64), records counts[chunk] and adds the count to its 1024-chunk group sum (one integer
+// atomic per warp: commutative, so the result is deterministic).  k_gather then turns group sums + counts into
+// exact offsets and moves the chunk windows into the dense queue, preserving input order -- which keeps all
+// rays of one path-tree adjacent (k_runsum) without any warp ever waiting for another.
+constexpr int kGroup = 1024;  // chunks per k_gather block
 
-__device__ __forceinline__ int block_compact_offset(int n_out, int chunk, unsigned long long* status, int* base_out, int* smem_i)
+__global__ void __launch_bounds__(256) k_gather(const Queue stage, const Queue out, const int* __restrict__ counts,
+                                                const int* __restrict__ groupsum, int nch, int stride, int capacity, int tree,
+                                                int* out_count, unsigned long long* counters)
 {
-    // smem_i: kBlk/32 + 2 ints
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    int incl = n_out;
+    __shared__ int s_red[8];
+    __shared__ int s_base[kGroup];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = blockIdx.x;
+    // 1. offset of this group = sum of the sums of all earlier groups
+    int acc = 0;
+    for (int j = tid; j < g; j += 256) acc += groupsum[j];
+    acc = __reduce_add_sync(kFull, acc);
+    if (lane == 0) s_red[warp] = acc;
+    __syncthreads();
+    int gbase = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) gbase += s_red[w];
+    __syncthreads();
+    // 2. exclusive scan of this group's chunk counts (4 consecutive chunks per thread)
+    const int c0 = g * kGroup + 4 * tid;
+    int c[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) c[k] = (c0 + k < nch) ? counts[c0 + k] : 0;
+    const int tsum = c[0] + c[1] + c[2] + c[3];
+    int incl = tsum;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         int t = __shfl_up_sync(kFull, incl, o);
         if (lane >= o) incl += t;
     }
-    if (lane == 31) smem_i[warp] = incl;
+    if (lane == 31) s_red[warp] = incl;
     __syncthreads();
-    int wbase = 0, total = 0;
+    int wbase = 0, gtotal = 0;
 #pragma unroll
-    for (int w = 0; w < kBlk / 32; w++) {
-        int c = smem_i[w];
-        if (w < warp) wbase += c;
-        total += c;
-    }
-    if (threadIdx.x == 0) {
-        unsigned long long excl = 0;
-        volatile unsigned long long* st = status;
-        if (chunk == 0) {
-            st[0] = kFlagIncl | (unsigned long long)total;
-        } else {
-            st[chunk] = kFlagAgg | (unsigned long long)total;
-            __threadfence();
-            int j = chunk - 1;
-            for (;;) {
-                unsigned long long v = st[j];
-                if ((v >> 62) == 0) continue;  // predecessor not published yet
-                excl += v & kValMask;
-                if ((v >> 62) == 2) break;
-                j--;
-            }
-            st[chunk] = kFlagIncl | (excl + (unsigned long long)total);
-        }
-        __threadfence();
-        smem_i[kBlk / 32] = (int)excl;
-    }
+    for (int w = 0; w < 8; w++) { if (w < warp) wbase += s_red[w]; gtotal += s_red[w]; }
+    int run = gbase + wbase + incl - tsum;
+#pragma unroll
+    for (int k = 0; k < 4; k++) { s_base[4 * tid + k] = run; run += c[k]; }
     __syncthreads();
-    *base_out = smem_i[kBlk / 32];
-    int r = wbase + incl - n_out;
-    __syncthreads();  // smem_i reused by the next chunk
-    return r;
+    if (g == gridDim.x - 1 && tid == 0) {
+        const int total = gbase + gtotal;
+        *out_count = total < capacity ? total : capacity;
+        if (total > capacity) atomicAdd(counters + CNT_OVERFLOW, (unsigned long long)(total - capacity));
+    }
+    // 3. move the chunk windows: warp w owns chunks [w*128, w*128+128) of the group
+    for (int k = 0; k < kGroup / 8; k++) {
+        const int lc = warp * (kGroup / 8) + k, chunk = g * kGroup + lc;
+        if (chunk >= nch) break;
+        const int base = s_base[lc];
+        const int cnt = ((lc + 1 < kGroup && chunk + 1 < nch) ? s_base[lc + 1] : gbase + gtotal) - base;
+        for (int e = lane; e < cnt; e += 32) {
+            const int src = chunk * stride + e, dst = base + e;
+            if (dst < capacity) {
+                out.org[dst] = stage.org[src];
+                out.dir[dst] = stage.dir[src];
+                out.thr[dst] = stage.thr[src];
+                if (tree) out.node[dst] = stage.node[src];
+            }
+        }
+    }
 }
 
+// ---- shade prologue shared by k_lightprep and k_bounce: p, N, back-face / emissive classification ----------
+struct Vertex { f3 p, N; int mat, light; bool front; };
+
+__device__ __forceinline__ Vertex make_vertex(const DScene& s, int prim, float hb, float hg, f3 wo)
+{
+    const float4 v0 = __ldg(s.pverts + 3 * prim), v1 = __ldg(s.pverts + 3 * prim + 1), v2 = __ldg(s.pverts + 3 * prim + 2);
+    const float4 n0 = __ldg(s.pnorms + 3 * prim), n1 = __ldg(s.pnorms + 3 * prim + 1), n2 = __ldg(s.pnorms + 3 * prim + 2);
+    const float al = 1.0f - hb - hg;
+    Vertex v;
+    v.p = to_f3(v0) * al + to_f3(v1) * hb + to_f3(v2) * hg;                  // main.cpp:26-29,273
+    v.N = normalize_fast(to_f3(n0) * al + to_f3(n1) * hb + to_f3(n2) * hg);  // main.cpp:274
+    v.front = !(dot(v.N, wo) < 0.f);                                         // main.cpp:277-280
+    v.mat = __float_as_int(v0.w);
+    v.light = __float_as_int(v1.w);
+    return v;
+}
 
 // ---- primary rays ----------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kBlk) k_primary(DScene s, DCamera cam, int npix, float4* primary_hit)
@@ -210,6 +260,60 @@ __global__ void __launch_bounds__(kBlk) k_primary(DScene s, DCamera cam, int npi
     primary_hit[pixel] = make_float4(__int_as_float(h.prim), h.b, h.g, h.t);
 }
 
+// ---- first-vertex light selection, once per PIXEL ----------------------------------------------------------
+// Without jitter every sample of a pixel shoots the same camera ray (F4, main.cpp:563-577), so the first path
+// vertex -- and with it all L spherical-triangle weights and weights_sum -- is identical for the whole batch.
+// One warp computes the weights once per pixel (O(L)) and then draws one light per sample (O(L/32) each),
+// instead of O(L) per sample.  sel[slot] = (light index | weight bits), -1 when the sample draws no light
+// (unshadable vertex, or shade_with_mis's roulette, main.cpp:429-437, already ended it); wsum_pix[pixel].
+__global__ void __launch_bounds__(kBlk) k_lightprep(DScene s, DCamera cam, const float4* __restrict__ primary_hit, int npix,
+                                                    int batch_spp, int sample_base, uint64_t seed, float p_rr, int rr_first,
+                                                    int max_depth, int2* sel, float* wsum_pix)
+{
+    const int lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * kBlk + threadIdx.x) >> 5, nwarps = (gridDim.x * kBlk) >> 5;
+    const bool rr_forced = max_depth > 0 && 1 >= max_depth;
+    for (int pixel = warp; pixel < npix; pixel += nwarps) {
+        const float4 ph = __ldg(primary_hit + pixel);
+        const int prim = __float_as_int(ph.x);
+        bool shadable = false;
+        Vertex v;
+        v.p = v.N = mk<float>(0.f, 0.f, 1.f);
+        if (prim >= 0) {
+            v = make_vertex(s, prim, ph.y, ph.z, -camera_dir(cam, pixel, 0.f, 0.f));
+            shadable = v.front && v.light < 0;
+        }
+        float part = 0.f, incl = 0.f, total = 0.f;
+        if (shadable) {
+            part = warp_light_partial(s, v.p, v.N);
+            incl = warp_scan_incl(part);
+            total = __shfl_sync(kFull, incl, 31);
+        }
+        if (lane == 0) wsum_pix[pixel] = total;
+        for (int s0 = 0; s0 < batch_spp; s0 += 32) {
+            const int k = s0 + lane;
+            const uint32_t sample = (uint32_t)(sample_base + k);
+            bool need = false;
+            float u = 0.f;
+            if (k < batch_spp && shadable) {
+                need = true;
+                if (rr_first) need = !rr_forced && !(rng_draw4(seed, (uint32_t)pixel, sample, 1, 0).u[0] > p_rr);
+                if (need) u = rng_draw4(seed, (uint32_t)pixel, sample, 1, 1).u[0];
+            }
+            int mine = -1;
+            float wmine = 0.f;
+            unsigned todo = __ballot_sync(kFull, need);
+            while (todo) {
+                const int src = __ffs(todo) - 1;
+                todo &= todo - 1;
+                const LightPick pk = warp_light_pick(s, v.p, v.N, part, incl, total, __shfl_sync(kFull, u, src));
+                if (lane == src) { mine = pk.light; wmine = pk.w; }
+            }
+            if (k < batch_spp) sel[(size_t)k * npix + pixel] = make_int2(mine, __float_as_int(wmine));
+        }
+    }
+}
+
 // ---- one bounce --------------------------------------------------------------------------------------------
 struct Child { f3 o, d, thr; int exclude; uint64_t node; };
 
@@ -220,21 +324,19 @@ __global__ void __launch_bounds__(kBlk) k_bounce(const BounceArgs a)
     constexpr bool kNee = (STRAT == MCPT_NEE_SPHERICAL || STRAT == MCPT_NEE_UNIFORM);
     constexpr bool kSph = (STRAT == MCPT_NEE_SPHERICAL || STRAT == MCPT_MIS);
     __shared__ int stack[kStackSm * kBlk];
-    __shared__ int sm_i[kBlk / 32 + 2];
-    __shared__ int sm_chunk;
-    __shared__ unsigned long long sm_cnt[CNT_N];
     const DScene& s = a.s;
-    if (threadIdx.x < CNT_N) sm_cnt[threadIdx.x] = 0;
-    __syncthreads();
-    unsigned long long c_vert = 0, c_rays = 0, c_shadow = 0, c_lrays = 0, c_phits = 0, c_ovf = 0;
-    const int nchunks = (a.in_count + kBlk - 1) / kBlk;
+    const int lane = threadIdx.x & 31;
+    unsigned c_vert = 0, c_rays = 0, c_shadow = 0, c_lrays = 0, c_phits = 0;
+    const int nchunks = (a.in_count + 31) >> 5;
+    const bool presel = FIRST && kSph && !(a.flags & MCPT_JITTER);  // lights already drawn by k_lightprep
 
+    int next = 0;
+    if (lane == 0) next = atomicAdd(a.ticket, 1);
     for (;;) {
-        if (threadIdx.x == 0) sm_chunk = atomicAdd(a.ticket, 1);
-        __syncthreads();
-        const int chunk = sm_chunk;
+        const int chunk = __shfl_sync(kFull, next, 0);
         if (chunk >= nchunks) break;
-        const int i = chunk * kBlk + threadIdx.x;
+        if (lane == 0) next = atomicAdd(a.ticket, 1);  // prefetch the next ticket behind this chunk's work
+        const int i = chunk * 32 + lane;
         const bool valid = i < a.in_count;
 
         // -- A. ray + path state, closest hit (extend) ------------------------------------------------
@@ -282,21 +384,15 @@ __global__ void __launch_bounds__(kBlk) k_bounce(const BounceArgs a)
         PhongMat<float> mat;
         mat.kd = mat.ks = mk<float>(0.f, 0.f, 0.f); mat.ns = 1.f;
         if (alive) {
-            const float4 v0 = __ldg(s.pverts + 3 * h.prim), v1 = __ldg(s.pverts + 3 * h.prim + 1), v2 = __ldg(s.pverts + 3 * h.prim + 2);
-            const float4 n0 = __ldg(s.pnorms + 3 * h.prim), n1 = __ldg(s.pnorms + 3 * h.prim + 1), n2 = __ldg(s.pnorms + 3 * h.prim + 2);
-            const float al = 1.0f - h.b - h.g;
-            p = to_f3(v0) * al + to_f3(v1) * h.b + to_f3(v2) * h.g;
-            N = normalize_fast(to_f3(n0) * al + to_f3(n1) * h.b + to_f3(n2) * h.g);
-            if (dot(N, wo) < 0.f) alive = false;  // hit from behind -> 0
-            else {
-                const int li = __float_as_int(v1.w);
-                if (li >= 0) {  // emissive: self-emission only
-                    // shade(): an indirect ray that lands on a light contributes 0 (main.cpp:338); the emission
-                    // return of main.cpp:284-288 is only reachable from the camera ray.
-                    if (!kNee || FIRST) contrib = thr * to_f3(__ldg(s.lights + 5 * li + 4));
-                    alive = false;
-                } else mat = load_mat(s, __float_as_int(v0.w));
-            }
+            const Vertex v = make_vertex(s, h.prim, h.b, h.g, wo);
+            p = v.p; N = v.N;
+            if (!v.front) alive = false;  // hit from behind -> 0
+            else if (v.light >= 0) {      // emissive: self-emission only
+                // shade(): an indirect ray that lands on a light contributes 0 (main.cpp:338); the emission
+                // return of main.cpp:284-288 is only reachable from the camera ray.
+                if (!kNee || FIRST) contrib = thr * to_f3(__ldg(s.lights + 5 * v.light + 4));
+                alive = false;
+            } else mat = load_mat(s, v.mat);
         }
         const int depth = a.bounce + 1;
         const bool rr_forced = a.max_depth > 0 && depth >= a.max_depth;
@@ -315,8 +411,14 @@ __global__ void __launch_bounds__(kBlk) k_bounce(const BounceArgs a)
         int n_out = 0;
         float wsum = 0.f;
         if (kSph) {
-            int chosen; float wch;
-            warp_light_select(s, alive, p, N, r1.u[0], &chosen, &wsum, &wch);
+            int chosen = -1; float wch = 0.f;
+            if (presel) {
+                if (alive) {
+                    const int2 v = a.sel[slot];
+                    chosen = v.x; wch = __int_as_float(v.y);
+                    wsum = a.wsum_pix[pixel];
+                }
+            } else warp_light_select(s, alive, p, N, r1.u[0], &chosen, &wsum, &wch);
             if (alive && chosen >= 0) {
                 // Arvo sample of the chosen triangle (Mylight.cpp:285-317): FP32 for comfortably large solid angles,
                 // FP64 below (alpha+beta+gamma-pi and the edge-angle algebra lose all FP32 digits on tiny lights)
@@ -428,31 +530,35 @@ __global__ void __launch_bounds__(kBlk) k_bounce(const BounceArgs a)
                 a.Lacc[slot] = L;
             }
         }
-        int base;
-        int off = block_compact_offset(n_out, chunk, a.status, &base, sm_i);
-        for (int k = 0; k < n_out; k++) {
-            const int dst = base + off + k;
-            if (dst < a.capacity) {
+        {
+            const unsigned m1 = __ballot_sync(kFull, n_out >= 1), m2 = __ballot_sync(kFull, n_out >= 2);
+            const unsigned below = (1u << lane) - 1u;
+            const int off = chunk * (kTree ? 64 : 32) + __popc(m1 & below) + __popc(m2 & below);
+            for (int k = 0; k < n_out; k++) {
+                const int dst = off + k;
                 const Child& c = ch[k];
                 a.out.org[dst] = make_float4(c.o.x, c.o.y, c.o.z, __int_as_float(c.exclude));
                 a.out.dir[dst] = make_float4(c.d.x, c.d.y, c.d.z, __int_as_float(slot));
                 a.out.thr[dst] = make_float4(c.thr.x, c.thr.y, c.thr.z, 0.f);
                 if (kTree) a.out.node[dst] = make_uint2((uint32_t)c.node, (uint32_t)(c.node >> 32));
-            } else c_ovf++;
-        }
-        if (chunk == nchunks - 1 && threadIdx.x == 0) {
-            // the last chunk's inclusive prefix is the size of the out queue
-            volatile unsigned long long* st = a.status;
-            unsigned long long v = st[chunk];
-            int total = (int)(v & kValMask);
-            *a.out_count = total < a.capacity ? total : a.capacity;
+            }
+            if (lane == 0) {
+                const int total = __popc(m1) + __popc(m2);
+                a.counts[chunk] = total;
+                if (total) atomicAdd(a.groupsum + chunk / kGroup, total);
+            }
         }
     }
-    // block-level counter reduction: one atomic per counter per block
-    atomicAdd(&sm_cnt[CNT_VERTICES], c_vert); atomicAdd(&sm_cnt[CNT_RAYS], c_rays); atomicAdd(&sm_cnt[CNT_SHADOW], c_shadow);
-    atomicAdd(&sm_cnt[CNT_LIGHTRAYS], c_lrays); atomicAdd(&sm_cnt[CNT_PRIMARY_HITS], c_phits); atomicAdd(&sm_cnt[CNT_OVERFLOW], c_ovf);
-    __syncthreads();
-    if (threadIdx.x < CNT_N && sm_cnt[threadIdx.x]) atomicAdd(a.counters + threadIdx.x, sm_cnt[threadIdx.x]);
+    // warp-level counter reduction: one atomic per counter per warp
+    c_vert = __reduce_add_sync(kFull, c_vert); c_rays = __reduce_add_sync(kFull, c_rays); c_shadow = __reduce_add_sync(kFull, c_shadow);
+    c_lrays = __reduce_add_sync(kFull, c_lrays); c_phits = __reduce_add_sync(kFull, c_phits);
+    if (lane == 0) {
+        if (c_vert) atomicAdd(a.counters + CNT_VERTICES, (unsigned long long)c_vert);
+        if (c_rays) atomicAdd(a.counters + CNT_RAYS, (unsigned long long)c_rays);
+        if (c_shadow) atomicAdd(a.counters + CNT_SHADOW, (unsigned long long)c_shadow);
+        if (c_lrays) atomicAdd(a.counters + CNT_LIGHTRAYS, (unsigned long long)c_lrays);
+        if (c_phits) atomicAdd(a.counters + CNT_PRIMARY_HITS, (unsigned long long)c_phits);
+    }
 }
 
 
@@ -572,18 +678,24 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     const size_t slots = npix * (size_t)batch;
     if (slots > (1u << 30)) throw Error(MCPT_ERR_INVALID, "batch_spp * pixels too large");
     const size_t cap = tree ? slots * 3 : slots;
-    const size_t chunks = (cap + kBlk - 1) / kBlk + 1;
+    const size_t chunks = (cap + 31) / 32 + 1;
+    const bool sph = prm->strategy == MCPT_NEE_SPHERICAL || prm->strategy == MCPT_MIS;
 
     // workspace carve-up
     size_t off = 0;
     auto place = [&](size_t bytes) { size_t at = off; off = (off + bytes + 255) & ~(size_t)255; return at; };
+    // Q[0]: dense ray queue (cap entries).  Q[1]: staging queue, one window of `stride` entries per 32-ray chunk.
+    const size_t stride = tree ? 64 : 32;
+    const size_t qn[2] = {cap, chunks * stride};
     size_t o_q[2][4];
     for (int q = 0; q < 2; q++) {
-        o_q[q][0] = place(cap * 16); o_q[q][1] = place(cap * 16); o_q[q][2] = place(cap * 16);
-        o_q[q][3] = place(tree ? cap * 8 : 16);
+        o_q[q][0] = place(qn[q] * 16); o_q[q][1] = place(qn[q] * 16); o_q[q][2] = place(qn[q] * 16);
+        o_q[q][3] = place(tree ? qn[q] * 8 : 16);
     }
     const size_t o_lacc = place(slots * 16), o_contrib = place(tree ? cap * 16 : 16), o_ph = place(npix * 16), o_img = place(npix * 16);
-    const size_t o_status = place(chunks * 8), o_small = place(256);
+    const size_t groups = (chunks + kGroup - 1) / kGroup;
+    const size_t o_counts = place(chunks * 4), o_small = place(256 + groups * 4);
+    const size_t o_sel = place(sph ? slots * 8 : 16), o_wsum = place(sph ? npix * 4 : 16);
     Workspace& ws = scene->ws;
     if (ws.bytes < off) {
         if (ws.base) MCPT_CUDA(cudaFree(ws.base));
@@ -602,11 +714,14 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     float4* contrib = (float4*)(base + o_contrib);
     float4* primary = (float4*)(base + o_ph);
     float4* image = (float4*)(base + o_img);
-    unsigned long long* status = (unsigned long long*)(base + o_status);
-    // small block: [0] ticket (int), [1] out_count (int), [8..] counters (u64 x CNT_N)
+    int* counts = (int*)(base + o_counts);
+    int2* sel = (int2*)(base + o_sel);
+    float* wsum_pix = (float*)(base + o_wsum);
+    // small block: [0] ticket (int), [1] out_count (int), [64..] counters (u64 x CNT_N), [256..] group sums (int x groups)
     int* d_ticket = (int*)(base + o_small);
     int* d_count = d_ticket + 1;
     unsigned long long* d_counters = (unsigned long long*)(base + o_small + 64);
+    int* d_groupsum = (int*)(base + o_small + 256);
     volatile int* h_count = (volatile int*)ws.pinned;
     unsigned long long* h_counters = (unsigned long long*)((char*)ws.pinned + 64);
 
@@ -651,19 +766,27 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
         const int b = std::min(batch, prm->spp - done);
         BounceArgs a;
         a.s = scene->d; a.cam = dc;
-        a.Lacc = Lacc; a.contrib = contrib; a.primary_hit = primary; a.status = status; a.ticket = d_ticket; a.out_count = d_count;
+        a.Lacc = Lacc; a.contrib = contrib; a.primary_hit = primary; a.sel = sel; a.wsum_pix = wsum_pix; a.counts = counts; a.groupsum = d_groupsum; a.ticket = d_ticket;
         a.counters = d_counters; a.seed = prm->seed; a.capacity = (int)cap; a.npix = (int)npix; a.batch_spp = b;
         a.sample_base = prm->spp_offset + done; a.max_depth = prm->max_depth; a.flags = prm->flags; a.p_rr = p_rr;
         int count = (int)(npix * (size_t)b);
-        int cur = 0;
+        a.in = Q[0]; a.out = Q[1];
+        if (sph && !jitter) {
+            // first-vertex light draws, weights computed once per pixel (F4: all samples share the camera ray)
+            const int warps_needed = (int)std::min<size_t>(npix, (size_t)sms * 16);
+            k_lightprep<<<(warps_needed * 32 + kBlk - 1) / kBlk, kBlk, 0, st>>>(scene->d, dc, primary, (int)npix, b, a.sample_base, prm->seed, p_rr,
+                                                                           tree ? 1 : 0, prm->max_depth, sel, wsum_pix);
+            MCPT_CUDA(cudaGetLastError());
+            S.kernel_launches++;
+        }
         for (int bounce = 0; count > 0; bounce++) {
             if (prm->max_depth <= 0 && bounce >= 256) break;  // unlimited depth: RR has long emptied the queue
-            a.in = Q[cur]; a.out = Q[cur ^ 1]; a.in_count = count; a.bounce = bounce;
-            const int nch = (count + kBlk - 1) / kBlk;
-            MCPT_CUDA(cudaMemsetAsync(status, 0, (size_t)nch * 8, st));
+            a.in_count = count; a.bounce = bounce;
+            const int nch = (count + 31) / 32, ngroups = (nch + kGroup - 1) / kGroup;
             MCPT_CUDA(cudaMemsetAsync(d_ticket, 0, 8, st));
+            MCPT_CUDA(cudaMemsetAsync(d_groupsum, 0, (size_t)ngroups * 4, st));
             MCPT_CUDA(cudaEventRecord(scene->ev[2], st));
-            const int grid = std::min(nch, max_grid);
+            const int grid = std::min((nch + kBlk / 32 - 1) / (kBlk / 32), max_grid);
             switch (prm->strategy) {
                 case MCPT_NEE_SPHERICAL: launch_bounce<MCPT_NEE_SPHERICAL>(bounce == 0, a, grid, st); break;
                 case MCPT_BRDF_ONLY: launch_bounce<MCPT_BRDF_ONLY>(bounce == 0, a, grid, st); break;
@@ -673,20 +796,24 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
             MCPT_CUDA(cudaGetLastError());
             MCPT_CUDA(cudaEventRecord(scene->ev[3], st));
             S.kernel_launches++;
+            const bool last = prm->max_depth > 0 && bounce + 1 >= prm->max_depth + 1;  // vertices deeper than max_depth never spawn
+            if (!last) {
+                k_gather<<<ngroups, 256, 0, st>>>(Q[1], Q[0], counts, d_groupsum, nch, (int)stride, (int)cap, tree ? 1 : 0, d_count, d_counters);
+                S.kernel_launches++;
+            }
             if (tree && bounce > 0) {
                 k_runsum<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(contrib, count, Lacc);
                 S.kernel_launches++;
             }
-            MCPT_CUDA(cudaMemcpyAsync((void*)h_count, d_count, 4, cudaMemcpyDeviceToHost, st));
+            if (!last) MCPT_CUDA(cudaMemcpyAsync((void*)h_count, d_count, 4, cudaMemcpyDeviceToHost, st));
             MCPT_CUDA(cudaStreamSynchronize(st));
             float ms = 0.f;
             cudaEventElapsedTime(&ms, scene->ev[2], scene->ev[3]);
             ms_bounce += ms;
             S.queue_peak = std::max<uint32_t>(S.queue_peak, (uint32_t)count);
             S.bounces++;
+            if (last) break;
             count = *h_count;
-            cur ^= 1;
-            if (prm->max_depth > 0 && bounce + 1 >= prm->max_depth + 1) break;  // vertices deeper than max_depth never spawn
         }
         k_accumulate<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(Lacc, (int)npix, b, image, pass == 0);
         S.kernel_launches++;

@@ -8,6 +8,8 @@
 //   mats   [M][2] float4 : (kd.rgb, ns), (ks.rgb, 0)              (main.cpp:292,313)
 //   lights [L][5] float4 : v0|prim bits, v1|class bits, v2|area, ng|Lsum (R+G+B), Le|0 -- in the
 //                          reference's light order (Mylight.cpp:169-173); FP32 copy for the renderer
+//   lsoa   [4][Lpad] float4 : the same lights as four planes (v0, v1, v2 | cull threshold, 2 area ng | Lsum) for
+//                          the O(L) spherical-triangle weight loop (lights.cuh); Lpad = L rounded up to 64
 //   lng64 [L][3], larea64 [L], crad64 [C][3] : FP64 originals for the parity entry points
 //   class_begin [C+1], class_cdf [C], tri_cdf [L] : the two discrete distributions of
 //                          select_a_point_from_lights (Mylight.cpp:112-135) as normalised cumulative tables
@@ -26,13 +28,14 @@ struct DScene {
     const float4* pnorms;
     const float4* mats;
     const float4* lights;
+    const float4* lsoa;
     const double* lng64;
     const double* larea64;
     const double* crad64;
     const int32_t* class_begin;
     const float* class_cdf;
     const float* tri_cdf;
-    int32_t P, L, C, M;
+    int32_t P, L, C, M, Lpad;
     float tmin;  // FP32 leaf test: reject t < tmin (scene-scale aware stand-in for the reference's 1e-8)
 };
 

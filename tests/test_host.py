@@ -1,0 +1,174 @@
+"""CPU-only tests of the host side: the C ABI surface, the host loaders, the SAH BVH builder, the scene
+generators, the spp sharding and its reduce (2 ranks over gloo), and the no-GPU error path.  No compute
+entry point is called here (there is no GPU and no CPU fallback)."""
+import ctypes as C
+import os
+import re
+import socket
+
+import numpy as np
+import pytest
+
+import util
+from monte_carlo_path_tracing_b200 import api, dist as mdist, scenes
+
+ROOT = util.ROOT
+
+
+def test_abi_exports_every_declared_symbol():
+    """libmcpt.so loads and exports every function include/mcpt.h declares; api.SYMBOLS lists them all."""
+    hdr = open(os.path.join(ROOT, "include", "mcpt.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = sorted(set(re.findall(r"\b(mcpt_[a-z0-9_]+)\s*\(", hdr)))
+    assert len(declared) >= 25
+    lib = api.load()
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert sorted(api.SYMBOLS) == declared
+    assert lib.mcpt_version() == 100
+
+
+def test_abi_struct_layouts_match_header():
+    """ctypes mirrors of the PODs have the sizes the C compiler gives them (LP64)."""
+    assert C.sizeof(api.CameraC) == 10 * 8
+    assert C.sizeof(api.RenderParams) == 4 * 8 + 8 + 4 + 4
+    assert C.sizeof(api.Stats) == 6 * 8 + 4 * 4 + 3 * 4 + 4  # tail padding to 8
+    assert C.sizeof(api.SceneDesc) == 5 * 4 + 4 + 10 * 8
+
+
+@pytest.mark.skipif(os.path.exists("/dev/nvidiactl"), reason="a GPU is present")
+def test_no_gpu_fails_loudly(arrays_of):
+    """No CUDA device -> MCPT_ERR_NO_DEVICE (or a CUDA error), never a silent CPU path."""
+    a, _ = arrays_of("cornell-box")
+    with pytest.raises(api.McptError) as e:
+        api.Scene(a, 0)
+    assert e.value.code in (-3, -2)
+
+
+def test_loader_errors_do_not_exit(tmp_path):
+    """The reference exit(1)s on a missing file (Myobj.cpp:15-20, Mylight.cpp:16-20); the ABI returns a code."""
+    with pytest.raises(api.McptError) as e:
+        api.load_scene_files(str(tmp_path / "nope.obj"), str(tmp_path / "nope.xml"))
+    assert e.value.code == -4
+    (tmp_path / "a.obj").write_text("v 0 0 0\nv 1 0 0\nv 0 1 0\nvn 0 0 1\nf 1//1 2//1 3//1\n")
+    with pytest.raises(api.McptError):
+        api.load_scene_files(str(tmp_path / "a.obj"), str(tmp_path / "missing.xml"))
+
+
+def test_loader_camera_and_light_order(scene_files):
+    """<camera> node parsed (README.md:339-343); lights ordered by class (mtlname ascending) then prim."""
+    sc, stem = scene_files("veach-mis")
+    a, cam = api.load_scene_files(stem + ".obj", stem + ".xml")
+    assert cam is not None and (cam.width, cam.height) == (sc.camera.width, sc.camera.height)
+    assert np.allclose(cam.eye, sc.camera.eye) and abs(cam.fovy_deg - sc.camera.fovy_deg) < 1e-12
+    assert np.all(np.diff(a.light_class) >= 0)
+    for c in np.unique(a.light_class):
+        assert np.all(np.diff(a.light_prim[a.light_class == c]) > 0)
+    assert a.shape_offset[0] == 0 and a.shape_offset[-1] == len(a.material_id)
+    assert a.material_id.min() >= 0 and a.material_id.max() < len(a.mat_ns)
+
+
+@pytest.mark.parametrize("name", ["cornell-box", "veach-mis"])
+def test_host_bvh_is_valid(name, arrays_of):
+    a, _ = arrays_of(name)
+    for lights_only in (False, True):
+        r = api.host_bvh_check(a, lights_only)
+        n = len(a.light_prim) if lights_only else len(a.material_id)
+        assert r["errors"] == 0 and r["max_depth"] < 64
+        assert r["leaves"] >= (n + 7) // 8 and r["nodes"] >= r["leaves"] - 1
+        assert r["sah"] > 0
+
+
+def test_host_bvh_triangle_soup():
+    """C4-style soup at 50 k triangles: structurally valid, depth far below the traversal stack."""
+    a = scenes.triangle_soup(50_000, 16, seed=3)
+    r = api.host_bvh_check(a, False)
+    assert r["errors"] == 0 and r["max_depth"] <= 48
+    r = api.host_bvh_check(a, True)
+    assert r["errors"] == 0
+
+
+def test_host_bvh_degenerate_inputs():
+    """All-coincident centroids and zero-area triangles must not break the builder."""
+    a = scenes.triangle_soup(64, 2, seed=4)
+    a.positions[:40] = a.positions[0]        # 40 identical triangles
+    a.positions[40:50, 1] = a.positions[40:50, 0]  # zero-area
+    r = api.host_bvh_check(a, False)
+    assert r["errors"] == 0
+
+
+def test_scene_generators():
+    c = scenes.cornell_box(width=32, height=32)
+    assert "usemtl" in c.obj and "vn " in c.obj and "<light" in c.xml and "<camera" in c.xml
+    v = scenes.veach_mis(width=32, height=18)
+    assert v.obj.count("\nf ") > 3000 * 0.8  # ~3 k facets like the reference's scene (README.md:212)
+    s = scenes.triangle_soup(1000, 8)
+    assert s.positions.shape == (1008, 3, 3) and len(s.light_prim) == 8
+
+
+def test_shard_spp_partitions():
+    for total in (1, 7, 16, 1024, 4096):
+        for world in (1, 2, 3, 4, 8):
+            parts = [mdist.shard_spp(total, world, r) for r in range(world)]
+            assert sum(c for _, c in parts) == total
+            off = 0
+            for o, c in parts:
+                assert o == off
+                off += c
+            counts = [c for _, c in parts]
+            assert max(counts) - min(counts) <= 1
+
+
+# ---- 2 ranks over gloo: the N>1 path of dist.render_sharded with the oracle standing in for the device ----------
+class _OracleScene:
+    """Test double with Scene.render_device's signature: fills the rank's film from the CPU oracle."""
+
+    def __init__(self, orc, film):
+        self.orc, self.film = orc, film
+
+    def render_device(self, cam, strategy, spp, d_out_ptr, stream=0, spp_offset=0, spp_total=0, **kw):
+        import torch
+        img, cnt = self.orc.render(cam, strategy, spp, spp_offset=spp_offset, spp_total=spp_total, **kw)
+        self.film.copy_(torch.from_numpy(img.reshape(-1).astype(np.float32)))
+        return dict(vertices=cnt["vertices"])
+
+
+def _gloo_worker(rank, world, port, total_spp, out_path):
+    import torch
+    import torch.distributed as td
+    import oracle
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    td.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import tempfile
+        sc = util.scene_text("cornell-box")
+        with tempfile.TemporaryDirectory() as d:
+            stem = sc.write(d)
+            a, cam = api.load_scene_files(stem + ".obj", stem + ".xml")
+        orc = oracle.OracleLib(a)
+        orc.build_grid(cam.eye, 100000)
+        film = torch.zeros(cam.width * cam.height * 3, dtype=torch.float32)
+        st = mdist.render_sharded(_OracleScene(orc, film), cam, oracle.NEE_UNIFORM, total_spp, rank, world, film,
+                                  max_depth=3, seed=5, flags=oracle.FIX_STALE_MIS)
+        assert st["vertices"] > 0
+        if rank == 0:
+            np.save(out_path, film.numpy())
+    finally:
+        td.destroy_process_group()
+
+
+def test_spp_sharding_two_ranks_gloo(tmp_path, oracle_of, arrays_of):
+    """World size 2: each rank renders its half of the global sample range (disjoint counter-RNG streams keyed
+    by the GLOBAL sample index), one reduce sums the films on rank 0 -> equals the 1-rank render."""
+    import torch.multiprocessing as mp
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    out = str(tmp_path / "film.npy")
+    total = 6
+    mp.spawn(_gloo_worker, args=(2, port, total, out), nprocs=2, join=True)
+    got = np.load(out)
+    import oracle
+    _, cam = arrays_of("cornell-box")
+    ref, _ = oracle_of("cornell-box").render(cam, oracle.NEE_UNIFORM, total, max_depth=3, seed=5, flags=oracle.FIX_STALE_MIS)
+    assert np.allclose(got, ref.reshape(-1), rtol=1e-5, atol=1e-6)
+    assert got.max() > 0
