@@ -172,7 +172,7 @@ __global__ void k_light_uniform(DScene s, size_t n, const double* u4, int* prim,
 
 // staged spherical-triangle sampling of one vertex: prepare (all lights), pick, Arvo sample, re-intersect,
 // pdf of the query prim (Mylight.cpp:322-493).  One thread per vertex, two passes over the lights.
-template <class T>
+template <class T, bool DIRECT = false>
 __global__ void k_light_spherical(DScene s, size_t n, const double* x1, const double* N, const double* u3, const int* query,
                                   int* prim, double* point, double* Le, double* pdf, double* wsum_out, int* nsurv,
                                   double* query_pdf)
@@ -229,6 +229,16 @@ __global__ void k_light_spherical(DScene s, size_t n, const double* x1, const do
     T xi1 = (T)u[ui++];
     T xi2 = (T)u[ui++];
     V3<T> Pd = arvo_sample<T>(cst, xi1, xi2);
+    if (DIRECT) {
+        // what the renderer runs (render.cu): solid angle from the FP32 Van Oosterom-Strackee weight, direction from
+        // arvo_direct<double>
+        const f3 xf = as<float>(ld3(x1, i)), nf = as<float>(ld3(N, i));
+        const float4 l0 = s.lights[5 * chosen], l1 = s.lights[5 * chosen + 1], l2 = s.lights[5 * chosen + 2];
+        const float sA = light_weight_fast(s, chosen, xf, nf) / s.lights[5 * chosen + 3].w;
+        d3 w = to_d3(nf);
+        arvo_direct<double>(to_d3(l0), to_d3(l1), to_d3(l2), to_d3(xf), to_d3(nf), (double)sA, (double)xi1, (double)xi2, &w);
+        Pd = as<T>(w);
+    }
     // Mylight.cpp:311,317: point = x1 + P * t with t from intersect_with_triangle (0 on a miss)
     double be, ga, tt = 0;
     bool ok = tri_test_exact(wide(x), wide(Pd), wide(clt.v0), wide(clt.v1), wide(clt.v2), &be, &ga, &tt);
@@ -375,6 +385,8 @@ int mcpt_light_sample_spherical_batch(McptScene* s, size_t n, const double* x1, 
         if (n) {
             if (precision == 0)
                 k_light_spherical<double><<<grid_for(n), kBlock>>>(s->d, n, x.p, nn.p, u.p, query ? q.p : nullptr, pr.p, pt.p, le.p, pd.p, ws.p, ns.p, qp.p);
+            else if (precision == 3)  // reference pick (FP64), direction from the renderer's sampler arvo_direct
+                k_light_spherical<double, true><<<grid_for(n), kBlock>>>(s->d, n, x.p, nn.p, u.p, query ? q.p : nullptr, pr.p, pt.p, le.p, pd.p, ws.p, ns.p, qp.p);
             else if (precision == 2)  // renderer weights only (Van Oosterom-Strackee): wsum, nsurv
                 k_light_wsum_fast<<<grid_for(n), kBlock>>>(s->d, n, x.p, nn.p, ws.p, ns.p);
             else

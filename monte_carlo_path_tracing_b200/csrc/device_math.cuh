@@ -30,7 +30,7 @@ template <> struct M<double> {
     static constexpr double pi = 3.14159265358979323846;
     static constexpr double eps = 1e-8;  // vec.h:7, Myobj.h:69, Mylight.h:101, BRDF.cpp:8
     static __device__ __forceinline__ double sqrt_(double x) { return ::sqrt(x); }
-    static __device__ __forceinline__ double rsqrt_(double x) { return 1.0 / ::sqrt(x); }
+    static __device__ __forceinline__ double rsqrt_(double x) { return ::rsqrt(x); }
     static __device__ __forceinline__ double sin_(double x) { return ::sin(x); }
     static __device__ __forceinline__ double cos_(double x) { return ::cos(x); }
     static __device__ __forceinline__ void sincos_(double x, double* s, double* c) { ::sincos(x, s, c); }

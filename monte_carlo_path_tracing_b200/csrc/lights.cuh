@@ -136,22 +136,69 @@ __device__ __forceinline__ float light_weight_fast(const DScene& s, int l, f3 x1
     return light_weight_soa(__ldg(P), __ldg(P + s.Lpad), __ldg(P + 2 * s.Lpad), __ldg(P + 3 * s.Lpad), x1, n);
 }
 
-// Sum over this lane's lights (l = lane, lane + 32, ...) of the weights seen from (x1, n).  All 32 lanes call.
-__device__ __forceinline__ float warp_light_partial(const DScene& s, f3 x1, f3 n)
+// Per-lane partial sums, over this lane's lights (l = lane, lane + 32, ...), of the weights seen from V vertices
+// at once: the four 16-byte loads of a light are shared by V evaluations (the loop is L1-bandwidth-bound at
+// V = 1).  With `cdf` (shared memory, [V][Lpad] floats) every running partial is also stored: cdf[v][l] = sum of
+// the lane's weights up to and including light l -- the per-lane columns k_lightprep inverts for its picks.
+// All 32 lanes call.
+template <int V>
+__device__ __forceinline__ void warp_light_partial(const DScene& s, const f3 (&x1)[V], const f3 (&n)[V], float (&part)[V],
+                                                   float* cdf = nullptr)
 {
     const int lane = threadIdx.x & 31;
     const float4* __restrict__ P0 = s.lsoa;
     const float4* __restrict__ P1 = P0 + s.Lpad;
     const float4* __restrict__ P2 = P1 + s.Lpad;
     const float4* __restrict__ P3 = P2 + s.Lpad;
-    float s0 = 0.f, s1 = 0.f;
-    for (int l = lane; l < s.Lpad; l += 64) {  // Lpad is a multiple of 64
+#pragma unroll
+    for (int v = 0; v < V; v++) part[v] = 0.f;
+#pragma unroll 2
+    for (int l = lane; l < s.Lpad; l += 32) {  // Lpad is a multiple of 64
         const float4 a0 = __ldg(P0 + l), a1 = __ldg(P1 + l), a2 = __ldg(P2 + l), a3 = __ldg(P3 + l);
-        const float4 b0 = __ldg(P0 + l + 32), b1 = __ldg(P1 + l + 32), b2 = __ldg(P2 + l + 32), b3 = __ldg(P3 + l + 32);
-        s0 += light_weight_soa(a0, a1, a2, a3, x1, n);
-        s1 += light_weight_soa(b0, b1, b2, b3, x1, n);
+#pragma unroll
+        for (int v = 0; v < V; v++) {
+            part[v] += light_weight_soa(a0, a1, a2, a3, x1[v], n[v]);
+            if (cdf) cdf[v * s.Lpad + l] = part[v];
+        }
     }
-    return s0 + s1;
+}
+
+// ---- Arvo SampleTriangle without inverse trigonometry ------------------------------------------------------
+// Same map (xi1, xi2) -> direction as Mylight.cpp:200-211,289-297, but fed with cos/sin of the vertex angle alpha
+// straight from the edge-plane normals and with the solid angle sA the weight loop already has (Van Oosterom-
+// Strackee), instead of nine acos() and cos/sin of their results.  s = sin(xi1 sA - alpha) and t = cos(...) come
+// from the angle-difference identities.  Instantiated in FP64 for small lights (u = t - cos(alpha) and
+// v = s + sin(alpha) cos(c) cancel to ~sA^2) and in FP32 for comfortably large ones.
+template <class T>
+__device__ __forceinline__ bool arvo_direct(V3<T> v0, V3<T> v1, V3<T> v2, V3<T> x1, V3<T> n, T sA, T xi1, T xi2, V3<T>* dir)
+{
+    V3<T> A = v0 - x1, B = v1 - x1, C = v2 - x1;
+    A = A * M<T>::rsqrt_(dot(A, A)); B = B * M<T>::rsqrt_(dot(B, B)); C = C * M<T>::rsqrt_(dot(C, C));
+    // winding (:206-211): the sign of ((C-A)^ x (B-A)^).n is that of ((C-A) x (B-A)).n
+    if (dot(cross(C - A, B - A), n) < T(0)) { V3<T> t = B; B = C; C = t; }
+    const V3<T> nab = cross(A, B), nac = cross(A, C);
+    const T lab = dot(nab, nab), lac = dot(nac, nac);
+    if (!(lab > T(0)) || !(lac > T(0)) || !(sA > T(0))) return false;
+    const T ca = clamp1(dot(nab, nac) * M<T>::rsqrt_(lab * lac));     // cos(alpha) = (AxB)^.(AxC)^   (:225)
+    const T sa = M<T>::sqrt_(M<T>::max_(T(0), T(1) - ca * ca));
+    const T cc = clamp1(dot(A, B));                                   // cos(c)                       (:217)
+    T sd, cd;
+    M<T>::sincos_(xi1 * sA, &sd, &cd);
+    const T s = sd * ca - cd * sa, t = cd * ca + sd * sa;             // sin / cos(xi1 sA - alpha)    (:290)
+    const T u = t - ca, v = s + sa * cc;                              // (:291)
+    const T q = clamp1(((v * t - u * s) * ca - v) / ((v * s + u * t) * sa));  // (:292)
+    V3<T> Ct = C - A * dot(C, A);
+    Ct = Ct * M<T>::rsqrt_(dot(Ct, Ct));
+    V3<T> C1 = A * q + Ct * M<T>::sqrt_(M<T>::max_(T(0), T(1) - q * q));      // (:293)
+    C1 = C1 * M<T>::rsqrt_(dot(C1, C1));
+    const T z = T(1) - xi2 * (T(1) - dot(C1, B));                     // (:295)
+    V3<T> Bt = C1 - B * dot(C1, B);
+    const T lbt = dot(Bt, Bt);
+    V3<T> P = B * z;
+    if (lbt > T(0)) P = P + Bt * (M<T>::rsqrt_(lbt) * M<T>::sqrt_(M<T>::max_(T(0), T(1) - z * z)));  // (:296)
+    P = P * M<T>::rsqrt_(dot(P, P));
+    *dir = P;
+    return !M<T>::bad_(P.x + P.y + P.z);
 }
 
 // ---- uniform-area sampling, Mylight.cpp:102-160 --------------------------------------------------------

@@ -139,7 +139,8 @@ __device__ __forceinline__ float warp_scan_incl(float v)
     return v;
 }
 
-// Must be called by all 32 lanes; lanes with need == false only help.
+// Must be called by all 32 lanes; lanes with need == false only help.  Two vertices are served per sweep of the
+// light table (warp_light_partial<2>): the loads are shared and the two evaluations interleave.
 __device__ __forceinline__ void warp_light_select(const DScene& s, bool need, f3 x, f3 n, float u, int* chosen, float* wsum_out,
                                                   float* w_chosen)
 {
@@ -147,16 +148,29 @@ __device__ __forceinline__ void warp_light_select(const DScene& s, bool need, f3
     unsigned todo = __ballot_sync(kFull, need);
     *chosen = -1; *wsum_out = 0.f; *w_chosen = 0.f;
     while (todo) {
-        const int src = __ffs(todo) - 1;
+        int src[2];
+        src[0] = __ffs(todo) - 1;
         todo &= todo - 1;
-        f3 X = mk<float>(__shfl_sync(kFull, x.x, src), __shfl_sync(kFull, x.y, src), __shfl_sync(kFull, x.z, src));
-        f3 Nn = mk<float>(__shfl_sync(kFull, n.x, src), __shfl_sync(kFull, n.y, src), __shfl_sync(kFull, n.z, src));
-        const float uu = __shfl_sync(kFull, u, src);
-        const float part = warp_light_partial(s, X, Nn);
-        const float incl = warp_scan_incl(part);
-        const float total = __shfl_sync(kFull, incl, 31);
-        const LightPick pk = warp_light_pick(s, X, Nn, part, incl, total, uu);
-        if (lane == src) { *chosen = pk.light; *wsum_out = total; *w_chosen = pk.w; }
+        const bool two = todo != 0;
+        src[1] = two ? __ffs(todo) - 1 : src[0];
+        todo &= todo - 1;  // no-op when todo is already 0
+        f3 X[2], Nn[2];
+        float part[2];
+#pragma unroll
+        for (int v = 0; v < 2; v++) {
+            X[v] = mk<float>(__shfl_sync(kFull, x.x, src[v]), __shfl_sync(kFull, x.y, src[v]), __shfl_sync(kFull, x.z, src[v]));
+            Nn[v] = mk<float>(__shfl_sync(kFull, n.x, src[v]), __shfl_sync(kFull, n.y, src[v]), __shfl_sync(kFull, n.z, src[v]));
+        }
+        warp_light_partial<2>(s, X, Nn, part);
+#pragma unroll
+        for (int v = 0; v < 2; v++) {
+            if (v == 1 && !two) break;
+            const float uu = __shfl_sync(kFull, u, src[v]);
+            const float incl = warp_scan_incl(part[v]);
+            const float total = __shfl_sync(kFull, incl, 31);
+            const LightPick pk = warp_light_pick(s, X[v], Nn[v], part[v], incl, total, uu);
+            if (lane == src[v]) { *chosen = pk.light; *wsum_out = total; *w_chosen = pk.w; }
+        }
     }
 }
 
@@ -213,20 +227,21 @@ __global__ void __launch_bounds__(256) k_gather(const Queue stage, const Queue o
         *out_count = total < capacity ? total : capacity;
         if (total > capacity) atomicAdd(counters + CNT_OVERFLOW, (unsigned long long)(total - capacity));
     }
-    // 3. move the chunk windows: warp w owns chunks [w*128, w*128+128) of the group
-    for (int k = 0; k < kGroup / 8; k++) {
-        const int lc = warp * (kGroup / 8) + k, chunk = g * kGroup + lc;
-        if (chunk >= nch) break;
-        const int base = s_base[lc];
-        const int cnt = ((lc + 1 < kGroup && chunk + 1 < nch) ? s_base[lc + 1] : gbase + gtotal) - base;
-        for (int e = lane; e < cnt; e += 32) {
-            const int src = chunk * stride + e, dst = base + e;
-            if (dst < capacity) {
-                out.org[dst] = stage.org[src];
-                out.dir[dst] = stage.dir[src];
-                out.thr[dst] = stage.thr[src];
-                if (tree) out.node[dst] = stage.node[src];
-            }
+    // 3. move the staged entries: one thread per dense destination, its chunk found by bisection of the bases
+    //    (largest chunk whose base <= destination; empty chunks share a base with their successor and lose)
+    for (int e = tid; e < gtotal; e += 256) {
+        const int dst = gbase + e;
+        int lo = 0, hi = kGroup - 1;
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (s_base[mid] <= dst) lo = mid; else hi = mid - 1;
+        }
+        const int src = (g * kGroup + lo) * stride + (dst - s_base[lo]);
+        if (dst < capacity) {
+            out.org[dst] = stage.org[src];
+            out.dir[dst] = stage.dir[src];
+            out.thr[dst] = stage.thr[src];
+            if (tree) out.node[dst] = stage.node[src];
         }
     }
 }
@@ -263,54 +278,102 @@ __global__ void __launch_bounds__(kBlk) k_primary(DScene s, DCamera cam, int npi
 // ---- first-vertex light selection, once per PIXEL ----------------------------------------------------------
 // Without jitter every sample of a pixel shoots the same camera ray (F4, main.cpp:563-577), so the first path
 // vertex -- and with it all L spherical-triangle weights and weights_sum -- is identical for the whole batch.
-// One warp computes the weights once per pixel (O(L)) and then draws one light per sample (O(L/32) each),
-// instead of O(L) per sample.  sel[slot] = (light index | weight bits), -1 when the sample draws no light
-// (unshadable vertex, or shade_with_mis's roulette, main.cpp:429-437, already ended it); wsum_pix[pixel].
+// One warp sweeps the light table once for a PAIR of neighbouring pixels (O(L), loads shared), leaving the
+// per-lane running sums in shared memory; then lane k draws the light of sample k by inverting that two-level
+// CDF (lane totals, then the lane's column) with two short binary searches -- O(log L) per sample instead of
+// O(L).  sel[slot] = (light index | weight bits), -1 when the sample draws no light (unshadable vertex, or
+// shade_with_mis's roulette, main.cpp:429-437, already ended it); wsum_pix[pixel] = weights_sum.
 __global__ void __launch_bounds__(kBlk) k_lightprep(DScene s, DCamera cam, const float4* __restrict__ primary_hit, int npix,
                                                     int batch_spp, int sample_base, uint64_t seed, float p_rr, int rr_first,
-                                                    int max_depth, int2* sel, float* wsum_pix)
+                                                    int max_depth, int use_cdf, int2* sel, float* wsum_pix)
 {
+    extern __shared__ float sm_prep[];
     const int lane = threadIdx.x & 31;
+    float* cdf = sm_prep + (threadIdx.x >> 5) * (2 * s.Lpad + 64);  // [2][Lpad] running sums of the lane columns
+    float* sinc = cdf + 2 * s.Lpad;                                  // [2][32] inclusive scan of the lane totals
     const int warp = (blockIdx.x * kBlk + threadIdx.x) >> 5, nwarps = (gridDim.x * kBlk) >> 5;
     const bool rr_forced = max_depth > 0 && 1 >= max_depth;
-    for (int pixel = warp; pixel < npix; pixel += nwarps) {
-        const float4 ph = __ldg(primary_hit + pixel);
-        const int prim = __float_as_int(ph.x);
-        bool shadable = false;
-        Vertex v;
-        v.p = v.N = mk<float>(0.f, 0.f, 1.f);
-        if (prim >= 0) {
-            v = make_vertex(s, prim, ph.y, ph.z, -camera_dir(cam, pixel, 0.f, 0.f));
-            shadable = v.front && v.light < 0;
-        }
-        float part = 0.f, incl = 0.f, total = 0.f;
-        if (shadable) {
-            part = warp_light_partial(s, v.p, v.N);
-            incl = warp_scan_incl(part);
-            total = __shfl_sync(kFull, incl, 31);
-        }
-        if (lane == 0) wsum_pix[pixel] = total;
-        for (int s0 = 0; s0 < batch_spp; s0 += 32) {
-            const int k = s0 + lane;
-            const uint32_t sample = (uint32_t)(sample_base + k);
-            bool need = false;
-            float u = 0.f;
-            if (k < batch_spp && shadable) {
-                need = true;
-                if (rr_first) need = !rr_forced && !(rng_draw4(seed, (uint32_t)pixel, sample, 1, 0).u[0] > p_rr);
-                if (need) u = rng_draw4(seed, (uint32_t)pixel, sample, 1, 1).u[0];
+    const int K = s.Lpad >> 5;
+    for (int pair = warp; 2 * pair < npix; pair += nwarps) {
+        f3 X[2], Nn[2];
+        bool shad[2];
+#pragma unroll
+        for (int v = 0; v < 2; v++) {
+            const int pixel = 2 * pair + v;
+            shad[v] = false;
+            X[v] = Nn[v] = mk<float>(0.f, 0.f, 1.f);
+            if (pixel < npix) {
+                const float4 ph = __ldg(primary_hit + pixel);
+                const int prim = __float_as_int(ph.x);
+                if (prim >= 0) {
+                    const Vertex vx = make_vertex(s, prim, ph.y, ph.z, -camera_dir(cam, pixel, 0.f, 0.f));
+                    shad[v] = vx.front && vx.light < 0;
+                    X[v] = vx.p; Nn[v] = vx.N;
+                }
             }
-            int mine = -1;
-            float wmine = 0.f;
-            unsigned todo = __ballot_sync(kFull, need);
-            while (todo) {
-                const int src = __ffs(todo) - 1;
-                todo &= todo - 1;
-                const LightPick pk = warp_light_pick(s, v.p, v.N, part, incl, total, __shfl_sync(kFull, u, src));
-                if (lane == src) { mine = pk.light; wmine = pk.w; }
-            }
-            if (k < batch_spp) sel[(size_t)k * npix + pixel] = make_int2(mine, __float_as_int(wmine));
         }
+        float part[2] = {0.f, 0.f}, incl[2] = {0.f, 0.f}, total[2] = {0.f, 0.f};
+        if (shad[0] || shad[1]) {
+            if (!shad[0]) { X[0] = X[1]; Nn[0] = Nn[1]; }
+            if (!shad[1]) { X[1] = X[0]; Nn[1] = Nn[0]; }
+            warp_light_partial<2>(s, X, Nn, part, use_cdf ? cdf : nullptr);
+#pragma unroll
+            for (int v = 0; v < 2; v++) {
+                incl[v] = warp_scan_incl(part[v]);
+                total[v] = __shfl_sync(kFull, incl[v], 31);
+                if (use_cdf) sinc[32 * v + lane] = incl[v];
+            }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int v = 0; v < 2; v++) {
+            const int pixel = 2 * pair + v;
+            if (pixel >= npix) break;
+            if (lane == 0) wsum_pix[pixel] = shad[v] ? total[v] : 0.f;
+            for (int s0 = 0; s0 < batch_spp; s0 += 32) {
+                const int k = s0 + lane;
+                const uint32_t sample = (uint32_t)(sample_base + k);
+                bool need = false;
+                float u = 0.f;
+                if (k < batch_spp && shad[v] && total[v] > 0.f) {
+                    need = true;
+                    if (rr_first) need = !rr_forced && !(rng_draw4(seed, (uint32_t)pixel, sample, 1, 0).u[0] > p_rr);
+                    if (need) u = rng_draw4(seed, (uint32_t)pixel, sample, 1, 1).u[0];
+                }
+                int mine = -1;
+                float wmine = 0.f;
+                if (use_cdf) {
+                    if (need) {
+                        const float* si = sinc + 32 * v;
+                        const float target = fmaxf(u, 1e-7f) * total[v];
+                        int j = 0;  // first lane whose inclusive total reaches the target
+#pragma unroll
+                        for (int step = 16; step; step >>= 1)
+                            if (si[j + step - 1] < target) j += step;
+                        const float* col = cdf + v * s.Lpad + j;  // col[32 k]: running sum of lane j's lights
+                        const float rem = fminf(target - (j ? si[j - 1] : 0.f), col[32 * (K - 1)]);
+                        int lo = 0, hi = K - 1;
+                        while (lo < hi) {
+                            const int mid = (lo + hi) >> 1;
+                            if (col[32 * mid] < rem) lo = mid + 1; else hi = mid;
+                        }
+                        mine = j + 32 * lo;
+                        wmine = col[32 * lo] - (lo ? col[32 * (lo - 1)] : 0.f);
+                        if (!(wmine > 0.f) || mine >= s.L) mine = -1;
+                    }
+                } else {
+                    unsigned todo = __ballot_sync(kFull, need);
+                    while (todo) {
+                        const int src = __ffs(todo) - 1;
+                        todo &= todo - 1;
+                        const LightPick pk = warp_light_pick(s, X[v], Nn[v], part[v], incl[v], total[v], __shfl_sync(kFull, u, src));
+                        if (lane == src) { mine = pk.light; wmine = pk.w; }
+                    }
+                }
+                if (k < batch_spp) sel[(size_t)k * npix + pixel] = make_int2(mine, __float_as_int(wmine));
+            }
+        }
+        __syncwarp();  // the next pair overwrites cdf / sinc
     }
 }
 
@@ -420,25 +483,18 @@ __global__ void __launch_bounds__(kBlk) k_bounce(const BounceArgs a)
                 }
             } else warp_light_select(s, alive, p, N, r1.u[0], &chosen, &wsum, &wch);
             if (alive && chosen >= 0) {
-                // Arvo sample of the chosen triangle (Mylight.cpp:285-317): FP32 for comfortably large solid angles,
-                // FP64 below (alpha+beta+gamma-pi and the edge-angle algebra lose all FP32 digits on tiny lights)
-                const float lsum_f = __ldg(s.lights + 5 * chosen + 3).w;
-                f3 wl; bool ok;
-                int lprim;
-                f3 Le, ngl, lv0;
-                if (wch > 1e-2f * lsum_f) {
-                    LightTri<float> lt = load_light<float>(s, chosen);
-                    SphTri<float> st = spherical_project<float>(lt, p, N);
-                    ok = st.ok;
-                    wl = ok ? arvo_sample<float>(st, r1.u[1], r1.u[2]) : N;
-                    lprim = lt.prim; Le = lt.Le; ngl = lt.ng; lv0 = lt.v0;
-                } else {
-                    LightTri<double> lt = load_light<double>(s, chosen);
-                    SphTri<double> st = spherical_project<double>(lt, to_d3(p), to_d3(N));
-                    ok = st.ok;
-                    wl = ok ? to_f3(arvo_sample<double>(st, (double)r1.u[1], (double)r1.u[2])) : N;
-                    lprim = lt.prim; Le = to_f3(lt.Le); ngl = to_f3(lt.ng); lv0 = to_f3(lt.v0);
-                }
+                // Arvo sample of the chosen triangle (Mylight.cpp:285-317) through arvo_direct (lights.cuh), in FP64:
+                // the q of :292 is a ratio of two O(sA^2) differences, and FP32 misses the 1e-5 direction bar even on
+                // large lights (measured 5e-5 on the Cornell ceiling light)
+                const float4 l0 = __ldg(s.lights + 5 * chosen), l1 = __ldg(s.lights + 5 * chosen + 1), l2 = __ldg(s.lights + 5 * chosen + 2);
+                const float4 l3 = __ldg(s.lights + 5 * chosen + 3);
+                const float lsum_f = l3.w;
+                const int lprim = __float_as_int(l0.w);
+                const f3 Le = to_f3(__ldg(s.lights + 5 * chosen + 4)), ngl = to_f3(l3), lv0 = to_f3(l0);
+                d3 wd = to_d3(N);
+                const bool ok = arvo_direct<double>(to_d3(l0), to_d3(l1), to_d3(l2), to_d3(p), to_d3(N), (double)(wch / lsum_f),
+                                                    (double)r1.u[1], (double)r1.u[2], &wd);
+                const f3 wl = to_f3(wd);
                 const float pl = lsum_f / wsum;  // solid-angle pdf, Mylight.cpp:317
                 const float cosN = dot(wl, N);
                 if (ok && cosN > 0.f) {
@@ -773,9 +829,16 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
         a.in = Q[0]; a.out = Q[1];
         if (sph && !jitter) {
             // first-vertex light draws, weights computed once per pixel (F4: all samples share the camera ray)
-            const int warps_needed = (int)std::min<size_t>(npix, (size_t)sms * 16);
-            k_lightprep<<<(warps_needed * 32 + kBlk - 1) / kBlk, kBlk, 0, st>>>(scene->d, dc, primary, (int)npix, b, a.sample_base, prm->seed, p_rr,
-                                                                           tree ? 1 : 0, prm->max_depth, sel, wsum_pix);
+            const size_t per_block = (size_t)(kBlk / 32) * (2 * (size_t)scene->d.Lpad + 64) * sizeof(float);
+            const int use_cdf = per_block <= 200 * 1024;  // larger light tables: per-sample warp picks instead
+            const size_t dyn = use_cdf ? per_block : 0;
+            if (dyn > 48 * 1024) MCPT_CUDA(cudaFuncSetAttribute(k_lightprep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+            int pbps = 1;
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pbps, k_lightprep, kBlk, dyn);
+            const size_t npairs = (npix + 1) / 2;
+            const int pgrid = (int)std::min<size_t>((npairs + kBlk / 32 - 1) / (kBlk / 32), (size_t)sms * std::max(1, pbps));
+            k_lightprep<<<pgrid, kBlk, dyn, st>>>(scene->d, dc, primary, (int)npix, b, a.sample_base, prm->seed, p_rr, tree ? 1 : 0,
+                                                  prm->max_depth, use_cdf, sel, wsum_pix);
             MCPT_CUDA(cudaGetLastError());
             S.kernel_launches++;
         }

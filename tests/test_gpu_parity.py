@@ -159,6 +159,24 @@ def test_light_spherical(scene_name, golden, gpu_scene_of, arrays_of):
     assert np.max(util.rel_err(f["wsum"][same], g["ls_wsum"][same])) < 1e-4
 
 
+def test_light_spherical_renderer_sampler(scene_name, golden, gpu_scene_of, arrays_of):
+    """The sampler the renderer runs (arvo_direct: no inverse trigonometry, solid angle from the FP32
+    Van Oosterom-Strackee weight, FP64 algebra from FP32 inputs) maps the SAME (xi1, xi2) to the same
+    direction as Mylight.cpp:289-297: north-star bar, sample directions within 1e-5 relative."""
+    g = golden(scene_name)
+    a, _ = arrays_of(scene_name)
+    x, Nn, u3, _ = util.shading_points(a, 600, 107)
+    query = a.light_prim[np.random.default_rng(108).integers(0, len(a.light_prim), size=600)]
+    r = gpu_scene_of(scene_name).light_sample_spherical(x, Nn, u3, query, 3)
+    has = (g["ls_nsurv"] > 0) & np.isfinite(g["ls_point"]).all(1) & (r["prim"] == g["ls_prim"])
+    moved = has & (np.linalg.norm(g["ls_point"] - x, axis=1) > 0) & (np.linalg.norm(r["point"] - x, axis=1) > 0)
+    assert moved.sum() > 0.5 * (g["ls_nsurv"] > 0).sum()
+    dir_g = util.unit(g["ls_point"][moved] - x[moved]); dir_r = util.unit(r["point"][moved] - x[moved])
+    assert np.max(np.abs(dir_g - dir_r)) < 1e-5
+    # and the sampled point lies on the chosen light (the re-intersection of Mylight.cpp:311 succeeded as often)
+    assert abs(moved.sum() - (has & (np.linalg.norm(g["ls_point"] - x, axis=1) > 0)).sum()) <= 0.01 * has.sum() + 2
+
+
 def test_tonemap(gpu_scene_of, golden):
     vals = np.abs(np.random.default_rng(109).normal(size=(200, 3))) * 200
     out = gpu_scene_of("cornell-box").tonemap(vals.astype(np.float32))
