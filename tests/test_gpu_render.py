@@ -153,3 +153,27 @@ def test_axis_aligned_cornell_is_finite(tmp_path):
             assert np.isfinite(img).all() and img.mean() > 0
     finally:
         s.close()
+
+
+def test_cpp_driver_end_to_end(scene_files, tmp_path, gpu_scene_of, arrays_of):
+    """mcpt_render: the C++ replacement of main() -- load, render through the C ABI, tone-map, write PPM/PFM.
+    Same seed and parameters as a ctypes render -> the PFM holds exactly the same linear film."""
+    import os
+    import subprocess
+    drv = os.path.join(util.ROOT, "monte_carlo_path_tracing_b200", "mcpt_render")
+    _, stem = scene_files("cornell-box")
+    _, cam = arrays_of("cornell-box")
+    ppm, pfm = tmp_path / "o.ppm", tmp_path / "o.pfm"
+    r = subprocess.run([drv, stem + ".obj", stem + ".xml", str(ppm), "--spp", "8", "--strategy", "nee_uniform",
+                        "--max-depth", "4", "--seed", "7", "--pfm", str(pfm)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    raw = ppm.read_bytes()
+    hdr = ("P6\n%d %d\n255\n" % (cam.width, cam.height)).encode()
+    assert raw.startswith(hdr) and len(raw) == len(hdr) + cam.width * cam.height * 3
+    data = pfm.read_bytes()
+    h2 = ("PF\n%d %d\n-1.0\n" % (cam.width, cam.height)).encode()
+    film = np.frombuffer(data[len(h2):], np.float32).reshape(cam.height, cam.width, 3)[::-1]
+    img, _ = gpu_scene_of("cornell-box").render(cam, api.NEE_UNIFORM, 8, max_depth=4, seed=7)
+    assert np.array_equal(film, img)
+    rgb8 = np.frombuffer(raw[len(hdr):], np.uint8).reshape(cam.height, cam.width, 3)
+    assert np.array_equal(rgb8, gpu_scene_of("cornell-box").tonemap(img))

@@ -172,3 +172,23 @@ def test_spp_sharding_two_ranks_gloo(tmp_path, oracle_of, arrays_of):
     ref, _ = oracle_of("cornell-box").render(cam, oracle.NEE_UNIFORM, total, max_depth=3, seed=5, flags=oracle.FIX_STALE_MIS)
     assert np.allclose(got, ref.reshape(-1), rtol=1e-5, atol=1e-6)
     assert got.max() > 0
+
+
+def _driver():
+    p = os.path.join(ROOT, "monte_carlo_path_tracing_b200", "mcpt_render")
+    if not os.path.exists(p):
+        api.build()
+    return p
+
+
+@pytest.mark.skipif(os.path.exists("/dev/nvidiactl"), reason="a GPU is present")
+def test_cpp_driver_fails_loudly_without_gpu(scene_files, tmp_path):
+    """mcpt_render (main.cpp minus EasyX, C++ over the C ABI) loads the scene on the host, then stops with the
+    library's message -- it never falls back to a CPU renderer and never exit()s from inside the library."""
+    import subprocess
+    _, stem = scene_files("cornell-box")
+    r = subprocess.run([_driver(), stem + ".obj", stem + ".xml", str(tmp_path / "o.ppm"), "--spp", "1"],
+                       capture_output=True, text=True, timeout=120)
+    assert r.returncode == 1
+    assert "light triangles" in r.stdout and "no CPU fallback" in r.stderr
+    assert not (tmp_path / "o.ppm").exists()
