@@ -35,6 +35,11 @@ WORKLOADS = {
     # name: (scene generator kwargs, strategy name, max_depth)
     "veach-mis": dict(scene="veach-mis", kw=dict(width=1280, height=720), strategy="MIS", max_depth=0),
     "cornell-box": dict(scene="cornell-box", kw=dict(width=512, height=512), strategy="NEE_UNIFORM", max_depth=5),
+    # configs[2]: stand-in for the unavailable bathroom scene: generated interior, ~185 k triangles
+    "interior": dict(scene="interior", kw=dict(width=1280, height=720), strategy="MIS", max_depth=0),
+    # configs[3]: 1 M random triangles + 64 emissive triangles, 1024x1024, uniform-area NEE (BVH traversal stress)
+    "soup-1m": dict(scene="soup", kw=dict(num_tris=1_000_000, num_lights=64, width=1024, height=1024), strategy="NEE_UNIFORM",
+                    max_depth=5),
 }
 STRAT = {"NEE_SPHERICAL": 0, "BRDF_ONLY": 1, "MIS": 2, "NEE_UNIFORM": 3}
 # compulsory wavefront state traffic per sample-bounce (rays, hit, path state, queue words)
@@ -94,7 +99,12 @@ def _cpu_worker(args):
     import oracle
     from monte_carlo_path_tracing_b200.scenes import Camera
     cam = Camera(**cam_d)
-    if use_ref:
+    if isinstance(stem, dict):  # array scene (triangle soup): no OBJ files, so the C restatement renders it
+        from monte_carlo_path_tracing_b200 import scenes as _sc
+        lib = oracle.OracleLib(_sc.triangle_soup(**stem))
+        lib.build_grid(cam.eye, 100000)
+        render = lambda r0, r1, k: lib.render(cam, STRAT[strategy], 1, max_depth=max_depth, seed=seed, rows=(r0, r1), spp_offset=k, spp_total=1)
+    elif use_ref:
         lib = oracle.RefLib(stem + ".obj", stem + ".xml")
         lib.build_grid(cam.eye, 100000)
         strat = {"NEE_SPHERICAL": 0, "BRDF_ONLY": 1, "MIS": 2}[strategy]
@@ -126,7 +136,7 @@ def cpu_reference_run(stem, cam, strategy, max_depth, budget_s, seed=1, procs=No
     """All host cores, one reference process each, for ~budget_s seconds.  Returns dict(value Msamples/s, ...)."""
     import multiprocessing as mp
     import oracle
-    use_ref = oracle.ref_available() and strategy in ("NEE_SPHERICAL", "BRDF_ONLY", "MIS")
+    use_ref = oracle.ref_available() and strategy in ("NEE_SPHERICAL", "BRDF_ONLY", "MIS") and not isinstance(stem, dict)
     if not os.path.exists(oracle.ORACLE_SO):
         oracle.build(ref=False)
     nproc = procs or os.cpu_count() or 1
@@ -146,8 +156,18 @@ def cpu_reference_run(stem, cam, strategy, max_depth, budget_s, seed=1, procs=No
 
 # ---- arms -------------------------------------------------------------------------------------------------------
 def write_scene(wl, td):
+    """(scene object with .camera, stem of the OBJ/XML files) -- for the array scene the 'stem' is the generator kwargs."""
+    if wl["scene"] == "soup":
+        return scenes.triangle_soup(**wl["kw"]), dict(wl["kw"])
     sc = scenes.SCENES[wl["scene"]](**wl["kw"])
     return sc, sc.write(td)
+
+
+def load_arrays(sc, stem):
+    from monte_carlo_path_tracing_b200 import api
+    if isinstance(stem, dict):
+        return sc
+    return api.load_scene_files(stem + ".obj", stem + ".xml")[0]
 
 
 def base_line(args, wl_name, wl, cam, spp_per_step):
@@ -203,7 +223,7 @@ def run_ours(args, wl_name, wl):
     td = tempfile.mkdtemp(prefix="mcpt_bench_")
     sc, stem = write_scene(wl, td)
     cam = sc.camera
-    arrays, _ = api.load_scene_files(stem + ".obj", stem + ".xml")
+    arrays = load_arrays(sc, stem)
     scene = api.Scene(arrays, local)
     npix = cam.width * cam.height
     film = torch.zeros(npix * 3, dtype=torch.float32, device="cuda")

@@ -40,6 +40,14 @@ struct Queue {
     uint2* node;   // path-tree node code (MIS only)
 };
 
+struct ShadowQueue {
+    float4* org;   // o.xyz | t of the sampled light point (the ray's tmax)
+    float4* dir;   // d.xyz | slot (int bits)
+    float4* ctr;   // contribution if visible, rgb | unused
+    int2* ids;     // origin prim (excluded, Myobj.cpp:417) | sampled light prim
+    int* count;
+};
+
 struct BounceArgs {
     DScene s;
     DCamera cam;
@@ -47,6 +55,8 @@ struct BounceArgs {
     float4* Lacc;              // [slots] per-slot radiance accumulator (owner-exclusive)
     float4* contrib;           // [capacity] MIS: per-element emission contribution | slot
     const float4* primary_hit; // [npix] prim | beta | gamma | t
+    const float4* hit;         // [capacity] closest hit of in-queue ray i, written by k_extend: prim | beta | gamma | t
+    ShadowQueue sq;            // NEE visibility rays of this bounce with their pending contributions
     const int2* sel;           // [slots] first-vertex light drawn by k_lightprep: index | weight bits
     const float* wsum_pix;     // [npix] first-vertex weights_sum
     int* counts;               // [chunks] children staged by each chunk
@@ -380,8 +390,11 @@ __global__ void __launch_bounds__(kBlk) k_lightprep(DScene s, DCamera cam, const
 // ---- one bounce --------------------------------------------------------------------------------------------
 struct Child { f3 o, d, thr; int exclude; uint64_t node; };
 
+// k_shade: everything shade* does at one vertex except the scene-BVH traversals, which the wavefront hands to
+// k_extend (closest hit of the children) and k_shadow (NEE visibility).  FIRST = primary vertices without jitter:
+// the ray comes from the camera formula and the hit from k_primary's per-pixel table.
 template <int STRAT, bool FIRST>
-__global__ void __launch_bounds__(kBlk) k_bounce(const BounceArgs a)
+__global__ void __launch_bounds__(kBlk) k_shade(const BounceArgs a)
 {
     constexpr bool kTree = (STRAT == MCPT_MIS);
     constexpr bool kNee = (STRAT == MCPT_NEE_SPHERICAL || STRAT == MCPT_NEE_UNIFORM);
@@ -389,9 +402,9 @@ __global__ void __launch_bounds__(kBlk) k_bounce(const BounceArgs a)
     __shared__ int stack[kStackSm * kBlk];
     const DScene& s = a.s;
     const int lane = threadIdx.x & 31;
-    unsigned c_vert = 0, c_rays = 0, c_shadow = 0, c_lrays = 0, c_phits = 0;
+    unsigned c_vert = 0, c_lrays = 0, c_phits = 0;
     const int nchunks = (a.in_count + 31) >> 5;
-    const bool presel = FIRST && kSph && !(a.flags & MCPT_JITTER);  // lights already drawn by k_lightprep
+    const bool presel = FIRST && kSph;  // lights already drawn by k_lightprep
 
     int next = 0;
     if (lane == 0) next = atomicAdd(a.ticket, 1);
@@ -415,16 +428,9 @@ __global__ void __launch_bounds__(kBlk) k_bounce(const BounceArgs a)
                 pixel = (uint32_t)(i % a.npix);
                 sample = (uint32_t)(a.sample_base + i / a.npix);
                 o = mk<float>(a.cam.eye[0], a.cam.eye[1], a.cam.eye[2]);
-                if (a.flags & MCPT_JITTER) {
-                    Rng4 r = rng_draw4(a.seed, pixel, sample, 1, 2);
-                    d = camera_dir(a.cam, (int)pixel, r.u[0] - 0.5f, r.u[1] - 0.5f);
-                    h = trace_fast<false>(s.nodes, s.tris, o, d, -1, s.tmin, 3.0e38f, stack + threadIdx.x, kBlk);
-                    c_rays++;
-                } else {
-                    d = camera_dir(a.cam, (int)pixel, 0.f, 0.f);
-                    const float4 ph = __ldg(a.primary_hit + pixel);
-                    h.prim = __float_as_int(ph.x); h.b = ph.y; h.g = ph.z; h.t = ph.w;
-                }
+                d = camera_dir(a.cam, (int)pixel, 0.f, 0.f);
+                const float4 ph = __ldg(a.primary_hit + pixel);
+                h.prim = __float_as_int(ph.x); h.b = ph.y; h.g = ph.z; h.t = ph.w;
                 if (h.prim >= 0) c_phits++;
             } else {
                 const float4 qo = a.in.org[i], qd = a.in.dir[i], qt = a.in.thr[i];
@@ -435,8 +441,9 @@ __global__ void __launch_bounds__(kBlk) k_bounce(const BounceArgs a)
                 sample = (uint32_t)(a.sample_base + slot / a.npix);
                 if (kTree) { const uint2 nd = a.in.node[i]; node = ((uint64_t)nd.y << 32) | nd.x; }
                 else node = (uint64_t)a.bounce + 1;
-                h = trace_fast<false>(s.nodes, s.tris, o, d, exclude, s.tmin, 3.0e38f, stack + threadIdx.x, kBlk);
-                c_rays++;
+                const float4 qh = a.hit[i];
+                h.prim = __float_as_int(qh.x); h.b = qh.y; h.g = qh.z; h.t = qh.w;
+                if (a.bounce == 0 && h.prim >= 0) c_phits++;  // jittered camera rays
             }
         }
 
@@ -453,7 +460,7 @@ __global__ void __launch_bounds__(kBlk) k_bounce(const BounceArgs a)
             else if (v.light >= 0) {      // emissive: self-emission only
                 // shade(): an indirect ray that lands on a light contributes 0 (main.cpp:338); the emission
                 // return of main.cpp:284-288 is only reachable from the camera ray.
-                if (!kNee || FIRST) contrib = thr * to_f3(__ldg(s.lights + 5 * v.light + 4));
+                if (!kNee || a.bounce == 0) contrib = thr * to_f3(__ldg(s.lights + 5 * v.light + 4));
                 alive = false;
             } else mat = load_mat(s, v.mat);
         }
@@ -473,6 +480,11 @@ __global__ void __launch_bounds__(kBlk) k_bounce(const BounceArgs a)
         Child ch[2];
         int n_out = 0;
         float wsum = 0.f;
+        // NEE visibility ray (main.cpp:309-311): visible iff the closest hit along wl IS the sampled triangle
+        bool sh_need = false;
+        f3 sh_d = d, sh_c = mk<float>(0.f, 0.f, 0.f);
+        float sh_t = 0.f;
+        int sh_prim = -1;
         if (kSph) {
             int chosen = -1; float wch = 0.f;
             if (presel) {
@@ -512,13 +524,10 @@ __global__ void __launch_bounds__(kBlk) k_bounce(const BounceArgs a)
                             const float4 q1 = __ldg(s.lights + 5 * chosen + 1), q2 = __ldg(s.lights + 5 * chosen + 2);
                             float be, ga, tl;
                             if (tri_test_fast(p, wl, lv0, to_f3(q1), to_f3(q2), s.tmin, &be, &ga, &tl)) {
-                                Hit sh = trace_fast<true>(s.nodes, s.tris, p, wl, h.prim, s.tmin, tl, stack + threadIdx.x, kBlk, lprim);
-                                c_shadow++;
-                                if (sh.prim == lprim) {
-                                    const f3 f = phong_eval<float>(N, wl, wo, mat);
-                                    const float g = (a.flags & MCPT_FIX_NEE_MEASURE) ? cosN / pl : cosN * cosL / (tl * tl) / pl;  // F9
-                                    contrib = contrib + thr * Le * f * g;
-                                }
+                                const f3 f = phong_eval<float>(N, wl, wo, mat);
+                                const float g = (a.flags & MCPT_FIX_NEE_MEASURE) ? cosN / pl : cosN * cosL / (tl * tl) / pl;  // F9
+                                sh_need = true; sh_d = wl; sh_t = tl; sh_prim = lprim;
+                                sh_c = thr * Le * f * g;
                             }
                         }
                     }
@@ -536,12 +545,9 @@ __global__ void __launch_bounds__(kBlk) k_bounce(const BounceArgs a)
                     const float4 q0 = __ldg(s.lights + 5 * lp.light), q1 = __ldg(s.lights + 5 * lp.light + 1), q2 = __ldg(s.lights + 5 * lp.light + 2);
                     float be, ga, tl;
                     if (tri_test_fast(p, wl, to_f3(q0), to_f3(q1), to_f3(q2), s.tmin, &be, &ga, &tl)) {
-                        Hit sh = trace_fast<true>(s.nodes, s.tris, p, wl, h.prim, s.tmin, tl, stack + threadIdx.x, kBlk, lp.prim);
-                        c_shadow++;
-                        if (sh.prim == lp.prim) {
-                            const f3 f = phong_eval<float>(N, wl, wo, mat);
-                            contrib = contrib + thr * lp.Le * f * (cosN * cosL / d2 / lp.prob);  // main.cpp:314
-                        }
+                        const f3 f = phong_eval<float>(N, wl, wo, mat);
+                        sh_need = true; sh_d = wl; sh_t = tl; sh_prim = lp.prim;
+                        sh_c = thr * lp.Le * f * (cosN * cosL / d2 / lp.prob);  // main.cpp:314
                     }
                 }
             }
@@ -604,19 +610,94 @@ __global__ void __launch_bounds__(kBlk) k_bounce(const BounceArgs a)
                 if (total) atomicAdd(a.groupsum + chunk / kGroup, total);
             }
         }
+        if (kNee) {
+            // visibility rays: unordered append (every slot owns at most one per bounce, so k_shadow's
+            // Lacc[slot] += contribution needs no ordering), one atomic per warp
+            const unsigned ms = __ballot_sync(kFull, sh_need);
+            if (ms) {
+                int base = 0;
+                if (lane == 0) base = atomicAdd(a.sq.count, __popc(ms));
+                base = __shfl_sync(kFull, base, 0);
+                if (sh_need) {
+                    const int dst = base + __popc(ms & ((1u << lane) - 1u));
+                    a.sq.org[dst] = make_float4(p.x, p.y, p.z, sh_t);
+                    a.sq.dir[dst] = make_float4(sh_d.x, sh_d.y, sh_d.z, __int_as_float(slot));
+                    a.sq.ctr[dst] = make_float4(sh_c.x, sh_c.y, sh_c.z, 0.f);
+                    a.sq.ids[dst] = make_int2(h.prim, sh_prim);
+                }
+            }
+        }
     }
     // warp-level counter reduction: one atomic per counter per warp
-    c_vert = __reduce_add_sync(kFull, c_vert); c_rays = __reduce_add_sync(kFull, c_rays); c_shadow = __reduce_add_sync(kFull, c_shadow);
+    c_vert = __reduce_add_sync(kFull, c_vert);
     c_lrays = __reduce_add_sync(kFull, c_lrays); c_phits = __reduce_add_sync(kFull, c_phits);
     if (lane == 0) {
         if (c_vert) atomicAdd(a.counters + CNT_VERTICES, (unsigned long long)c_vert);
-        if (c_rays) atomicAdd(a.counters + CNT_RAYS, (unsigned long long)c_rays);
-        if (c_shadow) atomicAdd(a.counters + CNT_SHADOW, (unsigned long long)c_shadow);
         if (c_lrays) atomicAdd(a.counters + CNT_LIGHTRAYS, (unsigned long long)c_lrays);
         if (c_phits) atomicAdd(a.counters + CNT_PRIMARY_HITS, (unsigned long long)c_phits);
     }
 }
 
+
+// ---- wavefront trace kernels: persistent warps, dynamic ray refill (traverse.cuh: trace_stream) -------------------
+// k_extend: closest hit of every ray of the dense queue (closet_ray_intersect, Myobj.cpp:334-474) -> hit[i]
+__global__ void __launch_bounds__(kBlk) k_extend(DScene s, const float4* __restrict__ org, const float4* __restrict__ dir,
+                                                 const int* __restrict__ n_ptr, int* counter, float4* hit)
+{
+    __shared__ int stack[kStackSm * kBlk];
+    const int n = *n_ptr;
+    trace_stream<false>(
+        s.nodes, s.tris, s.tmin, n, counter, stack + threadIdx.x, kBlk,
+        [&](int i, f3& o, f3& d, int& exclude, float& tmax, int& init_prim) {
+            const float4 qo = org[i], qd = dir[i];
+            o = to_f3(qo); d = to_f3(qd);
+            exclude = __float_as_int(qo.w); tmax = 3.0e38f; init_prim = -1;
+        },
+        [&](int i, const Hit& h) { hit[i] = make_float4(__int_as_float(h.prim), h.b, h.g, h.t); });
+}
+
+// k_shadow: the visibility test of main.cpp:309-311 -- "the closest hit along wl IS the sampled light triangle" -- as
+// an any-hit search for something that beats the light point under the closest-hit order; survivors add their
+// pending contribution to the slot's accumulator (each slot has at most one visibility ray per bounce).
+__global__ void __launch_bounds__(kBlk) k_shadow(DScene s, const ShadowQueue sq, int* counter, float4* Lacc, unsigned long long* counters)
+{
+    __shared__ int stack[kStackSm * kBlk];
+    const int n = *sq.count;
+    if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(counters + CNT_SHADOW, (unsigned long long)n);
+    trace_stream<true>(
+        s.nodes, s.tris, s.tmin, n, counter, stack + threadIdx.x, kBlk,
+        [&](int i, f3& o, f3& d, int& exclude, float& tmax, int& init_prim) {
+            const float4 qo = sq.org[i], qd = sq.dir[i];
+            const int2 id = sq.ids[i];
+            o = to_f3(qo); d = to_f3(qd);
+            exclude = id.x; tmax = qo.w; init_prim = id.y;
+        },
+        [&](int i, const Hit& h) {
+            if (h.prim == sq.ids[i].y) {
+                const float4 c = sq.ctr[i];
+                const int slot = __float_as_int(sq.dir[i].w);
+                float4 L = Lacc[slot];
+                L.x += c.x; L.y += c.y; L.z += c.z;
+                Lacc[slot] = L;
+            }
+        });
+}
+
+// jittered camera rays (extension F4): one ray per slot into the dense queue; the first k_extend traces them
+__global__ void k_raygen(DCamera cam, int npix, int slots, int sample_base, uint64_t seed, Queue q, int tree, float4* Lacc, int* out_count)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) *out_count = slots;
+    if (i >= slots) return;
+    const uint32_t pixel = (uint32_t)(i % npix), sample = (uint32_t)(sample_base + i / npix);
+    const Rng4 r = rng_draw4(seed, pixel, sample, 1, 2);
+    const f3 d = camera_dir(cam, (int)pixel, r.u[0] - 0.5f, r.u[1] - 0.5f);
+    q.org[i] = make_float4(cam.eye[0], cam.eye[1], cam.eye[2], __int_as_float(-1));
+    q.dir[i] = make_float4(d.x, d.y, d.z, __int_as_float(i));
+    q.thr[i] = make_float4(1.f, 1.f, 1.f, 0.f);
+    if (tree) q.node[i] = make_uint2(1u, 0u);
+    Lacc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
 
 // ---- MIS path tree: per-slot sums of per-element contributions ----------------------------------------------
 // The compaction is order preserving and the initial queue is sorted by slot, so all elements of one slot
@@ -679,15 +760,15 @@ __global__ void k_tonemap(const float* __restrict__ rgb, size_t n3, double A, do
 template <int STRAT>
 void launch_bounce(bool first, const BounceArgs& a, int grid, cudaStream_t st)
 {
-    if (first) k_bounce<STRAT, true><<<grid, kBlk, 0, st>>>(a);
-    else k_bounce<STRAT, false><<<grid, kBlk, 0, st>>>(a);
+    if (first) k_shade<STRAT, true><<<grid, kBlk, 0, st>>>(a);
+    else k_shade<STRAT, false><<<grid, kBlk, 0, st>>>(a);
 }
 
 template <int STRAT> int bounce_blocks_per_sm()
 {
     int a = 0, b = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, k_bounce<STRAT, true>, kBlk, 0);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, k_bounce<STRAT, false>, kBlk, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, k_shade<STRAT, true>, kBlk, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, k_shade<STRAT, false>, kBlk, 0);
     return std::max(1, std::min(a, b));
 }
 
@@ -752,6 +833,10 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     const size_t groups = (chunks + kGroup - 1) / kGroup;
     const size_t o_counts = place(chunks * 4), o_small = place(256 + groups * 4);
     const size_t o_sel = place(sph ? slots * 8 : 16), o_wsum = place(sph ? npix * 4 : 16);
+    const bool nee = prm->strategy == MCPT_NEE_SPHERICAL || prm->strategy == MCPT_NEE_UNIFORM;
+    const size_t o_hit = place(cap * 16);
+    const size_t sqn = nee ? cap : 1;
+    const size_t o_sq[4] = {place(sqn * 16), place(sqn * 16), place(sqn * 16), place(sqn * 8)};
     Workspace& ws = scene->ws;
     if (ws.bytes < off) {
         if (ws.base) MCPT_CUDA(cudaFree(ws.base));
@@ -773,9 +858,16 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     int* counts = (int*)(base + o_counts);
     int2* sel = (int2*)(base + o_sel);
     float* wsum_pix = (float*)(base + o_wsum);
-    // small block: [0] ticket (int), [1] out_count (int), [64..] counters (u64 x CNT_N), [256..] group sums (int x groups)
-    int* d_ticket = (int*)(base + o_small);
-    int* d_count = d_ticket + 1;
+    float4* hit = (float4*)(base + o_hit);
+    // small block: [0] out_count, [1] shade ticket, [2] shadow-queue length, [3] k_extend cursor, [4] k_shadow cursor (ints),
+    //              [64..] counters (u64 x CNT_N), [256..] group sums (int x groups)
+    int* d_count = (int*)(base + o_small);
+    int* d_ticket = d_count + 1;
+    ShadowQueue SQ;
+    SQ.org = (float4*)(base + o_sq[0]); SQ.dir = (float4*)(base + o_sq[1]); SQ.ctr = (float4*)(base + o_sq[2]);
+    SQ.ids = (int2*)(base + o_sq[3]); SQ.count = d_count + 2;
+    int* d_ext_cursor = d_count + 3;
+    int* d_sh_cursor = d_count + 4;
     unsigned long long* d_counters = (unsigned long long*)(base + o_small + 64);
     int* d_groupsum = (int*)(base + o_small + 256);
     volatile int* h_count = (volatile int*)ws.pinned;
@@ -803,6 +895,10 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
               : prm->strategy == MCPT_MIS         ? bounce_blocks_per_sm<MCPT_MIS>()
                                                   : bounce_blocks_per_sm<MCPT_NEE_UNIFORM>();
     const int max_grid = sms * bps;
+    int ebps = 1, sbps = 1;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ebps, k_extend, kBlk, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sbps, k_shadow, kBlk, 0);
+    const int ext_grid = sms * std::max(1, ebps), sh_grid = sms * std::max(1, sbps);
 
     McptStats S;
     std::memset(&S, 0, sizeof S);
@@ -823,6 +919,7 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
         BounceArgs a;
         a.s = scene->d; a.cam = dc;
         a.Lacc = Lacc; a.contrib = contrib; a.primary_hit = primary; a.sel = sel; a.wsum_pix = wsum_pix; a.counts = counts; a.groupsum = d_groupsum; a.ticket = d_ticket;
+        a.hit = hit; a.sq = SQ;
         a.counters = d_counters; a.seed = prm->seed; a.capacity = (int)cap; a.npix = (int)npix; a.batch_spp = b;
         a.sample_base = prm->spp_offset + done; a.max_depth = prm->max_depth; a.flags = prm->flags; a.p_rr = p_rr;
         int count = (int)(npix * (size_t)b);
@@ -842,32 +939,48 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
             MCPT_CUDA(cudaGetLastError());
             S.kernel_launches++;
         }
+        if (jitter) {
+            // jittered camera rays differ per sample: generate them into the dense queue and trace them like any bounce
+            k_raygen<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(dc, (int)npix, count, a.sample_base, prm->seed, Q[0], tree ? 1 : 0, Lacc, d_count);
+            MCPT_CUDA(cudaMemsetAsync(d_ticket, 0, 16, st));
+            k_extend<<<std::min(ext_grid, (count + kBlk - 1) / kBlk), kBlk, 0, st>>>(scene->d, Q[0].org, Q[0].dir, d_count, d_ext_cursor, hit);
+            MCPT_CUDA(cudaGetLastError());
+            S.kernel_launches += 2;
+            S.rays_closest += (uint64_t)count;
+        }
         for (int bounce = 0; count > 0; bounce++) {
             if (prm->max_depth <= 0 && bounce >= 256) break;  // unlimited depth: RR has long emptied the queue
             a.in_count = count; a.bounce = bounce;
             const int nch = (count + 31) / 32, ngroups = (nch + kGroup - 1) / kGroup;
-            MCPT_CUDA(cudaMemsetAsync(d_ticket, 0, 8, st));
+            MCPT_CUDA(cudaMemsetAsync(d_ticket, 0, 16, st));
             MCPT_CUDA(cudaMemsetAsync(d_groupsum, 0, (size_t)ngroups * 4, st));
             MCPT_CUDA(cudaEventRecord(scene->ev[2], st));
             const int grid = std::min((nch + kBlk / 32 - 1) / (kBlk / 32), max_grid);
+            const bool first = bounce == 0 && !jitter;
             switch (prm->strategy) {
-                case MCPT_NEE_SPHERICAL: launch_bounce<MCPT_NEE_SPHERICAL>(bounce == 0, a, grid, st); break;
-                case MCPT_BRDF_ONLY: launch_bounce<MCPT_BRDF_ONLY>(bounce == 0, a, grid, st); break;
-                case MCPT_MIS: launch_bounce<MCPT_MIS>(bounce == 0, a, grid, st); break;
-                default: launch_bounce<MCPT_NEE_UNIFORM>(bounce == 0, a, grid, st); break;
+                case MCPT_NEE_SPHERICAL: launch_bounce<MCPT_NEE_SPHERICAL>(first, a, grid, st); break;
+                case MCPT_BRDF_ONLY: launch_bounce<MCPT_BRDF_ONLY>(first, a, grid, st); break;
+                case MCPT_MIS: launch_bounce<MCPT_MIS>(first, a, grid, st); break;
+                default: launch_bounce<MCPT_NEE_UNIFORM>(first, a, grid, st); break;
             }
             MCPT_CUDA(cudaGetLastError());
-            MCPT_CUDA(cudaEventRecord(scene->ev[3], st));
             S.kernel_launches++;
             const bool last = prm->max_depth > 0 && bounce + 1 >= prm->max_depth + 1;  // vertices deeper than max_depth never spawn
             if (!last) {
                 k_gather<<<ngroups, 256, 0, st>>>(Q[1], Q[0], counts, d_groupsum, nch, (int)stride, (int)cap, tree ? 1 : 0, d_count, d_counters);
+                k_extend<<<std::min(ext_grid, (count * (tree ? 2 : 1) + kBlk - 1) / kBlk), kBlk, 0, st>>>(scene->d, Q[0].org, Q[0].dir, d_count, d_ext_cursor, hit);
+                S.kernel_launches += 2;
+            }
+            if (nee) {
+                k_shadow<<<std::min(sh_grid, (count + kBlk - 1) / kBlk), kBlk, 0, st>>>(scene->d, SQ, d_sh_cursor, Lacc, d_counters);
                 S.kernel_launches++;
             }
-            if (tree && bounce > 0) {
+            if (tree && !first) {
                 k_runsum<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(contrib, count, Lacc);
                 S.kernel_launches++;
             }
+            MCPT_CUDA(cudaGetLastError());
+            MCPT_CUDA(cudaEventRecord(scene->ev[3], st));
             if (!last) MCPT_CUDA(cudaMemcpyAsync((void*)h_count, d_count, 4, cudaMemcpyDeviceToHost, st));
             MCPT_CUDA(cudaStreamSynchronize(st));
             float ms = 0.f;
@@ -877,6 +990,7 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
             S.bounces++;
             if (last) break;
             count = *h_count;
+            S.rays_closest += (uint64_t)count;
         }
         k_accumulate<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(Lacc, (int)npix, b, image, pass == 0);
         S.kernel_launches++;
@@ -893,7 +1007,6 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     cudaEventElapsedTime(&ms_total, scene->ev[0], scene->ev[1]);
     S.passes = (uint32_t)pass;
     S.vertices = h_counters[CNT_VERTICES];
-    S.rays_closest += h_counters[CNT_RAYS];
     S.rays_shadow = h_counters[CNT_SHADOW];
     S.rays_light = h_counters[CNT_LIGHTRAYS];
     S.primary_hits = h_counters[CNT_PRIMARY_HITS];

@@ -222,4 +222,119 @@ __device__ __forceinline__ HitD trace_exact(const float4* __restrict__ nodes, co
     return best;
 }
 
+// ---- ray-stream tracing with dynamic refill ---------------------------------------------------------------
+// The wavefront trace kernels (k_extend: closest hit, k_shadow: any hit) run persistent warps over a compact
+// array of rays.  A lane keeps its ray until the traversal ends; when fewer than kRefill lanes of the warp are
+// still traversing, the idle lanes pull the next rays of the stream (one atomicAdd per refill, ballot/popc
+// ranks) instead of waiting for the slowest ray of their original group of 32 -- incoherent rays through a
+// deep BVH differ by an order of magnitude in node visits.  Results are written by ray index, so the order in
+// which rays finish is irrelevant.
+//   load(idx, o, d, exclude, tmax, init_prim)   fetches ray idx
+//   store(idx, hit)                             consumes its result
+constexpr int kRefill = 20;
+
+template <bool ANY, class Load, class Store>
+__device__ __forceinline__ void trace_stream(const float4* __restrict__ nodes, const float4* __restrict__ tris, float tmin, int n,
+                                             int* counter, int* stack_sm, int stack_stride, Load load, Store store)
+{
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    TStack st;
+    st.init(stack_sm, stack_stride);
+    bool active = false, more = true;
+    int idx = -1, exclude = -1, node = 0;
+    f3 o = mk<float>(0.f, 0.f, 0.f), d = mk<float>(0.f, 0.f, 1.f), id = d, ood = o;
+    Hit best;
+    best.prim = -1; best.b = best.g = 0.f; best.t = 0.f;
+    for (;;) {
+        const unsigned act = __ballot_sync(full, active);
+        if (more && __popc(act) < kRefill) {
+            const unsigned idle = ~act;
+            int base = 0;
+            if (lane == 0) base = atomicAdd(counter, __popc(idle));
+            base = __shfl_sync(full, base, 0);
+            if (!active) {
+                const int my = base + __popc(idle & ((1u << lane) - 1u));
+                if (my < n) {
+                    float tmax;
+                    int init_prim;
+                    idx = my;
+                    load(idx, o, d, exclude, tmax, init_prim);
+                    id = mk<float>(safe_rcp(d.x), safe_rcp(d.y), safe_rcp(d.z));
+                    ood = mk<float>(o.x * id.x, o.y * id.y, o.z * id.z);
+                    best.prim = init_prim; best.b = 0.f; best.g = 0.f; best.t = tmax;
+                    st.sp = 0;
+                    node = 0;
+                    active = true;
+                }
+            }
+            if (base + __popc(idle) >= n) more = false;
+        }
+        if (!__any_sync(full, active)) {
+            if (!more) break;
+            continue;
+        }
+        for (;;) {
+            if (active) {
+                bool done = false;
+                // descend through inner nodes until a leaf comes up (or the stack runs dry)
+                while (node >= 0) {
+                    const float4 n0 = __ldg(nodes + 4 * node + 0);
+                    const float4 n1 = __ldg(nodes + 4 * node + 1);
+                    const float4 n2 = __ldg(nodes + 4 * node + 2);
+                    const float4 n3 = __ldg(nodes + 4 * node + 3);
+                    float ax = n0.x * id.x - ood.x, bx = n0.y * id.x - ood.x;
+                    float ay = n0.z * id.y - ood.y, by = n0.w * id.y - ood.y;
+                    float az = n2.x * id.z - ood.z, bz = n2.y * id.z - ood.z;
+                    const float t0n = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.f));
+                    const float t0f = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best.t));
+                    ax = n1.x * id.x - ood.x; bx = n1.y * id.x - ood.x;
+                    ay = n1.z * id.y - ood.y; by = n1.w * id.y - ood.y;
+                    az = n2.z * id.z - ood.z; bz = n2.w * id.z - ood.z;
+                    const float t1n = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.f));
+                    const float t1f = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best.t));
+                    const bool h0 = t0n <= t0f, h1 = t1n <= t1f;
+                    const int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
+                    if (h0 && h1) {
+                        const bool swap = t1n < t0n;
+                        st.push(swap ? c0 : c1);
+                        node = swap ? c1 : c0;
+                    } else if (h0) node = c0;
+                    else if (h1) node = c1;
+                    else if (st.sp == 0) { done = true; break; }
+                    else node = st.pop();
+                }
+                if (!done) {
+                    const int code = ~node;
+                    const int first = code >> 3, cnt = (code & 7) + 1;
+                    for (int i = 0; i < cnt; i++) {
+                        const float4 v0 = __ldg(tris + 3 * (first + i) + 0);
+                        const int prim = __float_as_int(v0.w);
+                        if (prim == exclude) continue;
+                        const float4 v1 = __ldg(tris + 3 * (first + i) + 1);
+                        const float4 v2 = __ldg(tris + 3 * (first + i) + 2);
+                        float be, ga, tt;
+                        if (tri_test_fast(o, d, to_f3(v0), to_f3(v1), to_f3(v2), tmin, &be, &ga, &tt)) {
+                            if (tt < best.t || (tt == best.t && (unsigned)prim < (unsigned)best.prim)) {
+                                best.prim = prim; best.b = be; best.g = ga; best.t = tt;
+                                if (ANY) { done = true; break; }
+                            }
+                        }
+                    }
+                    if (!done) {
+                        if (st.sp == 0) done = true;
+                        else node = st.pop();
+                    }
+                }
+                if (done) {
+                    store(idx, best);
+                    active = false;
+                }
+            }
+            const unsigned m = __ballot_sync(full, active);
+            if (m == 0u || (more && __popc(m) < kRefill)) break;
+        }
+    }
+}
+
 }  // namespace mcpt

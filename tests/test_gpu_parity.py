@@ -194,3 +194,54 @@ def test_error_paths(arrays_of):
     assert e.value.code == -1
     with pytest.raises(api.McptError):
         api.Scene(a, device=1000)
+
+
+@pytest.fixture(scope="module")
+def soup():
+    """BASELINE.json configs[3] family: random triangle soup (BVH-traversal stress), 300 k triangles here so the
+    oracle's exhaustive search over a ray subset stays in seconds."""
+    from monte_carlo_path_tracing_b200 import scenes
+    import oracle
+    a = scenes.triangle_soup(300_000, 64, seed=77, width=256, height=256)
+    s = api.Scene(a, 0)
+    o = oracle.OracleLib(a)
+    yield a, s, o
+    s.close()
+
+
+def test_soup_closest_hit_bit_exact(soup):
+    """Deep BVH (depth > 20), 3e5 leaves: FP64 traversal == exhaustive search, ids and (beta, gamma, t) bits."""
+    a, s, o = soup
+    info = s.bvh_info()
+    assert info["max_depth"] >= 16 and info["max_depth"] < 64
+    rng = np.random.default_rng(5)
+    n = 400
+    ro = np.tile(np.array(a.camera.eye, np.float64), (n, 1))
+    tgt = a.positions.reshape(-1, 3)[rng.integers(0, a.positions.size // 3, n)].astype(np.float64)
+    rd = util.unit(tgt - ro + rng.normal(size=(n, 3)) * 0.05)
+    p1, b1 = s.closest(ro, rd, None, False, api.FP64)
+    p0, b0 = o.closest(ro, rd, None, 2)
+    assert np.array_equal(p1, p0) and np.array_equal(b1, b0)
+    assert (p0 >= 0).mean() > 0.3
+    # rays leaving surfaces, origin triangle excluded by id (Myobj.cpp:417), scene and light-only searches
+    ro, rd, ex = util.surface_rays(a, 300, 6)
+    for light_only, mode in ((False, 2), (True, 3)):
+        p1, b1 = s.closest(ro, rd, ex, light_only, api.FP64)
+        p0, b0 = o.closest(ro, rd, ex, mode)
+        assert np.array_equal(p1, p0) and np.array_equal(b1, b0)
+    # the renderer's FP32 traversal: same ids except grazing edge hits
+    p32, _ = s.closest(ro, rd, ex, False, api.FP32)
+    p64, _ = s.closest(ro, rd, ex, False, api.FP64)
+    assert np.mean(p32 != p64) < 0.01
+
+
+def test_soup_render_properties(soup):
+    a, s, _ = soup
+    cam = a.camera
+    x, st = s.render(cam, api.NEE_UNIFORM, 8, max_depth=5, seed=3)
+    y, _ = s.render(cam, api.NEE_UNIFORM, 8, max_depth=5, seed=3)
+    assert np.array_equal(x, y) and np.isfinite(x).all() and x.max() > 0
+    lo, _ = s.render(cam, api.NEE_UNIFORM, 4, max_depth=5, seed=3, spp_offset=0, spp_total=8)
+    hi, _ = s.render(cam, api.NEE_UNIFORM, 4, max_depth=5, seed=3, spp_offset=4, spp_total=8)
+    assert np.allclose(lo + hi, x, rtol=1e-5, atol=1e-6)
+    assert st["primary_hits"] > 0.3 * cam.width * cam.height
