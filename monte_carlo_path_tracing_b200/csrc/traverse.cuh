@@ -275,10 +275,12 @@ __device__ __forceinline__ void trace_stream(const float4* __restrict__ nodes, c
             continue;
         }
         for (;;) {
-            if (active) {
-                bool done = false;
-                // descend through inner nodes until a leaf comes up (or the stack runs dry)
-                while (node >= 0) {
+            // phase 1 (warp-synchronous "while-while", Aila & Laine): every lane with an inner node takes one step per
+            // trip; the vote at the loop head keeps the warp converged -- a per-lane `while (node >= 0)` lets the lanes
+            // drift apart for good (measured 4.9 of 32 threads per instruction on the 1 M-triangle soup)
+            bool done = false;
+            while (__any_sync(full, active && !done && node >= 0)) {
+                if (active && !done && node >= 0) {
                     const float4 n0 = __ldg(nodes + 4 * node + 0);
                     const float4 n1 = __ldg(nodes + 4 * node + 1);
                     const float4 n2 = __ldg(nodes + 4 * node + 2);
@@ -295,41 +297,40 @@ __device__ __forceinline__ void trace_stream(const float4* __restrict__ nodes, c
                     const float t1f = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best.t));
                     const bool h0 = t0n <= t0f, h1 = t1n <= t1f;
                     const int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
-                    if (h0 && h1) {
-                        const bool swap = t1n < t0n;
-                        st.push(swap ? c0 : c1);
-                        node = swap ? c1 : c0;
-                    } else if (h0) node = c0;
-                    else if (h1) node = c1;
-                    else if (st.sp == 0) { done = true; break; }
+                    const bool swap = t1n < t0n;
+                    const int near_c = (h0 && h1) ? (swap ? c1 : c0) : (h0 ? c0 : c1);
+                    if (h0 && h1) st.push(swap ? c0 : c1);
+                    if (h0 || h1) node = near_c;
+                    else if (st.sp == 0) done = true;
                     else node = st.pop();
                 }
-                if (!done) {
-                    const int code = ~node;
-                    const int first = code >> 3, cnt = (code & 7) + 1;
-                    for (int i = 0; i < cnt; i++) {
-                        const float4 v0 = __ldg(tris + 3 * (first + i) + 0);
-                        const int prim = __float_as_int(v0.w);
-                        if (prim == exclude) continue;
-                        const float4 v1 = __ldg(tris + 3 * (first + i) + 1);
-                        const float4 v2 = __ldg(tris + 3 * (first + i) + 2);
-                        float be, ga, tt;
-                        if (tri_test_fast(o, d, to_f3(v0), to_f3(v1), to_f3(v2), tmin, &be, &ga, &tt)) {
-                            if (tt < best.t || (tt == best.t && (unsigned)prim < (unsigned)best.prim)) {
-                                best.prim = prim; best.b = be; best.g = ga; best.t = tt;
-                                if (ANY) { done = true; break; }
-                            }
+            }
+            // phase 2: every lane that arrived at a leaf tests its triangles, then pops
+            if (active && !done) {
+                const int code = ~node;
+                const int first = code >> 3, cnt = (code & 7) + 1;
+                for (int i = 0; i < cnt; i++) {
+                    const float4 v0 = __ldg(tris + 3 * (first + i) + 0);
+                    const int prim = __float_as_int(v0.w);
+                    if (prim == exclude) continue;
+                    const float4 v1 = __ldg(tris + 3 * (first + i) + 1);
+                    const float4 v2 = __ldg(tris + 3 * (first + i) + 2);
+                    float be, ga, tt;
+                    if (tri_test_fast(o, d, to_f3(v0), to_f3(v1), to_f3(v2), tmin, &be, &ga, &tt)) {
+                        if (tt < best.t || (tt == best.t && (unsigned)prim < (unsigned)best.prim)) {
+                            best.prim = prim; best.b = be; best.g = ga; best.t = tt;
+                            if (ANY) { done = true; break; }
                         }
                     }
-                    if (!done) {
-                        if (st.sp == 0) done = true;
-                        else node = st.pop();
-                    }
                 }
-                if (done) {
-                    store(idx, best);
-                    active = false;
+                if (!done) {
+                    if (st.sp == 0) done = true;
+                    else node = st.pop();
                 }
+            }
+            if (active && done) {
+                store(idx, best);
+                active = false;
             }
             const unsigned m = __ballot_sync(full, active);
             if (m == 0u || (more && __popc(m) < kRefill)) break;
