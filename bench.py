@@ -42,8 +42,11 @@ WORKLOADS = {
                     max_depth=5),
 }
 STRAT = {"NEE_SPHERICAL": 0, "BRDF_ONLY": 1, "MIS": 2, "NEE_UNIFORM": 3}
-# compulsory wavefront state traffic per sample-bounce (rays, hit, path state, queue words)
-ALGO_BYTES_PER_VERTEX = {"MIS": 384, "NEE_UNIFORM": 256, "NEE_SPHERICAL": 256, "BRDF_ONLY": 160}
+# Compulsory wavefront state traffic per sample-bounce of the split pipeline: k_extend reads the
+# ray (32 B) and writes the hit (16); k_shade reads ray + throughput (48, +8 tree node for MIS) + hit (16) and stages
+# ~1 child (48, +8); k_gather moves it (2 x 48); the slot accumulator is read and written (32); NEE adds one visibility
+# record written and read (2 x 56); MIS stages / moves / extends a second child and writes its contribution word.
+ALGO_BYTES_PER_VERTEX = {"MIS": 576, "NEE_UNIFORM": 400, "NEE_SPHERICAL": 400, "BRDF_ONLY": 288}
 
 
 def measured_peaks():
@@ -264,18 +267,21 @@ def run_ours(args, wl_name, wl):
     clocks = sampler.stop() if sampler else None
 
     # ---- e2e through the host-buffer C ABI: scene upload (pinned H2D) + render + film D2H, every step
-    host_out = np.zeros((cam.height, cam.width, 3), np.float32)
     scene.upload(); scene.render(cam, strategy, min(S, 2), **kw)
     sync()
+    pinned = torch.empty(npix * 3, dtype=torch.float32).pin_memory()
     t0 = time.perf_counter()
     for k in range(args.steps):
-        scene.upload()
-        img, _ = scene.render(cam, strategy, S, spp_offset=(k * world + rank) * S, spp_total=S * world, **kw)
-        if world > 1:
-            film.copy_(torch.from_numpy(img.reshape(-1)), non_blocking=False)
+        scene.upload()  # pinned H2D of the whole scene blob (geometry, BVHs, lights, materials)
+        if world == 1:
+            img, _ = scene.render(cam, strategy, S, spp_offset=(k * world + rank) * S, spp_total=S * world, **kw)  # film D2H inside
+        else:
+            # N ranks: the public multi-GPU path -- device film per rank, one NCCL sum, rank 0 reads the film back
+            scene.render_device(cam, strategy, S, film.data_ptr(), stream=stream, spp_offset=(k * world + rank) * S,
+                                spp_total=S * world, **kw)
             mdist.reduce_film(film, 0)
             if rank == 0:
-                host_out[...] = film.cpu().numpy().reshape(host_out.shape)
+                pinned.copy_(film, non_blocking=False)
     sync()
     e2e_s = torch.tensor([time.perf_counter() - t0], device="cuda")
     if world > 1:
@@ -301,7 +307,7 @@ def run_ours(args, wl_name, wl):
             "clocks": clocks,
             "e2e": {"value": samples / e2e_s / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": scene.device_bytes(),
                     "d2h_bytes_per_step": npix * 12},
-            "roofline": {"bound": "hbm", "kernel": "k_bounce<%s>" % wl["strategy"], "achieved": achieved, "peak": peaks["hbm_gbs"],
+            "roofline": {"bound": "hbm", "kernel": "bounce pipeline k_shade<%s> + k_extend + k_shadow + k_gather" % wl["strategy"], "achieved": achieved, "peak": peaks["hbm_gbs"],
                          "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": which,
                          "algorithmic_bytes_per_sample_bounce": algo_b,
                          "sample_bounces_per_launch": tot["vertices"] / launches_bounce,
