@@ -33,13 +33,13 @@ from monte_carlo_path_tracing_b200 import scenes  # noqa: E402
 
 WORKLOADS = {
     # name: (scene generator kwargs, strategy name, max_depth)
-    "veach-mis": dict(scene="veach-mis", kw=dict(width=1280, height=720), strategy="MIS", max_depth=0),
-    "cornell-box": dict(scene="cornell-box", kw=dict(width=512, height=512), strategy="NEE_UNIFORM", max_depth=5),
+    "veach-mis": dict(scene="veach-mis", kw=dict(width=1280, height=720), strategy="MIS", max_depth=0, spp=64),
+    "cornell-box": dict(scene="cornell-box", kw=dict(width=512, height=512), strategy="NEE_UNIFORM", max_depth=5, spp=256),
     # configs[2]: stand-in for the unavailable bathroom scene: generated interior, ~185 k triangles
-    "interior": dict(scene="interior", kw=dict(width=1280, height=720), strategy="MIS", max_depth=0),
+    "interior": dict(scene="interior", kw=dict(width=1280, height=720), strategy="MIS", max_depth=0, spp=32),
     # configs[3]: 1 M random triangles + 64 emissive triangles, 1024x1024, uniform-area NEE (BVH traversal stress)
     "soup-1m": dict(scene="soup", kw=dict(num_tris=1_000_000, num_lights=64, width=1024, height=1024), strategy="NEE_UNIFORM",
-                    max_depth=5),
+                    max_depth=5, spp=64),
 }
 STRAT = {"NEE_SPHERICAL": 0, "BRDF_ONLY": 1, "MIS": 2, "NEE_UNIFORM": 3}
 # Compulsory wavefront state traffic per sample-bounce of the split pipeline: k_extend reads the
@@ -338,13 +338,15 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="veach-mis", choices=sorted(WORKLOADS))
-    ap.add_argument("--spp-per-step", type=int, default=16)
+    ap.add_argument("--spp-per-step", type=int, default=0, help="samples per pixel per GPU per step (0 = the workload's default)")
     ap.add_argument("--batch-spp", type=int, default=0)
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
+    if args.spp_per_step <= 0:
+        args.spp_per_step = wl["spp"]
     if args.impl == "reference":
         run_reference(args, args.workload, wl)
     else:

@@ -29,7 +29,7 @@ namespace {
 
 constexpr int kBlk = 128;             // threads per block (4 warps; a warp owns one 32-ray chunk at a time)
 constexpr unsigned kFull = 0xffffffffu;
-constexpr size_t kTargetSlots = 16u << 20;  // auto batch: ~16M path slots in flight per pass
+constexpr size_t kTargetSlots = 64u << 20;  // auto batch: up to 64 Mi path slots in flight per pass (memory permitting)
 
 enum { CNT_VERTICES = 0, CNT_RAYS, CNT_SHADOW, CNT_LIGHTRAYS, CNT_PRIMARY_HITS, CNT_OVERFLOW, CNT_N };
 
@@ -191,7 +191,7 @@ __device__ __forceinline__ void warp_light_select(const DScene& s, bool need, f3
 // atomic per warp: commutative, so the result is deterministic).  k_gather then turns group sums + counts into
 // exact offsets and moves the chunk windows into the dense queue, preserving input order -- which keeps all
 // rays of one path-tree adjacent (k_runsum) without any warp ever waiting for another.
-constexpr int kGroup = 1024;  // chunks per k_gather block
+constexpr int kGroup = 256;   // chunks per k_gather block (one per thread)
 
 __global__ void __launch_bounds__(256) k_gather(const Queue stage, const Queue out, const int* __restrict__ counts,
                                                 const int* __restrict__ groupsum, int nch, int stride, int capacity, int tree,
@@ -211,12 +211,9 @@ __global__ void __launch_bounds__(256) k_gather(const Queue stage, const Queue o
 #pragma unroll
     for (int w = 0; w < 8; w++) gbase += s_red[w];
     __syncthreads();
-    // 2. exclusive scan of this group's chunk counts (4 consecutive chunks per thread)
-    const int c0 = g * kGroup + 4 * tid;
-    int c[4];
-#pragma unroll
-    for (int k = 0; k < 4; k++) c[k] = (c0 + k < nch) ? counts[c0 + k] : 0;
-    const int tsum = c[0] + c[1] + c[2] + c[3];
+    // 2. exclusive scan of this group's chunk counts (one chunk per thread)
+    const int c0 = g * kGroup + tid;
+    const int tsum = (c0 < nch) ? counts[c0] : 0;
     int incl = tsum;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -228,9 +225,7 @@ __global__ void __launch_bounds__(256) k_gather(const Queue stage, const Queue o
     int wbase = 0, gtotal = 0;
 #pragma unroll
     for (int w = 0; w < 8; w++) { if (w < warp) wbase += s_red[w]; gtotal += s_red[w]; }
-    int run = gbase + wbase + incl - tsum;
-#pragma unroll
-    for (int k = 0; k < 4; k++) { s_base[4 * tid + k] = run; run += c[k]; }
+    s_base[tid] = gbase + wbase + incl - tsum;
     __syncthreads();
     if (g == gridDim.x - 1 && tid == 0) {
         const int total = gbase + gtotal;
@@ -810,7 +805,17 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     const bool tree = prm->strategy == MCPT_MIS;
     const int spp_total = prm->spp_total > 0 ? prm->spp_total : prm->spp;
     const float p_rr = prm->p_rr > 0.f ? prm->p_rr : 0.6f;
-    int batch = prm->batch_spp > 0 ? prm->batch_spp : (int)std::max<size_t>(1, kTargetSlots / npix);
+    size_t target = kTargetSlots;
+    {
+        // keep the workspace below half of the device memory that is free (or already ours)
+        size_t free_b = 0, total_b = 0;
+        MCPT_CUDA(cudaSetDevice(scene->device));
+        if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
+            const size_t per_slot = tree ? 640 : 208;  // bytes of queues + staging + hit + accumulators per path slot
+            target = std::min(target, std::max<size_t>(npix, (free_b + scene->ws.bytes) / 2 / per_slot));
+        } else cudaGetLastError();
+    }
+    int batch = prm->batch_spp > 0 ? prm->batch_spp : (int)std::max<size_t>(1, target / npix);
     batch = std::min(batch, prm->spp);
     const size_t slots = npix * (size_t)batch;
     if (slots > (1u << 30)) throw Error(MCPT_ERR_INVALID, "batch_spp * pixels too large");

@@ -1,3 +1,10 @@
-python bench.py --steps 1 --warmup 1 --no-cpu-baseline > /dev/null 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r1k_launches_veach.csv python bench.py --steps 1 --warmup 1 --no-cpu-baseline > /dev/null 2>&1
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r1k_launches_cornell.csv python bench.py --steps 1 --warmup 1 --no-cpu-baseline --workload cornell-box --spp-per-step 64 > /dev/null 2>&1
-ncu --set full --clock-control none --import-source on -k regex:"k_shade|k_lightprep|k_extend" --launch-skip 0 --launch-count 5 -o gpurun_out/r1k_veach_head -f python bench.py --steps 1 --warmup 1 --no-cpu-baseline > /dev/null 2>&1
+python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+for cfg in "veach-mis 16" "veach-mis 64" "interior 8" "interior 32" "cornell-box 64" "cornell-box 256" "soup-1m 16" "soup-1m 64"; do
+  set -- $cfg
+  python bench.py --steps 3 --warmup 3 --workload $1 --spp-per-step $2 --no-cpu-baseline > gpurun_out/tmp.json 2> gpurun_out/tmp.err || tail -3 gpurun_out/tmp.err
+  python - <<PY
+import json
+j=json.loads(open("gpurun_out/tmp.json").read().strip().splitlines()[-1])
+print("$1 spp/step $2: value %.1f Msamples/s  ms/step %.2f  e2e %.1f  Msb/s %.0f launches %d"%(j["value"],j["ms_per_step"],j["e2e"]["value"],j["extra"]["Msample_bounces_per_s"],j["gpu_launches"]))
+PY
+done
