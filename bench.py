@@ -69,6 +69,30 @@ class ClockSampler:
         self.thread = threading.Thread(target=self._run, daemon=True)
 
     def _run(self):
+        # NVML in-process (nvidia_ml_py): one query costs microseconds.  Spawning nvidia-smi every 200 ms inside the
+        # timed region measurably slowed the host-driven bounce loop (driver lock + a busy host core).
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.gpu)
+            mx = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+            bits = [(pynvml.nvmlClocksEventReasonHwSlowdown, 0), (pynvml.nvmlClocksEventReasonHwThermalSlowdown, 1),
+                    (pynvml.nvmlClocksEventReasonSwThermalSlowdown, 2), (pynvml.nvmlClocksEventReasonSwPowerCap, 3)]
+            while not self.stop_flag:
+                sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+                try:
+                    r = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                row = [str(sm), str(mx)] + ["Not Active"] * 4
+                for bit, k in bits:
+                    if r & bit:
+                        row[2 + k] = "Active"
+                self.rows.append(row)
+                time.sleep(0.05)
+            return
+        except Exception:
+            pass
         while not self.stop_flag:
             try:
                 o = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],

@@ -12,7 +12,7 @@ void set_last_error(const std::string& msg) { g_last_error = msg; }
 
 namespace {
 struct BlobLayout {
-    size_t off_nodes, off_tris, off_lnodes, off_ltris, off_pverts, off_pnorms, off_mats, off_lights, off_lsoa, off_lng64, off_larea64,
+    size_t off_nodes, off_nodes4, off_tris, off_lnodes, off_ltris, off_pverts, off_pnorms, off_mats, off_lights, off_lsoa, off_lng64, off_larea64,
         off_crad64, off_class_begin, off_class_cdf, off_tri_cdf, total;
 };
 size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -120,6 +120,8 @@ int mcpt_scene_create(const McptSceneDesc* desc, int device, McptScene** out)
         std::vector<int32_t> lp(s->light_prim);
         std::sort(lp.begin(), lp.end());
         s->lbvh = build_bvh(s->positions.data(), lp.data(), lp.size());
+        if (s->bvh.max_depth4 * 3 + 1 > (uint32_t)kBvhStackDepth)
+            throw Error(MCPT_ERR_INVALID, "scene BVH is too deep for the traversal stack (degenerate geometry?)");
         s->extent = std::max({s->bvh.hi[0] - s->bvh.lo[0], s->bvh.hi[1] - s->bvh.lo[1], s->bvh.hi[2] - s->bvh.lo[2], 1e-30f});
 
         // pack the blob
@@ -127,6 +129,7 @@ int mcpt_scene_create(const McptSceneDesc* desc, int device, McptScene** out)
         size_t o = 0;
         auto place = [&](size_t bytes) { size_t at = o; o = align_up(o + std::max<size_t>(bytes, 16)); return at; };
         B.off_nodes = place(s->bvh.nodes.size() * sizeof(BvhNode));
+        B.off_nodes4 = place(s->bvh.nodes4.size() * sizeof(f4));
         B.off_tris = place(s->bvh.tris.size() * sizeof(f4));
         B.off_lnodes = place(s->lbvh.nodes.size() * sizeof(BvhNode));
         B.off_ltris = place(s->lbvh.tris.size() * sizeof(f4));
@@ -148,6 +151,7 @@ int mcpt_scene_create(const McptSceneDesc* desc, int device, McptScene** out)
         std::memset(s->h_blob, 0, B.total);
         char* hb = (char*)s->h_blob;
         std::memcpy(hb + B.off_nodes, s->bvh.nodes.data(), s->bvh.nodes.size() * sizeof(BvhNode));
+        std::memcpy(hb + B.off_nodes4, s->bvh.nodes4.data(), s->bvh.nodes4.size() * sizeof(f4));
         std::memcpy(hb + B.off_tris, s->bvh.tris.data(), s->bvh.tris.size() * sizeof(f4));
         std::memcpy(hb + B.off_lnodes, s->lbvh.nodes.data(), s->lbvh.nodes.size() * sizeof(BvhNode));
         std::memcpy(hb + B.off_ltris, s->lbvh.tris.data(), s->lbvh.tris.size() * sizeof(f4));
@@ -221,6 +225,7 @@ int mcpt_scene_create(const McptSceneDesc* desc, int device, McptScene** out)
         char* db = (char*)s->d_blob;
         DScene& d = s->d;
         d.nodes = (const float4*)(db + B.off_nodes); d.tris = (const float4*)(db + B.off_tris);
+        d.nodes4 = (const float4*)(db + B.off_nodes4);
         d.lnodes = (const float4*)(db + B.off_lnodes); d.ltris = (const float4*)(db + B.off_ltris);
         d.pverts = (const float4*)(db + B.off_pverts); d.pnorms = (const float4*)(db + B.off_pnorms);
         d.mats = (const float4*)(db + B.off_mats); d.lights = (const float4*)(db + B.off_lights);
@@ -324,6 +329,47 @@ int mcpt_host_bvh_check(const McptSceneDesc* desc, int lights_only, uint32_t out
             }
         }
         for (int32_t id : ids) if (seen[id] != 1) errors++;
+        // the 4-wide collapse of the same tree (bvh.h, nodes4): same leaves, same containment
+        {
+            std::vector<uint32_t> seen4(desc->num_prims, 0);
+            stack.push_back(Item{0, {-inf, -inf, -inf}, {inf, inf, inf}});
+            while (!stack.empty()) {
+                Item it = stack.back();
+                stack.pop_back();
+                if (it.code >= 0) {
+                    if ((size_t)it.code * 7 + 6 >= b.nodes4.size()) { errors++; continue; }
+                    const f4* q = &b.nodes4[(size_t)it.code * 7];
+                    for (int k = 0; k < 4; k++) {
+                        auto comp = [k](const f4& v) { return k == 0 ? v.x : k == 1 ? v.y : k == 2 ? v.z : v.w; };
+                        Item c;
+                        float cf = comp(q[6]);
+                        std::memcpy(&c.code, &cf, 4);
+                        for (int a = 0; a < 3; a++) { c.lo[a] = comp(q[2 * a]); c.hi[a] = comp(q[2 * a + 1]); }
+                        if (c.lo[0] > c.hi[0]) continue;  // unused slot
+                        for (int a = 0; a < 3; a++)
+                            if (c.lo[a] < it.lo[a] - 1e-3f * std::fabs(it.lo[a]) - 1e-6f || c.hi[a] > it.hi[a] + 1e-3f * std::fabs(it.hi[a]) + 1e-6f) errors++;
+                        stack.push_back(c);
+                    }
+                } else {
+                    int code = ~it.code, first = code >> 3, cnt = (code & 7) + 1;
+                    for (int i = 0; i < cnt; i++) {
+                        if ((size_t)(first + i) * 3 + 2 >= b.tris.size()) { errors++; continue; }
+                        int32_t prim;
+                        std::memcpy(&prim, &b.tris[3 * (first + i)].w, 4);
+                        if (prim < 0 || (uint32_t)prim >= desc->num_prims) { errors++; continue; }
+                        seen4[prim]++;
+                        for (int v = 0; v < 3; v++) {
+                            const f4& p = b.tris[3 * (first + i) + v];
+                            float c[3] = {p.x, p.y, p.z};
+                            for (int a = 0; a < 3; a++)
+                                if (c[a] < it.lo[a] || c[a] > it.hi[a]) errors++;
+                        }
+                    }
+                }
+            }
+            for (int32_t id : ids) if (seen4[id] != 1) errors++;
+            if (b.max_depth4 > b.max_depth + 1 || b.max_depth4 * 3 + 1 > (uint32_t)kBvhStackDepth) errors++;
+        }
         uint32_t total = 0;
         for (uint32_t v : seen) total += v;
         if (total != ids.size()) errors++;

@@ -13,6 +13,13 @@
 //                     child < 0 leaf: ~child = (first_tri << 3) | (count - 1), count in 1..8
 //   triangle (48 B): v0.xyz | prim id bits, v1.xyz | 0, v2.xyz | 0  in leaf order
 // An empty child has an inverted box (lo = +inf, hi = -inf) and is never entered.
+//
+// nodes4: the same tree collapsed to 4-wide nodes for the renderer's stream traversal (traverse.cuh,
+// trace_stream): the child with the largest surface area is replaced by its own two children until the node has
+// four (or only leaves are left).  112 B per node, seven 16-byte vectors, child k in component k:
+//   q0 = lo.x[4], q1 = hi.x[4], q2 = lo.y[4], q3 = hi.y[4], q4 = lo.z[4], q5 = hi.z[4], q6 = child[4] (int bits,
+//   same inner / leaf encoding as above; unused slots hold kBvhNoChild and an inverted box).  Half the levels of the binary tree
+//   means half as many dependent node fetches per ray, which is what bounds incoherent rays in a deep BVH.
 #pragma once
 #include <cstdint>
 #include <vector>
@@ -26,13 +33,15 @@ static_assert(sizeof(BvhNode) == 64, "node must be 64 bytes");
 
 struct Bvh {
     std::vector<BvhNode> nodes;  // nodes[0] is the root (always an inner node)
+    std::vector<f4> nodes4;      // 7 per 4-wide node; nodes4[0..6] is the root
     std::vector<f4> tris;        // 3 per triangle, leaf order
-    uint32_t num_leaves = 0, max_depth = 0;
+    uint32_t num_leaves = 0, max_depth = 0, max_depth4 = 0;
     double sah_cost = 0;
     float lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};  // bounds of everything inside
 };
 
 constexpr int kBvhMaxLeaf = 4;
+constexpr int32_t kBvhNoChild = INT32_MIN;  // child word of an unused nodes4 slot (its box is inverted, too)
 constexpr int kBvhStackDepth = 64;  // traversal stack entries; the builder falls back to median splits to stay below
 
 // positions: [P][3][3] floats; prims: the subset to build over (ids kept as triangle payload).

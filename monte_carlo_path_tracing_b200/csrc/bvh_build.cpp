@@ -119,6 +119,52 @@ inline void pad_box(const Box& b, float tiny, float lo[3], float hi[3])
     }
 }
 
+
+// Collapse the binary tree into 4-wide nodes (bvh.h, nodes4), depth-first so a subtree stays contiguous.
+void emit_wide(const std::vector<TmpNode>& tmp, int32_t root, float tiny, Bvh& out)
+{
+    const float inf = std::numeric_limits<float>::infinity();
+    auto leaf_code = [](const TmpNode& t) { return (int32_t)~((t.first << 3) | (t.count - 1)); };
+    struct Item { int32_t tmp_idx, out_idx; uint32_t depth; };
+    std::vector<Item> todo;
+    auto alloc = [&]() { int32_t i = (int32_t)(out.nodes4.size() / 7); out.nodes4.resize(out.nodes4.size() + 7, f4{0, 0, 0, 0}); return i; };
+    todo.push_back({root, alloc(), 1});
+    while (!todo.empty()) {
+        const Item it = todo.back();
+        todo.pop_back();
+        out.max_depth4 = std::max(out.max_depth4, it.depth);
+        int32_t kids[4];
+        int nk = 0;
+        if (tmp[it.tmp_idx].left < 0) kids[nk++] = it.tmp_idx;  // lone leaf root
+        else { kids[nk++] = tmp[it.tmp_idx].left; kids[nk++] = tmp[it.tmp_idx].right; }
+        while (nk < 4) {
+            int best = -1;
+            float best_area = -1.f;
+            for (int k = 0; k < nk; k++)
+                if (tmp[kids[k]].left >= 0 && tmp[kids[k]].box.half_area() > best_area) { best = k; best_area = tmp[kids[k]].box.half_area(); }
+            if (best < 0) break;
+            const int32_t open = kids[best];
+            kids[best] = tmp[open].left;
+            kids[nk++] = tmp[open].right;
+        }
+        float q[7][4];
+        for (int k = 0; k < 4; k++) {
+            for (int a = 0; a < 3; a++) { q[2 * a][k] = inf; q[2 * a + 1][k] = -inf; }
+            int32_t code = kBvhNoChild;
+            if (k < nk) {
+                const TmpNode& c = tmp[kids[k]];
+                float lo[3], hi[3];
+                pad_box(c.box, tiny, lo, hi);
+                for (int a = 0; a < 3; a++) { q[2 * a][k] = lo[a]; q[2 * a + 1][k] = hi[a]; }
+                if (c.left < 0) code = leaf_code(c);
+                else { code = alloc(); todo.push_back({kids[k], code, it.depth + 1}); }
+            }
+            std::memcpy(&q[6][k], &code, 4);
+        }
+        for (int r = 0; r < 7; r++) out.nodes4[(size_t)it.out_idx * 7 + r] = f4{q[r][0], q[r][1], q[r][2], q[r][3]};
+    }
+}
+
 }  // namespace
 
 Bvh build_bvh(const float* positions, const int32_t* prims, size_t count)
@@ -143,6 +189,8 @@ Bvh build_bvh(const float* positions, const int32_t* prims, size_t count)
         n.c0 = n.c1 = ~0;
         out.nodes.push_back(n);
         for (int k = 0; k < 3; k++) out.tris.push_back(f4{0, 0, 0, 0});
+        for (int k = 0; k < 6; k++) out.nodes4.push_back(k % 2 ? f4{-inf, -inf, -inf, -inf} : f4{inf, inf, inf, inf});
+        { float nc; int32_t code = kBvhNoChild; std::memcpy(&nc, &code, 4); out.nodes4.push_back(f4{nc, nc, nc, nc}); }
         return out;
     }
     for (int a = 0; a < 3; a++) { out.lo[a] = all.lo[a]; out.hi[a] = all.hi[a]; }
@@ -190,6 +238,7 @@ Bvh build_bvh(const float* positions, const int32_t* prims, size_t count)
         out.nodes.push_back(n);
         out.num_leaves = 1;
         out.sah_cost = kCostTrav + B.tmp[root].count * kCostTri;
+        emit_wide(B.tmp, root, tiny, out);
         return out;
     }
     out.nodes.resize(n_inner);
@@ -206,6 +255,7 @@ Bvh build_bvh(const float* positions, const int32_t* prims, size_t count)
         out.nodes[out_index[i]] = n;
     }
     out.sah_cost = sah;
+    emit_wide(B.tmp, root, tiny, out);
     return out;
 }
 

@@ -642,7 +642,7 @@ __global__ void __launch_bounds__(kBlk) k_extend(DScene s, const float4* __restr
     __shared__ int stack[kStackSm * kBlk];
     const int n = *n_ptr;
     trace_stream<false>(
-        s.nodes, s.tris, s.tmin, n, counter, stack + threadIdx.x, kBlk,
+        s.nodes4, s.tris, s.tmin, n, counter, stack + threadIdx.x, kBlk,
         [&](int i, f3& o, f3& d, int& exclude, float& tmax, int& init_prim) {
             const float4 qo = org[i], qd = dir[i];
             o = to_f3(qo); d = to_f3(qd);
@@ -660,7 +660,7 @@ __global__ void __launch_bounds__(kBlk) k_shadow(DScene s, const ShadowQueue sq,
     const int n = *sq.count;
     if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(counters + CNT_SHADOW, (unsigned long long)n);
     trace_stream<true>(
-        s.nodes, s.tris, s.tmin, n, counter, stack + threadIdx.x, kBlk,
+        s.nodes4, s.tris, s.tmin, n, counter, stack + threadIdx.x, kBlk,
         [&](int i, f3& o, f3& d, int& exclude, float& tmax, int& init_prim) {
             const float4 qo = sq.org[i], qd = sq.dir[i];
             const int2 id = sq.ids[i];

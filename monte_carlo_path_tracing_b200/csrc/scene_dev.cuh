@@ -2,6 +2,7 @@
 //
 // HBM layout (everything 16-byte vectors, read through the read-only path):
 //   nodes / tris, lnodes / ltris : the two BVHs of bvh.h (whole scene; emissive triangles only)
+//   nodes4 [N4][7] float4 : the scene BVH collapsed to 4-wide nodes (bvh.h) for k_extend / k_shadow
 //   pverts [P][3] float4 : prim-order vertices; v0.w = material id bits, v1.w = light index bits (-1 = not a light)
 //   pnorms [P][3] float4 : prim-order vertex normals (shading normal = normalised barycentric blend,
 //                          main.cpp:273-274)
@@ -21,6 +22,7 @@ namespace mcpt {
 
 struct DScene {
     const float4* nodes;
+    const float4* nodes4;  // the scene BVH collapsed to 4-wide nodes (bvh.h), what the trace kernels traverse
     const float4* tris;
     const float4* lnodes;
     const float4* ltris;

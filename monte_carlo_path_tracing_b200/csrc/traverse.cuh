@@ -16,6 +16,7 @@
 #include "bvh.h"
 #include "device_math.cuh"
 #include "scene_dev.cuh"
+#include <math_constants.h>
 
 namespace mcpt {
 
@@ -285,27 +286,40 @@ __device__ __forceinline__ void trace_stream(const float4* __restrict__ nodes, c
             bool done = false;
             if (__popc(mi) >= __popc(ml)) {
                 if (at_inner) {
-                    const float4 n0 = __ldg(nodes + 4 * node + 0);
-                    const float4 n1 = __ldg(nodes + 4 * node + 1);
-                    const float4 n2 = __ldg(nodes + 4 * node + 2);
-                    const float4 n3 = __ldg(nodes + 4 * node + 3);
-                    float ax = n0.x * id.x - ood.x, bx = n0.y * id.x - ood.x;
-                    float ay = n0.z * id.y - ood.y, by = n0.w * id.y - ood.y;
-                    float az = n2.x * id.z - ood.z, bz = n2.y * id.z - ood.z;
-                    const float t0n = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.f));
-                    const float t0f = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best.t));
-                    ax = n1.x * id.x - ood.x; bx = n1.y * id.x - ood.x;
-                    ay = n1.z * id.y - ood.y; by = n1.w * id.y - ood.y;
-                    az = n2.z * id.z - ood.z; bz = n2.w * id.z - ood.z;
-                    const float t1n = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.f));
-                    const float t1f = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best.t));
-                    const bool h0 = t0n <= t0f, h1 = t1n <= t1f;
-                    const int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
-                    const bool swap = t1n < t0n;
-                    if (h0 && h1) { st.push(swap ? c0 : c1); node = swap ? c1 : c0; }
-                    else if (h0) node = c0;
-                    else if (h1) node = c1;
-                    else if (st.sp == 0) done = true;
+                    // 4-wide node (bvh.h nodes4): seven 16-byte vectors, child k in component k
+                    const float4* q = nodes + 7 * node;
+                    const float4 lx = __ldg(q + 0), hx = __ldg(q + 1), ly = __ldg(q + 2), hy = __ldg(q + 3);
+                    const float4 lz = __ldg(q + 4), hz = __ldg(q + 5), cq = __ldg(q + 6);
+                    float dn[4];
+                    int cc[4];
+#define MCPT_SLAB(k, C)                                                                                      \
+                    {                                                                                        \
+                        const float ax = lx.C * id.x - ood.x, bx = hx.C * id.x - ood.x;                      \
+                        const float ay = ly.C * id.y - ood.y, by = hy.C * id.y - ood.y;                      \
+                        const float az = lz.C * id.z - ood.z, bz = hz.C * id.z - ood.z;                      \
+                        const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.f));      \
+                        const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best.t));   \
+                        cc[k] = __float_as_int(cq.C);                                                        \
+                        dn[k] = (tn <= tf && cc[k] != kBvhNoChild) ? tn : CUDART_INF_F;                      \
+                    }
+                    MCPT_SLAB(0, x) MCPT_SLAB(1, y) MCPT_SLAB(2, z) MCPT_SLAB(3, w)
+#undef MCPT_SLAB
+                    // sort the four (entry distance, child) pairs, nearest first (5-comparator network)
+#define MCPT_CSWAP(i, j)                                                                                     \
+                    {                                                                                        \
+                        const bool sw = dn[j] < dn[i];                                                       \
+                        const float td = sw ? dn[j] : dn[i], te = sw ? dn[i] : dn[j];                        \
+                        const int tc = sw ? cc[j] : cc[i], tg = sw ? cc[i] : cc[j];                          \
+                        dn[i] = td; dn[j] = te; cc[i] = tc; cc[j] = tg;                                      \
+                    }
+                    MCPT_CSWAP(0, 1) MCPT_CSWAP(2, 3) MCPT_CSWAP(0, 2) MCPT_CSWAP(1, 3) MCPT_CSWAP(1, 2)
+#undef MCPT_CSWAP
+                    if (dn[0] < CUDART_INF_F) {
+                        if (dn[3] < CUDART_INF_F) st.push(cc[3]);
+                        if (dn[2] < CUDART_INF_F) st.push(cc[2]);
+                        if (dn[1] < CUDART_INF_F) st.push(cc[1]);
+                        node = cc[0];
+                    } else if (st.sp == 0) done = true;
                     else node = st.pop();
                 }
             } else if (at_leaf) {

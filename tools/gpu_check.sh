@@ -1,9 +1,9 @@
 # usage: bash tools/gpu_check.sh <tag>   -- GPU parity tests + the two bench workloads, outputs under gpurun_out/<tag>_*
 tag=${1:-run}
-python -m pytest tests -m gpu -x -q 2>&1 | tail -15 > gpurun_out/${tag}_pytest_gpu.log
+timeout 400 python -m pytest tests -m gpu -x -q 2>&1 | tail -15 > gpurun_out/${tag}_pytest_gpu.log
 tail -3 gpurun_out/${tag}_pytest_gpu.log
-python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/${tag}_bench_veach.json 2> gpurun_out/${tag}_bench_veach.err
-python bench.py --steps 3 --warmup 3 --workload cornell-box --no-cpu-baseline > gpurun_out/${tag}_bench_cornell.json 2> gpurun_out/${tag}_bench_cornell.err
+timeout 300 python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/${tag}_bench_veach.json 2> gpurun_out/${tag}_bench_veach.err
+timeout 300 python bench.py --steps 3 --warmup 3 --workload cornell-box --no-cpu-baseline > gpurun_out/${tag}_bench_cornell.json 2> gpurun_out/${tag}_bench_cornell.err
 tail -c 600 gpurun_out/${tag}_bench_veach.err gpurun_out/${tag}_bench_cornell.err
 python - <<PY
 import json

@@ -1,7 +1,7 @@
 # usage: bash tools/gpu_check_big.sh <tag>  -- the two large-scene workloads (configs[2], configs[3])
 tag=${1:-run}
-python bench.py --steps 3 --warmup 3 --workload soup-1m --no-cpu-baseline > gpurun_out/${tag}_bench_soup.json 2> gpurun_out/${tag}_bench_soup.err; tail -c 400 gpurun_out/${tag}_bench_soup.err
-python bench.py --steps 3 --warmup 3 --workload interior --no-cpu-baseline > gpurun_out/${tag}_bench_interior.json 2> gpurun_out/${tag}_bench_interior.err; tail -c 400 gpurun_out/${tag}_bench_interior.err
+timeout 300 python bench.py --steps 3 --warmup 3 --workload soup-1m --no-cpu-baseline > gpurun_out/${tag}_bench_soup.json 2> gpurun_out/${tag}_bench_soup.err; tail -c 400 gpurun_out/${tag}_bench_soup.err
+timeout 300 python bench.py --steps 3 --warmup 3 --workload interior --no-cpu-baseline > gpurun_out/${tag}_bench_interior.json 2> gpurun_out/${tag}_bench_interior.err; tail -c 400 gpurun_out/${tag}_bench_interior.err
 python - <<PY
 import json
 for w in ("soup","interior"):
