@@ -229,10 +229,14 @@ def test_soup_closest_hit_bit_exact(soup):
         p1, b1 = s.closest(ro, rd, ex, light_only, api.FP64)
         p0, b0 = o.closest(ro, rd, ex, mode)
         assert np.array_equal(p1, p0) and np.array_equal(b1, b0)
-    # the renderer's FP32 traversal: same ids except grazing edge hits
-    p32, _ = s.closest(ro, rd, ex, False, api.FP32)
-    p64, _ = s.closest(ro, rd, ex, False, api.FP64)
-    assert np.mean(p32 != p64) < 0.01
+    # the renderer's FP32 traversal (precision FP32 runs k_extend's own code: trace_stream over the 4-wide BVH with
+    # dynamic refill): same ids except grazing edge hits, on enough rays to keep every warp refilling
+    ro, rd, ex = util.surface_rays(a, 200_000, 7)
+    p32, b32 = s.closest(ro, rd, ex, False, api.FP32)
+    p64, b64 = s.closest(ro, rd, ex, False, api.FP64)
+    assert np.mean(p32 != p64) < 2e-3
+    same = (p32 == p64) & (p64 >= 0)
+    assert same.sum() > 1000 and np.max(util.rel_err(b32[same, 2], b64[same, 2])) < 1e-3
 
 
 def test_soup_render_properties(soup):
