@@ -105,8 +105,11 @@ typedef struct McptStats {
     uint32_t kernel_launches;
     uint32_t queue_peak;     /* largest ray-queue length seen */
     float ms_total;          /* device time of the call, CUDA events on the launch stream */
-    float ms_bounce;         /* time in the bounce (extend+shade) kernels */
+    float ms_bounce;         /* time in the per-bounce pipeline: k_shade, k_gather, k_extend, k_shadow, k_runsum */
     float ms_other;
+    float ms_shade;          /* part of ms_bounce spent in k_shade (CUDA events on the launch stream) */
+    float ms_trace;          /* part of ms_bounce spent in k_gather + k_extend + k_shadow (+ k_runsum) */
+    uint64_t elements;       /* ray-queue elements processed by k_shade, summed over bounces (>= vertices) */
 } McptStats;
 
 typedef struct McptScene McptScene;

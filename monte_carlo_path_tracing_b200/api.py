@@ -62,7 +62,8 @@ class Stats(C.Structure):
     _fields_ = [("paths", C.c_uint64), ("primary_hits", C.c_uint64), ("vertices", C.c_uint64),
                 ("rays_closest", C.c_uint64), ("rays_shadow", C.c_uint64), ("rays_light", C.c_uint64),
                 ("passes", C.c_uint32), ("bounces", C.c_uint32), ("kernel_launches", C.c_uint32),
-                ("queue_peak", C.c_uint32), ("ms_total", C.c_float), ("ms_bounce", C.c_float), ("ms_other", C.c_float)]
+                ("queue_peak", C.c_uint32), ("ms_total", C.c_float), ("ms_bounce", C.c_float), ("ms_other", C.c_float),
+                ("ms_shade", C.c_float), ("ms_trace", C.c_float), ("elements", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

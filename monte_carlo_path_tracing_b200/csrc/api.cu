@@ -236,7 +236,7 @@ int mcpt_scene_create(const McptSceneDesc* desc, int device, McptScene** out)
         d.P = (int32_t)P; d.L = (int32_t)L; d.C = (int32_t)C; d.M = (int32_t)Mn;
         d.tmin = s->extent * 1e-6f;
         MCPT_CUDA(cudaMemcpy(s->d_blob, s->h_blob, B.total, cudaMemcpyHostToDevice));
-        for (int i = 0; i < 4; i++) MCPT_CUDA(cudaEventCreate(&s->ev[i]));
+        for (int i = 0; i < 6; i++) MCPT_CUDA(cudaEventCreate(&s->ev[i]));
         *out = s;
     });
     if (rc != MCPT_OK && s) { mcpt_scene_destroy(s); }
@@ -250,7 +250,7 @@ void mcpt_scene_destroy(McptScene* s)
     workspace_free(s->ws);
     if (s->d_blob) cudaFree(s->d_blob);
     if (s->h_blob) cudaFreeHost(s->h_blob);
-    for (int i = 0; i < 4; i++)
+    for (int i = 0; i < 6; i++)
         if (s->ev[i]) cudaEventDestroy(s->ev[i]);
     delete s;
 }

@@ -66,7 +66,7 @@ struct McptScene {
     mcpt::DScene d{};      // device pointers into d_blob
     float extent = 1.f;    // largest scene dimension
     mcpt::Workspace ws;
-    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 
 namespace mcpt {

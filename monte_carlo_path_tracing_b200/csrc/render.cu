@@ -916,7 +916,7 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
         S.kernel_launches++;
         S.rays_closest += npix;
     }
-    float ms_bounce = 0.f;
+    float ms_bounce = 0.f, ms_shade = 0.f;
     bool overflow = false;
     int done = 0, pass = 0;
     while (done < prm->spp) {
@@ -969,7 +969,9 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
                 default: launch_bounce<MCPT_NEE_UNIFORM>(first, a, grid, st); break;
             }
             MCPT_CUDA(cudaGetLastError());
+            MCPT_CUDA(cudaEventRecord(scene->ev[4], st));
             S.kernel_launches++;
+            S.elements += (uint64_t)count;
             const bool last = prm->max_depth > 0 && bounce + 1 >= prm->max_depth + 1;  // vertices deeper than max_depth never spawn
             if (!last) {
                 k_gather<<<ngroups, 256, 0, st>>>(Q[1], Q[0], counts, d_groupsum, nch, (int)stride, (int)cap, tree ? 1 : 0, d_count, d_counters);
@@ -991,6 +993,8 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
             float ms = 0.f;
             cudaEventElapsedTime(&ms, scene->ev[2], scene->ev[3]);
             ms_bounce += ms;
+            cudaEventElapsedTime(&ms, scene->ev[2], scene->ev[4]);
+            ms_shade += ms;
             S.queue_peak = std::max<uint32_t>(S.queue_peak, (uint32_t)count);
             S.bounces++;
             if (last) break;
@@ -1017,6 +1021,7 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     S.primary_hits = h_counters[CNT_PRIMARY_HITS];
     overflow = h_counters[CNT_OVERFLOW] != 0;
     S.ms_total = ms_total; S.ms_bounce = ms_bounce; S.ms_other = ms_total - ms_bounce;
+    S.ms_shade = ms_shade; S.ms_trace = ms_bounce - ms_shade;
     if (stats) *stats = S;
     if (overflow) throw Error(MCPT_ERR_QUEUE_OVERFLOW, "MIS path tree outgrew the ray queue; retry with a smaller batch_spp");
 }

@@ -32,7 +32,7 @@ def test_abi_struct_layouts_match_header():
     """ctypes mirrors of the PODs have the sizes the C compiler gives them (LP64)."""
     assert C.sizeof(api.CameraC) == 10 * 8
     assert C.sizeof(api.RenderParams) == 4 * 8 + 8 + 4 + 4
-    assert C.sizeof(api.Stats) == 6 * 8 + 4 * 4 + 3 * 4 + 4  # tail padding to 8
+    assert C.sizeof(api.Stats) == 6 * 8 + 4 * 4 + 5 * 4 + 4 + 8  # 5 floats, 4 bytes of padding, elements
     assert C.sizeof(api.SceneDesc) == 5 * 4 + 4 + 10 * 8
 
 
