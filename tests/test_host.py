@@ -192,3 +192,60 @@ def test_cpp_driver_fails_loudly_without_gpu(scene_files, tmp_path):
     assert r.returncode == 1
     assert "light triangles" in r.stdout and "no CPU fallback" in r.stderr
     assert not (tmp_path / "o.ppm").exists()
+
+
+# ---- loader edge cases (what tiny_obj_loader does with the files users of the reference have) --------
+_MTL = "newmtl white\nKd 0.7 0.6 0.5\nKs 0.1 0.2 0.3\nNs 25\nnewmtl lamp\nKd 0 0 0\n"
+_XML = '<?xml version="1.0"?>\n<camera type="perspective" width="64" height="48" fovy="35">\n <eye x="0" y="1" z="5"/>\n <lookat x="0" y="0" z="0"/>\n <up x="0" y="1" z="0"/>\n</camera>\n<light mtlname="lamp" radiance="10,20,30"/>\n'
+
+
+def _write(tmp_path, obj, xml=_XML, mtl=_MTL):
+    (tmp_path / "s.obj").write_text("mtllib s.mtl\n" + obj)
+    (tmp_path / "s.mtl").write_text(mtl)
+    (tmp_path / "s.xml").write_text(xml)
+    return str(tmp_path / "s.obj"), str(tmp_path / "s.xml")
+
+
+def test_loader_quads_ngons_negative_indices(tmp_path):
+    """tinyobj triangulates (tiny_obj_loader.h:509-531): quads split along the shorter diagonal, polygons as fans;
+    negative indices count back from the current end of the vertex list; o / g start new shapes."""
+    obj = ("v 0 0 0\nv 2 0 0\nv 2 1 0\nv 0 1 0\nvn 0 0 1\n"
+           "o floor\nusemtl white\nf 1//1 2//1 3//1 4//1\n"           # quad: diagonals equal -> (0,1,3),(1,2,3) branch
+           "v 0 0 1\nv 1 0 1\nv 1.5 1 1\nv 0.5 2 1\nv -0.5 1 1\n"
+           "g lampshape\nusemtl lamp\nf -5//1 -4//1 -3//1 -2//1 -1//1\n")  # pentagon by negative indices -> 3 triangles
+    a, cam = api.load_scene_files(*_write(tmp_path, obj))
+    assert len(a.material_id) == 5 and list(a.shape_offset) == [0, 2, 5]
+    assert a.material_id.tolist() == [0, 0, 1, 1, 1]
+    assert a.light_prim.tolist() == [2, 3, 4] and a.light_class.tolist() == [0, 0, 0]
+    assert np.allclose(a.class_radiance, [[10, 20, 30]])
+    assert np.allclose(a.mat_kd[0], [0.7, 0.6, 0.5]) and np.allclose(a.mat_ks[0], [0.1, 0.2, 0.3]) and a.mat_ns[0] == 25
+    # the quad's two triangles cover its area exactly once
+    v = a.positions[:2].astype(np.float64)
+    area = 0.5 * np.linalg.norm(np.cross(v[:, 1] - v[:, 0], v[:, 2] - v[:, 0]), axis=1)
+    assert abs(area.sum() - 2.0) < 1e-6
+    # pentagon fan: all triangles share the first vertex, z = 1
+    assert np.all(a.positions[2:, 0] == a.positions[2, 0]) and np.all(a.positions[2:, :, 2] == 1.0)
+    assert (cam.width, cam.height, cam.fovy_deg) == (64, 48, 35.0) and cam.eye == (0.0, 1.0, 5.0)
+    r = api.host_bvh_check(a, False)
+    assert r["errors"] == 0
+
+
+def test_loader_rejects_what_the_reference_reads_out_of_bounds(tmp_path):
+    """A face without vn makes the reference index attrib.normals[-3..] (Myobj.cpp:671-673), a face without usemtl
+    makes it call materials.at(-1) (main.cpp:292): both are reported as errors instead."""
+    with pytest.raises(api.McptError) as e:
+        api.load_scene_files(*_write(tmp_path, "v 0 0 0\nv 1 0 0\nv 0 1 0\nusemtl white\nf 1 2 3\n"))
+    assert e.value.code == -4 and "normal" in str(e.value)
+    with pytest.raises(api.McptError) as e:
+        api.load_scene_files(*_write(tmp_path, "v 0 0 0\nv 1 0 0\nv 0 1 0\nvn 0 0 1\nf 1//1 2//1 3//1\n"))
+    assert e.value.code == -4 and "material" in str(e.value)
+    with pytest.raises(api.McptError):
+        api.load_scene_files(*_write(tmp_path, "v 0 0 0\nv 1 0 0\nvn 0 0 1\nusemtl white\nf 1//1 2//1 7//1\n"))
+
+
+def test_loader_light_without_triangles_and_no_camera(tmp_path):
+    """<light> whose material no face uses: lightsTriangles.at() throws in the reference (Mylight.cpp:126); here the
+    scene loads and scene_create rejects it.  A file without <camera> reports has_camera = 0."""
+    obj = "v 0 0 0\nv 1 0 0\nv 0 1 0\nvn 0 0 1\nusemtl white\nf 1//1 2//1 3//1\n"
+    a, cam = api.load_scene_files(*_write(tmp_path, obj, xml='<light mtlname="lamp" radiance="1,1,1"/>\n'))
+    assert cam is None and len(a.light_prim) == 0
