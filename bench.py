@@ -67,32 +67,44 @@ class ClockSampler:
     def __init__(self, gpu_index=0):
         self.rows, self.stop_flag, self.gpu = [], False, gpu_index
         self.thread = threading.Thread(target=self._run, daemon=True)
-
-    def _run(self):
-        # NVML in-process (nvidia_ml_py): one query costs microseconds.  Spawning nvidia-smi every 200 ms inside the
-        # timed region measurably slowed the host-driven bounce loop (driver lock + a busy host core).
+        # NVML in-process (nvidia_ml_py).  nvmlInit / the first query take the driver lock for tens of ms, so they
+        # happen HERE, before the timed region; inside it one query costs microseconds.  (Spawning nvidia-smi every
+        # 200 ms inside the timed region measurably slowed the host-driven bounce loop.)
+        self.nv = None
         try:
             import pynvml
             pynvml.nvmlInit()
             h = pynvml.nvmlDeviceGetHandleByIndex(self.gpu)
-            mx = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
-            bits = [(pynvml.nvmlClocksEventReasonHwSlowdown, 0), (pynvml.nvmlClocksEventReasonHwThermalSlowdown, 1),
-                    (pynvml.nvmlClocksEventReasonSwThermalSlowdown, 2), (pynvml.nvmlClocksEventReasonSwPowerCap, 3)]
-            while not self.stop_flag:
-                sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
-                try:
-                    r = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
-                except Exception:
-                    r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
-                row = [str(sm), str(mx)] + ["Not Active"] * 4
-                for bit, k in bits:
-                    if r & bit:
-                        row[2 + k] = "Active"
-                self.rows.append(row)
-                time.sleep(0.05)
-            return
+            self.nv = (pynvml, h, pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            self._query()
+            self.rows.clear()
         except Exception:
-            pass
+            self.nv = None
+
+    def _query(self):
+        pynvml, h, mx = self.nv
+        bits = [(pynvml.nvmlClocksEventReasonHwSlowdown, 0), (pynvml.nvmlClocksEventReasonHwThermalSlowdown, 1),
+                (pynvml.nvmlClocksEventReasonSwThermalSlowdown, 2), (pynvml.nvmlClocksEventReasonSwPowerCap, 3)]
+        sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+        try:
+            r = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
+        except Exception:
+            r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+        row = [str(sm), str(mx)] + ["Not Active"] * 4
+        for bit, k in bits:
+            if r & bit:
+                row[2 + k] = "Active"
+        self.rows.append(row)
+
+    def _run(self):
+        if self.nv is not None:
+            try:
+                while not self.stop_flag:
+                    self._query()
+                    time.sleep(0.05)
+                return
+            except Exception:
+                pass
         while not self.stop_flag:
             try:
                 o = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
@@ -331,25 +343,34 @@ def run_ours(args, wl_name, wl):
         passes_n = sum(s["passes"] for s in stats)
         children = max(0, tot["rays_closest"] - npix * passes_n)   # rays k_extend traced = entries staged and gathered
         rec = 56 if tree else 48
-        shade_bytes = elements * (rec + 16 + 16) + children * rec + tot["rays_shadow"] * 56
+        sph = wl["strategy"] in ("MIS", "NEE_SPHERICAL")
+        later_el = max(0, elements - npix * passes_n)              # elements of the later bounces
+        # k_shade: ray + hit in, slot accumulator read-modify-write, children staged, visibility records out;
+        # k_lightsel (spherical strategies, later bounces): ray direction + hit in, selection out, read again by k_shade
+        shade_bytes = elements * (rec + 16 + 16) + children * rec + tot["rays_shadow"] * 56 + (later_el * (32 + 16 + 16) if sph else 0)
         trace_bytes = children * (32 + 16 + 2 * rec) + tot["rays_shadow"] * (56 + 32) + (elements * 32 if tree else 0)
         if ms_shade >= ms_trace:
-            dom, dom_ms, dom_bytes, dom_launches = "k_shade<%s>" % wl["strategy"], ms_shade, shade_bytes, launches_bounce
+            dom = ("k_lightsel + k_shade<%s>" if sph else "k_shade<%s>") % wl["strategy"]
+            dom_ms, dom_bytes, dom_launches = ms_shade, shade_bytes, launches_bounce
         else:
             dom, dom_ms, dom_bytes = "trace kernels k_gather + k_extend + k_shadow", ms_trace, trace_bytes
             dom_launches = launches_bounce
         achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
-        traffic = None
+        # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel(s) of ONE bounce, from the committed
+        # `ncu --set full` capture (profiles/ncu_traffic.json); compare with `algorithmic_bytes_captured_launch` there
+        traffic, traffic_detail = None, None
         try:
             t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))[wl_name]
-            traffic = t if t.get("kernel", "").split("<")[0] in dom else None
+            if t.get("kernel") == dom:
+                traffic, traffic_detail = t["dram_bytes_per_launch"], t
+                if t.get("dram_bytes_per_element"):   # captured launch -> average launch of this run
+                    traffic = t["dram_bytes_per_element"] * elements / dom_launches
         except Exception:
             pass
         L = len(arrays.light_prim)
         # FP32 work actually executed (estimate): ~320 flops of shading per vertex, plus ~70 flops per light per sweep of
         # the light table; without jitter the first vertex of a pixel is swept once per pass (k_lightprep), later
         # vertices once each -- for MIS only the 60 % that survive the roulette taken before sampling (main.cpp:429-437)
-        sph = wl["strategy"] in ("MIS", "NEE_SPHERICAL")
         passes = sum(s["passes"] for s in stats)
         later = max(0, tot["vertices"] - sum(s["primary_hits"] for s in stats))
         sweeps = (npix * passes + later * (0.6 if wl["strategy"] == "MIS" else 1.0)) if sph else 0
@@ -364,7 +385,7 @@ def run_ours(args, wl_name, wl):
             "e2e": {"value": samples / e2e_s / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": scene.device_bytes(),
                     "d2h_bytes_per_step": npix * 12},
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                         "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "peak_source": which,
+                         "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "traffic_detail": traffic_detail, "peak_source": which,
                          "algorithmic_bytes_per_launch": dom_bytes / dom_launches, "avg_launch_ms": dom_ms / dom_launches,
                          "launches": dom_launches, "kernel_share_of_step": dom_ms / ms,
                          "pipeline": {"ms_shade": ms_shade, "ms_trace": ms_trace, "ms_bounce": ms_bounce, "share_of_step": ms_bounce / ms,

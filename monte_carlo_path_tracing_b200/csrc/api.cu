@@ -200,7 +200,7 @@ int mcpt_scene_create(const McptSceneDesc* desc, int device, McptScene** out)
             so[l] = f4{v[0], v[1], v[2], 0.f};
             so[Lpad + l] = f4{v[3], v[4], v[5], 0.f};
             so[2 * Lpad + l] = f4{v[6], v[7], v[8], (float)(1e-8 * a2)};
-            so[3 * Lpad + l] = f4{(float)(g[0] * a2), (float)(g[1] * a2), (float)(g[2] * a2), (float)(r[0] + r[1] + r[2])};
+            so[3 * Lpad + l] = f4{-(float)(g[0] * a2), -(float)(g[1] * a2), -(float)(g[2] * a2), 2.0f * (float)(r[0] + r[1] + r[2])};
             for (int c = 0; c < 3; c++) lng[3 * l + c] = g[c];
             lar[l] = s->light_area[l];
         }

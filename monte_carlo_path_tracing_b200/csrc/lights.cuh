@@ -90,42 +90,68 @@ __device__ __forceinline__ V3<T> arvo_sample(const SphTri<T>& st, T xi1, T xi2)
 // The loop reads the SoA table `lsoa` (scene_dev.cuh): four float4 planes of Lpad entries, so a warp's 32
 // lanes fetch 32 consecutive 16-byte vectors per plane (4 x 512 B, fully coalesced):
 //   plane0 = v0 | -, plane1 = v1 | -, plane2 = v2 | cull threshold 1e-8 * 2 area,
-//   plane3 = Ns = 2 area * ng | Lsum;  padding entries have threshold = +inf and evaluate to 0.
-// Branch-free on purpose: two evaluations are interleaved per loop trip and every load is hoisted.
+//   plane3 = -Ns = -2 area * ng | 2 Lsum;  padding entries have threshold = +inf and evaluate to 0.
+// Branch-free on purpose.
 
 // atan(q) for q in [0,1]: Abramowitz & Stegun 4.4.49, |error| <= 2e-8; exact to first order as q -> 0
+#define MCPT_ATAN_C0 0.0028662257f
+#define MCPT_ATAN_C1 -0.0161657367f
+#define MCPT_ATAN_C2 0.0429096138f
+#define MCPT_ATAN_C3 -0.0752896400f
+#define MCPT_ATAN_C4 0.1065626393f
+#define MCPT_ATAN_C5 -0.1420889944f
+#define MCPT_ATAN_C6 0.1999355085f
+#define MCPT_ATAN_C7 -0.3333314528f
 __device__ __forceinline__ float atan_unit(float q)
 {
-    const float s = q * q;
-    float p = 0.0028662257f;
-    p = fmaf(p, s, -0.0161657367f);
-    p = fmaf(p, s, 0.0429096138f);
-    p = fmaf(p, s, -0.0752896400f);
-    p = fmaf(p, s, 0.1065626393f);
-    p = fmaf(p, s, -0.1420889944f);
-    p = fmaf(p, s, 0.1999355085f);
-    p = fmaf(p, s, -0.3333314528f);
-    return fmaf(q, p * s, q);
+    const float s = __fmul_rn(q, q);
+    float p = MCPT_ATAN_C0;
+    p = __fmaf_rn(p, s, MCPT_ATAN_C1);
+    p = __fmaf_rn(p, s, MCPT_ATAN_C2);
+    p = __fmaf_rn(p, s, MCPT_ATAN_C3);
+    p = __fmaf_rn(p, s, MCPT_ATAN_C4);
+    p = __fmaf_rn(p, s, MCPT_ATAN_C5);
+    p = __fmaf_rn(p, s, MCPT_ATAN_C6);
+    p = __fmaf_rn(p, s, MCPT_ATAN_C7);
+    return __fmaf_rn(q, __fmul_rn(p, s), q);
 }
-// atan2(y, x) for y > 0, result in (0, pi)
-__device__ __forceinline__ float atan2_pos(float y, float x)
+__device__ __forceinline__ float rcp_fast(float x)  // MUFU.RCP
 {
-    const float ax = fabsf(x);
-    const float mx = fmaxf(ax, y), mn = fminf(ax, y);
-    float r = atan_unit(__fdividef(mn, mx));
-    r = (y > ax) ? 1.57079632679489662f - r : r;
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+// the octant fix-ups of atan2(y, x) for y > 0 (result in (0, pi)), given r = atan(min/max) of (|x|, y)
+__device__ __forceinline__ float atan2_fix(float r, float y, float x)
+{
+    r = (y > fabsf(x)) ? 1.57079632679489662f - r : r;
     return (x < 0.f) ? 3.14159265358979324f - r : r;
 }
 
+// One light, one vertex.  Written with explicit round-to-nearest intrinsics in exactly the operation order of the
+// packed version below (light_weight_pair), so the short second pass of warp_light_pick reproduces the sweep's
+// weights bit for bit.  p3 = -2 area ng | 2 Lsum.
+__device__ __forceinline__ float dot_rn(float ax, float ay, float az, float bx, float by, float bz)
+{
+    return __fmaf_rn(az, bz, __fmaf_rn(ay, by, __fmul_rn(ax, bx)));
+}
 __device__ __forceinline__ float light_weight_soa(float4 p0, float4 p1, float4 p2, float4 p3, f3 x1, f3 n)
 {
-    const f3 a = to_f3(p0) - x1, b = to_f3(p1) - x1, c = to_f3(p2) - x1;
-    const float num = -(p3.x * a.x + p3.y * a.y + p3.z * a.z);         // 2 area * (ng . (x1 - v0)), :178-185
-    const float hmax = fmaxf(dot(n, a), fmaxf(dot(n, b), dot(n, c)));  // :187-197
-    const float aa = dot(a, a), bb = dot(b, b), cc = dot(c, c);
-    const float la = aa * rsqrtf(aa), lb = bb * rsqrtf(bb), lc = cc * rsqrtf(cc);
-    const float den = la * lb * lc + dot(a, b) * lc + dot(a, c) * lb + dot(b, c) * la;
-    const float w = 2.0f * atan2_pos(num, den) * p3.w;
+    const float ax = __fadd_rn(p0.x, -x1.x), ay = __fadd_rn(p0.y, -x1.y), az = __fadd_rn(p0.z, -x1.z);
+    const float bx = __fadd_rn(p1.x, -x1.x), by = __fadd_rn(p1.y, -x1.y), bz = __fadd_rn(p1.z, -x1.z);
+    const float cx = __fadd_rn(p2.x, -x1.x), cy = __fadd_rn(p2.y, -x1.y), cz = __fadd_rn(p2.z, -x1.z);
+    const float num = dot_rn(p3.x, p3.y, p3.z, ax, ay, az);            // 2 area * (ng . (x1 - v0)), :178-185
+    const float hmax = fmaxf(dot_rn(n.x, n.y, n.z, ax, ay, az),
+                             fmaxf(dot_rn(n.x, n.y, n.z, bx, by, bz), dot_rn(n.x, n.y, n.z, cx, cy, cz)));  // :187-197
+    const float aa = dot_rn(ax, ay, az, ax, ay, az), bb = dot_rn(bx, by, bz, bx, by, bz), cc = dot_rn(cx, cy, cz, cx, cy, cz);
+    const float la = __fmul_rn(aa, rsqrtf(aa)), lb = __fmul_rn(bb, rsqrtf(bb)), lc = __fmul_rn(cc, rsqrtf(cc));
+    float den = __fmul_rn(__fmul_rn(la, lb), lc);
+    den = __fmaf_rn(dot_rn(ax, ay, az, bx, by, bz), lc, den);
+    den = __fmaf_rn(dot_rn(ax, ay, az, cx, cy, cz), lb, den);
+    den = __fmaf_rn(dot_rn(bx, by, bz, cx, cy, cz), la, den);
+    const float ad = fabsf(den);
+    const float q = __fmul_rn(fminf(ad, num), rcp_fast(fmaxf(ad, num)));
+    const float w = __fmul_rn(atan2_fix(atan_unit(q), num, den), p3.w);
     const bool ok = num >= p2.w && hmax >= 1e-8f && w > 0.f && w < CUDART_INF_F;
     return ok ? w : 0.f;
 }
@@ -136,31 +162,93 @@ __device__ __forceinline__ float light_weight_fast(const DScene& s, int l, f3 x1
     return light_weight_soa(__ldg(P), __ldg(P + s.Lpad), __ldg(P + 2 * s.Lpad), __ldg(P + 3 * s.Lpad), x1, n);
 }
 
-// Per-lane partial sums, over this lane's lights (l = lane, lane + 32, ...), of the weights seen from V vertices
-// at once: the four 16-byte loads of a light are shared by V evaluations (the loop is L1-bandwidth-bound at
-// V = 1).  With `cdf` (shared memory, [V][Lpad] floats) every running partial is also stored: cdf[v][l] = sum of
-// the lane's weights up to and including light l -- the per-lane columns k_lightprep inverts for its picks.
-// All 32 lanes call.
+// ---- packed FP32 (sm_100 FFMA2 / FADD2 / FMUL2) --------------------------------------------------------------
+// Blackwell issues ONE instruction for two independent FP32 operations on a 64-bit register pair, and any operand
+// may instead be a 32-bit register broadcast to both halves (SASS `R4.F32`) or an immediate.  The O(L) loop is
+// issue-bound (ncu: 77 % issue-active at 29 threads/instruction in its scalar form), so a sweep evaluates one
+// light against TWO VERTICES per instruction: the vertex pair lives in the two halves, the light's scalars and the
+// polynomial constants are broadcast operands.  Only min/max, the three reciprocal square roots, the reciprocal
+// (MUFU) and the final selects stay scalar.  Same operations in the same order as light_weight_soa.
+__device__ __forceinline__ float2 bc2(float a) { return make_float2(a, a); }
+__device__ __forceinline__ float2 dot2_rn(float2 ax, float2 ay, float2 az, float2 bx, float2 by, float2 bz)
+{
+    return __ffma2_rn(az, bz, __ffma2_rn(ay, by, __fmul2_rn(ax, bx)));
+}
+// two vertices side by side: -x1 and n per component, (vertex 0, vertex 1)
+struct VertexPair2 { float2 mx, my, mz, nx, ny, nz; };
+__device__ __forceinline__ VertexPair2 make_vertex2(f3 xa, f3 na, f3 xb, f3 nb)
+{
+    VertexPair2 v;
+    v.mx = make_float2(-xa.x, -xb.x); v.my = make_float2(-xa.y, -xb.y); v.mz = make_float2(-xa.z, -xb.z);
+    v.nx = make_float2(na.x, nb.x); v.ny = make_float2(na.y, nb.y); v.nz = make_float2(na.z, nb.z);
+    return v;
+}
+__device__ __forceinline__ float2 light_weight_pair(float4 p0, float4 p1, float4 p2, float4 p3, const VertexPair2& v)
+{
+    const float2 ax = __fadd2_rn(bc2(p0.x), v.mx), ay = __fadd2_rn(bc2(p0.y), v.my), az = __fadd2_rn(bc2(p0.z), v.mz);
+    const float2 bx = __fadd2_rn(bc2(p1.x), v.mx), by = __fadd2_rn(bc2(p1.y), v.my), bz = __fadd2_rn(bc2(p1.z), v.mz);
+    const float2 cx = __fadd2_rn(bc2(p2.x), v.mx), cy = __fadd2_rn(bc2(p2.y), v.my), cz = __fadd2_rn(bc2(p2.z), v.mz);
+    const float2 num = dot2_rn(bc2(p3.x), bc2(p3.y), bc2(p3.z), ax, ay, az);
+    const float2 ha = dot2_rn(v.nx, v.ny, v.nz, ax, ay, az), hb = dot2_rn(v.nx, v.ny, v.nz, bx, by, bz),
+                 hc = dot2_rn(v.nx, v.ny, v.nz, cx, cy, cz);
+    const float2 aa = dot2_rn(ax, ay, az, ax, ay, az), bb = dot2_rn(bx, by, bz, bx, by, bz), cc = dot2_rn(cx, cy, cz, cx, cy, cz);
+    const float2 la = __fmul2_rn(aa, make_float2(rsqrtf(aa.x), rsqrtf(aa.y)));
+    const float2 lb = __fmul2_rn(bb, make_float2(rsqrtf(bb.x), rsqrtf(bb.y)));
+    const float2 lc = __fmul2_rn(cc, make_float2(rsqrtf(cc.x), rsqrtf(cc.y)));
+    float2 den = __fmul2_rn(__fmul2_rn(la, lb), lc);
+    den = __ffma2_rn(dot2_rn(ax, ay, az, bx, by, bz), lc, den);
+    den = __ffma2_rn(dot2_rn(ax, ay, az, cx, cy, cz), lb, den);
+    den = __ffma2_rn(dot2_rn(bx, by, bz, cx, cy, cz), la, den);
+    const float adx = fabsf(den.x), ady = fabsf(den.y);
+    const float2 q = __fmul2_rn(make_float2(fminf(adx, num.x), fminf(ady, num.y)),
+                                make_float2(rcp_fast(fmaxf(adx, num.x)), rcp_fast(fmaxf(ady, num.y))));
+    const float2 s = __fmul2_rn(q, q);
+    float2 p = bc2(MCPT_ATAN_C0);
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C1));
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C2));
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C3));
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C4));
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C5));
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C6));
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C7));
+    const float2 r = __ffma2_rn(q, __fmul2_rn(p, s), q);
+    const float2 w = __fmul2_rn(make_float2(atan2_fix(r.x, num.x, den.x), atan2_fix(r.y, num.y, den.y)), bc2(p3.w));
+    const bool ok0 = num.x >= p2.w && fmaxf(ha.x, fmaxf(hb.x, hc.x)) >= 1e-8f && w.x > 0.f && w.x < CUDART_INF_F;
+    const bool ok1 = num.y >= p2.w && fmaxf(ha.y, fmaxf(hb.y, hc.y)) >= 1e-8f && w.y > 0.f && w.y < CUDART_INF_F;
+    return make_float2(ok0 ? w.x : 0.f, ok1 ? w.y : 0.f);
+}
+
+// Per-lane partial sums, over this lane's lights (l = lane, lane + 32, ...), of the weights seen from V = 2 or 4
+// vertices (one packed evaluation per light and vertex pair: the four 16-byte loads of a light serve all).  With `cdf` (shared memory,
+// [2][Lpad] floats) every running partial is also stored: cdf[v][l] = sum of the lane's weights up to and
+// including light l -- the per-lane columns k_lightprep inverts for its picks.  All 32 lanes call.
+#ifndef MCPT_SWEEP_UNROLL
+#define MCPT_SWEEP_UNROLL 2
+#endif
+constexpr int kSweepUnroll = MCPT_SWEEP_UNROLL;
 template <int V>
 __device__ __forceinline__ void warp_light_partial(const DScene& s, const f3 (&x1)[V], const f3 (&n)[V], float (&part)[V],
                                                    float* cdf = nullptr)
 {
+    static_assert(V == 2 || V == 4, "the sweep is packed over vertex pairs");
     const int lane = threadIdx.x & 31;
+    VertexPair2 vp[V / 2];
+    float2 acc[V / 2];
+#pragma unroll
+    for (int h = 0; h < V / 2; h++) { vp[h] = make_vertex2(x1[2 * h], n[2 * h], x1[2 * h + 1], n[2 * h + 1]); acc[h] = make_float2(0.f, 0.f); }
     const float4* __restrict__ P0 = s.lsoa;
     const float4* __restrict__ P1 = P0 + s.Lpad;
     const float4* __restrict__ P2 = P1 + s.Lpad;
     const float4* __restrict__ P3 = P2 + s.Lpad;
-#pragma unroll
-    for (int v = 0; v < V; v++) part[v] = 0.f;
-#pragma unroll 2
+#pragma unroll kSweepUnroll
     for (int l = lane; l < s.Lpad; l += 32) {  // Lpad is a multiple of 64
         const float4 a0 = __ldg(P0 + l), a1 = __ldg(P1 + l), a2 = __ldg(P2 + l), a3 = __ldg(P3 + l);
 #pragma unroll
-        for (int v = 0; v < V; v++) {
-            part[v] += light_weight_soa(a0, a1, a2, a3, x1[v], n[v]);
-            if (cdf) cdf[v * s.Lpad + l] = part[v];
-        }
+        for (int h = 0; h < V / 2; h++) acc[h] = __fadd2_rn(acc[h], light_weight_pair(a0, a1, a2, a3, vp[h]));
+        if (V == 2 && cdf) { cdf[l] = acc[0].x; cdf[s.Lpad + l] = acc[0].y; }
     }
+#pragma unroll
+    for (int h = 0; h < V / 2; h++) { part[2 * h] = acc[h].x; part[2 * h + 1] = acc[h].y; }
 }
 
 // ---- Arvo SampleTriangle without inverse trigonometry ------------------------------------------------------

@@ -59,6 +59,7 @@ struct BounceArgs {
     ShadowQueue sq;            // NEE visibility rays of this bounce with their pending contributions
     const int2* sel;           // [slots] first-vertex light drawn by k_lightprep: index | weight bits
     const float* wsum_pix;     // [npix] first-vertex weights_sum
+    float4* sel4;              // [capacity] later vertices, drawn by k_lightsel for in-queue ray i: index bits | weight | weights_sum
     int* counts;               // [chunks] children staged by each chunk
     int* groupsum;             // [chunks / kGroup] sums of counts, filled with one integer atomic per chunk
     int* ticket;               // chunk ticket counter
@@ -149,8 +150,12 @@ __device__ __forceinline__ float warp_scan_incl(float v)
     return v;
 }
 
-// Must be called by all 32 lanes; lanes with need == false only help.  Two vertices are served per sweep of the
-// light table (warp_light_partial<2>): the loads are shared and the two evaluations interleave.
+// Must be called by all 32 lanes; lanes with need == false only help.  V (2 or 4) vertices are served per sweep of
+// the light table (warp_light_partial<V>): the loads are shared and the packed evaluations interleave.
+#ifndef MCPT_SELECT_V
+#define MCPT_SELECT_V 2
+#endif
+template <int V = MCPT_SELECT_V>
 __device__ __forceinline__ void warp_light_select(const DScene& s, bool need, f3 x, f3 n, float u, int* chosen, float* wsum_out,
                                                   float* w_chosen)
 {
@@ -158,23 +163,25 @@ __device__ __forceinline__ void warp_light_select(const DScene& s, bool need, f3
     unsigned todo = __ballot_sync(kFull, need);
     *chosen = -1; *wsum_out = 0.f; *w_chosen = 0.f;
     while (todo) {
-        int src[2];
-        src[0] = __ffs(todo) - 1;
-        todo &= todo - 1;
-        const bool two = todo != 0;
-        src[1] = two ? __ffs(todo) - 1 : src[0];
-        todo &= todo - 1;  // no-op when todo is already 0
-        f3 X[2], Nn[2];
-        float part[2];
+        int src[V];
+        int cnt = 0;
 #pragma unroll
-        for (int v = 0; v < 2; v++) {
+        for (int v = 0; v < V; v++) {
+            src[v] = todo ? __ffs(todo) - 1 : src[0];  // short groups re-evaluate the first vertex
+            if (todo) cnt++;
+            todo &= todo - 1;  // no-op when todo is already 0
+        }
+        f3 X[V], Nn[V];
+        float part[V];
+#pragma unroll
+        for (int v = 0; v < V; v++) {
             X[v] = mk<float>(__shfl_sync(kFull, x.x, src[v]), __shfl_sync(kFull, x.y, src[v]), __shfl_sync(kFull, x.z, src[v]));
             Nn[v] = mk<float>(__shfl_sync(kFull, n.x, src[v]), __shfl_sync(kFull, n.y, src[v]), __shfl_sync(kFull, n.z, src[v]));
         }
-        warp_light_partial<2>(s, X, Nn, part);
+        warp_light_partial<V>(s, X, Nn, part);
 #pragma unroll
-        for (int v = 0; v < 2; v++) {
-            if (v == 1 && !two) break;
+        for (int v = 0; v < V; v++) {
+            if (v >= cnt) break;
             const float uu = __shfl_sync(kFull, u, src[v]);
             const float incl = warp_scan_incl(part[v]);
             const float total = __shfl_sync(kFull, incl, 31);
@@ -288,7 +295,7 @@ __global__ void __launch_bounds__(kBlk) k_primary(DScene s, DCamera cam, int npi
 // CDF (lane totals, then the lane's column) with two short binary searches -- O(log L) per sample instead of
 // O(L).  sel[slot] = (light index | weight bits), -1 when the sample draws no light (unshadable vertex, or
 // shade_with_mis's roulette, main.cpp:429-437, already ended it); wsum_pix[pixel] = weights_sum.
-__global__ void __launch_bounds__(kBlk) k_lightprep(DScene s, DCamera cam, const float4* __restrict__ primary_hit, int npix,
+__global__ void __launch_bounds__(kBlk, 5) k_lightprep(DScene s, DCamera cam, const float4* __restrict__ primary_hit, int npix,
                                                     int batch_spp, int sample_base, uint64_t seed, float p_rr, int rr_first,
                                                     int max_depth, int use_cdf, int2* sel, float* wsum_pix)
 {
@@ -382,6 +389,60 @@ __global__ void __launch_bounds__(kBlk) k_lightprep(DScene s, DCamera cam, const
     }
 }
 
+// ---- light selection at the later vertices ---------------------------------------------------------------------
+// The O(L) sweeps are the most expensive thing the spherical strategies do.  This kernel does nothing else -- rebuild
+// the vertex, redo the (counter-based, hence repeatable) roulette and uniform draws that decide whether the vertex
+// samples a light, sweep, pick -- and leaves sel4[i] = (light index bits, its weight, weights_sum) for k_shade, which
+// then needs 94 instead of 126 registers.  Measured (veach-mis, B200): sweeps inside k_shade 34.2 ms per 64-spp step,
+// here 33.0 ms with two lights in flight per lane (unroll 2); 4, 5, 6, 7 or 8 resident blocks per SM make no
+// difference -- the loop is bound by the FMA-heavy pipe (FFMA2 occupies it for two cycles: 68 % busy at 61 % issue-
+// active) and the MUFU bursts, not by latency.  Four vertices per sweep lost 20 % to padded groups.
+#ifndef MCPT_SEL_MINBLK
+#define MCPT_SEL_MINBLK 5
+#endif
+template <int STRAT>
+__global__ void __launch_bounds__(kBlk, MCPT_SEL_MINBLK) k_lightsel(const BounceArgs a, int* cursor)
+{
+    constexpr bool kTree = (STRAT == MCPT_MIS);
+    const DScene& s = a.s;
+    const int lane = threadIdx.x & 31;
+    const int nchunks = (a.in_count + 31) >> 5;
+    const bool rr_forced = a.max_depth > 0 && a.bounce + 1 >= a.max_depth;
+    int next = 0;
+    if (lane == 0) next = atomicAdd(cursor, 1);
+    for (;;) {
+        const int chunk = __shfl_sync(kFull, next, 0);
+        if (chunk >= nchunks) break;
+        if (lane == 0) next = atomicAdd(cursor, 1);
+        const int i = chunk * 32 + lane;
+        bool need = false;
+        f3 p = mk<float>(0.f, 0.f, 0.f), N = mk<float>(0.f, 0.f, 1.f);
+        float u = 0.f;
+        if (i < a.in_count) {
+            const float4 qh = a.hit[i];
+            const int prim = __float_as_int(qh.x);
+            if (prim >= 0) {
+                const float4 qd = a.in.dir[i];
+                const Vertex v = make_vertex(s, prim, qh.y, qh.z, -to_f3(qd));
+                if (v.front && v.light < 0) {
+                    const int slot = __float_as_int(qd.w);
+                    const uint32_t pixel = (uint32_t)(slot % a.npix), sample = (uint32_t)(a.sample_base + slot / a.npix);
+                    uint64_t node = (uint64_t)a.bounce + 1;
+                    if (kTree) { const uint2 nd = a.in.node[i]; node = ((uint64_t)nd.y << 32) | nd.x; }
+                    need = true;
+                    // MIS: roulette before any sampling (main.cpp:429-437); NEE samples the light first (:300-316)
+                    if (kTree) need = !rr_forced && !(rng_draw4(a.seed, pixel, sample, node, 0).u[0] > a.p_rr);
+                    if (need) { u = rng_draw4(a.seed, pixel, sample, node, 1).u[0]; p = v.p; N = v.N; }
+                }
+            }
+        }
+        int chosen = -1;
+        float wsum = 0.f, wch = 0.f;
+        if (__any_sync(kFull, need)) warp_light_select(s, need, p, N, u, &chosen, &wsum, &wch);
+        if (i < a.in_count) a.sel4[i] = make_float4(__int_as_float(chosen), wch, wsum, 0.f);
+    }
+}
+
 // ---- one bounce --------------------------------------------------------------------------------------------
 struct Child { f3 o, d, thr; int exclude; uint64_t node; };
 
@@ -389,7 +450,10 @@ struct Child { f3 o, d, thr; int exclude; uint64_t node; };
 // k_extend (closest hit of the children) and k_shadow (NEE visibility).  FIRST = primary vertices without jitter:
 // the ray comes from the camera formula and the hit from k_primary's per-pixel table.
 template <int STRAT, bool FIRST>
-__global__ void __launch_bounds__(kBlk) k_shade(const BounceArgs a)
+#ifndef MCPT_SHADE_MINBLK
+#define MCPT_SHADE_MINBLK 1
+#endif
+__global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceArgs a)
 {
     constexpr bool kTree = (STRAT == MCPT_MIS);
     constexpr bool kNee = (STRAT == MCPT_NEE_SPHERICAL || STRAT == MCPT_NEE_UNIFORM);
@@ -399,7 +463,6 @@ __global__ void __launch_bounds__(kBlk) k_shade(const BounceArgs a)
     const int lane = threadIdx.x & 31;
     unsigned c_vert = 0, c_lrays = 0, c_phits = 0;
     const int nchunks = (a.in_count + 31) >> 5;
-    const bool presel = FIRST && kSph;  // lights already drawn by k_lightprep
 
     int next = 0;
     if (lane == 0) next = atomicAdd(a.ticket, 1);
@@ -482,13 +545,16 @@ __global__ void __launch_bounds__(kBlk) k_shade(const BounceArgs a)
         int sh_prim = -1;
         if (kSph) {
             int chosen = -1; float wch = 0.f;
-            if (presel) {
-                if (alive) {
+            if (alive) {
+                if (FIRST) {  // drawn once per pixel by k_lightprep
                     const int2 v = a.sel[slot];
                     chosen = v.x; wch = __int_as_float(v.y);
                     wsum = a.wsum_pix[pixel];
+                } else {      // drawn by k_lightsel
+                    const float4 v = a.sel4[i];
+                    chosen = __float_as_int(v.x); wch = v.y; wsum = v.z;
                 }
-            } else warp_light_select(s, alive, p, N, r1.u[0], &chosen, &wsum, &wch);
+            }
             if (alive && chosen >= 0) {
                 // Arvo sample of the chosen triangle (Mylight.cpp:285-317) through arvo_direct (lights.cuh), in FP64:
                 // the q of :292 is a ratio of two O(sA^2) differences, and FP32 misses the 1e-5 direction bar even on
@@ -753,10 +819,13 @@ __global__ void k_tonemap(const float* __restrict__ rgb, size_t n3, double A, do
 }
 
 template <int STRAT>
-void launch_bounce(bool first, const BounceArgs& a, int grid, cudaStream_t st)
+int launch_bounce(bool first, const BounceArgs& a, int grid, int sel_grid, int* sel_cursor, cudaStream_t st)
 {
-    if (first) k_shade<STRAT, true><<<grid, kBlk, 0, st>>>(a);
-    else k_shade<STRAT, false><<<grid, kBlk, 0, st>>>(a);
+    constexpr bool kSph = (STRAT == MCPT_NEE_SPHERICAL || STRAT == MCPT_MIS);
+    if (first) { k_shade<STRAT, true><<<grid, kBlk, 0, st>>>(a); return 1; }
+    if constexpr (kSph) k_lightsel<STRAT><<<std::min(grid, sel_grid), kBlk, 0, st>>>(a, sel_cursor);
+    k_shade<STRAT, false><<<grid, kBlk, 0, st>>>(a);
+    return kSph ? 2 : 1;
 }
 
 template <int STRAT> int bounce_blocks_per_sm()
@@ -811,7 +880,7 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
         size_t free_b = 0, total_b = 0;
         MCPT_CUDA(cudaSetDevice(scene->device));
         if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
-            const size_t per_slot = tree ? 640 : 208;  // bytes of queues + staging + hit + accumulators per path slot
+            const size_t per_slot = tree ? 688 : 224;  // bytes of queues + staging + hit + accumulators per path slot
             target = std::min(target, std::max<size_t>(npix, (free_b + scene->ws.bytes) / 2 / per_slot));
         } else cudaGetLastError();
     }
@@ -837,7 +906,7 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     const size_t o_lacc = place(slots * 16), o_contrib = place(tree ? cap * 16 : 16), o_ph = place(npix * 16), o_img = place(npix * 16);
     const size_t groups = (chunks + kGroup - 1) / kGroup;
     const size_t o_counts = place(chunks * 4), o_small = place(256 + groups * 4);
-    const size_t o_sel = place(sph ? slots * 8 : 16), o_wsum = place(sph ? npix * 4 : 16);
+    const size_t o_sel = place(sph ? slots * 8 : 16), o_wsum = place(sph ? npix * 4 : 16), o_sel4 = place(sph ? cap * 16 : 16);
     const bool nee = prm->strategy == MCPT_NEE_SPHERICAL || prm->strategy == MCPT_NEE_UNIFORM;
     const size_t o_hit = place(cap * 16);
     const size_t sqn = nee ? cap : 1;
@@ -863,8 +932,10 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     int* counts = (int*)(base + o_counts);
     int2* sel = (int2*)(base + o_sel);
     float* wsum_pix = (float*)(base + o_wsum);
+    float4* sel4 = (float4*)(base + o_sel4);
     float4* hit = (float4*)(base + o_hit);
-    // small block: [0] out_count, [1] shade ticket, [2] shadow-queue length, [3] k_extend cursor, [4] k_shadow cursor (ints),
+    // small block: [0] out_count, [1] shade ticket, [2] shadow-queue length, [3] k_extend cursor, [4] k_shadow cursor,
+    //              [5] k_lightsel cursor (ints; [1..8] are zeroed before every bounce),
     //              [64..] counters (u64 x CNT_N), [256..] group sums (int x groups)
     int* d_count = (int*)(base + o_small);
     int* d_ticket = d_count + 1;
@@ -873,6 +944,7 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     SQ.ids = (int2*)(base + o_sq[3]); SQ.count = d_count + 2;
     int* d_ext_cursor = d_count + 3;
     int* d_sh_cursor = d_count + 4;
+    int* d_sel_cursor = d_count + 5;
     unsigned long long* d_counters = (unsigned long long*)(base + o_small + 64);
     int* d_groupsum = (int*)(base + o_small + 256);
     volatile int* h_count = (volatile int*)ws.pinned;
@@ -904,6 +976,10 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ebps, k_extend, kBlk, 0);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sbps, k_shadow, kBlk, 0);
     const int ext_grid = sms * std::max(1, ebps), sh_grid = sms * std::max(1, sbps);
+    int lbps = 1;
+    if (prm->strategy == MCPT_MIS) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&lbps, k_lightsel<MCPT_MIS>, kBlk, 0);
+    else if (prm->strategy == MCPT_NEE_SPHERICAL) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&lbps, k_lightsel<MCPT_NEE_SPHERICAL>, kBlk, 0);
+    const int sel_grid = sms * std::max(1, lbps);
 
     McptStats S;
     std::memset(&S, 0, sizeof S);
@@ -923,7 +999,7 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
         const int b = std::min(batch, prm->spp - done);
         BounceArgs a;
         a.s = scene->d; a.cam = dc;
-        a.Lacc = Lacc; a.contrib = contrib; a.primary_hit = primary; a.sel = sel; a.wsum_pix = wsum_pix; a.counts = counts; a.groupsum = d_groupsum; a.ticket = d_ticket;
+        a.Lacc = Lacc; a.contrib = contrib; a.primary_hit = primary; a.sel = sel; a.wsum_pix = wsum_pix; a.sel4 = sel4; a.counts = counts; a.groupsum = d_groupsum; a.ticket = d_ticket;
         a.hit = hit; a.sq = SQ;
         a.counters = d_counters; a.seed = prm->seed; a.capacity = (int)cap; a.npix = (int)npix; a.batch_spp = b;
         a.sample_base = prm->spp_offset + done; a.max_depth = prm->max_depth; a.flags = prm->flags; a.p_rr = p_rr;
@@ -947,7 +1023,7 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
         if (jitter) {
             // jittered camera rays differ per sample: generate them into the dense queue and trace them like any bounce
             k_raygen<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(dc, (int)npix, count, a.sample_base, prm->seed, Q[0], tree ? 1 : 0, Lacc, d_count);
-            MCPT_CUDA(cudaMemsetAsync(d_ticket, 0, 16, st));
+            MCPT_CUDA(cudaMemsetAsync(d_ticket, 0, 32, st));
             k_extend<<<std::min(ext_grid, (count + kBlk - 1) / kBlk), kBlk, 0, st>>>(scene->d, Q[0].org, Q[0].dir, d_count, d_ext_cursor, hit);
             MCPT_CUDA(cudaGetLastError());
             S.kernel_launches += 2;
@@ -957,20 +1033,21 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
             if (prm->max_depth <= 0 && bounce >= 256) break;  // unlimited depth: RR has long emptied the queue
             a.in_count = count; a.bounce = bounce;
             const int nch = (count + 31) / 32, ngroups = (nch + kGroup - 1) / kGroup;
-            MCPT_CUDA(cudaMemsetAsync(d_ticket, 0, 16, st));
+            MCPT_CUDA(cudaMemsetAsync(d_ticket, 0, 32, st));
             MCPT_CUDA(cudaMemsetAsync(d_groupsum, 0, (size_t)ngroups * 4, st));
             MCPT_CUDA(cudaEventRecord(scene->ev[2], st));
             const int grid = std::min((nch + kBlk / 32 - 1) / (kBlk / 32), max_grid);
             const bool first = bounce == 0 && !jitter;
+            int nl = 1;
             switch (prm->strategy) {
-                case MCPT_NEE_SPHERICAL: launch_bounce<MCPT_NEE_SPHERICAL>(first, a, grid, st); break;
-                case MCPT_BRDF_ONLY: launch_bounce<MCPT_BRDF_ONLY>(first, a, grid, st); break;
-                case MCPT_MIS: launch_bounce<MCPT_MIS>(first, a, grid, st); break;
-                default: launch_bounce<MCPT_NEE_UNIFORM>(first, a, grid, st); break;
+                case MCPT_NEE_SPHERICAL: nl = launch_bounce<MCPT_NEE_SPHERICAL>(first, a, grid, sel_grid, d_sel_cursor, st); break;
+                case MCPT_BRDF_ONLY: nl = launch_bounce<MCPT_BRDF_ONLY>(first, a, grid, sel_grid, d_sel_cursor, st); break;
+                case MCPT_MIS: nl = launch_bounce<MCPT_MIS>(first, a, grid, sel_grid, d_sel_cursor, st); break;
+                default: nl = launch_bounce<MCPT_NEE_UNIFORM>(first, a, grid, sel_grid, d_sel_cursor, st); break;
             }
             MCPT_CUDA(cudaGetLastError());
             MCPT_CUDA(cudaEventRecord(scene->ev[4], st));
-            S.kernel_launches++;
+            S.kernel_launches += nl;
             S.elements += (uint64_t)count;
             const bool last = prm->max_depth > 0 && bounce + 1 >= prm->max_depth + 1;  // vertices deeper than max_depth never spawn
             if (!last) {

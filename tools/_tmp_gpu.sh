@@ -1,5 +1,11 @@
-timeout 300 python bench.py --steps 1 --warmup 1 --no-cpu-baseline > /dev/null 2>&1 && timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r1q_launches_veach.csv python bench.py --steps 1 --warmup 1 --no-cpu-baseline > /dev/null 2>&1
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:"k_shade|k_lightprep|k_extend|k_gather" --launch-skip 0 --launch-count 7 -o gpurun_out/r1q_veach_head -f python bench.py --steps 1 --warmup 1 --no-cpu-baseline > /dev/null 2>&1
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r1q_launches_soup.csv python bench.py --steps 1 --warmup 1 --no-cpu-baseline --workload soup-1m > /dev/null 2>&1
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:"k_extend|k_shadow" --launch-skip 0 --launch-count 2 -o gpurun_out/r1q_soup_trace -f python bench.py --steps 1 --warmup 1 --no-cpu-baseline --workload soup-1m > /dev/null 2>&1
-ls -la gpurun_out | tail -5
+for v in $VARIANTS; do
+  cp build_variants/libmcpt_$v.so monte_carlo_path_tracing_b200/libmcpt.so
+  timeout 300 python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/var_$v.json 2> gpurun_out/var_$v.err
+  python - <<PY
+import json
+j=json.load(open("gpurun_out/var_$v.json"))
+p=j["roofline"].get("pipeline",{})
+print("$v", "value %.1f e2e %.1f ms_shade %.1f ms_trace %.1f"%(j["value"], j["e2e"]["value"], p.get("ms_shade",0)/3, p.get("ms_trace",0)/3))
+PY
+done
+timeout 400 python -m pytest tests -m gpu -x -q 2>&1 | tail -5
