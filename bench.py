@@ -171,8 +171,9 @@ def _cpu_worker(args):
         k += 1
 
 
-def cpu_reference_run(stem, cam, strategy, max_depth, budget_s, seed=1, procs=None):
-    """All host cores, one reference process each, for ~budget_s seconds.  Returns dict(value Msamples/s, ...)."""
+def cpu_reference_run(stem, cam, strategy, max_depth, budget_s, seed=1, procs=None, row_stride=None):
+    """All host cores (or `procs`), one reference process each, for ~budget_s seconds.  Returns dict(value Msamples/s, ...).
+    Process w renders rows w, w + row_stride, ... (row_stride defaults to the process count)."""
     import multiprocessing as mp
     import oracle
     use_ref = oracle.ref_available() and strategy in ("NEE_SPHERICAL", "BRDF_ONLY", "MIS") and not isinstance(stem, dict)
@@ -183,7 +184,7 @@ def cpu_reference_run(stem, cam, strategy, max_depth, budget_s, seed=1, procs=No
     ctx = mp.get_context("spawn")
     t0 = time.time()
     with ctx.Pool(nproc) as pool:
-        res = pool.map(_cpu_worker, [(stem, cam_d, strategy, max_depth, w, nproc, budget_s, seed, use_ref) for w in range(nproc)])
+        res = pool.map(_cpu_worker, [(stem, cam_d, strategy, max_depth, w, row_stride or nproc, budget_s, seed, use_ref) for w in range(nproc)])
     wall = time.time() - t0
     samples = sum(r[0] for r in res)
     vertices = sum(r[1] for r in res)
@@ -403,6 +404,10 @@ def run_ours(args, wl_name, wl):
         })
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_reference_run(stem, cam, wl["strategy"], wl["max_depth"], args.cpu_seconds)
+            # the reference as designed is one thread (README.md:418): same rows, one process, a quarter of the budget
+            one = cpu_reference_run(stem, cam, wl["strategy"], wl["max_depth"], max(2.0, args.cpu_seconds / 4), procs=1,
+                                    row_stride=line["cpu_baseline"]["cores"])
+            line["cpu_baseline"]["value_1thread"] = one["value"]
             for k in ("samples", "seconds"):
                 line["cpu_baseline"].pop(k, None)
         print(json.dumps(line), flush=True)

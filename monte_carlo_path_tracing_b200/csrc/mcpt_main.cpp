@@ -10,9 +10,20 @@
 //   mcpt_render scene.obj scene.xml out.ppm [--spp 10] [--strategy mis|nee|nee_uniform|brdf] [--max-depth 0]
 //               [--width W --height H] [--seed 1] [--device 0] [--fix-pdf] [--fix-measure] [--jitter]
 //               [--lmax 380 --gamma 0.25] [--pfm out.pfm] [--ref-fov]
+//               [--every N] [--checkpoint file [--resume]] [--target-rel-error e] [--time-budget seconds]
+//
+// Progressive rendering (the reference keeps one all-or-nothing `buffer`, main.cpp:496,582, and lost day-long renders
+// to any crash): the spp are rendered in batches of N (default 64); the driver keeps the running sum of sample
+// radiances in FP64 and the sum of squared batch means of the luminance, writes both to the checkpoint file after
+// every batch (tmp + rename) and, with --resume, continues from it.  Samples are keyed by their global index
+// (spp_offset), so a resumed render adds exactly the samples an uninterrupted one would have.  --target-rel-error
+// stops when the mean over pixels of stderr(luminance) / (luminance + 1 % of the image mean) falls below e;
+// --time-budget stops after that many seconds of device time.
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <cstdint>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -22,6 +33,39 @@ static int fail(const char* what)
 {
     std::fprintf(stderr, "mcpt_render: %s: %s\n", what, mcpt_last_error());
     return 1;
+}
+
+// checkpoint file: header, then sum[W*H*3] and sumsq_lum[W*H] as doubles
+struct CkptHeader {
+    char magic[8];  // "MCPTCKP1"
+    int32_t width, height, strategy, max_depth, batch;
+    uint32_t flags, num_prims, num_lights, batches;
+    uint64_t seed, spp_done;
+};
+
+static bool ckpt_write(const std::string& path, const CkptHeader& h, const std::vector<double>& sum, const std::vector<double>& sq)
+{
+    const std::string tmp = path + ".tmp";
+    FILE* f = std::fopen(tmp.c_str(), "wb");
+    if (!f) return false;
+    bool ok = std::fwrite(&h, sizeof h, 1, f) == 1 && std::fwrite(sum.data(), 8, sum.size(), f) == sum.size() &&
+              std::fwrite(sq.data(), 8, sq.size(), f) == sq.size();
+    ok = (std::fclose(f) == 0) && ok;
+    return ok && std::rename(tmp.c_str(), path.c_str()) == 0;
+}
+
+static bool ckpt_read(const std::string& path, CkptHeader* h, std::vector<double>& sum, std::vector<double>& sq)
+{
+    FILE* f = std::fopen(path.c_str(), "rb");
+    if (!f) return false;
+    bool ok = std::fread(h, sizeof *h, 1, f) == 1 && std::memcmp(h->magic, "MCPTCKP1", 8) == 0 && h->width > 0 && h->height > 0;
+    if (ok) {
+        sum.resize((size_t)h->width * h->height * 3);
+        sq.resize((size_t)h->width * h->height);
+        ok = std::fread(sum.data(), 8, sum.size(), f) == sum.size() && std::fread(sq.data(), 8, sq.size(), f) == sq.size();
+    }
+    std::fclose(f);
+    return ok;
 }
 
 int main(int argc, char** argv)
@@ -39,7 +83,10 @@ int main(int argc, char** argv)
     double lmax = 380.0, gamma = 0.25;  // main.cpp:583
     bool ref_fov = false, have_cam_args = false;
     double eye[3] = {0, 0, 0}, lookat[3] = {0, 0, 1}, up[3] = {0, 1, 0}, fovy = 0;
-    std::string pfm;
+    std::string pfm, ckpt;
+    int every = 64;
+    bool resume = false;
+    double target_err = 0, time_budget = 0;
     auto vec3 = [&](int& i, double* v) { for (int k = 0; k < 3 && i + 1 < argc; k++) v[k] = std::atof(argv[++i]); };
     for (int i = 4; i < argc; i++) {
         std::string a = argv[i];
@@ -59,6 +106,11 @@ int main(int argc, char** argv)
         else if (a == "--lmax") lmax = std::atof(next());
         else if (a == "--gamma") gamma = std::atof(next());
         else if (a == "--pfm") pfm = next();
+        else if (a == "--every") every = std::atoi(next());
+        else if (a == "--checkpoint") ckpt = next();
+        else if (a == "--resume") resume = true;
+        else if (a == "--target-rel-error") target_err = std::atof(next());
+        else if (a == "--time-budget") time_budget = std::atof(next());
         else if (a == "--ref-fov") ref_fov = true;  // F7: the reference's tan(fovy/360) instead of tan(fovy/2 in radians)
         else if (a == "--eye") { vec3(i, eye); have_cam_args = true; }
         else if (a == "--lookat") vec3(i, lookat);
@@ -96,15 +148,75 @@ int main(int argc, char** argv)
     std::printf("bvh: %u nodes, %u leaves, depth %u, SAH cost %.2f; %.1f MB on device %d\n", nodes, leaves, depth, sah,
                 mcpt_scene_device_bytes(scene) / 1e6, device);
 
+    if (every <= 0) every = spp;
+    const size_t npix = (size_t)width * height;
+    std::vector<double> sum(npix * 3, 0.0), sq(npix, 0.0);
+    CkptHeader hd;
+    std::memset(&hd, 0, sizeof hd);
+    std::memcpy(hd.magic, "MCPTCKP1", 8);
+    hd.width = width; hd.height = height; hd.strategy = strategy; hd.max_depth = max_depth; hd.batch = every; hd.flags = flags;
+    hd.num_prims = desc->num_prims; hd.num_lights = desc->num_lights; hd.seed = seed;
+    if (resume && !ckpt.empty()) {
+        CkptHeader old;
+        std::vector<double> s0, q0;
+        if (ckpt_read(ckpt, &old, s0, q0)) {
+            const bool same = old.width == width && old.height == height && old.strategy == strategy && old.max_depth == max_depth &&
+                              old.batch == every && old.flags == flags && old.num_prims == hd.num_prims &&
+                              old.num_lights == hd.num_lights && old.seed == seed;
+            if (!same) { std::fprintf(stderr, "mcpt_render: %s was written for a different scene or different parameters\n", ckpt.c_str()); return 2; }
+            hd.spp_done = old.spp_done; hd.batches = old.batches;
+            sum.swap(s0); sq.swap(q0);
+            std::printf("resumed %s at %llu spp\n", ckpt.c_str(), (unsigned long long)hd.spp_done);
+        } else std::printf("no usable checkpoint at %s: starting from 0 spp\n", ckpt.c_str());
+    }
+
     McptRenderParams prm;
     std::memset(&prm, 0, sizeof prm);
-    prm.width = width; prm.height = height; prm.spp = spp; prm.spp_total = spp; prm.max_depth = max_depth;
+    prm.width = width; prm.height = height; prm.max_depth = max_depth;
     prm.strategy = strategy; prm.flags = flags; prm.seed = seed;
-    std::vector<float> film((size_t)width * height * 3);
-    McptStats st;
-    if (mcpt_render(scene, &cam, &prm, film.data(), &st)) return fail("rendering");
-    std::printf("%dx%d, %d spp: %.2f ms on the device, %.1f Msamples/s, %.1f Msample-bounces/s, %.1f Mrays/s, %u kernel launches\n",
-                width, height, spp, st.ms_total, st.paths / st.ms_total / 1e3, st.vertices / st.ms_total / 1e3,
+    std::vector<float> film(npix * 3);
+    McptStats tot;
+    std::memset(&tot, 0, sizeof tot);
+    double rel_err = 0;
+    while (hd.spp_done < (uint64_t)spp) {
+        const int n = (int)std::min<uint64_t>((uint64_t)every, (uint64_t)spp - hd.spp_done);
+        prm.spp = n; prm.spp_total = n; prm.spp_offset = (int32_t)hd.spp_done;  // film = mean of this batch
+        McptStats st;
+        if (mcpt_render(scene, &cam, &prm, film.data(), &st)) return fail("rendering");
+        double mean_lum = 0, err_acc = 0;
+        for (size_t p = 0; p < npix; p++) {
+            const double r = film[3 * p], g = film[3 * p + 1], b = film[3 * p + 2];
+            sum[3 * p] += n * r; sum[3 * p + 1] += n * g; sum[3 * p + 2] += n * b;
+            if (n == every) { const double l = (r + g + b) / 3; sq[p] += l * l; }  // full batches only: equal weights
+        }
+        hd.spp_done += (uint64_t)n;
+        if (n == every) hd.batches++;
+        tot.ms_total += st.ms_total; tot.paths += st.paths; tot.vertices += st.vertices; tot.kernel_launches += st.kernel_launches;
+        tot.rays_closest += st.rays_closest; tot.rays_shadow += st.rays_shadow; tot.rays_light += st.rays_light;
+        // standard error of the mean luminance from the spread of the batch means
+        const uint32_t B = hd.batches;
+        if (B >= 2) {
+            for (size_t p = 0; p < npix; p++) mean_lum += (sum[3 * p] + sum[3 * p + 1] + sum[3 * p + 2]) / 3 / (double)hd.spp_done;
+            mean_lum /= (double)npix;
+            for (size_t p = 0; p < npix; p++) {
+                const double m = (sum[3 * p] + sum[3 * p + 1] + sum[3 * p + 2]) / 3 / (double)hd.spp_done;
+                const double var = std::max(0.0, sq[p] / B - m * m) / (B - 1);
+                err_acc += std::sqrt(var) / (m + 0.01 * mean_lum + 1e-300);
+            }
+            rel_err = err_acc / (double)npix;
+        }
+        if (!ckpt.empty() && !ckpt_write(ckpt, hd, sum, sq)) { std::perror(ckpt.c_str()); return 1; }
+        if (spp > every)
+            std::printf("  %llu / %d spp, %.1f ms on the device%s\n", (unsigned long long)hd.spp_done, spp, tot.ms_total,
+                        B >= 2 ? (", mean relative error " + std::to_string(rel_err)).c_str() : "");
+        if (target_err > 0 && B >= 2 && rel_err < target_err) break;
+        if (time_budget > 0 && tot.ms_total >= time_budget * 1e3) break;
+    }
+    const double inv = hd.spp_done ? 1.0 / (double)hd.spp_done : 0.0;
+    for (size_t k = 0; k < film.size(); k++) film[k] = (float)(sum[k] * inv);
+    const McptStats& st = tot;
+    std::printf("%dx%d, %llu spp: %.2f ms on the device, %.1f Msamples/s, %.1f Msample-bounces/s, %.1f Mrays/s, %u kernel launches\n",
+                width, height, (unsigned long long)hd.spp_done, st.ms_total, st.paths / st.ms_total / 1e3, st.vertices / st.ms_total / 1e3,
                 (st.rays_closest + st.rays_shadow + st.rays_light) / st.ms_total / 1e3, st.kernel_launches);
 
     std::vector<uint8_t> rgb8(film.size());

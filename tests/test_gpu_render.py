@@ -177,3 +177,42 @@ def test_cpp_driver_end_to_end(scene_files, tmp_path, gpu_scene_of, arrays_of):
     assert np.array_equal(film, img)
     rgb8 = np.frombuffer(raw[len(hdr):], np.uint8).reshape(cam.height, cam.width, 3)
     assert np.array_equal(rgb8, gpu_scene_of("cornell-box").tonemap(img))
+
+
+@pytest.mark.gpu
+def test_cpp_driver_checkpoint_resume(scene_files, tmp_path, arrays_of):
+    """Progressive rendering: 12 spp in batches of 4 with a checkpoint after each batch; a run
+    stopped at 4 spp and resumed gives bit-for-bit the film of the uninterrupted run (samples are keyed by their global
+    index), and a checkpoint written with other parameters is refused."""
+    import os
+    import subprocess
+    drv = os.path.join(util.ROOT, "monte_carlo_path_tracing_b200", "mcpt_render")
+    _, stem = scene_files("cornell-box")
+    _, cam = arrays_of("cornell-box")
+    base = [drv, stem + ".obj", stem + ".xml"]
+    opts = ["--strategy", "mis", "--seed", "11", "--every", "4"]
+
+    def film_of(path):
+        data = path.read_bytes()
+        h2 = ("PF\n%d %d\n-1.0\n" % (cam.width, cam.height)).encode()
+        return np.frombuffer(data[len(h2):], np.float32).reshape(cam.height, cam.width, 3)[::-1]
+
+    full = tmp_path / "full.pfm"
+    r = subprocess.run(base + [str(tmp_path / "a.ppm"), "--spp", "12", "--pfm", str(full)] + opts, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    assert "12 / 12 spp" in r.stdout and "mean relative error" in r.stdout
+    ck = tmp_path / "render.ckpt"
+    r = subprocess.run(base + [str(tmp_path / "b.ppm"), "--spp", "4", "--checkpoint", str(ck)] + opts, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and ck.exists(), r.stderr
+    part = tmp_path / "part.pfm"
+    r = subprocess.run(base + [str(tmp_path / "c.ppm"), "--spp", "12", "--checkpoint", str(ck), "--resume", "--pfm", str(part)] + opts,
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "resumed" in r.stdout and "at 4 spp" in r.stdout, r.stdout + r.stderr
+    assert np.array_equal(film_of(full), film_of(part))
+    assert film_of(full).mean() > 0
+    r = subprocess.run(base + [str(tmp_path / "d.ppm"), "--spp", "12", "--checkpoint", str(ck), "--resume", "--seed", "12",
+                               "--strategy", "mis", "--every", "4"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 2 and "different" in r.stderr
+    # adaptive stop: a loose target ends the render before the spp budget is used up
+    r = subprocess.run(base + [str(tmp_path / "e.ppm"), "--spp", "4096", "--target-rel-error", "0.5"] + opts, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "4096 / 4096" not in r.stdout
