@@ -264,7 +264,8 @@ def run_ours(args, wl_name, wl):
     sc, stem = write_scene(wl, td)
     cam = sc.camera
     arrays = load_arrays(sc, stem)
-    scene = api.Scene(arrays, local)
+    scene = api.Scene(arrays, local, build=api.BUILD_GPU_LBVH if args.bvh == "gpu" else api.BUILD_HOST_SAH)
+    bvh_extra = dict(scene.build_info(), sah=scene.bvh_info()["sah"], nodes=scene.bvh_info()["nodes"])
     npix = cam.width * cam.height
     film = torch.zeros(npix * 3, dtype=torch.float32, device="cuda")
     stream = torch.cuda.current_stream().cuda_stream
@@ -307,11 +308,12 @@ def run_ours(args, wl_name, wl):
     scene.upload(); scene.render(cam, strategy, min(S, 2), **kw)
     sync()
     pinned = torch.empty(npix * 3, dtype=torch.float32).pin_memory()
+    pinned_np = pinned.numpy()  # the host film buffer the ABI call fills
     t0 = time.perf_counter()
     for k in range(args.steps):
         scene.upload()  # pinned H2D of the whole scene blob (geometry, BVHs, lights, materials)
         if world == 1:
-            img, _ = scene.render(cam, strategy, S, spp_offset=(k * world + rank) * S, spp_total=S * world, **kw)  # film D2H inside
+            scene.render(cam, strategy, S, spp_offset=(k * world + rank) * S, spp_total=S * world, out=pinned_np, **kw)  # film D2H inside
         else:
             # N ranks: the public multi-GPU path -- device film per rank, one NCCL sum, rank 0 reads the film back
             scene.render_device(cam, strategy, S, film.data_ptr(), stream=stream, spp_offset=(k * world + rank) * S,
@@ -400,7 +402,8 @@ def run_ours(args, wl_name, wl):
             "extra": {"Msample_bounces_per_s": tot["vertices"] * world / ms / 1e3,
                       "Mrays_per_s": (tot["rays_closest"] + tot["rays_shadow"] + tot["rays_light"]) * world / ms / 1e3,
                       "sample_bounces_per_path": tot["vertices"] / max(tot["paths"], 1),
-                      "time_to_1024spp_s": 1024.0 / (S * world) * (ms / args.steps) / 1e3},
+                      "time_to_1024spp_s": 1024.0 / (S * world) * (ms / args.steps) / 1e3,
+                      "bvh": bvh_extra},
         })
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_reference_run(stem, cam, wl["strategy"], wl["max_depth"], args.cpu_seconds)
@@ -428,6 +431,7 @@ def main():
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--bvh", default="host", choices=["host", "gpu"], help="scene BVH builder: host SAH (default) or device LBVH")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     if args.spp_per_step <= 0:

@@ -22,6 +22,7 @@ NEE_SPHERICAL, BRDF_ONLY, MIS, NEE_UNIFORM = 0, 1, 2, 3
 STRATEGY_NAMES = {0: "NEE_SPHERICAL", 1: "BRDF_ONLY", 2: "MIS", 3: "NEE_UNIFORM"}
 FIX_NEE_MEASURE, FIX_MIXTURE_PDF, JITTER, ACCUMULATE = 2, 4, 16, 64
 FP64, FP32 = 0, 1
+BUILD_HOST_SAH, BUILD_GPU_LBVH = 0, 1
 
 # every symbol include/mcpt.h declares (tests check the .so exports all of them)
 SYMBOLS = [
@@ -30,7 +31,8 @@ SYMBOLS = [
     "mcpt_phong_sample_batch", "mcpt_phong_pdf_batch", "mcpt_light_sample_uniform_batch",
     "mcpt_light_sample_spherical_batch", "mcpt_scene_geom_normals", "mcpt_scene_light_areas", "mcpt_scene_bvh_info",
     "mcpt_last_error", "mcpt_version", "mcpt_device_count", "mcpt_host_scene_load", "mcpt_host_scene_desc",
-    "mcpt_host_scene_camera", "mcpt_host_scene_free", "mcpt_host_bvh_check",
+    "mcpt_host_scene_camera", "mcpt_host_scene_free", "mcpt_host_bvh_check", "mcpt_scene_create_ex",
+    "mcpt_scene_build_info", "mcpt_scene_bvh_check",
 ]
 
 
@@ -180,13 +182,13 @@ def host_bvh_check(a: SceneArrays, lights_only: bool = False):
 class Scene:
     """A scene resident on one GPU (mcpt_scene_create)."""
 
-    def __init__(self, arrays: SceneArrays, device: int = 0):
+    def __init__(self, arrays: SceneArrays, device: int = 0, build: int = BUILD_HOST_SAH):
         self.lib = load()
         self.arrays = arrays
         d, self._keep = make_desc(arrays)
         self.P, self.L = d.num_prims, d.num_lights
         self.handle = C.c_void_p()
-        _check(self.lib.mcpt_scene_create(C.byref(d), C.c_int(device), C.byref(self.handle)))
+        _check(self.lib.mcpt_scene_create_ex(C.byref(d), C.c_int(device), C.c_uint32(build), C.byref(self.handle)))
         self.device = device
 
     def close(self):
@@ -209,9 +211,13 @@ class Scene:
         return p
 
     def render(self, cam: Camera, strategy: int, spp: int, max_depth: int = 0, flags: int = 0, seed: int = 1,
-               spp_offset: int = 0, spp_total: int = 0, batch_spp: int = 0, p_rr: float = 0.0):
-        """mcpt_render: host image out (H, W, 3) float32 linear radiance + stats dict."""
-        out = np.zeros((cam.height, cam.width, 3), np.float32)
+               spp_offset: int = 0, spp_total: int = 0, batch_spp: int = 0, p_rr: float = 0.0, out=None):
+        """mcpt_render: host image out (H, W, 3) float32 linear radiance + stats dict.  ``out``: an existing C-contiguous
+        float32 array of that shape (e.g. a view of pinned memory) to receive the film instead of a fresh one."""
+        if out is None:
+            out = np.zeros((cam.height, cam.width, 3), np.float32)
+        elif out.dtype != np.float32 or out.size != cam.height * cam.width * 3 or not out.flags.c_contiguous:
+            raise ValueError("out must be a C-contiguous float32 array of H*W*3 elements")
         st = Stats()
         p = self._params(cam, strategy, spp, max_depth, flags, seed, spp_offset, spp_total, batch_spp, p_rr)
         cc = camera_c(cam)
@@ -252,6 +258,18 @@ class Scene:
         out = np.zeros(self.L)
         _check(self.lib.mcpt_scene_light_areas(self.handle, _p(out)))
         return out
+
+    def build_info(self):
+        """ms spent on the scene BVH tree / on the whole scene_create, and the builder used (BUILD_*)."""
+        t = C.c_double(); a = C.c_double(); b = C.c_int32()
+        _check(self.lib.mcpt_scene_build_info(self.handle, C.byref(t), C.byref(a), C.byref(b)))
+        return dict(tree_ms=t.value, total_ms=a.value, builder=b.value)
+
+    def bvh_check(self) -> int:
+        """violations found in the scene BVH this scene holds (0 = sound)"""
+        e = C.c_uint32()
+        _check(self.lib.mcpt_scene_bvh_check(self.handle, C.byref(e)))
+        return e.value
 
     def bvh_info(self, lights=False):
         n = C.c_uint32(); l = C.c_uint32(); d = C.c_uint32(); s = C.c_double()

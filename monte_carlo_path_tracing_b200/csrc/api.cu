@@ -1,9 +1,11 @@
 // csrc/api.cu -- C ABI: scene lifetime, upload, introspection, host loaders, render entry points.
+#include <chrono>
 #include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <limits>
 #include <numeric>
+#include "bvh_tree.h"
 #include "mcpt_internal.h"
 
 namespace mcpt {
@@ -70,7 +72,23 @@ size_t mcpt_scene_device_bytes(const McptScene* s) { return s ? s->blob_bytes : 
 
 int mcpt_scene_create(const McptSceneDesc* desc, int device, McptScene** out)
 {
+    return mcpt_scene_create_ex(desc, device, MCPT_BUILD_HOST_SAH, out);
+}
+
+int mcpt_scene_build_info(const McptScene* s, double* tree_ms, double* total_ms, int32_t* builder)
+{
+    return guarded([&] {
+        if (!s) throw Error(MCPT_ERR_INVALID, "null scene");
+        if (tree_ms) *tree_ms = s->build_tree_ms;
+        if (total_ms) *total_ms = s->build_total_ms;
+        if (builder) *builder = s->builder;
+    });
+}
+
+int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_flags, McptScene** out)
+{
     if (out) *out = nullptr;
+    const auto t_begin = std::chrono::steady_clock::now();
     McptScene* s = nullptr;
     int rc = guarded([&] {
         if (!out) throw Error(MCPT_ERR_INVALID, "null output pointer");
@@ -116,7 +134,29 @@ int mcpt_scene_create(const McptSceneDesc* desc, int device, McptScene** out)
         // BVHs
         std::vector<int32_t> all(P);
         std::iota(all.begin(), all.end(), 0);
-        s->bvh = build_bvh(s->positions.data(), all.data(), P);
+        {
+            const auto t0 = std::chrono::steady_clock::now();
+            BvhTree T;
+            bool gpu = false;
+            if (build_flags & MCPT_BUILD_GPU_LBVH) {
+                gpu = build_tree_gpu(s->positions.data(), P, all.data(), P, device, T, nullptr);
+                s->build_tree_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+                if (gpu) {
+                    emit_bvh(s->positions.data(), T, s->bvh);
+                    if (s->bvh.max_depth4 * 3 + 1 > (uint32_t)kBvhStackDepth || s->bvh.max_depth + 1 > (uint32_t)kBvhStackDepth) {
+                        gpu = false;  // too deep for the traversal stacks (long runs of equal Morton codes): SAH instead
+                        s->bvh = Bvh();
+                        T = BvhTree();
+                    }
+                }
+            }
+            if (!gpu) {
+                build_tree_host(s->positions.data(), all.data(), P, T);
+                s->build_tree_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+                emit_bvh(s->positions.data(), T, s->bvh);
+            }
+            s->builder = gpu ? MCPT_BUILD_GPU_LBVH : MCPT_BUILD_HOST_SAH;
+        }
         std::vector<int32_t> lp(s->light_prim);
         std::sort(lp.begin(), lp.end());
         s->lbvh = build_bvh(s->positions.data(), lp.data(), lp.size());
@@ -237,6 +277,7 @@ int mcpt_scene_create(const McptSceneDesc* desc, int device, McptScene** out)
         d.tmin = s->extent * 1e-6f;
         MCPT_CUDA(cudaMemcpy(s->d_blob, s->h_blob, B.total, cudaMemcpyHostToDevice));
         for (int i = 0; i < 6; i++) MCPT_CUDA(cudaEventCreate(&s->ev[i]));
+        s->build_total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
         *out = s;
     });
     if (rc != MCPT_OK && s) { mcpt_scene_destroy(s); }
@@ -281,6 +322,98 @@ int mcpt_scene_bvh_info(const McptScene* s, int which, uint32_t* nodes, uint32_t
     });
 }
 
+// Structural check of a built BVH (both layouts): boxes nest, every listed prim sits in exactly one leaf with its own
+// vertices inside the leaf box, depths fit the traversal stacks.  Returns the number of violations.
+static uint32_t check_bvh(const mcpt::Bvh& b, const float* positions, uint32_t num_prims, const std::vector<int32_t>& ids)
+{
+    using namespace mcpt;
+    uint32_t errors = 0;
+    std::vector<uint32_t> seen(num_prims, 0);
+    struct Item { int32_t code; float lo[3], hi[3]; };
+    std::vector<Item> stack;
+    const float inf = std::numeric_limits<float>::infinity();
+    stack.push_back(Item{0, {-inf, -inf, -inf}, {inf, inf, inf}});
+    while (!stack.empty()) {
+        Item it = stack.back();
+        stack.pop_back();
+        if (it.code >= 0) {
+            if ((size_t)it.code >= b.nodes.size()) { errors++; continue; }
+            const BvhNode& n = b.nodes[it.code];
+            Item c0{n.c0, {n.n0.x, n.n0.z, n.n2.x}, {n.n0.y, n.n0.w, n.n2.y}};
+            Item c1{n.c1, {n.n1.x, n.n1.z, n.n2.z}, {n.n1.y, n.n1.w, n.n2.w}};
+            for (Item* c : {&c0, &c1}) {
+                if (c->lo[0] > c->hi[0]) continue;  // empty child
+                for (int k = 0; k < 3; k++)
+                    if (c->lo[k] < it.lo[k] - 1e-3f * std::fabs(it.lo[k]) - 1e-6f || c->hi[k] > it.hi[k] + 1e-3f * std::fabs(it.hi[k]) + 1e-6f) errors++;
+                stack.push_back(*c);
+            }
+        } else {
+            int code = ~it.code, first = code >> 3, cnt = (code & 7) + 1;
+            for (int i = 0; i < cnt; i++) {
+                if ((size_t)(first + i) * 3 + 2 >= b.tris.size()) { errors++; continue; }
+                int32_t prim;
+                std::memcpy(&prim, &b.tris[3 * (first + i)].w, 4);
+                if (prim < 0 || (uint32_t)prim >= num_prims) { errors++; continue; }
+                seen[prim]++;
+                for (int v = 0; v < 3; v++) {
+                    const f4& p = b.tris[3 * (first + i) + v];
+                    const float* q = positions + (size_t)prim * 9 + 3 * v;
+                    if (p.x != q[0] || p.y != q[1] || p.z != q[2]) errors++;
+                    float c[3] = {p.x, p.y, p.z};
+                    for (int k = 0; k < 3; k++)
+                        if (c[k] < it.lo[k] || c[k] > it.hi[k]) errors++;
+                }
+            }
+        }
+    }
+    for (int32_t id : ids) if (seen[id] != 1) errors++;
+    // the 4-wide collapse of the same tree (bvh.h, nodes4): same leaves, same containment
+    {
+        std::vector<uint32_t> seen4(num_prims, 0);
+        stack.push_back(Item{0, {-inf, -inf, -inf}, {inf, inf, inf}});
+        while (!stack.empty()) {
+            Item it = stack.back();
+            stack.pop_back();
+            if (it.code >= 0) {
+                if ((size_t)it.code * 7 + 6 >= b.nodes4.size()) { errors++; continue; }
+                const f4* q = &b.nodes4[(size_t)it.code * 7];
+                for (int k = 0; k < 4; k++) {
+                    auto comp = [k](const f4& v) { return k == 0 ? v.x : k == 1 ? v.y : k == 2 ? v.z : v.w; };
+                    Item c;
+                    float cf = comp(q[6]);
+                    std::memcpy(&c.code, &cf, 4);
+                    for (int a = 0; a < 3; a++) { c.lo[a] = comp(q[2 * a]); c.hi[a] = comp(q[2 * a + 1]); }
+                    if (c.lo[0] > c.hi[0]) continue;  // unused slot
+                    for (int a = 0; a < 3; a++)
+                        if (c.lo[a] < it.lo[a] - 1e-3f * std::fabs(it.lo[a]) - 1e-6f || c.hi[a] > it.hi[a] + 1e-3f * std::fabs(it.hi[a]) + 1e-6f) errors++;
+                    stack.push_back(c);
+                }
+            } else {
+                int code = ~it.code, first = code >> 3, cnt = (code & 7) + 1;
+                for (int i = 0; i < cnt; i++) {
+                    if ((size_t)(first + i) * 3 + 2 >= b.tris.size()) { errors++; continue; }
+                    int32_t prim;
+                    std::memcpy(&prim, &b.tris[3 * (first + i)].w, 4);
+                    if (prim < 0 || (uint32_t)prim >= num_prims) { errors++; continue; }
+                    seen4[prim]++;
+                    for (int v = 0; v < 3; v++) {
+                        const f4& p = b.tris[3 * (first + i) + v];
+                        float c[3] = {p.x, p.y, p.z};
+                        for (int a = 0; a < 3; a++)
+                            if (c[a] < it.lo[a] || c[a] > it.hi[a]) errors++;
+                    }
+                }
+            }
+        }
+        for (int32_t id : ids) if (seen4[id] != 1) errors++;
+        if (b.max_depth4 > b.max_depth + 1 || b.max_depth4 * 3 + 1 > (uint32_t)kBvhStackDepth) errors++;
+    }
+    uint32_t total = 0;
+    for (uint32_t v : seen) total += v;
+    if (total != ids.size()) errors++;
+    return errors;
+}
+
 int mcpt_host_bvh_check(const McptSceneDesc* desc, int lights_only, uint32_t out4[4], double* sah_cost)
 {
     return guarded([&] {
@@ -289,92 +422,20 @@ int mcpt_host_bvh_check(const McptSceneDesc* desc, int lights_only, uint32_t out
         if (lights_only) { ids.assign(desc->light_prim, desc->light_prim + desc->num_lights); std::sort(ids.begin(), ids.end()); }
         else { ids.resize(desc->num_prims); std::iota(ids.begin(), ids.end(), 0); }
         Bvh b = build_bvh(desc->positions, ids.data(), ids.size());
-        uint32_t errors = 0;
-        std::vector<uint32_t> seen(desc->num_prims, 0);
-        struct Item { int32_t code; float lo[3], hi[3]; };
-        std::vector<Item> stack;
-        const float inf = std::numeric_limits<float>::infinity();
-        stack.push_back(Item{0, {-inf, -inf, -inf}, {inf, inf, inf}});
-        while (!stack.empty()) {
-            Item it = stack.back();
-            stack.pop_back();
-            if (it.code >= 0) {
-                if ((size_t)it.code >= b.nodes.size()) { errors++; continue; }
-                const BvhNode& n = b.nodes[it.code];
-                Item c0{n.c0, {n.n0.x, n.n0.z, n.n2.x}, {n.n0.y, n.n0.w, n.n2.y}};
-                Item c1{n.c1, {n.n1.x, n.n1.z, n.n2.z}, {n.n1.y, n.n1.w, n.n2.w}};
-                for (Item* c : {&c0, &c1}) {
-                    if (c->lo[0] > c->hi[0]) continue;  // empty child
-                    for (int k = 0; k < 3; k++)
-                        if (c->lo[k] < it.lo[k] - 1e-3f * std::fabs(it.lo[k]) - 1e-6f || c->hi[k] > it.hi[k] + 1e-3f * std::fabs(it.hi[k]) + 1e-6f) errors++;
-                    stack.push_back(*c);
-                }
-            } else {
-                int code = ~it.code, first = code >> 3, cnt = (code & 7) + 1;
-                for (int i = 0; i < cnt; i++) {
-                    if ((size_t)(first + i) * 3 + 2 >= b.tris.size()) { errors++; continue; }
-                    int32_t prim;
-                    std::memcpy(&prim, &b.tris[3 * (first + i)].w, 4);
-                    if (prim < 0 || (uint32_t)prim >= desc->num_prims) { errors++; continue; }
-                    seen[prim]++;
-                    for (int v = 0; v < 3; v++) {
-                        const f4& p = b.tris[3 * (first + i) + v];
-                        const float* q = desc->positions + (size_t)prim * 9 + 3 * v;
-                        if (p.x != q[0] || p.y != q[1] || p.z != q[2]) errors++;
-                        float c[3] = {p.x, p.y, p.z};
-                        for (int k = 0; k < 3; k++)
-                            if (c[k] < it.lo[k] || c[k] > it.hi[k]) errors++;
-                    }
-                }
-            }
-        }
-        for (int32_t id : ids) if (seen[id] != 1) errors++;
-        // the 4-wide collapse of the same tree (bvh.h, nodes4): same leaves, same containment
-        {
-            std::vector<uint32_t> seen4(desc->num_prims, 0);
-            stack.push_back(Item{0, {-inf, -inf, -inf}, {inf, inf, inf}});
-            while (!stack.empty()) {
-                Item it = stack.back();
-                stack.pop_back();
-                if (it.code >= 0) {
-                    if ((size_t)it.code * 7 + 6 >= b.nodes4.size()) { errors++; continue; }
-                    const f4* q = &b.nodes4[(size_t)it.code * 7];
-                    for (int k = 0; k < 4; k++) {
-                        auto comp = [k](const f4& v) { return k == 0 ? v.x : k == 1 ? v.y : k == 2 ? v.z : v.w; };
-                        Item c;
-                        float cf = comp(q[6]);
-                        std::memcpy(&c.code, &cf, 4);
-                        for (int a = 0; a < 3; a++) { c.lo[a] = comp(q[2 * a]); c.hi[a] = comp(q[2 * a + 1]); }
-                        if (c.lo[0] > c.hi[0]) continue;  // unused slot
-                        for (int a = 0; a < 3; a++)
-                            if (c.lo[a] < it.lo[a] - 1e-3f * std::fabs(it.lo[a]) - 1e-6f || c.hi[a] > it.hi[a] + 1e-3f * std::fabs(it.hi[a]) + 1e-6f) errors++;
-                        stack.push_back(c);
-                    }
-                } else {
-                    int code = ~it.code, first = code >> 3, cnt = (code & 7) + 1;
-                    for (int i = 0; i < cnt; i++) {
-                        if ((size_t)(first + i) * 3 + 2 >= b.tris.size()) { errors++; continue; }
-                        int32_t prim;
-                        std::memcpy(&prim, &b.tris[3 * (first + i)].w, 4);
-                        if (prim < 0 || (uint32_t)prim >= desc->num_prims) { errors++; continue; }
-                        seen4[prim]++;
-                        for (int v = 0; v < 3; v++) {
-                            const f4& p = b.tris[3 * (first + i) + v];
-                            float c[3] = {p.x, p.y, p.z};
-                            for (int a = 0; a < 3; a++)
-                                if (c[a] < it.lo[a] || c[a] > it.hi[a]) errors++;
-                        }
-                    }
-                }
-            }
-            for (int32_t id : ids) if (seen4[id] != 1) errors++;
-            if (b.max_depth4 > b.max_depth + 1 || b.max_depth4 * 3 + 1 > (uint32_t)kBvhStackDepth) errors++;
-        }
-        uint32_t total = 0;
-        for (uint32_t v : seen) total += v;
-        if (total != ids.size()) errors++;
+        const uint32_t errors = check_bvh(b, desc->positions, desc->num_prims, ids);
         if (out4) { out4[0] = (uint32_t)b.nodes.size(); out4[1] = b.num_leaves; out4[2] = b.max_depth; out4[3] = errors; }
         if (sah_cost) *sah_cost = b.sah_cost;
+    });
+}
+
+// the same check on the scene BVH a McptScene actually holds (whichever builder made it)
+int mcpt_scene_bvh_check(const McptScene* s, uint32_t* errors)
+{
+    return guarded([&] {
+        if (!s || !errors) throw Error(MCPT_ERR_INVALID, "null argument");
+        std::vector<int32_t> ids(s->P);
+        std::iota(ids.begin(), ids.end(), 0);
+        *errors = check_bvh(s->bvh, s->positions.data(), s->P, ids);
     });
 }
 

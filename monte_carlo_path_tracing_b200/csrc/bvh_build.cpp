@@ -1,5 +1,6 @@
 // csrc/bvh_build.cpp -- binned-SAH top-down BVH builder (host), emitting the layout of bvh.h.
 #include "bvh.h"
+#include "bvh_tree.h"
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
@@ -9,26 +10,9 @@
 namespace mcpt {
 namespace {
 
-struct Box {
-    float lo[3], hi[3];
-    void reset() { for (int a = 0; a < 3; a++) { lo[a] = FLT_MAX; hi[a] = -FLT_MAX; } }
-    void grow(const float* p) { for (int a = 0; a < 3; a++) { lo[a] = std::min(lo[a], p[a]); hi[a] = std::max(hi[a], p[a]); } }
-    void grow(const Box& b) { for (int a = 0; a < 3; a++) { lo[a] = std::min(lo[a], b.lo[a]); hi[a] = std::max(hi[a], b.hi[a]); } }
-    float half_area() const
-    {
-        float d[3] = {hi[0] - lo[0], hi[1] - lo[1], hi[2] - lo[2]};
-        if (d[0] < 0 || d[1] < 0 || d[2] < 0) return 0.f;
-        return d[0] * d[1] + d[1] * d[2] + d[2] * d[0];
-    }
-};
-
+using Box = BvhBox;
+using TmpNode = BvhTmpNode;
 struct Ref { Box box; float c[3]; int32_t prim; };
-
-struct TmpNode {
-    Box box;
-    int32_t left = -1, right = -1;  // children (tmp indices) or -1
-    uint32_t first = 0, count = 0;  // leaf range into refs
-};
 
 constexpr int kBins = 16;
 constexpr float kCostTrav = 1.0f, kCostTri = 1.0f;
@@ -167,22 +151,12 @@ void emit_wide(const std::vector<TmpNode>& tmp, int32_t root, float tiny, Bvh& o
 
 }  // namespace
 
-Bvh build_bvh(const float* positions, const int32_t* prims, size_t count)
+// Tree -> the two traversal layouts of bvh.h.  Walks the tree from the root, so nodes a builder left unreachable
+// (the GPU builder's subtrees below a collapsed leaf) cost nothing; inner nodes are numbered depth-first.
+void emit_bvh(const float* positions, const BvhTree& T, Bvh& out)
 {
-    Bvh out;
-    Builder B;
-    B.refs.resize(count);
-    Box all; all.reset();
-    for (size_t i = 0; i < count; i++) {
-        Ref& r = B.refs[i];
-        r.prim = prims[i];
-        const float* v = positions + (size_t)prims[i] * 9;
-        r.box.reset();
-        for (int k = 0; k < 3; k++) r.box.grow(v + 3 * k);
-        for (int a = 0; a < 3; a++) r.c[a] = 0.5f * (r.box.lo[a] + r.box.hi[a]);
-        all.grow(r.box);
-    }
     const float inf = std::numeric_limits<float>::infinity();
+    const size_t count = T.order.size();
     if (count == 0) {
         BvhNode n; std::memset(&n, 0, sizeof n);
         n.n0 = {inf, -inf, inf, -inf}; n.n1 = n.n0; n.n2 = {inf, -inf, inf, -inf};
@@ -191,71 +165,106 @@ Bvh build_bvh(const float* positions, const int32_t* prims, size_t count)
         for (int k = 0; k < 3; k++) out.tris.push_back(f4{0, 0, 0, 0});
         for (int k = 0; k < 6; k++) out.nodes4.push_back(k % 2 ? f4{-inf, -inf, -inf, -inf} : f4{inf, inf, inf, inf});
         { float nc; int32_t code = kBvhNoChild; std::memcpy(&nc, &code, 4); out.nodes4.push_back(f4{nc, nc, nc, nc}); }
-        return out;
+        return;
     }
+    const std::vector<TmpNode>& tmp = T.tmp;
+    const int32_t root = T.root;
+    const Box& all = tmp[root].box;
     for (int a = 0; a < 3; a++) { out.lo[a] = all.lo[a]; out.hi[a] = all.hi[a]; }
     float ext = std::max(std::max(all.hi[0] - all.lo[0], all.hi[1] - all.lo[1]), all.hi[2] - all.lo[2]);
     float tiny = std::max(ext, 1e-30f) * 1e-7f;
-    B.tmp.reserve(count * 2);
-    int32_t root = B.build(0, (uint32_t)count, 0);
-    out.max_depth = B.max_depth;
 
-    // triangles in leaf order == refs order (leaves own contiguous ranges)
+    // triangles in leaf order == T.order (leaves own contiguous ranges)
     out.tris.resize(count * 3);
     for (size_t i = 0; i < count; i++) {
-        const float* v = positions + (size_t)B.refs[i].prim * 9;
+        const int32_t prim = T.order[i];
+        const float* v = positions + (size_t)prim * 9;
         f4 a = {v[0], v[1], v[2], 0.f};
-        std::memcpy(&a.w, &B.refs[i].prim, 4);
+        std::memcpy(&a.w, &prim, 4);
         out.tris[3 * i + 0] = a;
         out.tris[3 * i + 1] = f4{v[3], v[4], v[5], 0.f};
         out.tris[3 * i + 2] = f4{v[6], v[7], v[8], 0.f};
     }
 
-    // emit: every tmp inner node becomes one output node; a lone root leaf gets a wrapper node
     auto leaf_code = [](const TmpNode& t) { return (int32_t)~((t.first << 3) | (t.count - 1)); };
-    double root_area = std::max(B.tmp[root].box.half_area(), 1e-30f);
-    double sah = 0;
-    std::vector<int32_t> out_index(B.tmp.size(), -1);
-    uint32_t n_inner = 0;
-    for (size_t i = 0; i < B.tmp.size(); i++)
-        if (B.tmp[i].left >= 0) out_index[i] = (int32_t)n_inner++;
-    auto split_leaf = [&](TmpNode t, std::vector<TmpNode>& parts) {
-        // leaves larger than 8 cannot be encoded; cannot happen (kBvhMaxLeaf = 4) but keep it safe
-        while (t.count > 8) { TmpNode h = t; h.count = 8; parts.push_back(h); t.first += 8; t.count -= 8; }
-        parts.push_back(t);
-    };
-    (void)split_leaf;
     auto set_child = [&](BvhNode& n, int which, const TmpNode& c, int32_t code) {
         float lo[3], hi[3];
         pad_box(c.box, tiny, lo, hi);
         if (which == 0) { n.n0 = {lo[0], hi[0], lo[1], hi[1]}; n.n2.x = lo[2]; n.n2.y = hi[2]; n.c0 = code; }
         else { n.n1 = {lo[0], hi[0], lo[1], hi[1]}; n.n2.z = lo[2]; n.n2.w = hi[2]; n.c1 = code; }
     };
-    if (B.tmp[root].left < 0) {
+    if (tmp[root].left < 0) {  // a lone root leaf gets a wrapper node
         BvhNode n; std::memset(&n, 0, sizeof n);
-        set_child(n, 0, B.tmp[root], leaf_code(B.tmp[root]));
+        set_child(n, 0, tmp[root], leaf_code(tmp[root]));
         n.n1 = {inf, -inf, inf, -inf}; n.n2.z = inf; n.n2.w = -inf; n.c1 = ~0;
         out.nodes.push_back(n);
         out.num_leaves = 1;
-        out.sah_cost = kCostTrav + B.tmp[root].count * kCostTri;
-        emit_wide(B.tmp, root, tiny, out);
-        return out;
+        out.sah_cost = kCostTrav + tmp[root].count * kCostTri;
+        emit_wide(tmp, root, tiny, out);
+        return;
     }
-    out.nodes.resize(n_inner);
-    for (size_t i = 0; i < B.tmp.size(); i++) {
-        const TmpNode& t = B.tmp[i];
-        double rel = t.box.half_area() / root_area;
-        if (t.left < 0) { out.num_leaves++; sah += rel * t.count * kCostTri; continue; }
-        sah += rel * kCostTrav;
+    const double root_area = std::max(tmp[root].box.half_area(), 1e-30f);
+    double sah = 0;
+    struct Item { int32_t tmp_idx, out_idx; uint32_t depth; };
+    std::vector<Item> todo;
+    out.nodes.reserve(count);
+    out.nodes.emplace_back();
+    todo.push_back({root, 0, 0});
+    while (!todo.empty()) {
+        const Item it = todo.back();
+        todo.pop_back();
+        const TmpNode& t = tmp[it.tmp_idx];
+        sah += t.box.half_area() / root_area * kCostTrav;
         BvhNode n; std::memset(&n, 0, sizeof n);
-        const TmpNode& l = B.tmp[t.left];
-        const TmpNode& r = B.tmp[t.right];
-        set_child(n, 0, l, l.left >= 0 ? out_index[t.left] : leaf_code(l));
-        set_child(n, 1, r, r.left >= 0 ? out_index[t.right] : leaf_code(r));
-        out.nodes[out_index[i]] = n;
+        const int32_t kid[2] = {t.left, t.right};
+        for (int k = 0; k < 2; k++) {
+            const TmpNode& c = tmp[kid[k]];
+            int32_t code;
+            if (c.left < 0) {
+                code = leaf_code(c);
+                out.num_leaves++;
+                sah += c.box.half_area() / root_area * c.count * kCostTri;
+                out.max_depth = std::max(out.max_depth, it.depth + 1);
+            } else {
+                code = (int32_t)out.nodes.size();
+                out.nodes.emplace_back();
+                todo.push_back({kid[k], code, it.depth + 1});
+            }
+            set_child(n, k, c, code);
+        }
+        out.nodes[it.out_idx] = n;
     }
     out.sah_cost = sah;
-    emit_wide(B.tmp, root, tiny, out);
+    emit_wide(tmp, root, tiny, out);
+}
+
+bool build_tree_host(const float* positions, const int32_t* prims, size_t count, BvhTree& T)
+{
+    Builder B;
+    B.refs.resize(count);
+    for (size_t i = 0; i < count; i++) {
+        Ref& r = B.refs[i];
+        r.prim = prims[i];
+        const float* v = positions + (size_t)prims[i] * 9;
+        r.box.reset();
+        for (int k = 0; k < 3; k++) r.box.grow(v + 3 * k);
+        for (int a = 0; a < 3; a++) r.c[a] = 0.5f * (r.box.lo[a] + r.box.hi[a]);
+    }
+    T.order.resize(count);
+    if (count == 0) return true;
+    B.tmp.reserve(count * 2);
+    T.root = B.build(0, (uint32_t)count, 0);
+    for (size_t i = 0; i < count; i++) T.order[i] = B.refs[i].prim;
+    T.tmp.swap(B.tmp);
+    return true;
+}
+
+Bvh build_bvh(const float* positions, const int32_t* prims, size_t count)
+{
+    Bvh out;
+    BvhTree T;
+    build_tree_host(positions, prims, count, T);
+    emit_bvh(positions, T, out);
     return out;
 }
 

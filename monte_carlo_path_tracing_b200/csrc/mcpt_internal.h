@@ -59,6 +59,8 @@ struct McptScene {
     std::vector<double> geom_normals;  // [P][3]  get_unique_normal_of_facet
     std::vector<double> light_area;    // [L]
     mcpt::Bvh bvh, lbvh;
+    double build_tree_ms = 0, build_total_ms = 0;  // scene BVH: tree construction / whole scene_create
+    int32_t builder = 0;                           // MCPT_BUILD_*
     // one packed, pinned host image of everything the kernels read + its device twin
     void* h_blob = nullptr;
     void* d_blob = nullptr;

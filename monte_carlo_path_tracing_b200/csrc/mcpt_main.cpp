@@ -10,7 +10,7 @@
 //   mcpt_render scene.obj scene.xml out.ppm [--spp 10] [--strategy mis|nee|nee_uniform|brdf] [--max-depth 0]
 //               [--width W --height H] [--seed 1] [--device 0] [--fix-pdf] [--fix-measure] [--jitter]
 //               [--lmax 380 --gamma 0.25] [--pfm out.pfm] [--ref-fov]
-//               [--every N] [--checkpoint file [--resume]] [--target-rel-error e] [--time-budget seconds]
+//               [--gpu-bvh] [--every N] [--checkpoint file [--resume]] [--target-rel-error e] [--time-budget seconds]
 //
 // Progressive rendering (the reference keeps one all-or-nothing `buffer`, main.cpp:496,582, and lost day-long renders
 // to any crash): the spp are rendered in batches of N (default 64); the driver keeps the running sum of sample
@@ -85,7 +85,7 @@ int main(int argc, char** argv)
     double eye[3] = {0, 0, 0}, lookat[3] = {0, 0, 1}, up[3] = {0, 1, 0}, fovy = 0;
     std::string pfm, ckpt;
     int every = 64;
-    bool resume = false;
+    bool resume = false, gpu_bvh = false;
     double target_err = 0, time_budget = 0;
     auto vec3 = [&](int& i, double* v) { for (int k = 0; k < 3 && i + 1 < argc; k++) v[k] = std::atof(argv[++i]); };
     for (int i = 4; i < argc; i++) {
@@ -106,6 +106,7 @@ int main(int argc, char** argv)
         else if (a == "--lmax") lmax = std::atof(next());
         else if (a == "--gamma") gamma = std::atof(next());
         else if (a == "--pfm") pfm = next();
+        else if (a == "--gpu-bvh") gpu_bvh = true;  // Morton LBVH built on the device instead of the host SAH build
         else if (a == "--every") every = std::atoi(next());
         else if (a == "--checkpoint") ckpt = next();
         else if (a == "--resume") resume = true;
@@ -141,11 +142,14 @@ int main(int argc, char** argv)
     cam.pixellen = (ref_fov ? std::tan(cfov / 360.0) : std::tan(cfov * M_PI / 360.0)) * wl / (height * 0.5);
 
     McptScene* scene = nullptr;
-    if (mcpt_scene_create(desc, device, &scene)) return fail("creating the device scene");
+    if (mcpt_scene_create_ex(desc, device, gpu_bvh ? MCPT_BUILD_GPU_LBVH : MCPT_BUILD_HOST_SAH, &scene)) return fail("creating the device scene");
     uint32_t nodes = 0, leaves = 0, depth = 0;
-    double sah = 0;
+    double sah = 0, tree_ms = 0, total_ms = 0;
+    int32_t builder = 0;
     mcpt_scene_bvh_info(scene, 0, &nodes, &leaves, &depth, &sah);
-    std::printf("bvh: %u nodes, %u leaves, depth %u, SAH cost %.2f; %.1f MB on device %d\n", nodes, leaves, depth, sah,
+    mcpt_scene_build_info(scene, &tree_ms, &total_ms, &builder);
+    std::printf("bvh (%s, tree %.1f ms, scene ready in %.1f ms): %u nodes, %u leaves, depth %u, SAH cost %.2f; %.1f MB on device %d\n",
+                builder == MCPT_BUILD_GPU_LBVH ? "device LBVH" : "host SAH", tree_ms, total_ms, nodes, leaves, depth, sah,
                 mcpt_scene_device_bytes(scene) / 1e6, device);
 
     if (every <= 0) every = spp;

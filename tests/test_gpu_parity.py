@@ -4,6 +4,8 @@ restatement and the golden vectors of the compiled reference, on identical seede
 Bars (BASELINE.json north_star): intersection hit / triangle ids bit-exact; BRDF values, pdfs and
 sample directions within 1e-5 relative for fixed uniform inputs (tolerances written at each assert).
 """
+import copy
+
 import numpy as np
 import pytest
 
@@ -251,3 +253,55 @@ def test_soup_render_properties(soup):
     hi, _ = s.render(cam, api.NEE_UNIFORM, 4, max_depth=5, seed=3, spp_offset=4, spp_total=8)
     assert np.allclose(lo + hi, x, rtol=1e-5, atol=1e-6)
     assert st["primary_hits"] > 0.3 * cam.width * cam.height
+
+
+# ---- GPU BVH build --------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["cornell-box", "veach-mis"])
+def test_gpu_bvh_same_hits_and_images(name, golden, arrays_of, gpu_scene_of):
+    """A scene whose BVH was built on the device (Morton LBVH, csrc/bvh_gpu.cu) answers every query exactly like the
+    host-SAH scene: golden closest hits bit for bit in FP64, identical FP32 stream-traversal hits, identical film."""
+    a, cam = arrays_of(name)
+    g = golden(name)
+    s = api.Scene(a, 0, build=api.BUILD_GPU_LBVH)
+    try:
+        info = s.build_info()
+        assert info["builder"] == api.BUILD_GPU_LBVH and s.bvh_check() == 0
+        ro, rd = util.random_rays(a, 3000, 101)
+        prim, bgt = s.closest(ro, rd, None, False, api.FP64)
+        assert np.array_equal(prim, g["closest_brute_prim"]) and np.array_equal(bgt, g["closest_brute_bgt"])
+        ro, rd, ex = util.surface_rays(a, 3000, 102)
+        prim, bgt = s.closest(ro, rd, ex, False, api.FP64)
+        assert np.array_equal(prim, g["surf_brute_prim"]) and np.array_equal(bgt, g["surf_brute_bgt"])
+        ref = gpu_scene_of(name)
+        p1, b1 = s.closest(ro, rd, ex, False, api.FP32)
+        p0, b0 = ref.closest(ro, rd, ex, False, api.FP32)
+        assert np.array_equal(p1, p0) and np.array_equal(b1, b0)
+        small = copy.copy(cam)
+        small.width, small.height = 96, 64
+        for strat in (api.NEE_UNIFORM, api.MIS):
+            i1, _ = s.render(small, strat, 4, max_depth=4, seed=5)
+            i0, _ = ref.render(small, strat, 4, max_depth=4, seed=5)
+            assert np.array_equal(i1, i0)
+    finally:
+        s.close()
+
+
+def test_gpu_bvh_soup(soup):
+    """200 k random triangles: the device-built tree is sound (every prim in exactly one leaf, boxes nest, depths fit
+    the traversal stacks), is built much faster than the host SAH tree, and gives the same FP32 hits."""
+    a, s_host, _ = soup
+    s_gpu = api.Scene(a, 0, build=api.BUILD_GPU_LBVH)
+    try:
+        bi, hi = s_gpu.build_info(), s_host.build_info()
+        assert bi["builder"] == api.BUILD_GPU_LBVH and hi["builder"] == api.BUILD_HOST_SAH
+        assert s_gpu.bvh_check() == 0 and s_host.bvh_check() == 0
+        ig, ih = s_gpu.bvh_info(), s_host.bvh_info()
+        assert ig["leaves"] >= len(a.material_id) // 4 and ig["sah"] < 3.0 * ih["sah"]
+        ro, rd = util.random_rays(a, 50000, 31)
+        p1, b1 = s_gpu.closest(ro, rd, None, False, api.FP32)
+        p0, b0 = s_host.closest(ro, rd, None, False, api.FP32)
+        assert np.array_equal(p1, p0) and np.array_equal(b1, b0) and (p0 >= 0).mean() > 0.2
+        print("soup build ms: gpu tree %.1f (total %.1f), host tree %.1f (total %.1f); SAH %.1f vs %.1f" % (
+            bi["tree_ms"], bi["total_ms"], hi["tree_ms"], hi["total_ms"], ig["sah"], ih["sah"]))
+    finally:
+        s_gpu.close()

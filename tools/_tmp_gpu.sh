@@ -1,11 +1,8 @@
-for v in $VARIANTS; do
-  cp build_variants/libmcpt_$v.so monte_carlo_path_tracing_b200/libmcpt.so
-  timeout 300 python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/var_$v.json 2> gpurun_out/var_$v.err
-  python - <<PY
+timeout 600 python -m pytest tests -m gpu -x -q -k "gpu_bvh or checkpoint or cpp_driver" -s 2>&1 | tail -12
+for b in host gpu; do
+timeout 300 python bench.py --steps 3 --warmup 3 --workload soup-1m --no-cpu-baseline --bvh $b > gpurun_out/r1u_bench_soup_$b.json 2> gpurun_out/r1u_bench_soup_$b.err; tail -c 300 gpurun_out/r1u_bench_soup_$b.err
+python - <<PY
 import json
-j=json.load(open("gpurun_out/var_$v.json"))
-p=j["roofline"].get("pipeline",{})
-print("$v", "value %.1f e2e %.1f ms_shade %.1f ms_trace %.1f"%(j["value"], j["e2e"]["value"], p.get("ms_shade",0)/3, p.get("ms_trace",0)/3))
+j=json.load(open("gpurun_out/r1u_bench_soup_$b.json")); print("$b", j["value"], j["e2e"]["value"], j["extra"]["bvh"])
 PY
 done
-timeout 400 python -m pytest tests -m gpu -x -q 2>&1 | tail -5
