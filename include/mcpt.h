@@ -38,7 +38,12 @@ typedef enum McptStrategy {
     MCPT_NEE_SPHERICAL = 0, /* shade(): 1 spherical-triangle light sample + 1 BRDF sample (main.cpp:298) */
     MCPT_BRDF_ONLY = 1,     /* shade_with_brdf() */
     MCPT_MIS = 2,           /* shade_with_mis(): both samples recursed, balance heuristic (path tree, F6) */
-    MCPT_NEE_UNIFORM = 3    /* shade() with the uniform-area sampler of the commented line main.cpp:297 */
+    MCPT_NEE_UNIFORM = 3,   /* shade() with the uniform-area sampler of the commented line main.cpp:297 */
+    MCPT_MIS_SINGLE = 4     /* NOT a reference estimator: textbook single-path MIS -- the spherical-
+                             * triangle light sample contributes emitted light only (shadow ray, balance weight), only the
+                             * BRDF sample continues, and emission found by it is weighted pdf_b / (pdf_b + pdf_light).
+                             * Same expectation as MCPT_MIS with MCPT_FIX_MIXTURE_PDF | MCPT_FIX_NEE_MEASURE, no path
+                             * tree, one visibility ray per vertex: the fast mode. */
 } McptStrategy;
 
 /* flags: 0 == the reference's estimators as written (F8, F9 reproduced).  The stale-MIS-state bug

@@ -18,7 +18,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libmcpt.so")
 CSRC = os.path.join(HERE, "csrc")
 
-NEE_SPHERICAL, BRDF_ONLY, MIS, NEE_UNIFORM = 0, 1, 2, 3
+NEE_SPHERICAL, BRDF_ONLY, MIS, NEE_UNIFORM, MIS_SINGLE = 0, 1, 2, 3, 4
 STRATEGY_NAMES = {0: "NEE_SPHERICAL", 1: "BRDF_ONLY", 2: "MIS", 3: "NEE_UNIFORM"}
 FIX_NEE_MEASURE, FIX_MIXTURE_PDF, JITTER, ACCUMULATE = 2, 4, 16, 64
 FP64, FP32 = 0, 1

@@ -7,7 +7,7 @@
 // the image (saveimage, :597 -> binary PPM; the EasyX window is a graphics API and is not reproduced).
 // Every parameter the reference hard-codes in source is a command-line option.  Uses only include/mcpt.h.
 //
-//   mcpt_render scene.obj scene.xml out.ppm [--spp 10] [--strategy mis|nee|nee_uniform|brdf] [--max-depth 0]
+//   mcpt_render scene.obj scene.xml out.ppm [--spp 10] [--strategy mis|mis_single|nee|nee_uniform|brdf] [--max-depth 0]
 //               [--width W --height H] [--seed 1] [--device 0] [--fix-pdf] [--fix-measure] [--jitter]
 //               [--lmax 380 --gamma 0.25] [--pfm out.pfm] [--ref-fov]
 //               [--gpu-bvh] [--every N] [--checkpoint file [--resume]] [--target-rel-error e] [--time-budget seconds]
@@ -94,7 +94,7 @@ int main(int argc, char** argv)
         if (a == "--spp") spp = std::atoi(next());
         else if (a == "--strategy") {
             std::string s = next();
-            strategy = s == "mis" ? MCPT_MIS : s == "brdf" ? MCPT_BRDF_ONLY : s == "nee_uniform" ? MCPT_NEE_UNIFORM : MCPT_NEE_SPHERICAL;
+            strategy = s == "mis" ? MCPT_MIS : s == "mis_single" ? MCPT_MIS_SINGLE : s == "brdf" ? MCPT_BRDF_ONLY : s == "nee_uniform" ? MCPT_NEE_UNIFORM : MCPT_NEE_SPHERICAL;
         } else if (a == "--max-depth") max_depth = std::atoi(next());
         else if (a == "--width") width = std::atoi(next());
         else if (a == "--height") height = std::atoi(next());

@@ -430,8 +430,8 @@ __global__ void __launch_bounds__(kBlk, MCPT_SEL_MINBLK) k_lightsel(const Bounce
                     uint64_t node = (uint64_t)a.bounce + 1;
                     if (kTree) { const uint2 nd = a.in.node[i]; node = ((uint64_t)nd.y << 32) | nd.x; }
                     need = true;
-                    // MIS: roulette before any sampling (main.cpp:429-437); NEE samples the light first (:300-316)
-                    if (kTree) need = !rr_forced && !(rng_draw4(a.seed, pixel, sample, node, 0).u[0] > a.p_rr);
+                    // MIS (both forms): roulette before any sampling (main.cpp:429-437); NEE samples the light first (:300-316)
+                    if (kTree || STRAT == MCPT_MIS_SINGLE) need = !rr_forced && !(rng_draw4(a.seed, pixel, sample, node, 0).u[0] > a.p_rr);
                     if (need) { u = rng_draw4(a.seed, pixel, sample, node, 1).u[0]; p = v.p; N = v.N; }
                 }
             }
@@ -444,7 +444,7 @@ __global__ void __launch_bounds__(kBlk, MCPT_SEL_MINBLK) k_lightsel(const Bounce
 }
 
 // ---- one bounce --------------------------------------------------------------------------------------------
-struct Child { f3 o, d, thr; int exclude; uint64_t node; };
+struct Child { f3 o, d, thr; int exclude; uint64_t node; float misw; };
 
 // k_shade: everything shade* does at one vertex except the scene-BVH traversals, which the wavefront hands to
 // k_extend (closest hit of the children) and k_shadow (NEE visibility).  FIRST = primary vertices without jitter:
@@ -457,7 +457,9 @@ __global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceA
 {
     constexpr bool kTree = (STRAT == MCPT_MIS);
     constexpr bool kNee = (STRAT == MCPT_NEE_SPHERICAL || STRAT == MCPT_NEE_UNIFORM);
-    constexpr bool kSph = (STRAT == MCPT_NEE_SPHERICAL || STRAT == MCPT_MIS);
+    constexpr bool kSingle = (STRAT == MCPT_MIS_SINGLE);  // single-path MIS: NEE's visibility ray + MIS weights
+    constexpr bool kShadow = kNee || kSingle;              // strategies that queue a visibility ray per vertex
+    constexpr bool kSph = (STRAT == MCPT_NEE_SPHERICAL || STRAT == MCPT_MIS || kSingle);
     __shared__ int stack[kStackSm * kBlk];
     const DScene& s = a.s;
     const int lane = threadIdx.x & 31;
@@ -477,6 +479,7 @@ __global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceA
         f3 o = mk<float>(0.f, 0.f, 0.f), d = mk<float>(0.f, 0.f, 1.f), thr = mk<float>(1.f, 1.f, 1.f);
         int slot = 0, exclude = -1;
         uint64_t node = 1;
+        float misw = 1.f;  // single-path MIS: weight of emission found by this ray (1 for camera rays)
         Hit h;
         h.prim = -1; h.b = h.g = h.t = 0.f;
         uint32_t pixel = 0, sample = 0;
@@ -493,6 +496,7 @@ __global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceA
             } else {
                 const float4 qo = a.in.org[i], qd = a.in.dir[i], qt = a.in.thr[i];
                 o = to_f3(qo); d = to_f3(qd); thr = to_f3(qt);
+                if (kSingle && a.bounce > 0) misw = qt.w;
                 exclude = __float_as_int(qo.w);
                 slot = __float_as_int(qd.w);
                 pixel = (uint32_t)(slot % a.npix);
@@ -518,7 +522,7 @@ __global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceA
             else if (v.light >= 0) {      // emissive: self-emission only
                 // shade(): an indirect ray that lands on a light contributes 0 (main.cpp:338); the emission
                 // return of main.cpp:284-288 is only reachable from the camera ray.
-                if (!kNee || a.bounce == 0) contrib = thr * to_f3(__ldg(s.lights + 5 * v.light + 4));
+                if (!kNee || a.bounce == 0) contrib = thr * to_f3(__ldg(s.lights + 5 * v.light + 4)) * misw;
                 alive = false;
             } else mat = load_mat(s, v.mat);
         }
@@ -578,6 +582,7 @@ __global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceA
                         Child& c = ch[n_out++];
                         c.o = p; c.d = wl; c.exclude = h.prim; c.node = node * 2;
                         c.thr = thr * f * (cosN / (pl + pp) / a.p_rr);
+                        c.misw = 0.f;
                     } else {
                         // NEE (main.cpp:300-316): visible iff the closest hit along wl IS the sampled triangle
                         const float cosL = -dot(wl, ngl);
@@ -586,7 +591,9 @@ __global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceA
                             float be, ga, tl;
                             if (tri_test_fast(p, wl, lv0, to_f3(q1), to_f3(q2), s.tmin, &be, &ga, &tl)) {
                                 const f3 f = phong_eval<float>(N, wl, wo, mat);
-                                const float g = (a.flags & MCPT_FIX_NEE_MEASURE) ? cosN / pl : cosN * cosL / (tl * tl) / pl;  // F9
+                                float g = (a.flags & MCPT_FIX_NEE_MEASURE) ? cosN / pl : cosN * cosL / (tl * tl) / pl;  // F9
+                                // single-path MIS: solid-angle estimator with the balance weight pl / (pl + pp), after the roulette
+                                if (kSingle) g = cosN / (pl + phong_pdf<float>(N, wl, wo, mat)) / a.p_rr;
                                 sh_need = true; sh_d = wl; sh_t = tl; sh_prim = lprim;
                                 sh_c = thr * Le * f * g;
                             }
@@ -625,7 +632,7 @@ __global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceA
             if (!(cosN < 0.f) && pdf > 0.f) {
                 if (a.flags & MCPT_FIX_MIXTURE_PDF) pdf = phong_pdf<float>(N, wi, wo, mat);  // F8
                 float lpdf = 0.f;
-                if (STRAT == MCPT_MIS && wsum > 0.f) {
+                if ((STRAT == MCPT_MIS || kSingle) && wsum > 0.f) {
                     // pdf of wi under light sampling (main.cpp:484-489): nearest EMISSIVE triangle along wi, occluders
                     // ignored; it counts iff it survived this vertex's culls (Mylight.cpp:484-493, evaluated for the
                     // current vertex -- F10 not reproduced)
@@ -640,6 +647,11 @@ __global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceA
                 Child& c = ch[n_out++];
                 c.o = p; c.d = wi; c.exclude = h.prim; c.node = kTree ? node * 2 + 1 : 0;
                 c.thr = thr * f * (cosN / (pdf + lpdf) / a.p_rr);
+                c.misw = 0.f;
+                if (kSingle) {  // reflected light keeps weight 1; only emission found by this ray takes the balance weight
+                    c.thr = thr * f * (cosN / pdf / a.p_rr);
+                    c.misw = pdf / (pdf + lpdf);
+                }
             }
         }
 
@@ -662,7 +674,7 @@ __global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceA
                 const Child& c = ch[k];
                 a.out.org[dst] = make_float4(c.o.x, c.o.y, c.o.z, __int_as_float(c.exclude));
                 a.out.dir[dst] = make_float4(c.d.x, c.d.y, c.d.z, __int_as_float(slot));
-                a.out.thr[dst] = make_float4(c.thr.x, c.thr.y, c.thr.z, 0.f);
+                a.out.thr[dst] = make_float4(c.thr.x, c.thr.y, c.thr.z, kSingle ? c.misw : 0.f);
                 if (kTree) a.out.node[dst] = make_uint2((uint32_t)c.node, (uint32_t)(c.node >> 32));
             }
             if (lane == 0) {
@@ -671,7 +683,7 @@ __global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceA
                 if (total) atomicAdd(a.groupsum + chunk / kGroup, total);
             }
         }
-        if (kNee) {
+        if (kShadow) {
             // visibility rays: unordered append (every slot owns at most one per bounce, so k_shadow's
             // Lacc[slot] += contribution needs no ordering), one atomic per warp
             const unsigned ms = __ballot_sync(kFull, sh_need);
@@ -821,7 +833,7 @@ __global__ void k_tonemap(const float* __restrict__ rgb, size_t n3, double A, do
 template <int STRAT>
 int launch_bounce(bool first, const BounceArgs& a, int grid, int sel_grid, int* sel_cursor, cudaStream_t st)
 {
-    constexpr bool kSph = (STRAT == MCPT_NEE_SPHERICAL || STRAT == MCPT_MIS);
+    constexpr bool kSph = (STRAT == MCPT_NEE_SPHERICAL || STRAT == MCPT_MIS || STRAT == MCPT_MIS_SINGLE);
     if (first) { k_shade<STRAT, true><<<grid, kBlk, 0, st>>>(a); return 1; }
     if constexpr (kSph) k_lightsel<STRAT><<<std::min(grid, sel_grid), kBlk, 0, st>>>(a, sel_cursor);
     k_shade<STRAT, false><<<grid, kBlk, 0, st>>>(a);
@@ -867,7 +879,7 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
 {
     const int W = prm->width, H = prm->height;
     if (W <= 0 || H <= 0 || prm->spp <= 0) throw Error(MCPT_ERR_INVALID, "width, height and spp must be positive");
-    if (prm->strategy < 0 || prm->strategy > 3) throw Error(MCPT_ERR_INVALID, "unknown strategy");
+    if (prm->strategy < 0 || prm->strategy > 4) throw Error(MCPT_ERR_INVALID, "unknown strategy");
     if (prm->strategy != MCPT_BRDF_ONLY && scene->L == 0) throw Error(MCPT_ERR_INVALID, "light sampling needs at least one light");
     const size_t npix = (size_t)W * H;
     if (npix > (1u << 30)) throw Error(MCPT_ERR_INVALID, "image too large");
@@ -890,7 +902,8 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     if (slots > (1u << 30)) throw Error(MCPT_ERR_INVALID, "batch_spp * pixels too large");
     const size_t cap = tree ? slots * 3 : slots;
     const size_t chunks = (cap + 31) / 32 + 1;
-    const bool sph = prm->strategy == MCPT_NEE_SPHERICAL || prm->strategy == MCPT_MIS;
+    const bool single = prm->strategy == MCPT_MIS_SINGLE;
+    const bool sph = prm->strategy == MCPT_NEE_SPHERICAL || prm->strategy == MCPT_MIS || single;
 
     // workspace carve-up
     size_t off = 0;
@@ -907,7 +920,7 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     const size_t groups = (chunks + kGroup - 1) / kGroup;
     const size_t o_counts = place(chunks * 4), o_small = place(256 + groups * 4);
     const size_t o_sel = place(sph ? slots * 8 : 16), o_wsum = place(sph ? npix * 4 : 16), o_sel4 = place(sph ? cap * 16 : 16);
-    const bool nee = prm->strategy == MCPT_NEE_SPHERICAL || prm->strategy == MCPT_NEE_UNIFORM;
+    const bool nee = prm->strategy == MCPT_NEE_SPHERICAL || prm->strategy == MCPT_NEE_UNIFORM || prm->strategy == MCPT_MIS_SINGLE;  // queues visibility rays
     const size_t o_hit = place(cap * 16);
     const size_t sqn = nee ? cap : 1;
     const size_t o_sq[4] = {place(sqn * 16), place(sqn * 16), place(sqn * 16), place(sqn * 8)};
@@ -970,6 +983,7 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     int bps = prm->strategy == MCPT_NEE_SPHERICAL ? bounce_blocks_per_sm<MCPT_NEE_SPHERICAL>()
               : prm->strategy == MCPT_BRDF_ONLY   ? bounce_blocks_per_sm<MCPT_BRDF_ONLY>()
               : prm->strategy == MCPT_MIS         ? bounce_blocks_per_sm<MCPT_MIS>()
+              : prm->strategy == MCPT_MIS_SINGLE  ? bounce_blocks_per_sm<MCPT_MIS_SINGLE>()
                                                   : bounce_blocks_per_sm<MCPT_NEE_UNIFORM>();
     const int max_grid = sms * bps;
     int ebps = 1, sbps = 1;
@@ -979,6 +993,7 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     int lbps = 1;
     if (prm->strategy == MCPT_MIS) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&lbps, k_lightsel<MCPT_MIS>, kBlk, 0);
     else if (prm->strategy == MCPT_NEE_SPHERICAL) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&lbps, k_lightsel<MCPT_NEE_SPHERICAL>, kBlk, 0);
+    else if (prm->strategy == MCPT_MIS_SINGLE) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&lbps, k_lightsel<MCPT_MIS_SINGLE>, kBlk, 0);
     const int sel_grid = sms * std::max(1, lbps);
 
     McptStats S;
@@ -1015,7 +1030,7 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pbps, k_lightprep, kBlk, dyn);
             const size_t npairs = (npix + 1) / 2;
             const int pgrid = (int)std::min<size_t>((npairs + kBlk / 32 - 1) / (kBlk / 32), (size_t)sms * std::max(1, pbps));
-            k_lightprep<<<pgrid, kBlk, dyn, st>>>(scene->d, dc, primary, (int)npix, b, a.sample_base, prm->seed, p_rr, tree ? 1 : 0,
+            k_lightprep<<<pgrid, kBlk, dyn, st>>>(scene->d, dc, primary, (int)npix, b, a.sample_base, prm->seed, p_rr, (tree || single) ? 1 : 0,
                                                   prm->max_depth, use_cdf, sel, wsum_pix);
             MCPT_CUDA(cudaGetLastError());
             S.kernel_launches++;
@@ -1043,6 +1058,7 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
                 case MCPT_NEE_SPHERICAL: nl = launch_bounce<MCPT_NEE_SPHERICAL>(first, a, grid, sel_grid, d_sel_cursor, st); break;
                 case MCPT_BRDF_ONLY: nl = launch_bounce<MCPT_BRDF_ONLY>(first, a, grid, sel_grid, d_sel_cursor, st); break;
                 case MCPT_MIS: nl = launch_bounce<MCPT_MIS>(first, a, grid, sel_grid, d_sel_cursor, st); break;
+                case MCPT_MIS_SINGLE: nl = launch_bounce<MCPT_MIS_SINGLE>(first, a, grid, sel_grid, d_sel_cursor, st); break;
                 default: nl = launch_bounce<MCPT_NEE_UNIFORM>(first, a, grid, sel_grid, d_sel_cursor, st); break;
             }
             MCPT_CUDA(cudaGetLastError());

@@ -216,3 +216,37 @@ def test_cpp_driver_checkpoint_resume(scene_files, tmp_path, arrays_of):
     # adaptive stop: a loose target ends the render before the spp budget is used up
     r = subprocess.run(base + [str(tmp_path / "e.ppm"), "--spp", "4096", "--target-rel-error", "0.5"] + opts, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "4096 / 4096" not in r.stdout
+
+
+def test_single_path_mis_converges_to_the_same_image(scene_name, gpu_scene_of, oracle_of, arrays_of):
+    """MCPT_MIS_SINGLE (not a reference estimator): textbook single-path MIS.  Same expectation as
+    the corrected reference estimators: compared with the ORACLE's shade() with both fixes (solid-angle NEE, mixture
+    pdf) at equal spp -- error within the oracle's own seed-to-seed noise, mean energy within 4 standard errors -- and
+    with the GPU's path-tree MIS on block averages.  No path tree: at most one child and one visibility ray per vertex."""
+    _, cam = arrays_of(scene_name)
+    spp = SPP[scene_name]
+    o = oracle_of(scene_name)
+    of = oracle.FIX_STALE_MIS | oracle.FIX_NEE_MEASURE | oracle.FIX_MIXTURE_PDF
+    a, _ = o.render(cam, oracle.NEE_SPHERICAL, spp, max_depth=DEPTH, flags=of, seed=1)
+    b, _ = o.render(cam, oracle.NEE_SPHERICAL, spp, max_depth=DEPTH, flags=of, seed=2)
+    a = np.nan_to_num(a); b = np.nan_to_num(b)
+    s = gpu_scene_of(scene_name)
+    img, st = s.render(cam, api.MIS_SINGLE, spp, max_depth=DEPTH, flags=api.FIX_MIXTURE_PDF, seed=3)
+    assert np.isfinite(img).all()
+    noise, ref = util.rmse(a, b), 0.5 * (a + b)
+    assert util.rmse(img, a) <= 1.5 * noise + 2e-7 * ref.max(), (util.rmse(img, a), noise)
+    diff = (img.astype(np.float64) - ref).mean(axis=2).ravel()
+    se = diff.std() / np.sqrt(diff.size)
+    assert abs(diff.mean()) <= 4 * se + 0.01 * ref.mean(), (diff.mean(), se, ref.mean())
+    assert st["rays_shadow"] > 0 and st["rays_light"] > 0 and st["queue_peak"] <= cam.width * cam.height * spp
+    # against the path-tree MIS on the GPU, 8x8 block means of a 4x longer render
+    tree, _ = s.render(cam, api.MIS, 4 * spp, max_depth=DEPTH, flags=api.FIX_MIXTURE_PDF, seed=4)
+    single, _ = s.render(cam, api.MIS_SINGLE, 4 * spp, max_depth=DEPTH, flags=api.FIX_MIXTURE_PDF, seed=5)
+    H, W = cam.height // 8 * 8, cam.width // 8 * 8
+    blk = lambda im: np.minimum(im[:H, :W], 4.0).reshape(H // 8, 8, W // 8, 8, 3).mean(axis=(1, 3))
+    bt, bs = blk(tree), blk(single)
+    rel = np.linalg.norm(bt - bs) / np.linalg.norm(bt)
+    assert rel < 0.05, rel
+    # deterministic and batch-size independent like every other strategy
+    again, _ = s.render(cam, api.MIS_SINGLE, spp, max_depth=DEPTH, flags=api.FIX_MIXTURE_PDF, seed=3)
+    assert np.array_equal(img, again)

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """BASELINE.json configs[4]: light-sampling strategy sweep on the veach-mis scene.
 
-Strategies: uniform-area NEE, spherical-triangle NEE, BRDF-only, MIS.  For each: RMSE / relMSE of linear
+Strategies: uniform-area NEE, spherical-triangle NEE, BRDF-only, MIS (the reference's path tree) and single-path MIS.  For each: RMSE / relMSE of linear
 radiance against a converged reference at equal spp (1..1024) and at equal time (0.1 / 1 / 10 s of device time).
 All four run with the F8/F9 fixes (mixture pdf, solid-angle NEE estimator) and no depth cap, so they estimate
 the same integral; the reference image is MIS at --ref-spp (default 16384) with a different seed.  The
@@ -38,7 +38,8 @@ def main():
     cam = sc.camera
     scene = api.Scene(arrays, 0)
     fixes = api.FIX_MIXTURE_PDF | api.FIX_NEE_MEASURE
-    strategies = [("NEE_UNIFORM", api.NEE_UNIFORM), ("NEE_SPHERICAL", api.NEE_SPHERICAL), ("BRDF_ONLY", api.BRDF_ONLY), ("MIS", api.MIS)]
+    strategies = [("NEE_UNIFORM", api.NEE_UNIFORM), ("NEE_SPHERICAL", api.NEE_SPHERICAL), ("BRDF_ONLY", api.BRDF_ONLY), ("MIS", api.MIS),
+                  ("MIS_SINGLE", api.MIS_SINGLE)]
 
     def render(strat, spp, seed):
         # chunks of <= 1024 spp keep int32 sample indices and the film's FP32 sums comfortable
