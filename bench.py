@@ -294,8 +294,10 @@ def run_ours(args, wl_name, wl):
     stats = []
     sync()
     e0.record()
+    host_t = [time.perf_counter()]
     for k in range(args.steps):
         stats.append(step(args.warmup + k))
+        host_t.append(time.perf_counter())
     e1.record()
     sync()
     ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
@@ -403,7 +405,8 @@ def run_ours(args, wl_name, wl):
                       "Mrays_per_s": (tot["rays_closest"] + tot["rays_shadow"] + tot["rays_light"]) * world / ms / 1e3,
                       "sample_bounces_per_path": tot["vertices"] / max(tot["paths"], 1),
                       "time_to_1024spp_s": 1024.0 / (S * world) * (ms / args.steps) / 1e3,
-                      "bvh": bvh_extra},
+                      "bvh": bvh_extra, "device_ms_per_step": [round(float(x["ms_total"]), 3) for x in stats],
+                      "host_ms_per_step": [round(1e3 * (b - a), 3) for a, b in zip(host_t[:-1], host_t[1:])]},
         })
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_reference_run(stem, cam, wl["strategy"], wl["max_depth"], args.cpu_seconds)

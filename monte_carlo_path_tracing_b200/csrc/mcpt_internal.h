@@ -45,6 +45,7 @@ struct Workspace {
     void* pinned = nullptr;  // small pinned staging area for counters
     float* d_image = nullptr;  // W*H*3 output staging for mcpt_render
     size_t image_bytes = 0;
+    size_t mem_budget = 0;  // free device memory + our own workspace at the last cudaMemGetInfo (render.cu)
 };
 
 }  // namespace mcpt

@@ -15,6 +15,9 @@
 //   k_accumulate / k_finalize   per-pixel owner sums its slots (atomic-free), scales by 1/spp
 // Depth is implied by the bounce index: the vertex shaded at bounce b has depth b+1, because every
 // earlier vertex of its path was a non-emissive, front-facing vertex that passed RR.
+#include <chrono>
+#include <cstdlib>
+#include <cstdio>
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -877,6 +880,10 @@ void tonemap_device(McptScene* scene, const float* rgb, size_t n, double max_rad
 void render_device(McptScene* scene, const McptCamera* cam, const McptRenderParams* prm, float* d_out_rgb, cudaStream_t st,
                    McptStats* stats)
 {
+    const bool dbg_timing = std::getenv("MCPT_DEBUG_TIMING") != nullptr;
+    const auto dbg_t0 = std::chrono::steady_clock::now();
+    auto dbg_ms = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - dbg_t0).count(); };
+    double dbg_setup = 0, dbg_loop = 0;
     const int W = prm->width, H = prm->height;
     if (W <= 0 || H <= 0 || prm->spp <= 0) throw Error(MCPT_ERR_INVALID, "width, height and spp must be positive");
     if (prm->strategy < 0 || prm->strategy > 4) throw Error(MCPT_ERR_INVALID, "unknown strategy");
@@ -888,13 +895,19 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     const float p_rr = prm->p_rr > 0.f ? prm->p_rr : 0.6f;
     size_t target = kTargetSlots;
     {
-        // keep the workspace below half of the device memory that is free (or already ours)
-        size_t free_b = 0, total_b = 0;
+        // keep the workspace below half of the device memory that is free (or already ours).  cudaMemGetInfo goes to
+        // the kernel driver and was measured to stall for 30-65 ms now and then when another thread of the process is
+        // inside an NVML query (bench.py samples the clocks), so the answer is cached while the workspace lives.
         MCPT_CUDA(cudaSetDevice(scene->device));
-        if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
+        if (scene->ws.mem_budget == 0 || scene->ws.bytes == 0) {
+            size_t free_b = 0, total_b = 0;
+            if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) scene->ws.mem_budget = free_b + scene->ws.bytes;
+            else cudaGetLastError();
+        }
+        if (scene->ws.mem_budget) {
             const size_t per_slot = tree ? 688 : 224;  // bytes of queues + staging + hit + accumulators per path slot
-            target = std::min(target, std::max<size_t>(npix, (free_b + scene->ws.bytes) / 2 / per_slot));
-        } else cudaGetLastError();
+            target = std::min(target, std::max<size_t>(npix, scene->ws.mem_budget / 2 / per_slot));
+        }
     }
     int batch = prm->batch_spp > 0 ? prm->batch_spp : (int)std::max<size_t>(1, target / npix);
     batch = std::min(batch, prm->spp);
@@ -999,6 +1012,7 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     McptStats S;
     std::memset(&S, 0, sizeof S);
     S.paths = (uint64_t)npix * (uint64_t)prm->spp;
+    dbg_setup = dbg_ms();
     MCPT_CUDA(cudaEventRecord(scene->ev[0], st));
     MCPT_CUDA(cudaMemsetAsync(d_counters, 0, CNT_N * 8, st));
     const bool jitter = (prm->flags & MCPT_JITTER) != 0;
@@ -1103,8 +1117,10 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     S.kernel_launches++;
     MCPT_CUDA(cudaMemcpyAsync(h_counters, d_counters, CNT_N * 8, cudaMemcpyDeviceToHost, st));
     MCPT_CUDA(cudaEventRecord(scene->ev[1], st));
+    dbg_loop = dbg_ms();
     MCPT_CUDA(cudaStreamSynchronize(st));
     MCPT_CUDA(cudaGetLastError());
+    if (dbg_timing) std::fprintf(stderr, "render_device host ms: setup %.3f, loop issued at %.3f, synced at %.3f\n", dbg_setup, dbg_loop, dbg_ms());
     float ms_total = 0.f;
     cudaEventElapsedTime(&ms_total, scene->ev[0], scene->ev[1]);
     S.passes = (uint32_t)pass;
