@@ -250,3 +250,84 @@ def test_single_path_mis_converges_to_the_same_image(scene_name, gpu_scene_of, o
     # deterministic and batch-size independent like every other strategy
     again, _ = s.render(cam, api.MIS_SINGLE, spp, max_depth=DEPTH, flags=api.FIX_MIXTURE_PDF, seed=3)
     assert np.array_equal(img, again)
+
+
+# ---- edge cases -----------------------------------------------------------------------------------------------
+def _tiny_scene(num_tris, with_light):
+    """num_tris unit triangles facing the camera at z = 0 (x = 2k .. 2k+1), the last one emissive if with_light."""
+    from monte_carlo_path_tracing_b200.scenes import Camera, SceneArrays
+    pos = np.zeros((num_tris, 3, 3), np.float32)
+    for k in range(num_tris):
+        pos[k] = [[2 * k, 0, 0], [2 * k + 1, 0, 0], [2 * k, 1, 0]]
+    nor = np.zeros_like(pos); nor[..., 2] = 1.0
+    mat = np.zeros(num_tris, np.int32)
+    lights = np.array([num_tris - 1], np.int32) if with_light else np.zeros(0, np.int32)
+    if with_light:
+        mat[-1] = 1
+    cam = Camera(eye=(num_tris, 0.4, 6.0), lookat=(num_tris, 0.4, 0.0), up=(0, 1, 0), fovy_deg=60.0, width=64, height=32)
+    return SceneArrays(pos, nor, mat, np.array([0, num_tris], np.uint32), np.array([[0.5, 0.5, 0.5], [0, 0, 0]], np.float32),
+                       np.zeros((2, 3), np.float32), np.ones(2, np.float32), lights, np.zeros(len(lights), np.int32),
+                       np.array([[3.0, 2.0, 1.0]]) if with_light else np.zeros((0, 3)), cam)
+
+
+@pytest.mark.parametrize("build", [api.BUILD_HOST_SAH, api.BUILD_GPU_LBVH], ids=["host-sah", "gpu-lbvh"])
+@pytest.mark.parametrize("num_tris", [1, 2, 3, 5])
+def test_tiny_scenes(num_tris, build):
+    """One to five triangles (a lone root leaf gets a wrapper node; the GPU builder falls back to the host below two
+    triangles): closest hits agree with the oracle bit for bit, and the emissive triangle is seen with its radiance."""
+    a = _tiny_scene(num_tris, True)
+    s = api.Scene(a, 0, build=build)
+    try:
+        assert s.bvh_check() == 0
+        o = oracle.OracleLib(a)
+        rng = np.random.default_rng(num_tris)
+        ro = np.column_stack([rng.uniform(-1, 2 * num_tris + 1, 2000), rng.uniform(-0.5, 1.5, 2000), np.full(2000, 3.0)])
+        rd = util.unit(np.column_stack([rng.normal(0, 0.2, 2000), rng.normal(0, 0.2, 2000), np.full(2000, -1.0)]))
+        p1, b1 = s.closest(ro, rd, None, False, api.FP64)
+        p0, b0 = o.closest(ro, rd, None, 2)
+        assert np.array_equal(p1, p0) and np.array_equal(b1, b0) and (p0 >= 0).any()
+        for strat in (api.NEE_UNIFORM, api.NEE_SPHERICAL, api.MIS, api.MIS_SINGLE, api.BRDF_ONLY):
+            img, st = s.render(a.camera, strat, 4, max_depth=3, seed=1)
+            assert np.isfinite(img).all() and st["primary_hits"] > 0
+            assert np.isclose(img.max(axis=(0, 1)), [3.0, 2.0, 1.0]).all()  # the light seen directly
+    finally:
+        s.close()
+
+
+def test_scene_without_lights():
+    """BRDF_ONLY needs no light (black image, paths still traced); every light-sampling strategy refuses with INVALID."""
+    a = _tiny_scene(3, False)
+    s = api.Scene(a, 0)
+    try:
+        img, st = s.render(a.camera, api.BRDF_ONLY, 4, max_depth=3, seed=1)
+        assert not img.any() and st["primary_hits"] > 0 and st["vertices"] > 0
+        for strat in (api.NEE_UNIFORM, api.NEE_SPHERICAL, api.MIS, api.MIS_SINGLE):
+            with pytest.raises(api.McptError) as e:
+                s.render(a.camera, strat, 1)
+            assert e.value.code == -1
+    finally:
+        s.close()
+
+
+def test_veach_full_size_sharding_and_determinism():
+    """BASELINE.json configs[1] geometry at full resolution (1280x720, shade_with_mis, RR only): deterministic,
+    independent of the pass size, and the two halves of an spp-sharded render (what two GPUs do) add up to the whole."""
+    sc = scenes.veach_mis(width=1280, height=720)
+    import tempfile
+    with tempfile.TemporaryDirectory() as td:
+        stem = sc.write(td)
+        a, _ = api.load_scene_files(stem + ".obj", stem + ".xml")
+    s = api.Scene(a, 0)
+    try:
+        cam = sc.camera
+        full, st = s.render(cam, api.MIS, 6, seed=21)
+        again, _ = s.render(cam, api.MIS, 6, seed=21)
+        assert np.array_equal(full, again)
+        small, _ = s.render(cam, api.MIS, 6, seed=21, batch_spp=4)
+        assert np.allclose(full, small, rtol=1e-5, atol=1e-6)
+        lo, _ = s.render(cam, api.MIS, 3, seed=21, spp_offset=0, spp_total=6)
+        hi, _ = s.render(cam, api.MIS, 3, seed=21, spp_offset=3, spp_total=6)
+        assert np.allclose(lo + hi, full, rtol=1e-5, atol=1e-6)
+        assert st["paths"] == 1280 * 720 * 6 and st["bounces"] > 10 and np.isfinite(full).all() and full.mean() > 0
+    finally:
+        s.close()
