@@ -201,6 +201,7 @@ __device__ __forceinline__ void warp_light_select(const DScene& s, bool need, f3
 // atomic per warp: commutative, so the result is deterministic).  k_gather then turns group sums + counts into
 // exact offsets and moves the chunk windows into the dense queue, preserving input order -- which keeps all
 // rays of one path-tree adjacent (k_runsum) without any warp ever waiting for another.
+constexpr int kSerialLights = 32;  // at or below: per-lane light loop in k_lightsel instead of the warp-cooperative sweep
 constexpr int kGroup = 256;   // chunks per k_gather block (one per thread)
 
 __global__ void __launch_bounds__(256) k_gather(const Queue stage, const Queue out, const int* __restrict__ counts,
@@ -441,7 +442,25 @@ __global__ void __launch_bounds__(kBlk, MCPT_SEL_MINBLK) k_lightsel(const Bounce
         }
         int chosen = -1;
         float wsum = 0.f, wch = 0.f;
-        if (__any_sync(kFull, need)) warp_light_select(s, need, p, N, u, &chosen, &wsum, &wch);
+        if (s.L <= kSerialLights) {
+            // Few lights: the warp-cooperative sweep would spend most of its instructions on broadcasts, scans and the
+            // second pass (measured on the 16-light interior: 13 ms per 32-spp pass).  Each lane walks the whole table
+            // for its own vertex instead (all lanes read the same light: broadcast loads) and selects in the same pass
+            // by weighted reservoir sampling with ONE recycled uniform -- P(l) = w_l / weights_sum exactly.
+            if (need) {
+                float uu = fminf(u, 0.99999994f);
+                for (int l = 0; l < s.L; l++) {
+                    const float w = light_weight_fast(s, l, p, N);
+                    if (w > 0.f) {
+                        wsum += w;
+                        const float pr = __fdividef(w, wsum);
+                        if (uu < pr) { chosen = l; wch = w; uu = __fdividef(uu, pr); }
+                        else uu = __fdividef(uu - pr, 1.f - pr);
+                        uu = fminf(fmaxf(uu, 0.f), 0.99999994f);
+                    }
+                }
+            }
+        } else if (__any_sync(kFull, need)) warp_light_select(s, need, p, N, u, &chosen, &wsum, &wch);
         if (i < a.in_count) a.sel4[i] = make_float4(__int_as_float(chosen), wch, wsum, 0.f);
     }
 }

@@ -1,1 +1,2 @@
-timeout 900 python -m pytest tests -m gpu -x -q -k "tiny or without_lights or veach_full" 2>&1 | tail -15
+timeout 300 python bench.py --steps 1 --warmup 1 --no-cpu-baseline --workload interior > /dev/null 2>&1 && timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 700 --csv --log-file gpurun_out/r1w_launches_interior.csv python bench.py --steps 1 --warmup 1 --no-cpu-baseline --workload interior > /dev/null 2>&1
+ls -la gpurun_out/r1w_launches_interior.csv
