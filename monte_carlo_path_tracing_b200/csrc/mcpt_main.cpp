@@ -4,10 +4,11 @@
 // the emissive triangles (lights.read(); lights.gather_light_triangles(), :503-504), set up the camera
 // (:507-553, here from the XML <camera> node of README.md:339-343 or from --eye/--lookat/--up/--fovy), render
 // (:557-588 -> mcpt_render), tone-map (RadianceRGB::tone_mapping(380, 0.25), :583 -> mcpt_tonemap) and save
-// the image (saveimage, :597 -> binary PPM; the EasyX window is a graphics API and is not reproduced).
+// the image (saveimage, :597 -> a 24-bit BMP when the output name ends in .bmp, else binary PPM; the EasyX window is a
+// graphics API and is not reproduced).
 // Every parameter the reference hard-codes in source is a command-line option.  Uses only include/mcpt.h.
 //
-//   mcpt_render scene.obj scene.xml out.ppm [--spp 10] [--strategy mis|mis_single|nee|nee_uniform|brdf] [--max-depth 0]
+//   mcpt_render scene.obj scene.xml out.ppm|out.bmp [--spp 10] [--strategy mis|mis_single|nee|nee_uniform|brdf] [--max-depth 0]
 //               [--width W --height H] [--seed 1] [--device 0] [--fix-pdf] [--fix-measure] [--jitter]
 //               [--lmax 380 --gamma 0.25] [--pfm out.pfm] [--ref-fov]
 //               [--gpu-bvh] [--every N] [--checkpoint file [--resume]] [--target-rel-error e] [--time-budget seconds]
@@ -225,9 +226,29 @@ int main(int argc, char** argv)
 
     std::vector<uint8_t> rgb8(film.size());
     if (mcpt_tonemap(scene, film.data(), (size_t)width * height, lmax, gamma, rgb8.data())) return fail("tone mapping");
+    const std::string outs = out;
+    const bool bmp = outs.size() > 4 && (outs.substr(outs.size() - 4) == ".bmp" || outs.substr(outs.size() - 4) == ".BMP");
     if (FILE* f = std::fopen(out, "wb")) {
-        std::fprintf(f, "P6\n%d %d\n255\n", width, height);
-        std::fwrite(rgb8.data(), 1, rgb8.size(), f);
+        if (bmp) {
+            // what the reference's saveimage() leaves behind (main.cpp:597): 24-bit uncompressed BMP, bottom row first, BGR
+            const uint32_t row = ((uint32_t)width * 3 + 3) & ~3u, data = row * (uint32_t)height, off = 54;
+            uint8_t h[54] = {'B', 'M'};
+            auto put32 = [&](int at, uint32_t v) { h[at] = v & 255; h[at + 1] = (v >> 8) & 255; h[at + 2] = (v >> 16) & 255; h[at + 3] = v >> 24; };
+            put32(2, off + data); put32(10, off); put32(14, 40); put32(18, (uint32_t)width); put32(22, (uint32_t)height);
+            h[26] = 1; h[28] = 24; put32(34, data); put32(38, 2835); put32(42, 2835);
+            std::fwrite(h, 1, 54, f);
+            std::vector<uint8_t> line(row, 0);
+            for (int i = height - 1; i >= 0; i--) {
+                for (int j = 0; j < width; j++) {
+                    const uint8_t* p = &rgb8[((size_t)i * width + j) * 3];
+                    line[3 * j] = p[2]; line[3 * j + 1] = p[1]; line[3 * j + 2] = p[0];
+                }
+                std::fwrite(line.data(), 1, row, f);
+            }
+        } else {
+            std::fprintf(f, "P6\n%d %d\n255\n", width, height);
+            std::fwrite(rgb8.data(), 1, rgb8.size(), f);
+        }
         std::fclose(f);
     } else { std::perror(out); return 1; }
     if (!pfm.empty()) {

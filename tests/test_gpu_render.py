@@ -177,6 +177,17 @@ def test_cpp_driver_end_to_end(scene_files, tmp_path, gpu_scene_of, arrays_of):
     assert np.array_equal(film, img)
     rgb8 = np.frombuffer(raw[len(hdr):], np.uint8).reshape(cam.height, cam.width, 3)
     assert np.array_equal(rgb8, gpu_scene_of("cornell-box").tonemap(img))
+    # the reference's saveimage() format: 24-bit BMP, bottom-up, BGR, rows padded to 4 bytes
+    bmp = tmp_path / "o.bmp"
+    r = subprocess.run([drv, stem + ".obj", stem + ".xml", str(bmp), "--spp", "8", "--strategy", "nee_uniform",
+                        "--max-depth", "4", "--seed", "7"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    b = bmp.read_bytes()
+    row = (cam.width * 3 + 3) // 4 * 4
+    assert b[:2] == b"BM" and int.from_bytes(b[10:14], "little") == 54 and len(b) == 54 + row * cam.height
+    assert int.from_bytes(b[18:22], "little") == cam.width and int.from_bytes(b[22:26], "little") == cam.height
+    pix = np.frombuffer(b[54:], np.uint8).reshape(cam.height, row)[:, :cam.width * 3].reshape(cam.height, cam.width, 3)
+    assert np.array_equal(pix[::-1, :, ::-1], rgb8)
 
 
 @pytest.mark.gpu
