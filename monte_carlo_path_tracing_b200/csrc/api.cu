@@ -223,7 +223,8 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
         float* tcdf = (float*)(hb + B.off_tri_cdf);
         for (uint32_t c = 0; c < C * 3; c++) crd[c] = s->class_radiance[c];
         f4* so = (f4*)(hb + B.off_lsoa);
-        for (uint32_t l = L; l < Lpad; l++) so[2 * Lpad + l].w = std::numeric_limits<float>::infinity();  // padding: always culled
+        auto sidx = [](uint32_t l, int plane) { return (size_t)(l >> 5) * 128 + (size_t)plane * 32 + (l & 31); };  // lights.cuh lsoa_index
+        for (uint32_t l = L; l < Lpad; l++) so[sidx(l, 2)].w = std::numeric_limits<float>::infinity();  // padding: always culled
         for (uint32_t l = 0; l < L; l++) {
             int32_t prim = s->light_prim[l], cls = s->light_class[l];
             const float* v = &s->positions[(size_t)prim * 9];
@@ -237,10 +238,10 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
             std::memcpy(&lt[5 * l + 0].w, &prim, 4);
             std::memcpy(&lt[5 * l + 1].w, &cls, 4);
             const double a2 = 2.0 * s->light_area[l];
-            so[l] = f4{v[0], v[1], v[2], 0.f};
-            so[Lpad + l] = f4{v[3], v[4], v[5], 0.f};
-            so[2 * Lpad + l] = f4{v[6], v[7], v[8], (float)(1e-8 * a2)};
-            so[3 * Lpad + l] = f4{-(float)(g[0] * a2), -(float)(g[1] * a2), -(float)(g[2] * a2), 2.0f * (float)(r[0] + r[1] + r[2])};
+            so[sidx(l, 0)] = f4{v[0], v[1], v[2], 0.f};
+            so[sidx(l, 1)] = f4{v[3], v[4], v[5], 0.f};
+            so[sidx(l, 2)] = f4{v[6], v[7], v[8], (float)(1e-8 * a2)};
+            so[sidx(l, 3)] = f4{-(float)(g[0] * a2), -(float)(g[1] * a2), -(float)(g[2] * a2), 2.0f * (float)(r[0] + r[1] + r[2])};
             for (int c = 0; c < 3; c++) lng[3 * l + c] = g[c];
             lar[l] = s->light_area[l];
         }

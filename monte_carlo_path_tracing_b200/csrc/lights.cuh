@@ -87,8 +87,8 @@ __device__ __forceinline__ V3<T> arvo_sample(const SphTri<T>& st, T xi1, T xi2)
 // where a,b,c = vertices - x1.  a.(b x c) = (v0-x1).((v1-v0) x (v2-v0)) = 2 area * ng.(v0-x1) has no
 // cancellation, so tiny lights keep full FP32 relative accuracy where alpha+beta+gamma-pi has none.
 //
-// The loop reads the SoA table `lsoa` (scene_dev.cuh): four float4 planes of Lpad entries, so a warp's 32
-// lanes fetch 32 consecutive 16-byte vectors per plane (4 x 512 B, fully coalesced):
+// The loop reads the SoA table `lsoa` (scene_dev.cuh): four float4 planes per block of 32 lights, so a warp's 32
+// lanes fetch 32 consecutive 16-byte vectors per plane (4 x 512 B, fully coalesced, one pointer + constant offsets):
 //   plane0 = v0 | -, plane1 = v1 | -, plane2 = v2 | cull threshold 1e-8 * 2 area,
 //   plane3 = -Ns = -2 area * ng | 2 Lsum;  padding entries have threshold = +inf and evaluate to 0.
 // Branch-free on purpose.
@@ -152,14 +152,17 @@ __device__ __forceinline__ float light_weight_soa(float4 p0, float4 p1, float4 p
     const float ad = fabsf(den);
     const float q = __fmul_rn(fminf(ad, num), rcp_fast(fmaxf(ad, num)));
     const float w = __fmul_rn(atan2_fix(atan_unit(q), num, den), p3.w);
-    const bool ok = num >= p2.w && hmax >= 1e-8f && w > 0.f && w < CUDART_INF_F;
+    const bool ok = num >= p2.w && hmax >= 1e-8f && w < CUDART_INF_F;  // w < inf also rejects NaN; w == 0 adds nothing
     return ok ? w : 0.f;
 }
 
+// lsoa is blocked by 32 lights: [Lpad / 32][4 planes][32] float4, so one pointer with constant offsets serves a sweep
+__host__ __device__ __forceinline__ int lsoa_index(int l) { return ((l >> 5) << 7) + (l & 31); }
+
 __device__ __forceinline__ float light_weight_fast(const DScene& s, int l, f3 x1, f3 n)
 {
-    const float4* P = s.lsoa + l;
-    return light_weight_soa(__ldg(P), __ldg(P + s.Lpad), __ldg(P + 2 * s.Lpad), __ldg(P + 3 * s.Lpad), x1, n);
+    const float4* P = s.lsoa + lsoa_index(l);
+    return light_weight_soa(__ldg(P), __ldg(P + 32), __ldg(P + 64), __ldg(P + 96), x1, n);
 }
 
 // ---- packed FP32 (sm_100 FFMA2 / FADD2 / FMUL2) --------------------------------------------------------------
@@ -213,8 +216,8 @@ __device__ __forceinline__ float2 light_weight_pair(float4 p0, float4 p1, float4
     p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C7));
     const float2 r = __ffma2_rn(q, __fmul2_rn(p, s), q);
     const float2 w = __fmul2_rn(make_float2(atan2_fix(r.x, num.x, den.x), atan2_fix(r.y, num.y, den.y)), bc2(p3.w));
-    const bool ok0 = num.x >= p2.w && fmaxf(ha.x, fmaxf(hb.x, hc.x)) >= 1e-8f && w.x > 0.f && w.x < CUDART_INF_F;
-    const bool ok1 = num.y >= p2.w && fmaxf(ha.y, fmaxf(hb.y, hc.y)) >= 1e-8f && w.y > 0.f && w.y < CUDART_INF_F;
+    const bool ok0 = num.x >= p2.w && fmaxf(ha.x, fmaxf(hb.x, hc.x)) >= 1e-8f && w.x < CUDART_INF_F;
+    const bool ok1 = num.y >= p2.w && fmaxf(ha.y, fmaxf(hb.y, hc.y)) >= 1e-8f && w.y < CUDART_INF_F;
     return make_float2(ok0 ? w.x : 0.f, ok1 ? w.y : 0.f);
 }
 
@@ -236,13 +239,10 @@ __device__ __forceinline__ void warp_light_partial(const DScene& s, const f3 (&x
     float2 acc[V / 2];
 #pragma unroll
     for (int h = 0; h < V / 2; h++) { vp[h] = make_vertex2(x1[2 * h], n[2 * h], x1[2 * h + 1], n[2 * h + 1]); acc[h] = make_float2(0.f, 0.f); }
-    const float4* __restrict__ P0 = s.lsoa;
-    const float4* __restrict__ P1 = P0 + s.Lpad;
-    const float4* __restrict__ P2 = P1 + s.Lpad;
-    const float4* __restrict__ P3 = P2 + s.Lpad;
+    const float4* __restrict__ P = s.lsoa + lane;
 #pragma unroll kSweepUnroll
-    for (int l = lane; l < s.Lpad; l += 32) {  // Lpad is a multiple of 64
-        const float4 a0 = __ldg(P0 + l), a1 = __ldg(P1 + l), a2 = __ldg(P2 + l), a3 = __ldg(P3 + l);
+    for (int l = lane; l < s.Lpad; l += 32, P += 128) {  // Lpad is a multiple of 64
+        const float4 a0 = __ldg(P), a1 = __ldg(P + 32), a2 = __ldg(P + 64), a3 = __ldg(P + 96);
 #pragma unroll
         for (int h = 0; h < V / 2; h++) acc[h] = __fadd2_rn(acc[h], light_weight_pair(a0, a1, a2, a3, vp[h]));
         if (V == 2 && cdf) { cdf[l] = acc[0].x; cdf[s.Lpad + l] = acc[0].y; }

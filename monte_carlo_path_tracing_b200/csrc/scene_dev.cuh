@@ -9,7 +9,7 @@
 //   mats   [M][2] float4 : (kd.rgb, ns), (ks.rgb, 0)              (main.cpp:292,313)
 //   lights [L][5] float4 : v0|prim bits, v1|class bits, v2|area, ng|Lsum (R+G+B), Le|0 -- in the
 //                          reference's light order (Mylight.cpp:169-173); FP32 copy for the renderer
-//   lsoa   [4][Lpad] float4 : the same lights as four planes (v0, v1, v2 | cull threshold, -2 area ng | 2 Lsum) for
+//   lsoa   [Lpad/32][4][32] float4 : the same lights as four planes per block of 32 (v0, v1, v2 | cull threshold, -2 area ng | 2 Lsum) for
 //                          the O(L) spherical-triangle weight loop (lights.cuh); Lpad = L rounded up to 64
 //   lng64 [L][3], larea64 [L], crad64 [C][3] : FP64 originals for the parity entry points
 //   class_begin [C+1], class_cdf [C], tri_cdf [L] : the two discrete distributions of
