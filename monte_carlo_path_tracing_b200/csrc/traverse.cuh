@@ -20,7 +20,10 @@
 
 namespace mcpt {
 
-constexpr int kStackSm = 24;
+#ifndef MCPT_STACK_SM
+#define MCPT_STACK_SM 8
+#endif
+constexpr int kStackSm = MCPT_STACK_SM;
 constexpr int kStackLocal = kBvhStackDepth - kStackSm;
 
 struct Hit { int prim; float b, g, t; };       // a2: intersec_result as one float4 (prim = -1: miss)
