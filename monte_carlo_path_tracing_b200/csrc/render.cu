@@ -153,47 +153,6 @@ __device__ __forceinline__ float warp_scan_incl(float v)
     return v;
 }
 
-// Must be called by all 32 lanes; lanes with need == false only help.  V (2 or 4) vertices are served per sweep of
-// the light table (warp_light_partial<V>): the loads are shared and the packed evaluations interleave.
-#ifndef MCPT_SELECT_V
-#define MCPT_SELECT_V 2
-#endif
-template <int V = MCPT_SELECT_V>
-__device__ __forceinline__ void warp_light_select(const DScene& s, bool need, f3 x, f3 n, float u, int* chosen, float* wsum_out,
-                                                  float* w_chosen)
-{
-    const int lane = threadIdx.x & 31;
-    unsigned todo = __ballot_sync(kFull, need);
-    *chosen = -1; *wsum_out = 0.f; *w_chosen = 0.f;
-    while (todo) {
-        int src[V];
-        int cnt = 0;
-#pragma unroll
-        for (int v = 0; v < V; v++) {
-            src[v] = todo ? __ffs(todo) - 1 : src[0];  // short groups re-evaluate the first vertex
-            if (todo) cnt++;
-            todo &= todo - 1;  // no-op when todo is already 0
-        }
-        f3 X[V], Nn[V];
-        float part[V];
-#pragma unroll
-        for (int v = 0; v < V; v++) {
-            X[v] = mk<float>(__shfl_sync(kFull, x.x, src[v]), __shfl_sync(kFull, x.y, src[v]), __shfl_sync(kFull, x.z, src[v]));
-            Nn[v] = mk<float>(__shfl_sync(kFull, n.x, src[v]), __shfl_sync(kFull, n.y, src[v]), __shfl_sync(kFull, n.z, src[v]));
-        }
-        warp_light_partial<V>(s, X, Nn, part);
-#pragma unroll
-        for (int v = 0; v < V; v++) {
-            if (v >= cnt) break;
-            const float uu = __shfl_sync(kFull, u, src[v]);
-            const float incl = warp_scan_incl(part[v]);
-            const float total = __shfl_sync(kFull, incl, 31);
-            const LightPick pk = warp_light_pick(s, X[v], Nn[v], part[v], incl, total, uu);
-            if (lane == src[v]) { *chosen = pk.light; *wsum_out = total; *w_chosen = pk.w; }
-        }
-    }
-}
-
 // ---- order-preserving queue compaction, wait-free ------------------------------------------------------------
 // A chunk is the 32 rays one warp processes.  The warp packs its 0..2 children per lane with __ballot_sync /
 // popc prefix sums into the chunk's own window of a STAGING queue (stage[chunk * stride + k], stride = 32 or,
@@ -412,6 +371,29 @@ __global__ void __launch_bounds__(kBlk, MCPT_SEL_MINBLK) k_lightsel(const Bounce
     const int lane = threadIdx.x & 31;
     const int nchunks = (a.in_count + 31) >> 5;
     const bool rr_forced = a.max_depth > 0 && a.bounce + 1 >= a.max_depth;
+    // Warp path: a sweep serves two vertices, and only ~1 queue entry in 9 needs one at the second bounce of veach-mis
+    // (3.6 per chunk of 32), so pairing inside a chunk would leave every other chunk with a half-empty sweep.  The odd
+    // vertex is carried (warp-uniform registers) and paired with the first one of the next chunk; results are written
+    // by index from lane 0.
+    bool pend = false;
+    f3 PX = mk<float>(0.f, 0.f, 0.f), PN = mk<float>(0.f, 0.f, 1.f);
+    float Pu = 0.f;
+    int Pi = -1;
+    auto sweep_pair = [&](f3 X0, f3 N0, float u0, int i0, bool two, f3 X1, f3 N1, float u1, int i1) {
+        f3 X[2] = {X0, two ? X1 : X0}, Nn[2] = {N0, two ? N1 : N0};
+        const float uu[2] = {u0, u1};
+        const int ii[2] = {i0, i1};
+        float part[2];
+        warp_light_partial<2>(s, X, Nn, part);
+#pragma unroll
+        for (int v = 0; v < 2; v++) {
+            if (v == 1 && !two) break;
+            const float incl = warp_scan_incl(part[v]);
+            const float total = __shfl_sync(kFull, incl, 31);
+            const LightPick pk = warp_light_pick(s, X[v], Nn[v], part[v], incl, total, uu[v]);
+            if (lane == 0) a.sel4[ii[v]] = make_float4(__int_as_float(pk.light), pk.w, total, 0.f);
+        }
+    };
     int next = 0;
     if (lane == 0) next = atomicAdd(cursor, 1);
     for (;;) {
@@ -440,13 +422,13 @@ __global__ void __launch_bounds__(kBlk, MCPT_SEL_MINBLK) k_lightsel(const Bounce
                 }
             }
         }
-        int chosen = -1;
-        float wsum = 0.f, wch = 0.f;
         if (s.L <= kSerialLights) {
             // Few lights: the warp-cooperative sweep would spend most of its instructions on broadcasts, scans and the
             // second pass (measured on the 16-light interior: 13 ms per 32-spp pass).  Each lane walks the whole table
             // for its own vertex instead (all lanes read the same light: broadcast loads) and selects in the same pass
             // by weighted reservoir sampling with ONE recycled uniform -- P(l) = w_l / weights_sum exactly.
+            int chosen = -1;
+            float wsum = 0.f, wch = 0.f;
             if (need) {
                 float uu = fminf(u, 0.99999994f);
                 for (int l = 0; l < s.L; l++) {
@@ -460,9 +442,23 @@ __global__ void __launch_bounds__(kBlk, MCPT_SEL_MINBLK) k_lightsel(const Bounce
                     }
                 }
             }
-        } else if (__any_sync(kFull, need)) warp_light_select(s, need, p, N, u, &chosen, &wsum, &wch);
-        if (i < a.in_count) a.sel4[i] = make_float4(__int_as_float(chosen), wch, wsum, 0.f);
+            if (i < a.in_count) a.sel4[i] = make_float4(__int_as_float(chosen), wch, wsum, 0.f);
+            continue;
+        }
+        if (i < a.in_count && !need) a.sel4[i] = make_float4(__int_as_float(-1), 0.f, 0.f, 0.f);
+        unsigned todo = __ballot_sync(kFull, need);
+        while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const f3 X1 = mk<float>(__shfl_sync(kFull, p.x, src), __shfl_sync(kFull, p.y, src), __shfl_sync(kFull, p.z, src));
+            const f3 N1 = mk<float>(__shfl_sync(kFull, N.x, src), __shfl_sync(kFull, N.y, src), __shfl_sync(kFull, N.z, src));
+            const float u1 = __shfl_sync(kFull, u, src);
+            const int i1 = chunk * 32 + src;
+            if (!pend) { PX = X1; PN = N1; Pu = u1; Pi = i1; pend = true; }
+            else { sweep_pair(PX, PN, Pu, Pi, true, X1, N1, u1, i1); pend = false; }
+        }
     }
+    if (pend) sweep_pair(PX, PN, Pu, Pi, false, PX, PN, Pu, Pi);
 }
 
 // ---- one bounce --------------------------------------------------------------------------------------------
@@ -1121,6 +1117,11 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
             ms_bounce += ms;
             cudaEventElapsedTime(&ms, scene->ev[2], scene->ev[4]);
             ms_shade += ms;
+            if (dbg_timing) {
+                float mb = 0.f;
+                cudaEventElapsedTime(&mb, scene->ev[2], scene->ev[3]);
+                std::fprintf(stderr, "  bounce %d: %d rays, %.3f ms (shade %.3f)\n", bounce, count, mb, ms);
+            }
             S.queue_peak = std::max<uint32_t>(S.queue_peak, (uint32_t)count);
             S.bounces++;
             if (last) break;
