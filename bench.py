@@ -33,13 +33,13 @@ from monte_carlo_path_tracing_b200 import scenes  # noqa: E402
 
 WORKLOADS = {
     # name: (scene generator kwargs, strategy name, max_depth)
-    "veach-mis": dict(scene="veach-mis", kw=dict(width=1280, height=720), strategy="MIS", max_depth=0, spp=64),
-    "cornell-box": dict(scene="cornell-box", kw=dict(width=512, height=512), strategy="NEE_UNIFORM", max_depth=5, spp=256),
+    "veach-mis": dict(scene="veach-mis", kw=dict(width=1280, height=720), strategy="MIS", max_depth=0, spp=128),
+    "cornell-box": dict(scene="cornell-box", kw=dict(width=512, height=512), strategy="NEE_UNIFORM", max_depth=5, spp=512),
     # configs[2]: stand-in for the unavailable bathroom scene: generated interior, ~185 k triangles
-    "interior": dict(scene="interior", kw=dict(width=1280, height=720), strategy="MIS", max_depth=0, spp=32),
+    "interior": dict(scene="interior", kw=dict(width=1280, height=720), strategy="MIS", max_depth=0, spp=128),
     # configs[3]: 1 M random triangles + 64 emissive triangles, 1024x1024, uniform-area NEE (BVH traversal stress)
     "soup-1m": dict(scene="soup", kw=dict(num_tris=1_000_000, num_lights=64, width=1024, height=1024), strategy="NEE_UNIFORM",
-                    max_depth=5, spp=64),
+                    max_depth=5, spp=128),
 }
 STRAT = {"NEE_SPHERICAL": 0, "BRDF_ONLY": 1, "MIS": 2, "NEE_UNIFORM": 3}
 # Compulsory wavefront state traffic per sample-bounce of the split pipeline: k_extend reads the
@@ -270,6 +270,8 @@ def run_ours(args, wl_name, wl):
     film = torch.zeros(npix * 3, dtype=torch.float32, device="cuda")
     stream = torch.cuda.current_stream().cuda_stream
     kw = dict(max_depth=wl["max_depth"], seed=args.seed, batch_spp=args.batch_spp)
+    if args.light_tree:
+        kw["flags"] = api.LIGHT_TREE
 
     def step(k):
         # global sample range of this step: [k*world*S, (k+1)*world*S), rank r owns S of them
@@ -378,11 +380,14 @@ def run_ours(args, wl_name, wl):
         # vertices once each -- for MIS only the 60 % that survive the roulette taken before sampling (main.cpp:429-437)
         passes = sum(s["passes"] for s in stats)
         later = max(0, tot["vertices"] - sum(s["primary_hits"] for s in stats))
-        sweeps = (npix * passes + later * (0.6 if wl["strategy"] == "MIS" else 1.0)) if sph else 0
+        sweeps = (npix * passes + later * (0.6 if wl["strategy"] == "MIS" else 1.0)) if (sph and not args.light_tree) else 0
         flops = 320.0 * tot["vertices"] + 70.0 * L * sweeps
         flops_per_vertex = flops / max(tot["vertices"], 1)
         fp32_peak = 148 * 128 * 2 * 1.965e9
         line = base_line(args, wl_name, wl, cam, S)
+        if args.light_tree:
+            line["config"]["light_selection"] = "MCPT_LIGHT_TREE: O(log L) hierarchy instead of the reference's O(L) loop (not a reference estimator)"
+            line["config"]["workload"] += " light-tree"
         line.update({
             "value": value, "ms_per_step": ms / args.steps,
             "gpu_launches": int(tot["kernel_launches"]),
@@ -434,6 +439,7 @@ def main():
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--light-tree", action="store_true", help="MCPT_LIGHT_TREE light selection (SURVEY.md 8(f) row 4; not the headline)")
     ap.add_argument("--bvh", default="host", choices=["host", "gpu"], help="scene BVH builder: host SAH (default) or device LBVH")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]

@@ -53,7 +53,12 @@ enum {
     MCPT_FIX_NEE_MEASURE = 2,  /* F9: NEE_SPHERICAL uses the solid-angle estimator Le f cos / pdf */
     MCPT_FIX_MIXTURE_PDF = 4,  /* F8: BRDF-sampled directions are weighted with the mixture pdf */
     MCPT_JITTER = 16,          /* uniform sub-pixel jitter (the reference has none, F4) */
-    MCPT_ACCUMULATE = 64       /* mcpt_render_device: add into d_out instead of overwriting */
+    MCPT_ACCUMULATE = 64,      /* mcpt_render_device: add into d_out instead of overwriting */
+    MCPT_LIGHT_TREE = 128      /* NOT a reference estimator: the spherical strategies pick their
+                                * light triangle by descending a light hierarchy (csrc/light_tree.h, O(log L) per vertex)
+                                * instead of the O(L) loop of Mylight.cpp:169-276; the chosen triangle is still sampled by
+                                * Arvo's spherical-triangle sampler and the pdf used is P(triangle | vertex) / sA.  Same
+                                * expectation, different variance. */
 };
 
 /* Flattened Myobj + Mylight.  prim = shape_offset[s] + f for the reference's (s,f) (Myobj.h:44-66). */
@@ -194,6 +199,14 @@ int mcpt_scene_bvh_check(const McptScene*, uint32_t* errors);
  * every prim appears in exactly one leaf, every triangle lies inside its leaf box, every child box inside its
  * parent's.  out4 = {nodes, leaves, max_depth, errors}. */
 int mcpt_host_bvh_check(const McptSceneDesc* desc, int lights_only, uint32_t out4[4], double* sah_cost);
+/* Light hierarchy of MCPT_LIGHT_TREE.  Host-only structural check (every light in exactly one leaf, every ancestor's
+ * sphere / normal cone holds the light): out4 = {nodes, max_depth, errors, lights}. */
+int mcpt_host_light_tree_check(const McptSceneDesc* desc, uint32_t out4[4]);
+/* Parity / test entry point: at vertex (x1, N) draw a light with uniform u (prim, selection probability) and report
+ * the selection probability of every light in `query_light` [n] (index into the light list, -1 = none) together
+ * with that light's FP32 spherical-triangle weight sA * (R+G+B) (0 = culled at this vertex). */
+int mcpt_light_tree_batch(McptScene*, size_t n, const double* x1, const double* N, const double* u, const int32_t* query_light,
+                          int32_t* light, double* prob, double* query_prob, double* query_weight);
 const char* mcpt_last_error(void);
 int mcpt_version(void);
 int mcpt_device_count(void);

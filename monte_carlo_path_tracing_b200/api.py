@@ -20,7 +20,7 @@ CSRC = os.path.join(HERE, "csrc")
 
 NEE_SPHERICAL, BRDF_ONLY, MIS, NEE_UNIFORM, MIS_SINGLE = 0, 1, 2, 3, 4
 STRATEGY_NAMES = {0: "NEE_SPHERICAL", 1: "BRDF_ONLY", 2: "MIS", 3: "NEE_UNIFORM"}
-FIX_NEE_MEASURE, FIX_MIXTURE_PDF, JITTER, ACCUMULATE = 2, 4, 16, 64
+FIX_NEE_MEASURE, FIX_MIXTURE_PDF, JITTER, ACCUMULATE, LIGHT_TREE = 2, 4, 16, 64, 128
 FP64, FP32 = 0, 1
 BUILD_HOST_SAH, BUILD_GPU_LBVH = 0, 1
 
@@ -32,7 +32,7 @@ SYMBOLS = [
     "mcpt_light_sample_spherical_batch", "mcpt_scene_geom_normals", "mcpt_scene_light_areas", "mcpt_scene_bvh_info",
     "mcpt_last_error", "mcpt_version", "mcpt_device_count", "mcpt_host_scene_load", "mcpt_host_scene_desc",
     "mcpt_host_scene_camera", "mcpt_host_scene_free", "mcpt_host_bvh_check", "mcpt_scene_create_ex",
-    "mcpt_scene_build_info", "mcpt_scene_bvh_check",
+    "mcpt_scene_build_info", "mcpt_scene_bvh_check", "mcpt_host_light_tree_check", "mcpt_light_tree_batch",
 ]
 
 
@@ -177,6 +177,15 @@ def host_bvh_check(a: SceneArrays, lights_only: bool = False):
     out = (C.c_uint32 * 4)(); sah = C.c_double()
     _check(lib.mcpt_host_bvh_check(C.byref(d), C.c_int(int(lights_only)), out, C.byref(sah)))
     return dict(nodes=out[0], leaves=out[1], max_depth=out[2], errors=out[3], sah=sah.value)
+
+
+def host_light_tree_check(a: SceneArrays):
+    """Build the light hierarchy of LIGHT_TREE on the host and validate it structurally (no GPU needed)."""
+    lib = load()
+    d, keep = make_desc(a)
+    out = (C.c_uint32 * 4)()
+    _check(lib.mcpt_host_light_tree_check(C.byref(d), out))
+    return dict(nodes=out[0], max_depth=out[1], errors=out[2], lights=out[3])
 
 
 class Scene:
@@ -330,3 +339,14 @@ class Scene:
         _check(self.lib.mcpt_light_sample_spherical_batch(self.handle, C.c_size_t(n), _p(x1), _p(N), _p(u3), _p(q), precision,
                                                           _p(prim), _p(pt), _p(Le), _p(pdf), _p(wsum), _p(nsurv), _p(qpdf)))
         return dict(prim=prim, point=pt, Le=Le, pdf=pdf, wsum=wsum, nsurv=nsurv, query_pdf=qpdf)
+
+    def light_tree(self, x1, N, u, query_light=None):
+        """LIGHT_TREE selection at vertices (x1, N): one draw per vertex with uniform u, plus the selection
+        probability and FP32 spherical-triangle weight of light ``query_light`` (index into the light list)."""
+        x1, N, u = map(_f64, (x1, N, u))
+        n = len(x1)
+        q = _i32(query_light) if query_light is not None else np.full(n, -1, np.int32)
+        light = np.zeros(n, np.int32); prob = np.zeros(n); qprob = np.zeros(n); qw = np.zeros(n)
+        _check(self.lib.mcpt_light_tree_batch(self.handle, C.c_size_t(n), _p(x1), _p(N), _p(u), _p(q), _p(light), _p(prob),
+                                              _p(qprob), _p(qw)))
+        return dict(light=light, prob=prob, query_prob=qprob, query_weight=qw)

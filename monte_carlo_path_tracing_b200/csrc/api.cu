@@ -7,6 +7,7 @@
 #include <numeric>
 #include "bvh_tree.h"
 #include "mcpt_internal.h"
+#include "light_tree.h"
 
 namespace mcpt {
 static thread_local std::string g_last_error;
@@ -15,7 +16,7 @@ void set_last_error(const std::string& msg) { g_last_error = msg; }
 namespace {
 struct BlobLayout {
     size_t off_nodes, off_nodes4, off_tris, off_lnodes, off_ltris, off_pverts, off_pnorms, off_mats, off_lights, off_lsoa, off_lng64, off_larea64,
-        off_crad64, off_class_begin, off_class_cdf, off_tri_cdf, total;
+        off_crad64, off_class_begin, off_class_cdf, off_tri_cdf, off_ltree, off_ltree_leaf, total;
 };
 size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
@@ -160,6 +161,14 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
         std::vector<int32_t> lp(s->light_prim);
         std::sort(lp.begin(), lp.end());
         s->lbvh = build_bvh(s->positions.data(), lp.data(), lp.size());
+        {   // light hierarchy for MCPT_LIGHT_TREE (light_tree.h)
+            std::vector<double> lsum(L);
+            for (uint32_t l = 0; l < L; l++) {
+                const double* r = &s->class_radiance[(size_t)s->light_class[l] * 3];
+                lsum[l] = r[0] + r[1] + r[2];
+            }
+            s->ltree = build_light_tree(s->positions.data(), s->light_prim.data(), s->geom_normals.data(), s->light_area.data(), lsum.data(), L);
+        }
         if (s->bvh.max_depth4 * 3 + 1 > (uint32_t)kBvhStackDepth)
             throw Error(MCPT_ERR_INVALID, "scene BVH is too deep for the traversal stack (degenerate geometry?)");
         s->extent = std::max({s->bvh.hi[0] - s->bvh.lo[0], s->bvh.hi[1] - s->bvh.lo[1], s->bvh.hi[2] - s->bvh.lo[2], 1e-30f});
@@ -185,6 +194,8 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
         B.off_class_begin = place((size_t)(C + 1) * 4);
         B.off_class_cdf = place((size_t)C * 4);
         B.off_tri_cdf = place((size_t)L * 4);
+        B.off_ltree = place(s->ltree.nodes.size() * sizeof(f4));
+        B.off_ltree_leaf = place((size_t)L * 4);
         B.total = o;
         s->blob_bytes = B.total;
         MCPT_CUDA(cudaMallocHost(&s->h_blob, B.total));
@@ -195,6 +206,10 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
         std::memcpy(hb + B.off_tris, s->bvh.tris.data(), s->bvh.tris.size() * sizeof(f4));
         std::memcpy(hb + B.off_lnodes, s->lbvh.nodes.data(), s->lbvh.nodes.size() * sizeof(BvhNode));
         std::memcpy(hb + B.off_ltris, s->lbvh.tris.data(), s->lbvh.tris.size() * sizeof(f4));
+        if (L) {
+            std::memcpy(hb + B.off_ltree, s->ltree.nodes.data(), s->ltree.nodes.size() * sizeof(f4));
+            std::memcpy(hb + B.off_ltree_leaf, s->ltree.leaf_of_light.data(), (size_t)L * 4);
+        }
         std::vector<int32_t> light_of_prim(P, -1);
         for (uint32_t l = 0; l < L; l++) light_of_prim[s->light_prim[l]] = (int32_t)l;
         f4* pv = (f4*)(hb + B.off_pverts);
@@ -274,6 +289,7 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
         d.lng64 = (const double*)(db + B.off_lng64); d.larea64 = (const double*)(db + B.off_larea64);
         d.crad64 = (const double*)(db + B.off_crad64); d.class_begin = (const int32_t*)(db + B.off_class_begin);
         d.class_cdf = (const float*)(db + B.off_class_cdf); d.tri_cdf = (const float*)(db + B.off_tri_cdf);
+        d.ltree = (const float4*)(db + B.off_ltree); d.ltree_leaf = (const int32_t*)(db + B.off_ltree_leaf);
         d.P = (int32_t)P; d.L = (int32_t)L; d.C = (int32_t)C; d.M = (int32_t)Mn;
         d.tmin = s->extent * 1e-6f;
         MCPT_CUDA(cudaMemcpy(s->d_blob, s->h_blob, B.total, cudaMemcpyHostToDevice));
@@ -426,6 +442,32 @@ int mcpt_host_bvh_check(const McptSceneDesc* desc, int lights_only, uint32_t out
         const uint32_t errors = check_bvh(b, desc->positions, desc->num_prims, ids);
         if (out4) { out4[0] = (uint32_t)b.nodes.size(); out4[1] = b.num_leaves; out4[2] = b.max_depth; out4[3] = errors; }
         if (sah_cost) *sah_cost = b.sah_cost;
+    });
+}
+
+// Host-only: build the light hierarchy of MCPT_LIGHT_TREE for `desc` and validate it (light_tree.h).
+// out4 = {nodes, max_depth, errors, lights}.
+int mcpt_host_light_tree_check(const McptSceneDesc* desc, uint32_t out4[4])
+{
+    return guarded([&] {
+        validate(desc);
+        if (!out4) throw Error(MCPT_ERR_INVALID, "null argument");
+        const uint32_t L = desc->num_lights;
+        std::vector<double> gn((size_t)desc->num_prims * 3, 0.0), area(L), lsum(L);
+        for (uint32_t l = 0; l < L; l++) {
+            const int32_t p = desc->light_prim[l];
+            const dvec g = unique_normal(desc->positions + (size_t)p * 9, desc->normals + (size_t)p * 9);
+            for (int c = 0; c < 3; c++) gn[(size_t)p * 3 + c] = g[c];
+            const float* v = desc->positions + (size_t)p * 9;
+            double e1[3], e2[3];
+            for (int c = 0; c < 3; c++) { e1[c] = (double)v[3 + c] - v[c]; e2[c] = (double)v[6 + c] - v[c]; }
+            const double n[3] = {e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0]};
+            area[l] = 0.5 * std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+            const double* r = desc->class_radiance + (size_t)desc->light_class[l] * 3;
+            lsum[l] = r[0] + r[1] + r[2];
+        }
+        const LightTree T = build_light_tree(desc->positions, desc->light_prim, gn.data(), area.data(), lsum.data(), L);
+        out4[0] = T.num_nodes; out4[1] = T.max_depth; out4[2] = check_light_tree(T, desc->positions, desc->light_prim, gn.data(), L); out4[3] = L;
     });
 }
 

@@ -284,6 +284,22 @@ __global__ void k_light_wsum_fast(DScene s, size_t n, const double* x1, const do
     if (nsurv) nsurv[i] = cnt;
 }
 
+// light hierarchy (MCPT_LIGHT_TREE, lights.cuh): one draw + the selection probability / FP32 weight of a queried light
+__global__ void k_light_tree(DScene s, size_t n, const double* __restrict__ x1, const double* __restrict__ N, const double* __restrict__ u,
+                             const int* __restrict__ query, int* light, double* prob, double* qprob, double* qweight)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const f3 x = mk<float>((float)x1[3 * i], (float)x1[3 * i + 1], (float)x1[3 * i + 2]);
+    const f3 nn = mk<float>((float)N[3 * i], (float)N[3 * i + 1], (float)N[3 * i + 2]);
+    float p = 0.f;
+    light[i] = lt_pick(s, x, nn, (float)u[i], &p);
+    prob[i] = (double)p;
+    const int q = query ? query[i] : -1;
+    qprob[i] = (q >= 0 && q < s.L) ? (double)lt_prob(s, q, x, nn) : 0.0;
+    qweight[i] = (q >= 0 && q < s.L) ? (double)light_weight_fast(s, q, x, nn) : 0.0;
+}
+
 void need(const McptScene* s) { if (!s) throw Error(MCPT_ERR_INVALID, "null scene"); }
 
 }  // namespace
@@ -419,6 +435,21 @@ int mcpt_light_sample_spherical_batch(McptScene* s, size_t n, const double* x1, 
         finish();
         if (precision != 2) { pr.to_host(prim); pt.to_host(point); le.to_host(Le); pd.to_host(pdf); qp.to_host(query_pdf); }
         ws.to_host(wsum); ns.to_host(nsurv);
+    });
+}
+
+int mcpt_light_tree_batch(McptScene* s, size_t n, const double* x1, const double* N, const double* u, const int32_t* query_light,
+                          int32_t* light, double* prob, double* query_prob, double* query_weight)
+{
+    return guarded([&] {
+        need(s);
+        if (s->L == 0) throw Error(MCPT_ERR_INVALID, "scene has no lights");
+        MCPT_CUDA(cudaSetDevice(s->device));
+        DevBuf<double> x(x1, 3 * n), nn(N, 3 * n), uu(u, n), pr(n), qp(n), qw(n);
+        DevBuf<int> q(query_light, query_light ? n : 0), li(n);
+        if (n) k_light_tree<<<grid_for(n), kBlock>>>(s->d, n, x.p, nn.p, uu.p, query_light ? q.p : nullptr, li.p, pr.p, qp.p, qw.p);
+        finish();
+        li.to_host(light); pr.to_host(prob); qp.to_host(query_prob); qw.to_host(query_weight);
     });
 }
 

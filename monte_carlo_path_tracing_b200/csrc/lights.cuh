@@ -289,6 +289,83 @@ __device__ __forceinline__ bool arvo_direct(V3<T> v0, V3<T> v1, V3<T> v2, V3<T> 
     return !M<T>::bad_(P.x + P.y + P.z);
 }
 
+// ---- light hierarchy (MCPT_LIGHT_TREE, light_tree.h) ---------------------------------------------------------
+// O(log L) stand-in for the O(L) selection loop of Mylight.cpp:169-276: descend a binary tree over the light
+// triangles, choosing a child with probability proportional to a conservative estimate of what it can send to
+// the vertex.  The estimate is zero only where the culls of Mylight.cpp:180-197 remove every light below the node
+// (the vertex is behind all of them, or all of them are below its horizon), so every light with a non-zero
+// spherical-triangle weight keeps a non-zero probability and the estimator stays unbiased.
+//
+// cos(max(0, a - b)) and sin(max(0, a - b)) for angles in [0, pi] given by their sines and cosines
+__device__ __forceinline__ float cos_sub_clamped(float sa, float ca, float sb, float cb) { return ca > cb ? 1.f : ca * cb + sa * sb; }
+__device__ __forceinline__ float sin_sub_clamped(float sa, float ca, float sb, float cb) { return ca > cb ? 0.f : sa * cb - ca * sb; }
+
+// t0 = centre | radius, t1 = cone axis | cos(theta_o)
+__device__ __forceinline__ float lt_importance(float4 t0, float4 t1, float power, f3 x, f3 n)
+{
+    const f3 dv = mk<float>(x.x - t0.x, x.y - t0.y, x.z - t0.z);  // centre -> vertex
+    const float d2 = dot(dv, dv), r2 = t0.w * t0.w;
+    const f3 wi = dv * rsqrtf(fmaxf(d2, 1e-30f));
+    // half-angle under which the vertex sees the node's bounding sphere; pi when it is inside
+    const bool inside = !(d2 > r2);
+    const float sin2_b = inside ? 0.f : r2 / d2;
+    const float sin_b = sqrtf(sin2_b), cos_b = inside ? -1.f : sqrtf(fmaxf(0.f, 1.f - sin2_b));
+    // emitter side: angle between the cone axis and the direction to the vertex, less the cone, less the sphere
+    const float cos_w = dot(mk<float>(t1.x, t1.y, t1.z), wi), sin_w = sqrtf(fmaxf(0.f, 1.f - cos_w * cos_w));
+    const float cos_o = t1.w, sin_o = sqrtf(fmaxf(0.f, 1.f - cos_o * cos_o));
+    const float cos_x = cos_sub_clamped(sin_w, cos_w, sin_o, cos_o), sin_x = sin_sub_clamped(sin_w, cos_w, sin_o, cos_o);
+    const float cos_e = cos_sub_clamped(sin_x, cos_x, sin_b, cos_b);
+    // receiver side: angle between the vertex normal and the direction to the centre, less the sphere
+    const float cos_i = -dot(n, wi), sin_i = sqrtf(fmaxf(0.f, 1.f - cos_i * cos_i));
+    const float cos_r = cos_sub_clamped(sin_i, cos_i, sin_b, cos_b);
+    if (!(cos_e > 0.f) || !(cos_r > 0.f)) return 0.f;  // every light below faces away (:180-185) or is below the horizon (:187-197)
+    return power * cos_e * cos_r / fmaxf(d2, r2);
+}
+
+// probability of descending into the LEFT child of inner node `node`; writes the two children
+__device__ __forceinline__ float lt_left_prob(const DScene& s, int left, int right, f3 x, f3 n)
+{
+    const float4* L = s.ltree + 3 * left;
+    const float4* R = s.ltree + 3 * right;
+    const float pl = __ldg(L + 2).x, pr = __ldg(R + 2).x;
+    float il = lt_importance(__ldg(L), __ldg(L + 1), pl, x, n), ir = lt_importance(__ldg(R), __ldg(R + 1), pr, x, n);
+    if (!(il + ir > 0.f) || !(il + ir < CUDART_INF_F)) { il = pl; ir = pr; }  // nothing below can contribute: any choice will do
+    if (!(il + ir > 0.f)) return 0.5f;
+    return fminf(il / (il + ir), 1.f);  // the approximate division may land one ulp above 1
+}
+
+// draws a light with one uniform (rescaled on the way down); *prob = its selection probability
+__device__ __forceinline__ int lt_pick(const DScene& s, f3 x, f3 n, float u, float* prob)
+{
+    int node = 0;
+    float p = 1.f;
+    for (;;) {
+        const float4 t2 = __ldg(s.ltree + 3 * node + 2);
+        const int left = __float_as_int(t2.y), right = __float_as_int(t2.z);
+        if (left < 0) { *prob = p; return ~left; }
+        const float pl = lt_left_prob(s, left, right, x, n);
+        if (u < pl) { node = left; p *= pl; u = u / pl; }
+        else { node = right; p *= 1.f - pl; u = (u - pl) / (1.f - pl); }
+        u = fminf(fmaxf(u, 0.f), 0.99999994f);
+    }
+}
+
+// selection probability of a given light at this vertex (the same arithmetic as lt_pick, bottom-up)
+__device__ __forceinline__ float lt_prob(const DScene& s, int light, f3 x, f3 n)
+{
+    int node = __ldg(s.ltree_leaf + light);
+    float p = 1.f;
+    for (;;) {
+        const int parent = __float_as_int(__ldg(s.ltree + 3 * node + 2).w);
+        if (parent < 0) return p;
+        const float4 t2 = __ldg(s.ltree + 3 * parent + 2);
+        const int left = __float_as_int(t2.y), right = __float_as_int(t2.z);
+        const float pl = lt_left_prob(s, left, right, x, n);
+        p *= (node == left) ? pl : 1.f - pl;
+        node = parent;
+    }
+}
+
 // ---- uniform-area sampling, Mylight.cpp:102-160 --------------------------------------------------------
 template <class T> struct LightPoint { int prim; int light; V3<T> coord, Le; T prob; };
 

@@ -6,6 +6,7 @@
 #include "../../include/mcpt.h"
 #include "bvh.h"
 #include "host_scene.h"
+#include "light_tree.h"
 #include "scene_dev.cuh"
 
 namespace mcpt {
@@ -60,6 +61,7 @@ struct McptScene {
     std::vector<double> geom_normals;  // [P][3]  get_unique_normal_of_facet
     std::vector<double> light_area;    // [L]
     mcpt::Bvh bvh, lbvh;
+    mcpt::LightTree ltree;  // light hierarchy of MCPT_LIGHT_TREE
     double build_tree_ms = 0, build_total_ms = 0;  // scene BVH: tree construction / whole scene_create
     int32_t builder = 0;                           // MCPT_BUILD_*
     // one packed, pinned host image of everything the kernels read + its device twin

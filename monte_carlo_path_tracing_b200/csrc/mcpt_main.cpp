@@ -9,7 +9,7 @@
 // Every parameter the reference hard-codes in source is a command-line option.  Uses only include/mcpt.h.
 //
 //   mcpt_render scene.obj scene.xml out.ppm|out.bmp [--spp 10] [--strategy mis|mis_single|nee|nee_uniform|brdf] [--max-depth 0]
-//               [--width W --height H] [--seed 1] [--device 0] [--fix-pdf] [--fix-measure] [--jitter]
+//               [--width W --height H] [--seed 1] [--device 0] [--fix-pdf] [--fix-measure] [--jitter] [--light-tree]
 //               [--lmax 380 --gamma 0.25] [--pfm out.pfm] [--ref-fov]
 //               [--gpu-bvh] [--every N] [--checkpoint file [--resume]] [--target-rel-error e] [--time-budget seconds]
 //
@@ -104,6 +104,7 @@ int main(int argc, char** argv)
         else if (a == "--fix-pdf") flags |= MCPT_FIX_MIXTURE_PDF;
         else if (a == "--fix-measure") flags |= MCPT_FIX_NEE_MEASURE;
         else if (a == "--jitter") flags |= MCPT_JITTER;
+        else if (a == "--light-tree") flags |= MCPT_LIGHT_TREE;  // O(log L) light selection (not a reference estimator)
         else if (a == "--lmax") lmax = std::atof(next());
         else if (a == "--gamma") gamma = std::atof(next());
         else if (a == "--pfm") pfm = next();

@@ -32,7 +32,7 @@ namespace {
 
 constexpr int kBlk = 128;             // threads per block (4 warps; a warp owns one 32-ray chunk at a time)
 constexpr unsigned kFull = 0xffffffffu;
-constexpr size_t kTargetSlots = 64u << 20;  // auto batch: up to 64 Mi path slots in flight per pass (memory permitting)
+constexpr size_t kTargetSlots = 128u << 20;  // auto batch: up to 128 Mi path slots in flight per pass (memory permitting)
 
 enum { CNT_VERTICES = 0, CNT_RAYS, CNT_SHADOW, CNT_LIGHTRAYS, CNT_PRIMARY_HITS, CNT_OVERFLOW, CNT_N };
 
@@ -461,6 +461,87 @@ __global__ void __launch_bounds__(kBlk, MCPT_SEL_MINBLK) k_lightsel(const Bounce
     if (pend) sweep_pair(PX, PN, Pu, Pi, false, PX, PN, Pu, Pi);
 }
 
+// ---- light selection through the light hierarchy (MCPT_LIGHT_TREE) ------------------------------------------------
+// Stands in for k_lightsel at every vertex after the first (the first vertex of a pixel keeps the exact selection: its
+// O(L) sweep is shared by all samples of the pass, k_lightprep, and costs no more than a tree walk per sample).  Each
+// thread rebuilds the vertex of one queue entry and repeats the roulette / uniform draws exactly like k_lightsel; the
+// few entries that do sample a light (about 1 in 9 at the second bounce of veach-mis) are collected in a shared-memory
+// queue, and whenever 256 of them are waiting the whole block walks the tree of light_tree.h for them (lt_pick,
+// lights.cuh: O(log L) dependent node pairs per vertex instead of the O(L) sweep), one vertex per thread, so the walks
+// run at full warps.  Leaves sel4[i] = (light, its spherical-triangle weight w, w / P(light)): k_shade's
+// pl = Lsum / sel4.z is then the solid-angle pdf P(light) / sA of the direction it draws.
+template <int STRAT>
+__global__ void __launch_bounds__(256) k_lighttree(const BounceArgs a)
+{
+    constexpr bool kTree = (STRAT == MCPT_MIS);
+    __shared__ float4 q_xi[512], q_nu[512];  // vertex | queue index bits,  normal | uniform
+    __shared__ int q_n;
+    const DScene& s = a.s;
+    const bool rr_forced = a.max_depth > 0 && a.bounce + 1 >= a.max_depth;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int ntiles = (a.in_count + 255) >> 8;
+    if (tid == 0) q_n = 0;
+    __syncthreads();
+    auto flush = [&](int n) {  // walks for the top min(n, 256) waiting vertices; returns how many are left
+        const int m = min(n, 256);
+        if (tid < m) {
+            const float4 xi = q_xi[n - m + tid], nu = q_nu[n - m + tid];
+            const f3 X = to_f3(xi), Nn = to_f3(nu);
+            float prob = 0.f;
+            const int l = lt_pick(s, X, Nn, nu.w, &prob);
+            const float w = light_weight_fast(s, l, X, Nn);
+            float4 out = make_float4(__int_as_float(-1), 0.f, 0.f, 0.f);
+            if (w > 0.f && prob > 0.f) out = make_float4(__int_as_float(l), w, w / prob, 0.f);
+            a.sel4[__float_as_int(xi.w)] = out;
+        }
+        __syncthreads();
+        if (tid == 0) q_n = n - m;
+        __syncthreads();
+        return n - m;
+    };
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int i = (tile << 8) + tid;
+        bool need = false;
+        f3 p = mk<float>(0.f, 0.f, 0.f), N = mk<float>(0.f, 0.f, 1.f);
+        float u = 0.f;
+        if (i < a.in_count) {
+            const float4 qh = a.hit[i];
+            const int prim = __float_as_int(qh.x);
+            if (prim >= 0) {
+                const float4 qd = a.in.dir[i];
+                const Vertex v = make_vertex(s, prim, qh.y, qh.z, -to_f3(qd));
+                if (v.front && v.light < 0) {
+                    const int slot = __float_as_int(qd.w);
+                    const uint32_t pixel = (uint32_t)(slot % a.npix), sample = (uint32_t)(a.sample_base + slot / a.npix);
+                    uint64_t node = (uint64_t)a.bounce + 1;
+                    if (kTree) { const uint2 nd = a.in.node[i]; node = ((uint64_t)nd.y << 32) | nd.x; }
+                    need = true;
+                    if (kTree || STRAT == MCPT_MIS_SINGLE) need = !rr_forced && !(rng_draw4(a.seed, pixel, sample, node, 0).u[0] > a.p_rr);
+                    if (need) { u = rng_draw4(a.seed, pixel, sample, node, 1).u[0]; p = v.p; N = v.N; }
+                }
+            }
+            if (!need) a.sel4[i] = make_float4(__int_as_float(-1), 0.f, 0.f, 0.f);
+        }
+        const unsigned m = __ballot_sync(kFull, need);
+        if (m) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(&q_n, __popc(m));
+            base = __shfl_sync(kFull, base, 0);
+            if (need) {
+                const int at = base + __popc(m & ((1u << lane) - 1u));
+                q_xi[at] = make_float4(p.x, p.y, p.z, __int_as_float(i));
+                q_nu[at] = make_float4(N.x, N.y, N.z, u);
+            }
+        }
+        __syncthreads();
+        const int n = q_n;  // < 512: at most 255 were waiting before this tile
+        __syncthreads();    // everyone has read q_n before the next tile's pushes move it
+        if (n >= 256) flush(n);
+    }
+    __syncthreads();
+    for (int n = q_n; n > 0;) n = flush(n);
+}
+
 // ---- one bounce --------------------------------------------------------------------------------------------
 struct Child { f3 o, d, thr; int exclude; uint64_t node; float misw; };
 
@@ -572,7 +653,7 @@ __global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceA
                     const int2 v = a.sel[slot];
                     chosen = v.x; wch = __int_as_float(v.y);
                     wsum = a.wsum_pix[pixel];
-                } else {      // drawn by k_lightsel
+                } else {      // drawn by k_lightsel / k_lighttree
                     const float4 v = a.sel4[i];
                     chosen = __float_as_int(v.x); wch = v.y; wsum = v.z;
                 }
@@ -650,7 +731,8 @@ __global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceA
             if (!(cosN < 0.f) && pdf > 0.f) {
                 if (a.flags & MCPT_FIX_MIXTURE_PDF) pdf = phong_pdf<float>(N, wi, wo, mat);  // F8
                 float lpdf = 0.f;
-                if ((STRAT == MCPT_MIS || kSingle) && wsum > 0.f) {
+                const bool ltree = !FIRST && (a.flags & MCPT_LIGHT_TREE) != 0;  // the first vertex keeps the exact selection
+                if ((STRAT == MCPT_MIS || kSingle) && (wsum > 0.f || ltree)) {
                     // pdf of wi under light sampling (main.cpp:484-489): nearest EMISSIVE triangle along wi, occluders
                     // ignored; it counts iff it survived this vertex's culls (Mylight.cpp:484-493, evaluated for the
                     // current vertex -- F10 not reproduced)
@@ -658,7 +740,9 @@ __global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceA
                     c_lrays++;
                     if (lh.prim >= 0) {
                         const int li = __float_as_int(__ldg(s.pverts + 3 * lh.prim + 1).w);
-                        if (light_weight_fast(s, li, p, N) > 0.f) lpdf = __ldg(s.lights + 5 * li + 3).w / wsum;
+                        const float wli = light_weight_fast(s, li, p, N);
+                        // exact selection: Lsum / weights_sum (Mylight.cpp:484-493); light tree: P(li | vertex) / sA(li)
+                        if (wli > 0.f) lpdf = __ldg(s.lights + 5 * li + 3).w * (ltree ? lt_prob(s, li, p, N) / wli : 1.f / wsum);
                     }
                 }
                 const f3 f = phong_eval<float>(N, wi, wo, mat);
@@ -853,7 +937,10 @@ int launch_bounce(bool first, const BounceArgs& a, int grid, int sel_grid, int* 
 {
     constexpr bool kSph = (STRAT == MCPT_NEE_SPHERICAL || STRAT == MCPT_MIS || STRAT == MCPT_MIS_SINGLE);
     if (first) { k_shade<STRAT, true><<<grid, kBlk, 0, st>>>(a); return 1; }
-    if constexpr (kSph) k_lightsel<STRAT><<<std::min(grid, sel_grid), kBlk, 0, st>>>(a, sel_cursor);
+    if constexpr (kSph) {
+        if (a.flags & MCPT_LIGHT_TREE) k_lighttree<STRAT><<<std::max(1, std::min((a.in_count + 255) / 256, 148 * 8)), 256, 0, st>>>(a);
+        else k_lightsel<STRAT><<<std::min(grid, sel_grid), kBlk, 0, st>>>(a, sel_cursor);
+    }
     k_shade<STRAT, false><<<grid, kBlk, 0, st>>>(a);
     return kSph ? 2 : 1;
 }
@@ -909,6 +996,7 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     const int spp_total = prm->spp_total > 0 ? prm->spp_total : prm->spp;
     const float p_rr = prm->p_rr > 0.f ? prm->p_rr : 0.6f;
     size_t target = kTargetSlots;
+    if (const char* e = std::getenv("MCPT_TARGET_SLOTS_MI")) { const long v = std::atol(e); if (v > 0) target = (size_t)v << 20; }
     {
         // keep the workspace below half of the device memory that is free (or already ours).  cudaMemGetInfo goes to
         // the kernel driver and was measured to stall for 30-65 ms now and then when another thread of the process is

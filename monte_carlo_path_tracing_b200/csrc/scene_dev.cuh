@@ -12,6 +12,7 @@
 //   lsoa   [Lpad/32][4][32] float4 : the same lights as four planes per block of 32 (v0, v1, v2 | cull threshold, -2 area ng | 2 Lsum) for
 //                          the O(L) spherical-triangle weight loop (lights.cuh); Lpad = L rounded up to 64
 //   lng64 [L][3], larea64 [L], crad64 [C][3] : FP64 originals for the parity entry points
+//   ltree [2L-1][3] float4, ltree_leaf [L] : light hierarchy of MCPT_LIGHT_TREE (light_tree.h)
 //   class_begin [C+1], class_cdf [C], tri_cdf [L] : the two discrete distributions of
 //                          select_a_point_from_lights (Mylight.cpp:112-135) as normalised cumulative tables
 #pragma once
@@ -37,6 +38,8 @@ struct DScene {
     const int32_t* class_begin;
     const float* class_cdf;
     const float* tri_cdf;
+    const float4* ltree;        // [2L-1][3] light hierarchy nodes (light_tree.h), node 0 = root
+    const int32_t* ltree_leaf;  // [L] leaf node of each light
     int32_t P, L, C, M, Lpad;
     float tmin;  // FP32 leaf test: reject t < tmin (scene-scale aware stand-in for the reference's 1e-8)
 };

@@ -179,6 +179,40 @@ def test_light_spherical_renderer_sampler(scene_name, golden, gpu_scene_of, arra
     assert abs(moved.sum() - (has & (np.linalg.norm(g["ls_point"] - x, axis=1) > 0)).sum()) <= 0.01 * has.sum() + 2
 
 
+def test_light_tree_selection(scene_name, gpu_scene_of, arrays_of):
+    """MCPT_LIGHT_TREE (not a reference estimator, so checked through its own invariants): at
+    every vertex the selection probabilities of all lights sum to 1, every light with a non-zero spherical-triangle
+    weight (i.e. one the reference's loop Mylight.cpp:169-259 would keep) has a non-zero probability, the probability
+    reported with a draw equals the bottom-up query of the drawn light, and draws follow the probabilities."""
+    a, _ = arrays_of(scene_name)
+    s = gpu_scene_of(scene_name)
+    L = len(a.light_prim)
+    nv = 96
+    x, Nn, _, _ = util.shading_points(a, nv, 211)
+    X = np.repeat(x, L, axis=0); NN = np.repeat(Nn, L, axis=0)
+    q = np.tile(np.arange(L, dtype=np.int32), nv)
+    rng = np.random.default_rng(212)
+    r = s.light_tree(X, NN, rng.random(nv * L), q)
+    P = r["query_prob"].reshape(nv, L); Wt = r["query_weight"].reshape(nv, L)
+    assert np.all(P >= 0) and np.all(np.abs(P.sum(1) - 1.0) < 1e-4), np.abs(P.sum(1) - 1).max()
+    wsum = Wt.sum(1, keepdims=True)
+    visible = Wt > 1e-5 * np.maximum(wsum, 1e-30)   # well clear of the cull thresholds
+    assert visible.any() and np.all(P[visible] > 0)
+    # probability mass wasted on lights the culls reject stays small
+    assert (P * (Wt <= 0)).sum(1).mean() < 0.35
+    # the drawn light's probability == the query of that light
+    r2 = s.light_tree(X, NN, rng.random(nv * L), r["light"])
+    assert np.all((r["light"] >= 0) & (r["light"] < L))
+    assert np.max(util.rel_err(r["prob"], r2["query_prob"], 1e-30)) < 1e-5
+    # stratified uniforms at one vertex: frequencies follow the probabilities
+    n = 200_000
+    k = int(np.argmax(visible.sum(1)))
+    u = (np.arange(n) + 0.5) / n
+    d = s.light_tree(np.repeat(x[k:k + 1], n, 0), np.repeat(Nn[k:k + 1], n, 0), u, None)
+    freq = np.bincount(d["light"], minlength=L) / n
+    assert np.abs(freq - P[k]).max() < 2e-3, np.abs(freq - P[k]).max()
+
+
 def test_tonemap(gpu_scene_of, golden):
     vals = np.abs(np.random.default_rng(109).normal(size=(200, 3))) * 200
     out = gpu_scene_of("cornell-box").tonemap(vals.astype(np.float32))

@@ -263,6 +263,33 @@ def test_single_path_mis_converges_to_the_same_image(scene_name, gpu_scene_of, o
     assert np.array_equal(img, again)
 
 
+@pytest.mark.parametrize("strategy,flags", [(api.MIS, api.FIX_MIXTURE_PDF), (api.NEE_SPHERICAL, api.FIX_NEE_MEASURE | api.FIX_MIXTURE_PDF),
+                                            (api.MIS_SINGLE, api.FIX_MIXTURE_PDF)], ids=["MIS", "NEE_SPHERICAL", "MIS_SINGLE"])
+def test_light_tree_converges_to_the_same_image(scene_name, strategy, flags, gpu_scene_of, arrays_of):
+    """MCPT_LIGHT_TREE: picking the light through the hierarchy instead of the O(L) loop changes
+    the variance, not the expectation.  Compared with the exact selection on 8x8 block means of long renders and on
+    the mean image energy; deterministic and independent of the pass size like every other mode."""
+    _, cam = arrays_of(scene_name)
+    spp = 4 * SPP[scene_name]
+    s = gpu_scene_of(scene_name)
+    exact, _ = s.render(cam, strategy, spp, max_depth=DEPTH, flags=flags, seed=11)
+    tree, st = s.render(cam, strategy, spp, max_depth=DEPTH, flags=flags | api.LIGHT_TREE, seed=12)
+    assert np.isfinite(tree).all() and not np.array_equal(exact, tree)
+    H, W = cam.height // 8 * 8, cam.width // 8 * 8
+    blk = lambda im: np.minimum(im[:H, :W], 4.0).reshape(H // 8, 8, W // 8, 8, 3).mean(axis=(1, 3))
+    be, bt = blk(exact), blk(tree)
+    rel = np.linalg.norm(be - bt) / np.linalg.norm(be)
+    assert rel < 0.05, rel
+    diff = (tree.astype(np.float64) - exact).mean(axis=2).ravel()
+    se = diff.std() / np.sqrt(diff.size)
+    assert abs(diff.mean()) <= 4 * se + 0.01 * exact.mean(), (diff.mean(), se, exact.mean())
+    again, _ = s.render(cam, strategy, spp, max_depth=DEPTH, flags=flags | api.LIGHT_TREE, seed=12)
+    assert np.array_equal(tree, again)
+    small, _ = s.render(cam, strategy, spp, max_depth=DEPTH, flags=flags | api.LIGHT_TREE, seed=12, batch_spp=5)
+    assert np.allclose(tree, small, rtol=1e-5, atol=1e-6)
+    assert st["kernel_launches"] > 0 and st["vertices"] > 0
+
+
 # ---- edge cases -----------------------------------------------------------------------------------------------
 def _tiny_scene(num_tris, with_light):
     """num_tris unit triangles facing the camera at z = 0 (x = 2k .. 2k+1), the last one emissive if with_light."""

@@ -97,6 +97,37 @@ def test_host_bvh_degenerate_inputs():
     assert r["errors"] == 0
 
 
+@pytest.mark.parametrize("name", ["cornell-box", "veach-mis"])
+def test_host_light_tree_is_valid(name, arrays_of):
+    """Light hierarchy of MCPT_LIGHT_TREE (csrc/light_tree.h): 2L-1 nodes, every light in exactly one leaf, every
+    ancestor's bounding sphere holds the light's vertices and every ancestor's cone its normal, powers add up."""
+    a, _ = arrays_of(name)
+    r = api.host_light_tree_check(a)
+    L = len(a.light_prim)
+    assert r["errors"] == 0 and r["lights"] == L and r["nodes"] == 2 * L - 1
+    assert r["max_depth"] <= 4 * max(1, int(np.ceil(np.log2(max(L, 2)))))
+
+
+def test_host_light_tree_soup_and_degenerate():
+    """Full-size veach-mis light set (1282 triangles on four spheres), random lights, coincident lights, one light."""
+    sc = scenes.veach_mis()
+    import tempfile
+    with tempfile.TemporaryDirectory() as td:
+        stem = sc.write(td)
+        a, _ = api.load_scene_files(stem + ".obj", stem + ".xml")
+    r = api.host_light_tree_check(a)
+    assert r["errors"] == 0 and r["nodes"] == 2 * 1282 - 1 and r["max_depth"] <= 24
+    a = scenes.triangle_soup(2000, 500, seed=5)
+    r = api.host_light_tree_check(a)
+    assert r["errors"] == 0 and r["nodes"] == 999 and r["max_depth"] <= 30
+    a.positions[a.light_prim[:300]] = a.positions[a.light_prim[0]]  # 300 coincident lights: split by order
+    r = api.host_light_tree_check(a)
+    assert r["errors"] == 0 and r["nodes"] == 999
+    a = scenes.triangle_soup(100, 1, seed=6)
+    r = api.host_light_tree_check(a)
+    assert r["errors"] == 0 and r["nodes"] == 1 and r["max_depth"] == 0
+
+
 def test_scene_generators():
     c = scenes.cornell_box(width=32, height=32)
     assert "usemtl" in c.obj and "vn " in c.obj and "<light" in c.xml and "<camera" in c.xml
