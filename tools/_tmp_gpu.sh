@@ -1,11 +1,10 @@
-timeout 600 python -m pytest tests -m gpu -x -q -k "light_tree" 2>&1 | tail -5
-for w in veach-mis interior; do
-timeout 300 python bench.py --steps 3 --warmup 3 --no-cpu-baseline --workload $w --light-tree > gpurun_out/lt1_$w.json 2>gpurun_out/lt1_$w.err
+MCPT_DEBUG_TIMING=1 timeout 300 python bench.py --steps 1 --warmup 1 --no-cpu-baseline --workload veach-mis > gpurun_out/dbg.json 2>gpurun_out/dbg.err
+grep -n "bounce\|render_device" gpurun_out/dbg.err | head -80
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/ex_launches.csv python bench.py --steps 1 --warmup 1 --no-cpu-baseline > /dev/null 2>&1
 python - <<PY
-import json
-for t in ("lt1",):
-    try:
-        j=json.load(open("gpurun_out/%s_$w.json"%t)); p=j["roofline"]["pipeline"]; print(t, "$w", round(j["value"],1), "e2e", round(j["e2e"]["value"],1), "ms/step", round(j["ms_per_step"],2), "shade", round(p["ms_shade"]/3,2), "trace", round(p["ms_trace"]/3,2), "launches", j["gpu_launches"])
-    except Exception as e: print(t, "$w failed", e, open("gpurun_out/%s_$w.err"%t).read()[-800:])
+import csv
+rows=[r for r in csv.reader(open("gpurun_out/ex_launches.csv")) if len(r)>10]
+h=rows[0]; ki=h.index("Kernel Name"); vi=h.index("Metric Value")
+for r in rows[1:40]:
+    print(r[ki][:60], r[vi])
 PY
-done

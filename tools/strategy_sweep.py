@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """BASELINE.json configs[4]: light-sampling strategy sweep on the veach-mis scene.
 
-Strategies: uniform-area NEE, spherical-triangle NEE, BRDF-only, MIS (the reference's path tree) and single-path MIS.  For each: RMSE / relMSE of linear
+Strategies: uniform-area NEE, spherical-triangle NEE, BRDF-only, MIS (the reference's path tree) and single-path MIS,
+plus the three spherical ones with MCPT_LIGHT_TREE (light hierarchy instead of the O(L) selection loop).  For each: RMSE / relMSE of linear
 radiance against a converged reference at equal spp (1..1024) and at equal time (0.1 / 1 / 10 s of device time).
 All four run with the F8/F9 fixes (mixture pdf, solid-angle NEE estimator) and no depth cap, so they estimate
 the same integral; the reference image is MIS at --ref-spp (default 16384) with a different seed.  The
@@ -38,23 +39,26 @@ def main():
     cam = sc.camera
     scene = api.Scene(arrays, 0)
     fixes = api.FIX_MIXTURE_PDF | api.FIX_NEE_MEASURE
-    strategies = [("NEE_UNIFORM", api.NEE_UNIFORM), ("NEE_SPHERICAL", api.NEE_SPHERICAL), ("BRDF_ONLY", api.BRDF_ONLY), ("MIS", api.MIS),
-                  ("MIS_SINGLE", api.MIS_SINGLE)]
+    T = api.LIGHT_TREE  # "+tree": O(log L) light selection after the first vertex (csrc/light_tree.h) instead of the O(L) loop
+    strategies = [("NEE_UNIFORM", (api.NEE_UNIFORM, 0)), ("NEE_SPHERICAL", (api.NEE_SPHERICAL, 0)), ("BRDF_ONLY", (api.BRDF_ONLY, 0)),
+                  ("MIS", (api.MIS, 0)), ("MIS_SINGLE", (api.MIS_SINGLE, 0)), ("NEE_SPHERICAL+tree", (api.NEE_SPHERICAL, T)),
+                  ("MIS+tree", (api.MIS, T)), ("MIS_SINGLE+tree", (api.MIS_SINGLE, T))]
 
     def render(strat, spp, seed):
+        strat, extra = strat
         # chunks of <= 1024 spp keep int32 sample indices and the film's FP32 sums comfortable
         acc = np.zeros((cam.height, cam.width, 3), np.float64)
         ms = 0.0
         done = 0
         while done < spp:
             n = min(1024, spp - done)
-            img, st = scene.render(cam, strat, n, max_depth=0, flags=fixes, seed=seed, spp_offset=done, spp_total=spp)
+            img, st = scene.render(cam, strat, n, max_depth=0, flags=fixes | extra, seed=seed, spp_offset=done, spp_total=spp)
             acc += img
             ms += st["ms_total"]
             done += n
         return acc, ms
 
-    ref, ref_ms = render(api.MIS, args.ref_spp, seed=1234567)
+    ref, ref_ms = render((api.MIS, 0), args.ref_spp, seed=1234567)
     scale = float(np.mean(ref))
 
     def errors(img):
