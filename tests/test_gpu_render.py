@@ -288,6 +288,11 @@ def test_light_tree_converges_to_the_same_image(scene_name, strategy, flags, gpu
     small, _ = s.render(cam, strategy, spp, max_depth=DEPTH, flags=flags | api.LIGHT_TREE, seed=12, batch_spp=5)
     assert np.allclose(tree, small, rtol=1e-5, atol=1e-6)
     assert st["kernel_launches"] > 0 and st["vertices"] > 0
+    # with sub-pixel jitter the first vertex is walked through the tree as well (no per-pixel sweep to share)
+    jit, _ = s.render(cam, strategy, spp, max_depth=DEPTH, flags=flags | api.LIGHT_TREE | api.JITTER, seed=13)
+    jit_exact, _ = s.render(cam, strategy, spp, max_depth=DEPTH, flags=flags | api.JITTER, seed=14)
+    bj, bje = blk(jit), blk(jit_exact)
+    assert np.isfinite(jit).all() and np.linalg.norm(bj - bje) / np.linalg.norm(bje) < 0.05
 
 
 # ---- edge cases -----------------------------------------------------------------------------------------------
@@ -328,6 +333,29 @@ def test_tiny_scenes(num_tris, build):
             img, st = s.render(a.camera, strat, 4, max_depth=3, seed=1)
             assert np.isfinite(img).all() and st["primary_hits"] > 0
             assert np.isclose(img.max(axis=(0, 1)), [3.0, 2.0, 1.0]).all()  # the light seen directly
+    finally:
+        s.close()
+
+
+def test_light_tree_edge_cases():
+    """MCPT_LIGHT_TREE on a one-light scene (the root is a leaf: probability 1, same film as the exact selection up to
+    rounding of w / (w / 1)), with sub-pixel jitter (tree walks at the first vertex too) and on a strategy that never
+    selects a light spherically (flag ignored)."""
+    a = _tiny_scene(5, True)
+    s = api.Scene(a, 0)
+    try:
+        cam = a.camera
+        for strat in (api.MIS, api.NEE_SPHERICAL, api.MIS_SINGLE):
+            exact, _ = s.render(cam, strat, 16, max_depth=4, seed=5, flags=api.FIX_MIXTURE_PDF)
+            tree, _ = s.render(cam, strat, 16, max_depth=4, seed=5, flags=api.FIX_MIXTURE_PDF | api.LIGHT_TREE)
+            assert np.isfinite(tree).all() and np.allclose(exact, tree, rtol=1e-4, atol=1e-6)
+            jit, _ = s.render(cam, strat, 16, max_depth=4, seed=5, flags=api.FIX_MIXTURE_PDF | api.LIGHT_TREE | api.JITTER)
+            assert np.isfinite(jit).all() and abs(jit.mean() - exact.mean()) < 0.25 * exact.mean() + 1e-6
+        u0, _ = s.render(cam, api.NEE_UNIFORM, 8, max_depth=4, seed=6)
+        u1, _ = s.render(cam, api.NEE_UNIFORM, 8, max_depth=4, seed=6, flags=api.LIGHT_TREE)
+        assert np.array_equal(u0, u1)
+        r = s.light_tree(np.array([[2.0, 0.3, 3.0]]), np.array([[0.0, 0.0, -1.0]]), np.array([0.3]), np.array([0], np.int32))
+        assert r["light"][0] == 0 and r["prob"][0] == 1.0 and r["query_prob"][0] == 1.0
     finally:
         s.close()
 
