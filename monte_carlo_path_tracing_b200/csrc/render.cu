@@ -30,7 +30,7 @@
 namespace mcpt {
 namespace {
 
-constexpr int kBlk = 128;             // threads per block (4 warps; a warp owns one 32-ray chunk at a time)
+constexpr int kBlk = 128;             // threads per block (4 warps; a warp owns one chunk of queue entries at a time)
 constexpr unsigned kFull = 0xffffffffu;
 constexpr size_t kTargetSlots = 128u << 20;  // auto batch: up to 128 Mi path slots in flight per pass (memory permitting)
 
@@ -154,14 +154,15 @@ __device__ __forceinline__ float warp_scan_incl(float v)
 }
 
 // ---- order-preserving queue compaction, wait-free ------------------------------------------------------------
-// A chunk is the 32 rays one warp processes.  The warp packs its 0..2 children per lane with __ballot_sync /
-// popc prefix sums into the chunk's own window of a STAGING queue (stage[chunk * stride + k], stride = 32 or,
-// for the MIS path tree, 64), records counts[chunk] and adds the count to its 1024-chunk group sum (one integer
+// A chunk is the kChunk = 256 queue entries one warp takes per ticket.  The warp packs the 0..2 children of each entry
+// with __ballot_sync / popc prefix sums, in input order, into the chunk's own window of a STAGING queue
+// (stage[chunk * stride + k], stride = 256 or, for the MIS path tree, 512), records counts[chunk] and adds the count to the
+// sum of its group of kGroup = 64 chunks (one integer
 // atomic per warp: commutative, so the result is deterministic).  k_gather then turns group sums + counts into
 // exact offsets and moves the chunk windows into the dense queue, preserving input order -- which keeps all
 // rays of one path-tree adjacent (k_runsum) without any warp ever waiting for another.
 constexpr int kSerialLights = 32;  // at or below: per-lane light loop in k_lightsel instead of the warp-cooperative sweep
-constexpr int kGroup = 256;   // chunks per k_gather block (one per thread)
+constexpr int kGroup = 64;    // chunks per k_gather block (16 Ki queue entries; threads 0..63 scan one chunk count each)
 
 __global__ void __launch_bounds__(256) k_gather(const Queue stage, const Queue out, const int* __restrict__ counts,
                                                 const int* __restrict__ groupsum, int nch, int stride, int capacity, int tree,
@@ -183,7 +184,7 @@ __global__ void __launch_bounds__(256) k_gather(const Queue stage, const Queue o
     __syncthreads();
     // 2. exclusive scan of this group's chunk counts (one chunk per thread)
     const int c0 = g * kGroup + tid;
-    const int tsum = (c0 < nch) ? counts[c0] : 0;
+    const int tsum = (tid < kGroup && c0 < nch) ? counts[c0] : 0;
     int incl = tsum;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -195,7 +196,7 @@ __global__ void __launch_bounds__(256) k_gather(const Queue stage, const Queue o
     int wbase = 0, gtotal = 0;
 #pragma unroll
     for (int w = 0; w < 8; w++) { if (w < warp) wbase += s_red[w]; gtotal += s_red[w]; }
-    s_base[tid] = gbase + wbase + incl - tsum;
+    if (tid < kGroup) s_base[tid] = gbase + wbase + incl - tsum;
     __syncthreads();
     if (g == gridDim.x - 1 && tid == 0) {
         const int total = gbase + gtotal;
@@ -548,11 +549,19 @@ struct Child { f3 o, d, thr; int exclude; uint64_t node; float misw; };
 // k_shade: everything shade* does at one vertex except the scene-BVH traversals, which the wavefront hands to
 // k_extend (closest hit of the children) and k_shadow (NEE visibility).  FIRST = primary vertices without jitter:
 // the ray comes from the camera formula and the hit from k_primary's per-pixel table.
+// A warp owns a chunk of kChunk = 256 queue entries and works on it in two phases.  Phase A (every entry, cheap): hit
+// record, vertex, back-face / emission classification, the accumulator write, the roulette taken before sampling
+// (MIS / BRDF-only); the entries that go on to sample -- 60 % at the first vertex of veach-mis, about 1 in 9 at the second --
+// are listed, in order, in shared memory.  Phase B (32 listed entries at a time, all lanes busy): light sampling, BRDF
+// sampling, the MIS light-only ray, emission of the children into the chunk's staging window.  The list keeps the input
+// order, so the children land exactly where the one-phase kernel put them (it ran 6.9 threads per instruction at the
+// later bounces, 17.8 at the first).
+constexpr int kChunk = 256;  // queue entries per warp ticket / staging window (128: veach-mis 1378 instead of 1399 Msamples/s)
 template <int STRAT, bool FIRST>
 #ifndef MCPT_SHADE_MINBLK
 #define MCPT_SHADE_MINBLK 1
 #endif
-__global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceArgs a)
+__global__ void __launch_bounds__(kBlk, STRAT == MCPT_MIS ? 5 : MCPT_SHADE_MINBLK) k_shade(const BounceArgs a)
 {
     constexpr bool kTree = (STRAT == MCPT_MIS);
     constexpr bool kNee = (STRAT == MCPT_NEE_SPHERICAL || STRAT == MCPT_NEE_UNIFORM);
@@ -560,10 +569,15 @@ __global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceA
     constexpr bool kShadow = kNee || kSingle;              // strategies that queue a visibility ray per vertex
     constexpr bool kSph = (STRAT == MCPT_NEE_SPHERICAL || STRAT == MCPT_MIS || kSingle);
     __shared__ int stack[kStackSm * kBlk];
+    __shared__ int s_list[kBlk / 32][kChunk];
+    int* list = s_list[threadIdx.x >> 5];
     const DScene& s = a.s;
     const int lane = threadIdx.x & 31;
+    const unsigned below = (1u << lane) - 1u;
     unsigned c_vert = 0, c_lrays = 0, c_phits = 0;
-    const int nchunks = (a.in_count + 31) >> 5;
+    const int nchunks = (a.in_count + kChunk - 1) / kChunk;
+    const int depth = a.bounce + 1;
+    const bool rr_forced = a.max_depth > 0 && depth >= a.max_depth;
 
     int next = 0;
     if (lane == 0) next = atomicAdd(a.ticket, 1);
@@ -571,14 +585,88 @@ __global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceA
         const int chunk = __shfl_sync(kFull, next, 0);
         if (chunk >= nchunks) break;
         if (lane == 0) next = atomicAdd(a.ticket, 1);  // prefetch the next ticket behind this chunk's work
-        const int i = chunk * 32 + lane;
-        const bool valid = i < a.in_count;
+
+        // ==== phase A: classify every entry, write its accumulator, list the ones that sample ===========================
+        int n_list = 0;
+#pragma unroll 1
+        for (int sub = 0; sub < kChunk / 32; sub++) {
+            const int i = chunk * kChunk + sub * 32 + lane;
+            bool keep = false;
+            if (i < a.in_count) {
+                // shade prologue: p, N, back-face, emission (main.cpp:273-288 / 351-366 / 406-421)
+                int slot = i, prim;
+                float hb, hg;
+                f3 wo;
+                uint32_t pixel;
+                if (FIRST) {
+                    pixel = (uint32_t)(i % a.npix);
+                    const float4 ph = __ldg(a.primary_hit + pixel);
+                    prim = __float_as_int(ph.x); hb = ph.y; hg = ph.z;
+                    wo = -camera_dir(a.cam, (int)pixel, 0.f, 0.f);
+                    if (prim >= 0) c_phits++;
+                } else {
+                    const float4 qd = a.in.dir[i], qh = a.hit[i];
+                    wo = -to_f3(qd);
+                    slot = __float_as_int(qd.w);
+                    pixel = (uint32_t)(slot % a.npix);
+                    prim = __float_as_int(qh.x); hb = qh.y; hg = qh.z;
+                    if (a.bounce == 0 && prim >= 0) c_phits++;  // jittered camera rays
+                }
+                f3 contrib = mk<float>(0.f, 0.f, 0.f);
+                if (prim >= 0) {
+                    const Vertex v = make_vertex(s, prim, hb, hg, wo);
+                    if (v.front) {
+                        if (v.light >= 0) {  // emissive: self-emission only
+                            // shade(): an indirect ray that lands on a light contributes 0 (main.cpp:338); the emission
+                            // return of main.cpp:284-288 is only reachable from the camera ray.
+                            if (!kNee || a.bounce == 0) {
+                                f3 thr = mk<float>(1.f, 1.f, 1.f);
+                                float misw = 1.f;  // single-path MIS: weight of emission found by this ray (1 for camera rays)
+                                if (!FIRST) {
+                                    const float4 qt = a.in.thr[i];
+                                    thr = to_f3(qt);
+                                    if (kSingle && a.bounce > 0) misw = qt.w;
+                                }
+                                contrib = thr * to_f3(__ldg(s.lights + 5 * v.light + 4)) * misw;
+                            }
+                        } else {
+                            keep = true;
+                            c_vert++;
+                            if (!kNee) {  // MIS / BRDF-only: roulette before any sampling (main.cpp:375-383 / 429-437)
+                                uint64_t node = FIRST ? 1 : (uint64_t)a.bounce + 1;
+                                if (kTree && !FIRST) { const uint2 nd = a.in.node[i]; node = ((uint64_t)nd.y << 32) | nd.x; }
+                                const uint32_t sample = (uint32_t)(a.sample_base + slot / a.npix);
+                                keep = !rr_forced && !(rng_draw4(a.seed, pixel, sample, node, 0).u[0] > a.p_rr);
+                            }
+                        }
+                    }
+                }
+                // accumulate
+                if (FIRST) a.Lacc[slot] = make_float4(contrib.x, contrib.y, contrib.z, 0.f);
+                else if (kTree) a.contrib[i] = make_float4(contrib.x, contrib.y, contrib.z, __int_as_float(slot));
+                else if (contrib.x != 0.f || contrib.y != 0.f || contrib.z != 0.f) {
+                    float4 L = a.Lacc[slot];
+                    L.x += contrib.x; L.y += contrib.y; L.z += contrib.z;
+                    a.Lacc[slot] = L;
+                }
+            }
+            const unsigned mk_ = __ballot_sync(kFull, keep);
+            if (keep) list[n_list + __popc(mk_ & below)] = i;
+            n_list += __popc(mk_);
+        }
+        __syncwarp();
+
+        // ==== phase B: the listed entries, 32 at a time ===================================================================
+        int emitted = 0;
+#pragma unroll 1
+        for (int b0 = 0; b0 < n_list; b0 += 32) {
+        const bool valid = b0 + lane < n_list;
+        const int i = valid ? list[b0 + lane] : 0;
 
         // -- A. ray + path state, closest hit (extend) ------------------------------------------------
         f3 o = mk<float>(0.f, 0.f, 0.f), d = mk<float>(0.f, 0.f, 1.f), thr = mk<float>(1.f, 1.f, 1.f);
-        int slot = 0, exclude = -1;
+        int slot = 0;
         uint64_t node = 1;
-        float misw = 1.f;  // single-path MIS: weight of emission found by this ray (1 for camera rays)
         Hit h;
         h.prim = -1; h.b = h.g = h.t = 0.f;
         uint32_t pixel = 0, sample = 0;
@@ -591,12 +679,9 @@ __global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceA
                 d = camera_dir(a.cam, (int)pixel, 0.f, 0.f);
                 const float4 ph = __ldg(a.primary_hit + pixel);
                 h.prim = __float_as_int(ph.x); h.b = ph.y; h.g = ph.z; h.t = ph.w;
-                if (h.prim >= 0) c_phits++;
             } else {
                 const float4 qo = a.in.org[i], qd = a.in.dir[i], qt = a.in.thr[i];
                 o = to_f3(qo); d = to_f3(qd); thr = to_f3(qt);
-                if (kSingle && a.bounce > 0) misw = qt.w;
-                exclude = __float_as_int(qo.w);
                 slot = __float_as_int(qd.w);
                 pixel = (uint32_t)(slot % a.npix);
                 sample = (uint32_t)(a.sample_base + slot / a.npix);
@@ -604,38 +689,26 @@ __global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceA
                 else node = (uint64_t)a.bounce + 1;
                 const float4 qh = a.hit[i];
                 h.prim = __float_as_int(qh.x); h.b = qh.y; h.g = qh.z; h.t = qh.w;
-                if (a.bounce == 0 && h.prim >= 0) c_phits++;  // jittered camera rays
             }
         }
 
-        // -- B. shade prologue: p, N, back-face, emission (main.cpp:273-288 / 351-366 / 406-421) -----------
-        f3 contrib = mk<float>(0.f, 0.f, 0.f);
-        bool alive = valid && h.prim >= 0;
+        // -- B. the vertex again (phase A established: front-facing, not emissive, roulette survived) -------------------
+        bool alive = valid;
         f3 p = o, N = d, wo = -d;
         PhongMat<float> mat;
         mat.kd = mat.ks = mk<float>(0.f, 0.f, 0.f); mat.ns = 1.f;
         if (alive) {
             const Vertex v = make_vertex(s, h.prim, h.b, h.g, wo);
             p = v.p; N = v.N;
-            if (!v.front) alive = false;  // hit from behind -> 0
-            else if (v.light >= 0) {      // emissive: self-emission only
-                // shade(): an indirect ray that lands on a light contributes 0 (main.cpp:338); the emission
-                // return of main.cpp:284-288 is only reachable from the camera ray.
-                if (!kNee || a.bounce == 0) contrib = thr * to_f3(__ldg(s.lights + 5 * v.light + 4)) * misw;
-                alive = false;
-            } else mat = load_mat(s, v.mat);
+            mat = load_mat(s, v.mat);
         }
-        const int depth = a.bounce + 1;
-        const bool rr_forced = a.max_depth > 0 && depth >= a.max_depth;
         Rng4 r0, r1;
         r0.u[0] = r0.u[1] = r0.u[2] = r0.u[3] = 0.5f;
         r1 = r0;
         if (alive) { r0 = rng_draw4(a.seed, pixel, sample, node, 0); if (STRAT != MCPT_BRDF_ONLY) r1 = rng_draw4(a.seed, pixel, sample, node, 1); }
-        if (alive) c_vert++;
 
-        // MIS / BRDF-only: roulette before any sampling (main.cpp:375-383 / 429-437)
-        bool rr_ok = alive && !rr_forced && !(r0.u[0] > a.p_rr);
-        if (!kNee && !rr_ok) alive = false;
+        // NEE: the roulette comes after the direct term (main.cpp:321-329); the others took it in phase A
+        const bool rr_ok = alive && !rr_forced && !(r0.u[0] > a.p_rr);
 
         // -- C. light sampling ---------------------------------------------------------------------------
         Child ch[2];
@@ -757,20 +830,10 @@ __global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceA
             }
         }
 
-        // -- E. accumulate + emit children --------------------------------------------------------------
-        if (valid) {
-            if (FIRST) a.Lacc[slot] = make_float4(contrib.x, contrib.y, contrib.z, 0.f);
-            else if (kTree) a.contrib[i] = make_float4(contrib.x, contrib.y, contrib.z, __int_as_float(slot));
-            else if (contrib.x != 0.f || contrib.y != 0.f || contrib.z != 0.f) {
-                float4 L = a.Lacc[slot];
-                L.x += contrib.x; L.y += contrib.y; L.z += contrib.z;
-                a.Lacc[slot] = L;
-            }
-        }
+        // -- E. emit children into the chunk's staging window, in list (= input) order ---------------------------------------
         {
             const unsigned m1 = __ballot_sync(kFull, n_out >= 1), m2 = __ballot_sync(kFull, n_out >= 2);
-            const unsigned below = (1u << lane) - 1u;
-            const int off = chunk * (kTree ? 64 : 32) + __popc(m1 & below) + __popc(m2 & below);
+            const int off = chunk * (kTree ? 2 * kChunk : kChunk) + emitted + __popc(m1 & below) + __popc(m2 & below);
             for (int k = 0; k < n_out; k++) {
                 const int dst = off + k;
                 const Child& c = ch[k];
@@ -779,11 +842,7 @@ __global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceA
                 a.out.thr[dst] = make_float4(c.thr.x, c.thr.y, c.thr.z, kSingle ? c.misw : 0.f);
                 if (kTree) a.out.node[dst] = make_uint2((uint32_t)c.node, (uint32_t)(c.node >> 32));
             }
-            if (lane == 0) {
-                const int total = __popc(m1) + __popc(m2);
-                a.counts[chunk] = total;
-                if (total) atomicAdd(a.groupsum + chunk / kGroup, total);
-            }
+            emitted += __popc(m1) + __popc(m2);
         }
         if (kShadow) {
             // visibility rays: unordered append (every slot owns at most one per bounce, so k_shadow's
@@ -802,6 +861,12 @@ __global__ void __launch_bounds__(kBlk, MCPT_SHADE_MINBLK) k_shade(const BounceA
                 }
             }
         }
+        }  // batches of the list
+        if (lane == 0) {
+            a.counts[chunk] = emitted;
+            if (emitted) atomicAdd(a.groupsum + chunk / kGroup, emitted);
+        }
+        __syncwarp();  // the next chunk overwrites the list
     }
     // warp-level counter reduction: one atomic per counter per warp
     c_vert = __reduce_add_sync(kFull, c_vert);
@@ -1017,15 +1082,15 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     const size_t slots = npix * (size_t)batch;
     if (slots > (1u << 30)) throw Error(MCPT_ERR_INVALID, "batch_spp * pixels too large");
     const size_t cap = tree ? slots * 3 : slots;
-    const size_t chunks = (cap + 31) / 32 + 1;
+    const size_t chunks = (cap + kChunk - 1) / kChunk + 1;
     const bool single = prm->strategy == MCPT_MIS_SINGLE;
     const bool sph = prm->strategy == MCPT_NEE_SPHERICAL || prm->strategy == MCPT_MIS || single;
 
     // workspace carve-up
     size_t off = 0;
     auto place = [&](size_t bytes) { size_t at = off; off = (off + bytes + 255) & ~(size_t)255; return at; };
-    // Q[0]: dense ray queue (cap entries).  Q[1]: staging queue, one window of `stride` entries per 32-ray chunk.
-    const size_t stride = tree ? 64 : 32;
+    // Q[0]: dense ray queue (cap entries).  Q[1]: staging queue, one window of `stride` entries per chunk of kChunk queue entries.
+    const size_t stride = tree ? 2 * kChunk : kChunk;
     const size_t qn[2] = {cap, chunks * stride};
     size_t o_q[2][4];
     for (int q = 0; q < 2; q++) {
@@ -1164,7 +1229,7 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
         for (int bounce = 0; count > 0; bounce++) {
             if (prm->max_depth <= 0 && bounce >= 256) break;  // unlimited depth: RR has long emptied the queue
             a.in_count = count; a.bounce = bounce;
-            const int nch = (count + 31) / 32, ngroups = (nch + kGroup - 1) / kGroup;
+            const int nch = (count + kChunk - 1) / kChunk, ngroups = (nch + kGroup - 1) / kGroup;
             MCPT_CUDA(cudaMemsetAsync(d_ticket, 0, 32, st));
             MCPT_CUDA(cudaMemsetAsync(d_groupsum, 0, (size_t)ngroups * 4, st));
             MCPT_CUDA(cudaEventRecord(scene->ev[2], st));
