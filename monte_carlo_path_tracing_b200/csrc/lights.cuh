@@ -192,8 +192,16 @@ __device__ __forceinline__ float2 light_weight_pair(float4 p0, float4 p1, float4
     const float2 bx = __fadd2_rn(bc2(p1.x), v.mx), by = __fadd2_rn(bc2(p1.y), v.my), bz = __fadd2_rn(bc2(p1.z), v.mz);
     const float2 cx = __fadd2_rn(bc2(p2.x), v.mx), cy = __fadd2_rn(bc2(p2.y), v.my), cz = __fadd2_rn(bc2(p2.z), v.mz);
     const float2 num = dot2_rn(bc2(p3.x), bc2(p3.y), bc2(p3.z), ax, ay, az);
-    const float2 ha = dot2_rn(v.nx, v.ny, v.nz, ax, ay, az), hb = dot2_rn(v.nx, v.ny, v.nz, bx, by, bz),
-                 hc = dot2_rn(v.nx, v.ny, v.nz, cx, cy, cz);
+    // horizon cull (:187-197): the light counts iff ANY of its vertices is above the vertex's tangent plane.  The first
+    // vertex alone settles that for nearly every light; the other two are only looked at when some lane needs them
+    // (all 32 lanes are here together: the sweeps have warp-uniform trip counts).
+    const float2 ha = dot2_rn(v.nx, v.ny, v.nz, ax, ay, az);
+    bool up0 = ha.x >= 1e-8f, up1 = ha.y >= 1e-8f;
+    if (__any_sync(0xffffffffu, !(up0 && up1))) {
+        const float2 hb = dot2_rn(v.nx, v.ny, v.nz, bx, by, bz), hc = dot2_rn(v.nx, v.ny, v.nz, cx, cy, cz);
+        up0 = up0 || fmaxf(hb.x, hc.x) >= 1e-8f;
+        up1 = up1 || fmaxf(hb.y, hc.y) >= 1e-8f;
+    }
     const float2 aa = dot2_rn(ax, ay, az, ax, ay, az), bb = dot2_rn(bx, by, bz, bx, by, bz), cc = dot2_rn(cx, cy, cz, cx, cy, cz);
     const float2 la = __fmul2_rn(aa, make_float2(rsqrtf(aa.x), rsqrtf(aa.y)));
     const float2 lb = __fmul2_rn(bb, make_float2(rsqrtf(bb.x), rsqrtf(bb.y)));
@@ -216,8 +224,8 @@ __device__ __forceinline__ float2 light_weight_pair(float4 p0, float4 p1, float4
     p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C7));
     const float2 r = __ffma2_rn(q, __fmul2_rn(p, s), q);
     const float2 w = __fmul2_rn(make_float2(atan2_fix(r.x, num.x, den.x), atan2_fix(r.y, num.y, den.y)), bc2(p3.w));
-    const bool ok0 = num.x >= p2.w && fmaxf(ha.x, fmaxf(hb.x, hc.x)) >= 1e-8f && w.x < CUDART_INF_F;
-    const bool ok1 = num.y >= p2.w && fmaxf(ha.y, fmaxf(hb.y, hc.y)) >= 1e-8f && w.y < CUDART_INF_F;
+    const bool ok0 = num.x >= p2.w && up0 && w.x < CUDART_INF_F;
+    const bool ok1 = num.y >= p2.w && up1 && w.y < CUDART_INF_F;
     return make_float2(ok0 ? w.x : 0.f, ok1 ? w.y : 0.f);
 }
 
