@@ -202,6 +202,11 @@ int mcpt_host_bvh_check(const McptSceneDesc* desc, int lights_only, uint32_t out
 /* Light hierarchy of MCPT_LIGHT_TREE.  Host-only structural check (every light in exactly one leaf, every ancestor's
  * sphere / normal cone holds the light): out4 = {nodes, max_depth, errors, lights}. */
 int mcpt_host_light_tree_check(const McptSceneDesc* desc, uint32_t out4[4]);
+/* The hierarchy a McptScene holds: node count and depth; and the nodes themselves in the device layout of
+ * csrc/light_tree.h (12 floats per node: centre | radius, cone axis | cos theta_o, power | left | right | parent as int
+ * bits) with the leaf node of every light -- what a host-side restatement of the walk needs (tests/test_gpu_parity.py). */
+int mcpt_scene_light_tree_info(const McptScene*, uint32_t* nodes, uint32_t* max_depth);
+int mcpt_scene_light_tree_nodes(const McptScene*, float* out_nodes12, int32_t* out_leaf_of_light);
 /* Parity / test entry point: at vertex (x1, N) draw a light with uniform u (prim, selection probability) and report
  * the selection probability of every light in `query_light` [n] (index into the light list, -1 = none) together
  * with that light's FP32 spherical-triangle weight sA * (R+G+B) (0 = culled at this vertex). */

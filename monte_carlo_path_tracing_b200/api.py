@@ -33,6 +33,7 @@ SYMBOLS = [
     "mcpt_last_error", "mcpt_version", "mcpt_device_count", "mcpt_host_scene_load", "mcpt_host_scene_desc",
     "mcpt_host_scene_camera", "mcpt_host_scene_free", "mcpt_host_bvh_check", "mcpt_scene_create_ex",
     "mcpt_scene_build_info", "mcpt_scene_bvh_check", "mcpt_host_light_tree_check", "mcpt_light_tree_batch",
+    "mcpt_scene_light_tree_info", "mcpt_scene_light_tree_nodes",
 ]
 
 
@@ -350,3 +351,13 @@ class Scene:
         _check(self.lib.mcpt_light_tree_batch(self.handle, C.c_size_t(n), _p(x1), _p(N), _p(u), _p(q), _p(light), _p(prob),
                                               _p(qprob), _p(qw)))
         return dict(light=light, prob=prob, query_prob=qprob, query_weight=qw)
+
+    def light_tree_arrays(self):
+        """The light hierarchy as built for this scene: nodes [n, 12] float32 (csrc/light_tree.h layout, the three
+        child / parent words are int32 bit patterns) and the leaf node of every light."""
+        n = C.c_uint32(); d = C.c_uint32()
+        _check(self.lib.mcpt_scene_light_tree_info(self.handle, C.byref(n), C.byref(d)))
+        nodes = np.zeros((n.value, 12), np.float32)
+        leaf = np.zeros(len(self.arrays.light_prim), np.int32)
+        _check(self.lib.mcpt_scene_light_tree_nodes(self.handle, _p(nodes), _p(leaf)))
+        return nodes, leaf, d.value

@@ -471,6 +471,23 @@ int mcpt_host_light_tree_check(const McptSceneDesc* desc, uint32_t out4[4])
     });
 }
 
+int mcpt_scene_light_tree_info(const McptScene* s, uint32_t* nodes, uint32_t* max_depth)
+{
+    return guarded([&] {
+        if (!s) throw Error(MCPT_ERR_INVALID, "null scene");
+        if (nodes) *nodes = s->ltree.num_nodes;
+        if (max_depth) *max_depth = s->ltree.max_depth;
+    });
+}
+int mcpt_scene_light_tree_nodes(const McptScene* s, float* out_nodes12, int32_t* out_leaf)
+{
+    return guarded([&] {
+        if (!s || !out_nodes12 || !out_leaf) throw Error(MCPT_ERR_INVALID, "null argument");
+        std::memcpy(out_nodes12, s->ltree.nodes.data(), s->ltree.nodes.size() * sizeof(f4));
+        std::memcpy(out_leaf, s->ltree.leaf_of_light.data(), s->ltree.leaf_of_light.size() * sizeof(int32_t));
+    });
+}
+
 // the same check on the scene BVH a McptScene actually holds (whichever builder made it)
 int mcpt_scene_bvh_check(const McptScene* s, uint32_t* errors)
 {

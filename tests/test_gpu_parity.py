@@ -213,6 +213,62 @@ def test_light_tree_selection(scene_name, gpu_scene_of, arrays_of):
     assert np.abs(freq - P[k]).max() < 2e-3, np.abs(freq - P[k]).max()
 
 
+def _lt_importance_np(t0, t1, power, x, n):
+    """FP64 restatement of lt_importance (csrc/lights.cuh): Conty-Kulla importance of one node for vertex (x, n)."""
+    dv = x - t0[:3]
+    d2 = float(dv @ dv); r2 = float(t0[3]) ** 2
+    wi = dv / np.sqrt(max(d2, 1e-30))
+    inside = not (d2 > r2)
+    sin2_b = 0.0 if inside else r2 / d2
+    sin_b, cos_b = np.sqrt(sin2_b), (-1.0 if inside else np.sqrt(max(0.0, 1.0 - sin2_b)))
+    sub_c = lambda sa, ca, sb, cb: 1.0 if ca > cb else ca * cb + sa * sb
+    sub_s = lambda sa, ca, sb, cb: 0.0 if ca > cb else sa * cb - ca * sb
+    cos_w = float(t1[:3] @ wi); sin_w = np.sqrt(max(0.0, 1.0 - cos_w * cos_w))
+    cos_o = float(t1[3]); sin_o = np.sqrt(max(0.0, 1.0 - cos_o * cos_o))
+    cos_x, sin_x = sub_c(sin_w, cos_w, sin_o, cos_o), sub_s(sin_w, cos_w, sin_o, cos_o)
+    cos_e = sub_c(sin_x, cos_x, sin_b, cos_b)
+    cos_i = -float(n @ wi); sin_i = np.sqrt(max(0.0, 1.0 - cos_i * cos_i))
+    cos_r = sub_c(sin_i, cos_i, sin_b, cos_b)
+    if not (cos_e > 0.0) or not (cos_r > 0.0):
+        return 0.0
+    return power * cos_e * cos_r / max(d2, r2)
+
+
+def test_light_tree_matches_host_restatement(scene_name, gpu_scene_of, arrays_of):
+    """The device walk (lt_pick / lt_prob, FP32, approximate division) against an FP64 numpy restatement of the same
+    tree arithmetic on the node array the scene holds: selection probability of every light at a few vertices."""
+    a, _ = arrays_of(scene_name)
+    s = gpu_scene_of(scene_name)
+    nodes, leaf, depth = s.light_tree_arrays()
+    L = len(a.light_prim)
+    assert nodes.shape == (2 * L - 1, 12) and depth < 64
+    ints = nodes.view(np.int32)
+    nd = nodes.astype(np.float64)
+    x, Nn, _, _ = util.shading_points(a, 6, 311)
+
+    def prob(light, X, N):
+        node, p = int(leaf[light]), 1.0
+        while True:
+            parent = int(ints[node, 11])
+            if parent < 0:
+                return p
+            left, right = int(ints[parent, 9]), int(ints[parent, 10])
+            il = _lt_importance_np(nd[left, 0:4], nd[left, 4:8], nd[left, 8], X, N)
+            ir = _lt_importance_np(nd[right, 0:4], nd[right, 4:8], nd[right, 8], X, N)
+            if not (il + ir > 0.0):
+                il, ir = nd[left, 8], nd[right, 8]
+            pl = 0.5 if not (il + ir > 0.0) else min(il / (il + ir), 1.0)
+            p *= pl if node == left else 1.0 - pl
+            node = parent
+
+    lights = np.arange(L, dtype=np.int32) if L <= 64 else np.random.default_rng(312).choice(L, 64, replace=False).astype(np.int32)
+    for k in range(len(x)):
+        r = s.light_tree(np.repeat(x[k:k + 1], len(lights), 0), np.repeat(Nn[k:k + 1], len(lights), 0), np.full(len(lights), 0.5), lights)
+        want = np.array([prob(int(l), x[k], Nn[k]) for l in lights])
+        # a child the FP64 restatement gives exactly zero importance may get a few ulps on the device and vice versa
+        assert np.allclose(r["query_prob"], want, rtol=2e-3, atol=1e-6), np.abs(r["query_prob"] - want).max()
+
+
 def test_tonemap(gpu_scene_of, golden):
     vals = np.abs(np.random.default_rng(109).normal(size=(200, 3))) * 200
     out = gpu_scene_of("cornell-box").tonemap(vals.astype(np.float32))
