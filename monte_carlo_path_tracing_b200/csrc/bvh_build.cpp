@@ -15,7 +15,10 @@ using TmpNode = BvhTmpNode;
 struct Ref { Box box; float c[3]; int32_t prim; };
 
 constexpr int kBins = 16;
-constexpr float kCostTrav = 1.0f, kCostTri = 1.0f;
+#ifndef MCPT_COST_TRAV
+#define MCPT_COST_TRAV 1.0f
+#endif
+constexpr float kCostTrav = MCPT_COST_TRAV, kCostTri = 1.0f;
 
 struct Builder {
     std::vector<Ref> refs;
