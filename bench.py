@@ -375,13 +375,15 @@ def run_ours(args, wl_name, wl):
         except Exception:
             pass
         L = len(arrays.light_prim)
-        # FP32 work actually executed (estimate): ~320 flops of shading per vertex, plus ~70 flops per light per sweep of
+        # FP32 work actually executed (estimate): ~320 flops of shading per vertex, plus ~90 flops per light per sweep of
         # the light table; without jitter the first vertex of a pixel is swept once per pass (k_lightprep), later
         # vertices once each -- for MIS only the 60 % that survive the roulette taken before sampling (main.cpp:429-437)
         passes = sum(s["passes"] for s in stats)
         later = max(0, tot["vertices"] - sum(s["primary_hits"] for s in stats))
         sweeps = (npix * passes + later * (0.6 if wl["strategy"] == "MIS" else 1.0)) if (sph and not args.light_tree) else 0
-        flops = 320.0 * tot["vertices"] + 70.0 * L * sweeps
+        # per light and vertex (lights.cuh light_weight_pair): 10 FADD + 17 FMUL + 27 FFMA (eight dot products, three norms, the
+        # Van Oosterom-Strackee denominator, the 8-term atan polynomial) = 81 flops + 4 MUFU + ~5 min/max/select
+        flops = 320.0 * tot["vertices"] + 90.0 * L * sweeps
         flops_per_vertex = flops / max(tot["vertices"], 1)
         fp32_peak = 148 * 128 * 2 * 1.965e9
         line = base_line(args, wl_name, wl, cam, S)
