@@ -54,6 +54,13 @@ enum {
     MCPT_FIX_MIXTURE_PDF = 4,  /* F8: BRDF-sampled directions are weighted with the mixture pdf */
     MCPT_JITTER = 16,          /* uniform sub-pixel jitter (the reference has none, F4) */
     MCPT_ACCUMULATE = 64,      /* mcpt_render_device: add into d_out instead of overwriting */
+    MCPT_PARITY_FP64 = 256,    /* PARITY render mode: the whole estimator -- camera ray, closest hits, vertex, Phong eval /
+                                * sample / pdf, both light samplers, roulette, accumulation -- runs in FP64 in the reference's
+                                * expression order without FMA contraction (csrc/render_parity.cu), so a film is comparable
+                                * PIXEL BY PIXEL with the oracle fed the same keyed uniforms (oracle flag ORACLE_RNG_KEYED),
+                                * not just statistically.  Implies MCPT_LEAF_EXACT.  Orders of magnitude slower than the
+                                * FP32 wavefront; it exists so that the renderer itself, not a test kernel, meets the
+                                * bit-exact-ids / 1e-5 bar.  Ignores MCPT_JITTER-less shortcuts and MCPT_LIGHT_TREE. */
     MCPT_LIGHT_TREE = 128      /* NOT a reference estimator: the spherical strategies pick their
                                 * light triangle by descending a light hierarchy (csrc/light_tree.h, O(log L) per vertex)
                                 * instead of the O(L) loop of Mylight.cpp:169-276; the chosen triangle is still sampled by
@@ -90,6 +97,15 @@ typedef struct McptCamera {
     double pixellen;  /* tan(fovy/2) * |w| / (H/2); the reference's literal is F7 */
 } McptCamera;
 
+/* Ray/triangle test used by mcpt_render.  MCPT_LEAF_FAST: FP32 Moeller-Trumbore over the 4-wide
+ * BVH, any-hit visibility rays -- the throughput path.  MCPT_LEAF_EXACT: every ray of the render (camera, extension,
+ * visibility, light-only) is resolved by the reference's own test, the FP64 Cramer expression tree of
+ * Myobj::intersect_with_triangle (Myobj.cpp:165-192) evaluated without FMA contraction inside FP64 slab tests, and
+ * visibility is the reference's closest-hit-and-compare-ids (main.cpp:309-311) instead of an any-hit search: the ids
+ * the wavefront sees are the ones the reference's exhaustive search returns for the same ray.  Shading stays FP32
+ * unless MCPT_PARITY_FP64 is also set. */
+typedef enum McptLeafMode { MCPT_LEAF_FAST = 0, MCPT_LEAF_EXACT = 1 } McptLeafMode;
+
 typedef struct McptRenderParams {
     int32_t width, height;
     int32_t spp;         /* samples per pixel rendered by THIS call */
@@ -101,6 +117,8 @@ typedef struct McptRenderParams {
     uint64_t seed;
     float p_rr;          /* 0 -> 0.6 (main.cpp:321,375,429) */
     int32_t batch_spp;   /* samples per pixel in flight per wavefront pass; 0 -> auto */
+    int32_t leaf_mode;   /* McptLeafMode: which ray/triangle test every ray of the render uses */
+    int32_t reserved;    /* must be 0 */
 } McptRenderParams;
 
 typedef struct McptStats {
@@ -163,9 +181,19 @@ int mcpt_intersect_tri_batch(McptScene*, size_t n, const double* ro, const doubl
                              int precision, int32_t* hit, double* bgt);
 /* closest hit over all prims except `exclude` (Myobj::closet_ray_intersect, Myobj.cpp:334-474) or, with
  * light_only, over emissive prims (closet_ray_intersect_light_triangle, :476-622); semantics = exhaustive
- * search with strict < on t and ascending prim order (Myobj.cpp:194-213).  prim = -1 on miss. */
+ * search with strict < on t and ascending prim order (Myobj.cpp:194-213).  prim = -1 on miss.
+ * precision 1 runs the renderer's own FP32 code (k_extend's stream traversal of the 4-wide BVH; with light_only the
+ * trace_fast over the light BVH that k_shade calls for the MIS light pdf); precision 2 runs the wavefront's
+ * MCPT_LEAF_EXACT kernel (k_extend_exact) on the FP32 roundings of the rays, as the render queues hold them. */
 int mcpt_intersect_batch(McptScene*, size_t n, const double* ro, const double* rd, const int32_t* exclude,
                          int light_only, int precision, int32_t* prim, double* bgt);
+/* The NEE visibility test of main.cpp:309-311 -- "the closest hit along wl IS the sampled light triangle" -- on explicit
+ * rays (origin ro on prim `exclude`, unit direction rd aimed at light triangle `light_prim`), through the renderer's own
+ * kernels: leaf_mode MCPT_LEAF_FAST = k_shadow (any-hit search for something that beats the light point under the
+ * closest-hit order), MCPT_LEAF_EXACT = k_shadow_exact (closest hit, compare ids).  visible[i] = 1 / 0, or -1 when rd
+ * misses the light triangle itself (the renderer queues no visibility ray then). */
+int mcpt_visibility_batch(McptScene*, size_t n, const double* ro, const double* rd, const int32_t* exclude,
+                          const int32_t* light_prim, int leaf_mode, int32_t* visible);
 /* BRDF::get_brdf_phong / sample_from_phong / eval_sample_from_phong_pdf (BRDF.cpp:17-132) */
 int mcpt_phong_eval_batch(McptScene*, size_t n, const double* N, const double* wi, const double* wr,
                           const double* kd, const double* ks, const double* ns, int precision, double* rgb);

@@ -20,7 +20,8 @@ CSRC = os.path.join(HERE, "csrc")
 
 NEE_SPHERICAL, BRDF_ONLY, MIS, NEE_UNIFORM, MIS_SINGLE = 0, 1, 2, 3, 4
 STRATEGY_NAMES = {0: "NEE_SPHERICAL", 1: "BRDF_ONLY", 2: "MIS", 3: "NEE_UNIFORM"}
-FIX_NEE_MEASURE, FIX_MIXTURE_PDF, JITTER, ACCUMULATE, LIGHT_TREE = 2, 4, 16, 64, 128
+FIX_NEE_MEASURE, FIX_MIXTURE_PDF, JITTER, ACCUMULATE, LIGHT_TREE, PARITY_FP64 = 2, 4, 16, 64, 128, 256
+LEAF_FAST, LEAF_EXACT = 0, 1
 FP64, FP32 = 0, 1
 BUILD_HOST_SAH, BUILD_GPU_LBVH = 0, 1
 
@@ -33,7 +34,7 @@ SYMBOLS = [
     "mcpt_last_error", "mcpt_version", "mcpt_device_count", "mcpt_host_scene_load", "mcpt_host_scene_desc",
     "mcpt_host_scene_camera", "mcpt_host_scene_free", "mcpt_host_bvh_check", "mcpt_scene_create_ex",
     "mcpt_scene_build_info", "mcpt_scene_bvh_check", "mcpt_host_light_tree_check", "mcpt_light_tree_batch",
-    "mcpt_scene_light_tree_info", "mcpt_scene_light_tree_nodes",
+    "mcpt_scene_light_tree_info", "mcpt_scene_light_tree_nodes", "mcpt_visibility_batch",
 ]
 
 
@@ -58,7 +59,8 @@ class CameraC(C.Structure):
 class RenderParams(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("spp", C.c_int32), ("spp_offset", C.c_int32),
                 ("spp_total", C.c_int32), ("max_depth", C.c_int32), ("strategy", C.c_int32), ("flags", C.c_uint32),
-                ("seed", C.c_uint64), ("p_rr", C.c_float), ("batch_spp", C.c_int32)]
+                ("seed", C.c_uint64), ("p_rr", C.c_float), ("batch_spp", C.c_int32), ("leaf_mode", C.c_int32),
+                ("reserved", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -213,15 +215,17 @@ class Scene:
             pass
 
     # ---- render -------------------------------------------------------------------------------
-    def _params(self, cam, strategy, spp, max_depth, flags, seed, spp_offset, spp_total, batch_spp, p_rr):
+    def _params(self, cam, strategy, spp, max_depth, flags, seed, spp_offset, spp_total, batch_spp, p_rr, leaf_mode=LEAF_FAST):
         p = RenderParams()
         p.width, p.height = cam.width, cam.height
         p.spp, p.spp_offset, p.spp_total = spp, spp_offset, spp_total or spp
         p.max_depth, p.strategy, p.flags, p.seed, p.p_rr, p.batch_spp = max_depth, strategy, flags, seed, p_rr, batch_spp
+        p.leaf_mode, p.reserved = leaf_mode, 0
         return p
 
     def render(self, cam: Camera, strategy: int, spp: int, max_depth: int = 0, flags: int = 0, seed: int = 1,
-               spp_offset: int = 0, spp_total: int = 0, batch_spp: int = 0, p_rr: float = 0.0, out=None):
+               spp_offset: int = 0, spp_total: int = 0, batch_spp: int = 0, p_rr: float = 0.0, out=None,
+               leaf_mode: int = LEAF_FAST):
         """mcpt_render: host image out (H, W, 3) float32 linear radiance + stats dict.  ``out``: an existing C-contiguous
         float32 array of that shape (e.g. a view of pinned memory) to receive the film instead of a fresh one."""
         if out is None:
@@ -229,17 +233,17 @@ class Scene:
         elif out.dtype != np.float32 or out.size != cam.height * cam.width * 3 or not out.flags.c_contiguous:
             raise ValueError("out must be a C-contiguous float32 array of H*W*3 elements")
         st = Stats()
-        p = self._params(cam, strategy, spp, max_depth, flags, seed, spp_offset, spp_total, batch_spp, p_rr)
+        p = self._params(cam, strategy, spp, max_depth, flags, seed, spp_offset, spp_total, batch_spp, p_rr, leaf_mode)
         cc = camera_c(cam)
         _check(self.lib.mcpt_render(self.handle, C.byref(cc), C.byref(p), _p(out), C.byref(st)))
         return out, st.as_dict()
 
     def render_device(self, cam: Camera, strategy: int, spp: int, d_out_ptr: int, stream: int = 0, max_depth: int = 0,
                       flags: int = 0, seed: int = 1, spp_offset: int = 0, spp_total: int = 0, batch_spp: int = 0,
-                      p_rr: float = 0.0):
+                      p_rr: float = 0.0, leaf_mode: int = LEAF_FAST):
         """mcpt_render_device: writes W*H*3 floats at device pointer ``d_out_ptr`` on CUDA stream ``stream``."""
         st = Stats()
-        p = self._params(cam, strategy, spp, max_depth, flags, seed, spp_offset, spp_total, batch_spp, p_rr)
+        p = self._params(cam, strategy, spp, max_depth, flags, seed, spp_offset, spp_total, batch_spp, p_rr, leaf_mode)
         cc = camera_c(cam)
         _check(self.lib.mcpt_render_device(self.handle, C.byref(cc), C.byref(p), C.c_void_p(d_out_ptr),
                                            C.c_void_p(stream), C.byref(st)))
@@ -302,6 +306,17 @@ class Scene:
         _check(self.lib.mcpt_intersect_batch(self.handle, C.c_size_t(n), _p(ro), _p(rd), _p(ex), int(light_only), precision,
                                              _p(prim), _p(bgt)))
         return prim, bgt
+
+    def visibility(self, ro, rd, exclude, light_prim, leaf_mode=LEAF_FAST):
+        """mcpt_visibility_batch: the renderer's NEE visibility kernels on explicit rays (1 visible, 0 occluded,
+        -1 the ray misses its light triangle)."""
+        ro, rd = _f64(ro), _f64(rd)
+        n = len(ro)
+        ex = _i32(exclude) if exclude is not None else np.full(n, -1, np.int32)
+        lp = _i32(light_prim)
+        vis = np.zeros(n, np.int32)
+        _check(self.lib.mcpt_visibility_batch(self.handle, C.c_size_t(n), _p(ro), _p(rd), _p(ex), _p(lp), int(leaf_mode), _p(vis)))
+        return vis
 
     def brdf_eval(self, N, wi, wr, kd, ks, ns, precision=FP64):
         N, wi, wr, kd, ks, ns = map(_f64, (N, wi, wr, kd, ks, ns))

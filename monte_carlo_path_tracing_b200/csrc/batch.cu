@@ -300,6 +300,29 @@ __global__ void k_light_tree(DScene s, size_t n, const double* __restrict__ x1, 
     qweight[i] = (q >= 0 && q < s.L) ? (double)light_weight_fast(s, q, x, nn) : 0.0;
 }
 
+// explicit FP64 rays -> the FP32 ray records of the wavefront queues (o | exclude, d | index)
+__global__ void k_pack_rays(size_t n, const double* ro, const double* rd, const int* exclude, float4* org, float4* dir)
+{
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    org[i] = make_float4((float)ro[3 * i], (float)ro[3 * i + 1], (float)ro[3 * i + 2], __int_as_float(exclude ? exclude[i] : -1));
+    dir[i] = make_float4((float)rd[3 * i], (float)rd[3 * i + 1], (float)rd[3 * i + 2], __int_as_float((int)i));
+}
+__global__ void k_unpack_hits(size_t n, const float4* hit, int* prim, double* bgt)
+{
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 h = hit[i];
+    const int p = __float_as_int(h.x);
+    prim[i] = p;
+    bgt[3 * i] = p >= 0 ? h.y : 0; bgt[3 * i + 1] = p >= 0 ? h.z : 0; bgt[3 * i + 2] = p >= 0 ? h.w : 0;
+}
+__global__ void k_pack_ids(size_t n, const int* exclude, const int* light_prim, int2* ids)
+{
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i < n) ids[i] = make_int2(exclude ? exclude[i] : -1, light_prim[i]);
+}
+
 void need(const McptScene* s) { if (!s) throw Error(MCPT_ERR_INVALID, "null scene"); }
 
 }  // namespace
@@ -333,7 +356,16 @@ int mcpt_intersect_batch(McptScene* s, size_t n, const double* ro, const double*
         MCPT_CUDA(cudaSetDevice(s->device));
         DevBuf<double> dro(ro, 3 * n), drd(rd, 3 * n), dbgt(3 * n);
         DevBuf<int> dex(exclude, exclude ? n : 0), dprim(n);
-        if (n && precision == 1 && !light_only) {
+        if (n && precision == 2) {
+            // the wavefront's MCPT_LEAF_EXACT kernel itself (render.cu: k_extend_exact) on the FP32 roundings of the rays
+            if (light_only) throw Error(MCPT_ERR_INVALID, "precision 2 (k_extend_exact) traces the scene BVH only");
+            if (n > (size_t)1 << 30) throw Error(MCPT_ERR_INVALID, "too many rays in one batch");
+            DevBuf<float4> org(n), dir(n), hit(n);
+            k_pack_rays<<<grid_for(n), kBlock>>>(n, dro.p, drd.p, exclude ? dex.p : nullptr, org.p, dir.p);
+            MCPT_CUDA(cudaGetLastError());
+            trace_rays_device(s, (int)n, org.p, dir.p, MCPT_LEAF_EXACT, hit.p);
+            k_unpack_hits<<<grid_for(n), kBlock>>>(n, hit.p, dprim.p, dbgt.p);
+        } else if (n && precision == 1 && !light_only) {
             if (n > (size_t)1 << 30) throw Error(MCPT_ERR_INVALID, "too many rays in one batch");
             DevBuf<int> cursor(1);
             MCPT_CUDA(cudaMemset(cursor.p, 0, sizeof(int)));
@@ -342,6 +374,32 @@ int mcpt_intersect_batch(McptScene* s, size_t n, const double* ro, const double*
         } else if (n) k_intersect<<<grid_for(n), kBlock>>>(s->d, n, dro.p, drd.p, exclude ? dex.p : nullptr, light_only, precision, dprim.p, dbgt.p);
         finish();
         dprim.to_host(prim); dbgt.to_host(bgt);
+    });
+}
+
+int mcpt_visibility_batch(McptScene* s, size_t n, const double* ro, const double* rd, const int32_t* exclude, const int32_t* light_prim,
+                          int leaf_mode, int32_t* visible)
+{
+    return guarded([&] {
+        need(s);
+        if (!ro || !rd || !light_prim || !visible) throw Error(MCPT_ERR_INVALID, "null argument");
+        if (leaf_mode != MCPT_LEAF_FAST && leaf_mode != MCPT_LEAF_EXACT) throw Error(MCPT_ERR_INVALID, "unknown leaf_mode");
+        if (n > (size_t)1 << 30) throw Error(MCPT_ERR_INVALID, "too many rays in one batch");
+        for (size_t i = 0; i < n; i++)
+            if (light_prim[i] < 0 || (uint32_t)light_prim[i] >= s->P) throw Error(MCPT_ERR_INVALID, "light prim index out of range");
+        MCPT_CUDA(cudaSetDevice(s->device));
+        DevBuf<double> dro(ro, 3 * n), drd(rd, 3 * n);
+        DevBuf<int> dex(exclude, exclude ? n : 0), dlp(light_prim, n), dvis(n);
+        DevBuf<float4> org(n), dir(n);
+        DevBuf<int2> ids(n);
+        if (n) {
+            k_pack_rays<<<grid_for(n), kBlock>>>(n, dro.p, drd.p, exclude ? dex.p : nullptr, org.p, dir.p);
+            k_pack_ids<<<grid_for(n), kBlock>>>(n, exclude ? dex.p : nullptr, dlp.p, ids.p);
+            MCPT_CUDA(cudaGetLastError());
+            visibility_device(s, (int)n, org.p, dir.p, ids.p, leaf_mode, dvis.p);
+        }
+        finish();
+        dvis.to_host(visible);
     });
 }
 

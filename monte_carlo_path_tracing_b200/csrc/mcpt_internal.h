@@ -78,6 +78,12 @@ namespace mcpt {
 // render.cu
 void render_device(McptScene* scene, const McptCamera* cam, const McptRenderParams* params, float* d_out_rgb,
                    cudaStream_t stream, McptStats* stats);
+// render_parity.cu: MCPT_PARITY_FP64
+void render_parity_device(McptScene* scene, const McptCamera* cam, const McptRenderParams* params, float* d_out_rgb,
+                          cudaStream_t stream, McptStats* stats);
+// render.cu test hooks: the production trace kernels (k_extend / k_extend_exact, k_shadow / k_shadow_exact) on explicit rays
+void trace_rays_device(McptScene* scene, int n, const float4* d_org, const float4* d_dir, int leaf_mode, float4* d_hit);
+void visibility_device(McptScene* scene, int n, const float4* d_org, const float4* d_dir, const int2* d_ids, int leaf_mode, int* d_visible);
 void tonemap_device(McptScene* scene, const float* rgb, size_t n, double max_radiance, double gamma, uint8_t* out);
 void workspace_free(Workspace& ws);
 }  // namespace mcpt

@@ -10,6 +10,7 @@
 //
 //   mcpt_render scene.obj scene.xml out.ppm|out.bmp [--spp 10] [--strategy mis|mis_single|nee|nee_uniform|brdf] [--max-depth 0]
 //               [--width W --height H] [--seed 1] [--device 0] [--fix-pdf] [--fix-measure] [--jitter] [--light-tree]
+//               [--leaf fast|exact] [--parity]   (MCPT_LEAF_EXACT / MCPT_PARITY_FP64: the reference's FP64 arithmetic)
 //               [--lmax 380 --gamma 0.25] [--pfm out.pfm] [--ref-fov]
 //               [--gpu-bvh] [--every N] [--checkpoint file [--resume]] [--target-rel-error e] [--time-budget seconds]
 //
@@ -38,11 +39,31 @@ static int fail(const char* what)
 
 // checkpoint file: header, then sum[W*H*3] and sumsq_lum[W*H] as doubles
 struct CkptHeader {
-    char magic[8];  // "MCPTCKP1"
-    int32_t width, height, strategy, max_depth, batch;
+    char magic[8];  // "MCPTCKP2"
+    int32_t width, height, strategy, max_depth, batch, leaf_mode;
     uint32_t flags, num_prims, num_lights, batches;
     uint64_t seed, spp_done;
+    uint64_t scene_hash;  // FNV-1a over every array of the McptSceneDesc: an edited OBJ/MTL/XML with the same counts is a different scene
+    McptCamera cam;       // a resumed render must look through the same camera
 };
+
+static uint64_t fnv1a(uint64_t h, const void* data, size_t bytes)
+{
+    const unsigned char* p = (const unsigned char*)data;
+    for (size_t i = 0; i < bytes; i++) { h ^= p[i]; h *= 1099511628211ull; }
+    return h;
+}
+static uint64_t scene_hash(const McptSceneDesc* d)
+{
+    uint64_t h = 14695981039346656037ull;
+    h = fnv1a(h, d->positions, (size_t)d->num_prims * 36); h = fnv1a(h, d->normals, (size_t)d->num_prims * 36);
+    h = fnv1a(h, d->material_id, (size_t)d->num_prims * 4); h = fnv1a(h, d->shape_offset, (size_t)(d->num_shapes + 1) * 4);
+    h = fnv1a(h, d->mat_kd, (size_t)d->num_materials * 12); h = fnv1a(h, d->mat_ks, (size_t)d->num_materials * 12);
+    h = fnv1a(h, d->mat_ns, (size_t)d->num_materials * 4);
+    h = fnv1a(h, d->light_prim, (size_t)d->num_lights * 4); h = fnv1a(h, d->light_class, (size_t)d->num_lights * 4);
+    h = fnv1a(h, d->class_radiance, (size_t)d->num_classes * 24);
+    return h;
+}
 
 static bool ckpt_write(const std::string& path, const CkptHeader& h, const std::vector<double>& sum, const std::vector<double>& sq)
 {
@@ -59,7 +80,7 @@ static bool ckpt_read(const std::string& path, CkptHeader* h, std::vector<double
 {
     FILE* f = std::fopen(path.c_str(), "rb");
     if (!f) return false;
-    bool ok = std::fread(h, sizeof *h, 1, f) == 1 && std::memcmp(h->magic, "MCPTCKP1", 8) == 0 && h->width > 0 && h->height > 0;
+    bool ok = std::fread(h, sizeof *h, 1, f) == 1 && std::memcmp(h->magic, "MCPTCKP2", 8) == 0 && h->width > 0 && h->height > 0;
     if (ok) {
         sum.resize((size_t)h->width * h->height * 3);
         sq.resize((size_t)h->width * h->height);
@@ -78,11 +99,11 @@ int main(int argc, char** argv)
     const char *obj = argv[1], *xml = argv[2], *out = argv[3];
     int spp = 10;                    // main.cpp:567
     int strategy = MCPT_MIS;         // main.cpp:575 calls shade_with_mis as checked in
-    int max_depth = 0, width = 0, height = 0, device = 0;
+    int max_depth = 0, width = 0, height = 0, device = 0, leaf_mode = MCPT_LEAF_FAST;
     unsigned flags = 0;
     unsigned long long seed = 1;
     double lmax = 380.0, gamma = 0.25;  // main.cpp:583
-    bool ref_fov = false, have_cam_args = false;
+    bool ref_fov = false, have_cam_args = false, have_lookat = false, have_up = false;
     double eye[3] = {0, 0, 0}, lookat[3] = {0, 0, 1}, up[3] = {0, 1, 0}, fovy = 0;
     std::string pfm, ckpt;
     int every = 64;
@@ -95,8 +116,19 @@ int main(int argc, char** argv)
         if (a == "--spp") spp = std::atoi(next());
         else if (a == "--strategy") {
             std::string s = next();
-            strategy = s == "mis" ? MCPT_MIS : s == "mis_single" ? MCPT_MIS_SINGLE : s == "brdf" ? MCPT_BRDF_ONLY : s == "nee_uniform" ? MCPT_NEE_UNIFORM : MCPT_NEE_SPHERICAL;
-        } else if (a == "--max-depth") max_depth = std::atoi(next());
+            if (s == "mis") strategy = MCPT_MIS;
+            else if (s == "mis_single") strategy = MCPT_MIS_SINGLE;
+            else if (s == "brdf") strategy = MCPT_BRDF_ONLY;
+            else if (s == "nee_uniform") strategy = MCPT_NEE_UNIFORM;
+            else if (s == "nee") strategy = MCPT_NEE_SPHERICAL;
+            else { std::fprintf(stderr, "unknown --strategy %s (mis, mis_single, nee, nee_uniform, brdf)\n", s.c_str()); return 2; }
+        } else if (a == "--leaf") {
+            std::string s = next();
+            if (s == "exact") leaf_mode = MCPT_LEAF_EXACT;
+            else if (s == "fast") leaf_mode = MCPT_LEAF_FAST;
+            else { std::fprintf(stderr, "unknown --leaf %s (fast, exact)\n", s.c_str()); return 2; }
+        } else if (a == "--parity") flags |= MCPT_PARITY_FP64;
+        else if (a == "--max-depth") max_depth = std::atoi(next());
         else if (a == "--width") width = std::atoi(next());
         else if (a == "--height") height = std::atoi(next());
         else if (a == "--seed") seed = std::strtoull(next(), nullptr, 10);
@@ -116,8 +148,8 @@ int main(int argc, char** argv)
         else if (a == "--time-budget") time_budget = std::atof(next());
         else if (a == "--ref-fov") ref_fov = true;  // F7: the reference's tan(fovy/360) instead of tan(fovy/2 in radians)
         else if (a == "--eye") { vec3(i, eye); have_cam_args = true; }
-        else if (a == "--lookat") vec3(i, lookat);
-        else if (a == "--up") vec3(i, up);
+        else if (a == "--lookat") { vec3(i, lookat); have_lookat = true; }
+        else if (a == "--up") { vec3(i, up); have_up = true; }
         else if (a == "--fovy") fovy = std::atof(next());
         else { std::fprintf(stderr, "unknown option %s\n", a.c_str()); return 2; }
     }
@@ -136,7 +168,12 @@ int main(int argc, char** argv)
         if (!have_cam_args) { std::fprintf(stderr, "mcpt_render: the XML has no <camera>; pass --eye/--lookat/--up/--fovy\n"); return 2; }
         for (int k = 0; k < 3; k++) { cam.eye[k] = eye[k]; cam.w[k] = lookat[k] - eye[k]; cam.up[k] = up[k]; }
         cfov = fovy;
-    } else if (fovy > 0) cfov = fovy;
+    } else {
+        // the XML camera, with whichever of --lookat / --up / --fovy was given laid over it
+        if (have_lookat) for (int k = 0; k < 3; k++) cam.w[k] = lookat[k] - cam.eye[k];
+        if (have_up) for (int k = 0; k < 3; k++) cam.up[k] = up[k];
+        if (fovy > 0) cfov = fovy;
+    }
     if (width <= 0) width = cw > 0 ? cw : 1280;    // main.cpp:539
     if (height <= 0) height = chh > 0 ? chh : 720;
     const double wl = std::sqrt(cam.w[0] * cam.w[0] + cam.w[1] * cam.w[1] + cam.w[2] * cam.w[2]);
@@ -159,17 +196,19 @@ int main(int argc, char** argv)
     std::vector<double> sum(npix * 3, 0.0), sq(npix, 0.0);
     CkptHeader hd;
     std::memset(&hd, 0, sizeof hd);
-    std::memcpy(hd.magic, "MCPTCKP1", 8);
+    std::memcpy(hd.magic, "MCPTCKP2", 8);
     hd.width = width; hd.height = height; hd.strategy = strategy; hd.max_depth = max_depth; hd.batch = every; hd.flags = flags;
     hd.num_prims = desc->num_prims; hd.num_lights = desc->num_lights; hd.seed = seed;
+    hd.leaf_mode = leaf_mode; hd.scene_hash = scene_hash(desc); hd.cam = cam;
     if (resume && !ckpt.empty()) {
         CkptHeader old;
         std::vector<double> s0, q0;
         if (ckpt_read(ckpt, &old, s0, q0)) {
             const bool same = old.width == width && old.height == height && old.strategy == strategy && old.max_depth == max_depth &&
                               old.batch == every && old.flags == flags && old.num_prims == hd.num_prims &&
-                              old.num_lights == hd.num_lights && old.seed == seed;
-            if (!same) { std::fprintf(stderr, "mcpt_render: %s was written for a different scene or different parameters\n", ckpt.c_str()); return 2; }
+                              old.num_lights == hd.num_lights && old.seed == seed && old.leaf_mode == leaf_mode &&
+                              old.scene_hash == hd.scene_hash && std::memcmp(&old.cam, &cam, sizeof cam) == 0;
+            if (!same) { std::fprintf(stderr, "mcpt_render: %s was written for a different scene, camera or parameters\n", ckpt.c_str()); return 2; }
             hd.spp_done = old.spp_done; hd.batches = old.batches;
             sum.swap(s0); sq.swap(q0);
             std::printf("resumed %s at %llu spp\n", ckpt.c_str(), (unsigned long long)hd.spp_done);
@@ -179,7 +218,7 @@ int main(int argc, char** argv)
     McptRenderParams prm;
     std::memset(&prm, 0, sizeof prm);
     prm.width = width; prm.height = height; prm.max_depth = max_depth;
-    prm.strategy = strategy; prm.flags = flags; prm.seed = seed;
+    prm.strategy = strategy; prm.flags = flags; prm.seed = seed; prm.leaf_mode = leaf_mode;
     std::vector<float> film(npix * 3);
     McptStats tot;
     std::memset(&tot, 0, sizeof tot);

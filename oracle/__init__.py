@@ -20,7 +20,7 @@ ORACLE_SO = os.path.join(HERE, "liboracle.so")
 REF_SO = os.path.join(HERE, "_ref", "libmcpt_ref.so")
 
 NEE_SPHERICAL, BRDF_ONLY, MIS, NEE_UNIFORM = 0, 1, 2, 3
-FIX_STALE_MIS, FIX_NEE_MEASURE, FIX_MIXTURE_PDF, BRUTE_FORCE = 1, 2, 4, 8
+FIX_STALE_MIS, FIX_NEE_MEASURE, FIX_MIXTURE_PDF, BRUTE_FORCE, RNG_KEYED = 1, 2, 4, 8, 16
 
 _d3 = C.c_double * 3
 
@@ -196,6 +196,11 @@ class OracleLib(_Probes):
         out = np.zeros(self.L)
         self.lib.oracle_light_areas(self.scene, _p(out))
         return out
+
+    def keyed_uniforms(self, seed, pixel, sample, node, call):
+        out = (C.c_double * 4)()
+        self.lib.oracle_keyed_uniforms(C.c_uint64(seed), C.c_uint32(pixel), C.c_uint32(sample), C.c_uint64(node), C.c_uint32(call), out)
+        return np.array(out[:])
 
     def render(self, cam, strategy, spp, max_depth=0, flags=0, seed=1, rows=None, cols=None, spp_offset=0,
                spp_total=None):

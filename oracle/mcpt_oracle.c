@@ -93,7 +93,20 @@ struct OracleScene {
     oracle_stream stream;
     int max_depth, flags;
     uint64_t n_vertices, n_rays, n_light_rays;
+    /* ORACLE_RNG_KEYED: the (seed, pixel, sample) of the path being traced and the table row handed to the stream */
+    uint64_t k_seed;
+    uint32_t k_pixel, k_sample;
+    double k_buf[4];
 };
+
+/* ORACLE_RNG_KEYED: point the stream at positions [first, first + n) of table row (node, call) */
+static void keyed_list(OracleScene* s, uint64_t node, uint32_t call, int first, int n)
+{
+    if (!(s->flags & ORACLE_RNG_KEYED)) return;
+    oracle_keyed_draw4(s->k_seed, s->k_pixel, s->k_sample, node, call, s->k_buf);
+    oracle_stream_list(&s->stream, s->k_buf + first, (size_t)n);
+    s->stream.keyed = 1;
+}
 
 OracleScene* oracle_scene_create(int P, int S, int M, int L, int C, const float* positions, const float* normals,
                                  const int* material_id, const unsigned* shape_offset, const float* kd,
@@ -404,7 +417,7 @@ void oracle_closest(OracleScene* s, int n, const double* ro, const double* rd, c
  * with the last forced to 1.0, ONE canonical draw u, result = first index with cp >= u. */
 static int discrete_pick(oracle_stream* st, const double* w, int n, double* prob_out)
 {
-    if (n < 2) { if (prob_out) *prob_out = 1.0; return 0; }
+    if (n < 2) { if (st->keyed) st->list_i++; if (prob_out) *prob_out = 1.0; return 0; }
     double sum = 0.0;
     for (int i = 0; i < n; i++) sum += w[i];
     double u = oracle_stream_next(st);
@@ -660,6 +673,12 @@ void oracle_light_sample_spherical(OracleScene* s, int n, int staged, const doub
     }
 }
 
+/* the keyed table itself, for the tests (known-answer vectors of Philox4x32-10; equality with csrc/rng.cuh) */
+void oracle_keyed_uniforms(uint64_t seed, uint32_t pixel, uint32_t sample, uint64_t node, uint32_t call, double out[4])
+{
+    oracle_keyed_draw4(seed, pixel, sample, node, call, out);
+}
+
 /* ---- integrators (main.cpp) ------------------------------------------------------------------- */
 typedef struct { v3 p, N; int prim, mat, is_light; } vertex_t;
 
@@ -681,10 +700,11 @@ static int shade_prologue(OracleScene* s, hit_t point, v3 wo, vertex_t* vx, v3* 
 
 /* Russian roulette draw with the depth rule of rng_shim.h (oracle_rr_engine): at depth >= max_depth
  * the draw is forced to fail and consumes nothing. */
-static int rr_survives(OracleScene* s, int depth)
+static int rr_survives(OracleScene* s, int depth, uint64_t node)
 {
     s->n_vertices++;
     if (s->max_depth > 0 && depth >= s->max_depth) return 0;
+    keyed_list(s, node, 0, 0, 1);
     double ksi = oracle_stream_next(&s->stream);
     return !(ksi > P_RR);
 }
@@ -692,15 +712,15 @@ static int rr_survives(OracleScene* s, int depth)
 static inline v3 rgb_mul(v3 a, v3 b) { return V(a.x[0] * b.x[0], a.x[1] * b.x[1], a.x[2] * b.x[2]); } /* RadianceRGB.cpp:44-47 */
 
 /* shade(), main.cpp:269-344; uniform != 0 swaps in the commented-out sampler of main.cpp:297 */
-static v3 shade_nee(OracleScene* s, hit_t point, v3 wo, int depth, int uniform)
+static v3 shade_nee(OracleScene* s, hit_t point, v3 wo, int depth, int uniform, uint64_t node)
 {
     vertex_t vx; v3 out;
     if (shade_prologue(s, point, wo, &vx, &out)) return out;
     v3 kd = s->kd[vx.mat], ks = s->ks[vx.mat]; double ns = s->ns[vx.mat];
     v3 L_dir = V(0, 0, 0);
     light_pt lp;
-    if (uniform) lp = light_sample_uniform(s, &s->stream);
-    else { light_prepare(s, vx.p, vx.N); lp = light_sample_prepared(s, &s->stream, vx.p, vx.N); }
+    if (uniform) { keyed_list(s, node, 1, 0, 4); lp = light_sample_uniform(s, &s->stream); }
+    else { light_prepare(s, vx.p, vx.N); keyed_list(s, node, 1, 0, 3); lp = light_sample_prepared(s, &s->stream, vx.p, vx.N); }
     v3 x1 = lp.coord;
     v3 n1 = geom_normal(s, lp.prim);
     v3 wl = vnormalized(vsub(x1, vx.p));
@@ -716,51 +736,54 @@ static v3 shade_nee(OracleScene* s, hit_t point, v3 wo, int depth, int uniform)
     }
     v3 L_indir = V(0, 0, 0);
     depth++; /* the RR engine of this frame is now alive (rng_shim.h) */
-    if (!rr_survives(s, depth)) return vadd(L_dir, L_indir);
+    if (!rr_survives(s, depth, node)) return vadd(L_dir, L_indir);
     double pdf;
+    keyed_list(s, node, 0, 1, 3);
     v3 wi = brdf_sample(&s->stream, vx.N, wo, kd, ks, ns, &pdf);
     if (vdot(wi, vx.N) < 0) return vadd(L_dir, L_indir);
     if (s->flags & ORACLE_FIX_MIXTURE_PDF) pdf = brdf_pdf(vx.N, wi, wo, kd, ks, ns);
     hit_t rsq = closest(s, vx.p, wi, vx.prim);
     if (rsq.hit && s->light_of_prim[rsq.prim] < 0) { /* :338 indirect only off non-lights */
         v3 brdf = brdf_phong(vx.N, wi, wo, kd, ks, ns);
-        L_indir = vmul(rgb_mul(shade_nee(s, rsq, vmul(wi, -1), depth, uniform), brdf), vdot(wi, vx.N) / pdf / P_RR);
+        L_indir = vmul(rgb_mul(shade_nee(s, rsq, vmul(wi, -1), depth, uniform, (uint64_t)depth + 1), brdf), vdot(wi, vx.N) / pdf / P_RR);
     }
     return vadd(L_dir, L_indir);
 }
 
 /* shade_with_brdf(), main.cpp:348-399 */
-static v3 shade_brdf(OracleScene* s, hit_t point, v3 wo, int depth)
+static v3 shade_brdf(OracleScene* s, hit_t point, v3 wo, int depth, uint64_t node)
 {
     vertex_t vx; v3 out;
     if (shade_prologue(s, point, wo, &vx, &out)) return out;
     v3 kd = s->kd[vx.mat], ks = s->ks[vx.mat]; double ns = s->ns[vx.mat];
     v3 L = V(0, 0, 0);
     depth++;
-    if (!rr_survives(s, depth)) return L;
+    if (!rr_survives(s, depth, node)) return L;
     double pdf;
+    keyed_list(s, node, 0, 1, 3);
     v3 wi = brdf_sample(&s->stream, vx.N, wo, kd, ks, ns, &pdf);
     if (vdot(wi, vx.N) < 0) return L;
     if (s->flags & ORACLE_FIX_MIXTURE_PDF) pdf = brdf_pdf(vx.N, wi, wo, kd, ks, ns);
     hit_t rsq = closest(s, vx.p, wi, vx.prim);
     if (rsq.hit) {
         v3 brdf = brdf_phong(vx.N, wi, wo, kd, ks, ns);
-        L = vmul(rgb_mul(shade_brdf(s, rsq, vmul(wi, -1), depth), brdf), vdot(wi, vx.N) / pdf / P_RR);
+        L = vmul(rgb_mul(shade_brdf(s, rsq, vmul(wi, -1), depth, (uint64_t)depth + 1), brdf), vdot(wi, vx.N) / pdf / P_RR);
     }
     return L;
 }
 
 /* shade_with_mis(), main.cpp:402-494.  Without ORACLE_FIX_STALE_MIS the light pdf at :487 reads the
  * scratch left by the deepest prepare of recursion #1 (F10), exactly like the reference. */
-static v3 shade_mis(OracleScene* s, hit_t point, v3 wo, int depth)
+static v3 shade_mis(OracleScene* s, hit_t point, v3 wo, int depth, uint64_t node)
 {
     vertex_t vx; v3 out;
     if (shade_prologue(s, point, wo, &vx, &out)) return out;
     v3 kd = s->kd[vx.mat], ks = s->ks[vx.mat]; double ns = s->ns[vx.mat];
     depth++;
-    if (!rr_survives(s, depth)) return V(0, 0, 0);
+    if (!rr_survives(s, depth, node)) return V(0, 0, 0);
     v3 L_light = V(0, 0, 0);
     light_prepare(s, vx.p, vx.N);
+    keyed_list(s, node, 1, 0, 3);
     light_pt lp = light_sample_prepared(s, &s->stream, vx.p, vx.N);
     v3 x1 = lp.coord;
     v3 wl = vnormalized(vsub(x1, vx.p));
@@ -776,7 +799,7 @@ static v3 shade_mis(OracleScene* s, hit_t point, v3 wo, int depth)
         if (rstmp.hit) {
             v3 brdf = brdf_phong(vx.N, wl, wo, kd, ks, ns);
             double phongPdf = brdf_pdf(vx.N, wl, wo, kd, ks, ns);
-            L_light = vmul(rgb_mul(shade_mis(s, rstmp, vmul(wl, -1), depth), brdf), vdot(wl, vx.N) / (lp.prob + phongPdf) / P_RR);
+            L_light = vmul(rgb_mul(shade_mis(s, rstmp, vmul(wl, -1), depth, node * 2), brdf), vdot(wl, vx.N) / (lp.prob + phongPdf) / P_RR);
         }
     }
     if (own_in) {
@@ -786,6 +809,7 @@ static v3 shade_mis(OracleScene* s, hit_t point, v3 wo, int depth)
     }
     v3 L_brdf = V(0, 0, 0);
     double pdf;
+    keyed_list(s, node, 0, 1, 3);
     v3 wi = brdf_sample(&s->stream, vx.N, wo, kd, ks, ns, &pdf);
     if (vdot(wi, vx.N) < 0) return vadd(L_light, L_brdf);
     if (s->flags & ORACLE_FIX_MIXTURE_PDF) pdf = brdf_pdf(vx.N, wi, wo, kd, ks, ns);
@@ -796,7 +820,7 @@ static v3 shade_mis(OracleScene* s, hit_t point, v3 wo, int depth)
         hit_t rs = closest_light(s, vx.p, wi, vx.prim);
         if (rs.hit) light_pdf = light_pdf_prepared(s, rs.prim);
         else light_pdf = 0;
-        L_brdf = vmul(rgb_mul(shade_mis(s, rsq, vmul(wi, -1), depth), brdf), vdot(wi, vx.N) / (pdf + light_pdf) / P_RR);
+        L_brdf = vmul(rgb_mul(shade_mis(s, rsq, vmul(wi, -1), depth, node * 2 + 1), brdf), vdot(wi, vx.N) / (pdf + light_pdf) / P_RR);
     }
     return vadd(L_light, L_brdf);
 }
@@ -824,13 +848,14 @@ void oracle_render(OracleScene* s, const double eye[3], const double w_[3], cons
             v3 sum = V(0, 0, 0);
             for (int k = 0; k < spp; k++) {
                 oracle_stream_seed(&s->stream, seed, (uint64_t)i * (uint64_t)W + (uint64_t)j, (uint64_t)(spp_offset + k));
+                s->k_seed = seed; s->k_pixel = (uint32_t)(i * W + j); s->k_sample = (uint32_t)(spp_offset + k);
                 hit_t rs = closest(s, eyev, dir, -1);                                           /* :572 */
                 if (rs.hit) {
                     primary_hits++;
                     v3 wo = vmul(dir, -1);
-                    v3 I = strategy == ORACLE_BRDF_ONLY ? shade_brdf(s, rs, wo, 0)
-                         : strategy == ORACLE_MIS       ? shade_mis(s, rs, wo, 0)
-                         : shade_nee(s, rs, wo, 0, strategy == ORACLE_NEE_UNIFORM);
+                    v3 I = strategy == ORACLE_BRDF_ONLY ? shade_brdf(s, rs, wo, 0, 1)
+                         : strategy == ORACLE_MIS       ? shade_mis(s, rs, wo, 0, 1)
+                         : shade_nee(s, rs, wo, 0, strategy == ORACLE_NEE_UNIFORM, 1);
                     sum = vadd(sum, vmul(I, inv));                                              /* :575-576 */
                 }
             }

@@ -33,7 +33,10 @@ enum {
     ORACLE_FIX_STALE_MIS = 1,      /* F10: save/restore the Mylight scratch around recursion #1 (main.cpp:464) */
     ORACLE_FIX_NEE_MEASURE = 2,    /* F9: NEE_SPHERICAL uses the solid-angle estimator Le f cos / pdf */
     ORACLE_FIX_MIXTURE_PDF = 4,    /* F8: BRDF-sampled directions use the mixture pdf (BRDF.cpp:107-132) */
-    ORACLE_BRUTE_FORCE = 8         /* closest hit by exhaustive search (Myobj.cpp:194-213) instead of the grid */
+    ORACLE_BRUTE_FORCE = 8,        /* closest hit by exhaustive search (Myobj.cpp:194-213) instead of the grid */
+    ORACLE_RNG_KEYED = 16          /* uniforms from the keyed Philox table of libmcpt's renderer (stream.h) instead of
+                                      the sequential stream: the oracle then walks the same paths as an
+                                      MCPT_PARITY_FP64 render with the same seed */
 };
 
 /* Flat scene, same layout as McptSceneDesc (include/mcpt.h).  Arrays are copied. */
@@ -67,6 +70,9 @@ void oracle_light_sample_spherical(OracleScene*, int n, int staged, const double
                                    const int* query, int* prim, double* point, double* Le, double* pdf, double* wsum,
                                    int* nsurv, double* query_pdf);
 void oracle_tonemap(int n, const double* rgb, double max_radiance, double gamma, int* out);
+
+/* row (node, call) of the keyed uniform table of ORACLE_RNG_KEYED (stream.h) */
+void oracle_keyed_uniforms(uint64_t seed, uint32_t pixel, uint32_t sample, uint64_t node, uint32_t call, double out[4]);
 
 /* main.cpp:546-588 with literals as arguments; same signature as ref_render + flags.
  * counters[0] non-emissive vertices shaded, [1] primary hits, [2] closest-hit rays, [3] light-only rays */

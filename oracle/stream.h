@@ -24,6 +24,8 @@ typedef struct oracle_stream {
     size_t list_n;
     size_t list_i;
     uint64_t draws;
+    int keyed;   /* list entries are POSITIONS of a keyed table (oracle_keyed_draw4): a consumer that skips a draw
+                    (std::discrete_distribution below two weights) still steps over its position */
 } oracle_stream;
 
 static inline uint64_t oracle_mix64(uint64_t z)
@@ -40,6 +42,30 @@ static inline void oracle_stream_seed(oracle_stream* s, uint64_t seed, uint64_t 
     s->ctr = 0;
     s->list = 0;
     s->list_n = s->list_i = 0;
+    s->keyed = 0;
+}
+
+/* ---- keyed mode: the product renderer's own uniforms ------------------------------------------------
+ * Philox4x32-10 (Salmon et al., SC'11; public algorithm, constants from the paper) with counter
+ * (pixel, global sample, path-tree node lo, node hi * 4 + call) and key = seed: 4 uniforms of 24 bits each,
+ * u = (x >> 8) * 2^-24 -- the table libmcpt's renderer draws from (csrc/rng.cuh restated in C).  With
+ * ORACLE_RNG_KEYED the restatement feeds every sampling call from this table instead of the sequential
+ * stream, call 0 = (roulette, u_lobe, xi1, xi2), call 1 = (u_tri, xi1, xi2) / (u_class, u_tri, xi1, xi2),
+ * so that a PARITY render of libmcpt and the oracle walk the SAME paths and their films can be compared
+ * pixel by pixel. */
+static inline void oracle_keyed_draw4(uint64_t seed, uint32_t pixel, uint32_t sample, uint64_t node, uint32_t call, double out[4])
+{
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+    uint32_t c0 = pixel, c1 = sample, c2 = (uint32_t)node, c3 = (uint32_t)(node >> 32) * 4u + call;
+    uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+    for (int r = 0; r < 10; r++) {
+        uint64_t p0 = (uint64_t)M0 * c0, p1 = (uint64_t)M1 * c2;
+        uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0, n1 = (uint32_t)p1, n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1, n3 = (uint32_t)p0;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+        k0 += W0; k1 += W1;
+    }
+    out[0] = (double)(c0 >> 8) * (1.0 / 16777216.0); out[1] = (double)(c1 >> 8) * (1.0 / 16777216.0);
+    out[2] = (double)(c2 >> 8) * (1.0 / 16777216.0); out[3] = (double)(c3 >> 8) * (1.0 / 16777216.0);
 }
 
 static inline void oracle_stream_list(oracle_stream* s, const double* list, size_t n)

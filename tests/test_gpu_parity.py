@@ -78,6 +78,89 @@ def test_closest_hit_fp32_mismatch_rate(scene_name, golden, gpu_scene_of, arrays
     assert np.max(util.rel_err(bgt[hit, 2], g["closest_brute_bgt"][hit, 2])) < 1e-3
 
 
+def test_light_only_fp32_trace(scene_name, gpu_scene_of, arrays_of, oracle_of):
+    """a5, production path: the FP32 trace_fast over the light BVH that k_shade calls for the MIS light pdf
+    (main.cpp:484, closet_ray_intersect_light_triangle) against the oracle's exhaustive search over emissive prims."""
+    a, _ = arrays_of(scene_name)
+    s = gpu_scene_of(scene_name)
+    rng = np.random.default_rng(311)
+    ro, rd, ex = util.surface_rays(a, 20000, 310)
+    # aim two thirds of the rays at random points of random light triangles so that most of them hit one
+    lp = a.light_prim[rng.integers(0, len(a.light_prim), len(ro))]
+    b = rng.random(len(ro)); g = rng.random(len(ro)) * (1 - b)
+    v = a.positions[lp].astype(np.float64)
+    tgt = v[:, 0] * (1 - b - g)[:, None] + v[:, 1] * b[:, None] + v[:, 2] * g[:, None]
+    aim = rng.random(len(ro)) < 0.67
+    rd[aim] = util.unit(tgt[aim] - ro[aim])
+    p32, b32 = s.closest(ro, rd, ex, True, api.FP32)
+    p64, b64 = oracle_of(scene_name).closest(ro, rd, ex, 3)
+    assert (p64 >= 0).mean() > 0.3
+    mism = np.mean(p32 != p64)
+    assert mism < 5e-3, mism  # FP32 Moeller-Trumbore vs FP64 Cramer: edge hits only
+    hit = (p32 == p64) & (p64 >= 0)
+    assert np.max(util.rel_err(b32[hit, 2], b64[hit, 2])) < 1e-3
+    assert np.max(np.abs(b32[hit, :2] - b64[hit, :2])) < 1e-3
+    # FP64 instantiation: bit exact
+    pe, be = s.closest(ro, rd, ex, True, api.FP64)
+    assert np.array_equal(pe, p64) and np.array_equal(be, b64)
+
+
+def test_visibility_kernels_match_closest_hit_and_compare(scene_name, gpu_scene_of, arrays_of, oracle_of):
+    """a6: the NEE visibility test of main.cpp:309-311 -- "the closest hit along wl IS the sampled light triangle" -- on
+    fixed rays, through the production kernels.  k_shadow_exact (MCPT_LEAF_EXACT) must reproduce the oracle's
+    closest-hit-and-compare on every ray; k_shadow (any-hit search for something that beats the light point, FP32) may
+    differ only where an FP32 edge test does."""
+    a, _ = arrays_of(scene_name)
+    s = gpu_scene_of(scene_name)
+    o = oracle_of(scene_name)
+    rng = np.random.default_rng(321)
+    n = 30000
+    x, N, _, prim = util.shading_points(a, n, 320)
+    lp = a.light_prim[rng.integers(0, len(a.light_prim), n)].astype(np.int32)
+    b = rng.random(n); g = rng.random(n) * (1 - b)
+    v = a.positions[lp].astype(np.float64)
+    tgt = v[:, 0] * (1 - b - g)[:, None] + v[:, 1] * b[:, None] + v[:, 2] * g[:, None]
+    ro = x.astype(np.float32).astype(np.float64)          # the queues hold FP32 rays: test on their exact values
+    rd = util.unit(tgt - ro).astype(np.float32).astype(np.float64)
+    p_or, _ = o.closest(ro, rd, prim, 2)
+    hit_l, _ = o.intersect_tri(ro, rd, lp)                  # does the ray meet its light triangle at all
+    expect = np.where(hit_l == 1, (p_or == lp).astype(np.int32), -1)
+    vis_x = s.visibility(ro, rd, prim, lp, api.LEAF_EXACT)
+    assert np.array_equal(vis_x, expect)
+    assert (expect == 1).mean() > 0.05 and (expect == 0).mean() > 0.05
+    vis_f = s.visibility(ro, rd, prim, lp, api.LEAF_FAST)
+    assert np.mean(vis_f != expect) < 5e-3, np.mean(vis_f != expect)
+    # duplicate / coplanar light triangles are where any-hit and compare-ids could part (SURVEY.md a6): a second copy of a
+    # light triangle with a HIGHER prim id must not occlude the first, and the copy itself is not visible through the original
+    if scene_name == "cornell-box":
+        import copy as _copy
+        a2 = _copy.copy(a)
+        l0 = int(a.light_prim[0])
+        a2.positions = np.concatenate([a.positions, a.positions[l0:l0 + 1]])
+        a2.normals = np.concatenate([a.normals, a.normals[l0:l0 + 1]])
+        a2.material_id = np.concatenate([a.material_id, a.material_id[l0:l0 + 1]])
+        a2.shape_offset = a.shape_offset.copy(); a2.shape_offset[-1] += 1
+        dup = len(a.material_id)
+        order = np.argsort(np.concatenate([a.light_class, a.light_class[:1]]), kind="stable")
+        a2.light_prim = np.concatenate([a.light_prim, [dup]]).astype(np.int32)[order]
+        a2.light_class = np.concatenate([a.light_class, a.light_class[:1]]).astype(np.int32)[order]
+        s2 = api.Scene(a2, 0)
+        try:
+            import oracle as _oracle
+            o2 = _oracle.OracleLib(a2)
+            sel = np.nonzero((lp == l0) & (expect == 1))[0][:2000]
+            assert len(sel) > 50
+            for target in (l0, dup):
+                lt = np.full(len(sel), target, np.int32)
+                p2, _ = o2.closest(ro[sel], rd[sel], prim[sel], 2)
+                exp2 = (p2 == lt).astype(np.int32)
+                assert np.array_equal(s2.visibility(ro[sel], rd[sel], prim[sel], lt, api.LEAF_EXACT), exp2)
+                assert np.mean(s2.visibility(ro[sel], rd[sel], prim[sel], lt, api.LEAF_FAST) != exp2) < 5e-3
+            assert exp2.sum() == 0  # the copy (higher id, same t) never wins the strict < of the exhaustive search
+        finally:
+            s2.close()
+
+
 def test_phong_fp64(scene_name, golden, gpu_scene_of):
     g = golden(scene_name)
     s = gpu_scene_of(scene_name)

@@ -5,6 +5,7 @@ import ctypes as C
 import os
 import re
 import socket
+import subprocess
 
 import numpy as np
 import pytest
@@ -28,12 +29,28 @@ def test_abi_exports_every_declared_symbol():
     assert lib.mcpt_version() == 100
 
 
-def test_abi_struct_layouts_match_header():
-    """ctypes mirrors of the PODs have the sizes the C compiler gives them (LP64)."""
+def test_abi_struct_layouts_match_header(tmp_path):
+    """ctypes mirrors of the PODs have the sizes AND field offsets the C compiler gives include/mcpt.h."""
     assert C.sizeof(api.CameraC) == 10 * 8
-    assert C.sizeof(api.RenderParams) == 4 * 8 + 8 + 4 + 4
+    assert C.sizeof(api.RenderParams) == 4 * 8 + 8 + 4 + 4 + 4 + 4
     assert C.sizeof(api.Stats) == 6 * 8 + 4 * 4 + 5 * 4 + 4 + 8  # 5 floats, 4 bytes of padding, elements
     assert C.sizeof(api.SceneDesc) == 5 * 4 + 4 + 10 * 8
+    structs = {"McptCamera": api.CameraC, "McptRenderParams": api.RenderParams, "McptStats": api.Stats, "McptSceneDesc": api.SceneDesc}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "mcpt.h"', 'int main(void){']
+    for cname, ct in structs.items():
+        lines.append('printf("%s %%zu\\n", sizeof(%s));' % (cname, cname))
+        for f, _ in ct._fields_:
+            lines.append('printf("%s.%s %%zu\\n", offsetof(%s, %s));' % (cname, f, cname, f))
+    lines.append("return 0;}")
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), "-o", str(exe), str(src)])
+    got = dict(l.split() for l in subprocess.check_output([str(exe)], text=True).splitlines())
+    for cname, ct in structs.items():
+        assert int(got[cname]) == C.sizeof(ct), cname
+        for f, _ in ct._fields_:
+            assert int(got["%s.%s" % (cname, f)]) == getattr(ct, f).offset, (cname, f)
 
 
 @pytest.mark.skipif(os.path.exists("/dev/nvidiactl"), reason="a GPU is present")

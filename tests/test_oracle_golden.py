@@ -122,3 +122,18 @@ def test_known_answers():
     a = util.scenes.triangle_soup(8, 2, seed=1)
     prim, pt, Le, pdf = o.light_sample_uniform(np.array([[0.0, 0.0, 0.0, 0.0]]))
     assert np.allclose(pt[0], a.positions[prim[0], 0])
+
+
+def test_keyed_uniform_table_is_philox4x32_10():
+    """ORACLE_RNG_KEYED (oracle/stream.h) restates the renderer's counter-based generator: Philox4x32-10, checked
+    against the known-answer vectors published with Random123 (kat_vectors: counter, key -> output)."""
+    import oracle
+    from monte_carlo_path_tracing_b200 import scenes
+    o = oracle.OracleLib(scenes.triangle_soup(8, 1, seed=1))
+    kat = [((0, 0, 0, 0), (0, 0), (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+           ((0xffffffff,) * 4, (0xffffffff,) * 2, (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+           ((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0), (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1))]
+    for ctr, key, out in kat:
+        # counter = (pixel, sample, node lo, node hi * 4 + call): node hi = ctr[3] // 4, call = ctr[3] % 4
+        u = o.keyed_uniforms(key[0] | (key[1] << 32), ctr[0], ctr[1], ctr[2] | ((ctr[3] // 4) << 32), ctr[3] % 4)
+        assert np.array_equal(u, [(x >> 8) / 16777216.0 for x in out]), (ctr, u)

@@ -125,3 +125,50 @@ def rel_err(a, b, floor=1e-300):
 def rmse(a, b):
     a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
     return float(np.sqrt(np.mean((a - b) ** 2)))
+
+
+# ---- oracle renders over all host cores -----------------------------------------------------------------
+# The oracle is single-threaded like the reference; with the keyed (or hashed) uniform streams a film does not depend on how
+# its rows are split, so the full-size parity tests render disjoint row bands in worker processes.  `spawn`, not
+# `fork`: the parent holds a CUDA context.
+def _oracle_band(args):
+    arrays, cam, strategy, spp, kw, rows = args
+    import oracle
+    o = oracle.OracleLib(arrays)
+    o.build_grid(cam.eye, 100000)
+    img, cnt = o.render(cam, strategy, spp, rows=rows, **kw)
+    return rows, img, cnt
+
+
+def oracle_render_mp(arrays, cam, strategy, spp, procs=None, **kw):
+    """oracle.OracleLib(arrays).render(cam, strategy, spp, **kw) over `procs` processes (row bands)."""
+    import concurrent.futures as cf
+    import multiprocessing as mp
+    procs = procs or min(os.cpu_count() or 1, 32)
+    H = cam.height
+    nb = max(1, min(H, procs * 4))
+    edges = np.linspace(0, H, nb + 1).astype(int)
+    jobs = [(arrays, cam, strategy, spp, kw, (int(a), int(b))) for a, b in zip(edges[:-1], edges[1:]) if b > a]
+    out = np.zeros((H, cam.width, 3))
+    total = {}
+    with cf.ProcessPoolExecutor(max_workers=procs, mp_context=mp.get_context("spawn")) as ex:
+        for rows, img, cnt in ex.map(_oracle_band, jobs):
+            out[rows[0]:rows[1]] = img
+            for k, v in cnt.items():
+                total[k] = total.get(k, 0) + int(v)
+    return out, total
+
+
+def camera_rays(cam):
+    """All primary rays of `cam` (main.cpp:546-553,563-564) in FP64: origins (H*W, 3), unit directions (H*W, 3)."""
+    w = np.array(cam.w, np.float64); up = np.array(cam.up, np.float64)
+    N = w / np.linalg.norm(w)
+    V = np.cross(N, up); V /= np.linalg.norm(V)
+    U = np.cross(V, N); U /= np.linalg.norm(U)
+    i = np.arange(cam.height, dtype=np.float64)[:, None]; j = np.arange(cam.width, dtype=np.float64)[None, :]
+    dx = -cam.pixellen * (i - (cam.height - 1) * 0.5) + 0 * j
+    dy = cam.pixellen * (j - (cam.width - 1) * 0.5) + 0 * i
+    d = U[None, None, :] * dx[..., None] + V[None, None, :] * dy[..., None] + N[None, None, :] * np.linalg.norm(w)
+    d = (d / np.linalg.norm(d, axis=-1, keepdims=True)).reshape(-1, 3)
+    o = np.broadcast_to(np.array(cam.eye, np.float64), d.shape).copy()
+    return o, d
