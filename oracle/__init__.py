@@ -158,6 +158,19 @@ class RefLib(_Probes):
         return out, dict(vertices=cnt[0], primary_hits=cnt[1])
 
 
+    def render_variant(self, cam, strategy, spp, max_depth=0, flags=0, seed=1, rows=None, cols=None, spp_offset=0, spp_total=None):
+        """The estimator re-hosted on the reference's own objects with the ORACLE_FIX_* switches (ref_driver.cpp:
+        ref_render_variant); strategy 3 = uniform-area NEE.  flags == 0, strategy 0..2 equals ``render`` bit for bit."""
+        W, H = cam.width, cam.height
+        i0, i1 = rows or (0, H)
+        j0, j1 = cols or (0, W)
+        out = np.zeros((i1 - i0, j1 - j0, 3)); cnt = (C.c_uint64 * 2)()
+        e, w, u, pl = camera_args(cam)
+        self.lib.ref_render_variant(e, w, u, pl, W, H, i0, i1, j0, j1, spp, spp_offset, spp_total or spp, strategy, max_depth,
+                                    flags, C.c_uint64(seed), _p(out), cnt)
+        return out, dict(vertices=cnt[0], primary_hits=cnt[1])
+
+
 class OracleLib(_Probes):
     """The plain-C restatement on a flat scene (monte_carlo_path_tracing_b200.scenes.SceneArrays)."""
     _pre = "oracle_"

@@ -16,6 +16,7 @@
 #include <array>
 #include <cstdint>
 #include <iostream>
+#include <map>
 #include <sstream>
 #include <vector>
 
@@ -317,3 +318,133 @@ void ref_render(const double eye[3], const double w_[3], const double up[3], dou
 }
 
 }  // extern "C"
+
+// ---- estimator VARIANTS on the reference's own objects -------------------------------------------
+// The product never reproduces F10 (stale Mylight scratch) and offers switches for F8 / F9 and the uniform-area sampler
+// of the commented-out line main.cpp:297; the C restatement (oracle/mcpt_oracle.c) has the same switches.  To pin THOSE
+// variants to the compiled reference too, the estimator is re-hosted here once, parametrised, on top of the reference's
+// unmodified object code: every geometric, BRDF and light-sampling value comes from Myobj / Mylight / BRDF exactly as in
+// shade* (main.cpp:269-494); only the control flow around them is ours.  With flags == 0 and strategy 0..2 it must
+// reproduce the reference's own shade / shade_with_brdf / shade_with_mis bit for bit (tests/golden/make_golden.py
+// asserts that before it writes anything), which validates the re-hosting itself.
+namespace {
+enum { V_FIX_STALE_MIS = 1, V_FIX_NEE_MEASURE = 2, V_FIX_MIXTURE_PDF = 4 };  // == ORACLE_FIX_* (mcpt_oracle.h)
+int g_vstrategy = 0, g_vflags = 0;
+
+inline vec blend3(const std::array<vec, 3>& v, double a, double b, double c) { return v[0] * a + v[1] * b + v[2] * c; }  // main.cpp:26-29
+
+// one Russian-roulette decision with the depth rule of rng_shim.h (oracle_rr_engine)
+bool roulette_survives(int depth)
+{
+    ++g_oracle_vertices;
+    if (g_oracle_max_depth > 0 && depth >= g_oracle_max_depth) return false;
+    const double ksi = oracle_stream_next(&g_oracle_stream);
+    return !(ksi > 0.6);
+}
+
+RadianceRGB variant_shade(intersec_result point, vec wo, int depth)
+{
+    const bool nee = g_vstrategy == 0 || g_vstrategy == 3, mis = g_vstrategy == 2;
+    vec p = blend3(veach.get_vertexes_of_facet(point.s, point.f), 1.0 - point.beta - point.gamma, point.beta, point.gamma);
+    vec N = blend3(veach.get_normals_of_facet(point.s, point.f), 1.0 - point.beta - point.gamma, point.beta, point.gamma).normalized();
+    if (N.dot_product(wo) < 0) return RadianceRGB(0, 0, 0);
+    const triangle self(point.s, point.f);
+    auto lit = lights.islight.find(self);
+    if (lit != lights.islight.end()) return lit->second;
+    const tinyobj::material_t& mtl = veach.reader.GetMaterials().at(veach.reader.GetShapes().at(point.s).mesh.material_ids[point.f]);
+    const vec kd(mtl.diffuse[0], mtl.diffuse[1], mtl.diffuse[2]), ks(mtl.specular[0], mtl.specular[1], mtl.specular[2]);
+    const double ns = mtl.shininess, P_RR = 0.6;
+    depth++;
+
+    RadianceRGB L_first;  // NEE: direct light; MIS: the light-sample branch
+    if (nee) {
+        sampledLightPoint lp = g_vstrategy == 3 ? lights.select_a_point_from_lights(veach)
+                                                : lights.select_a_point_from_lights_spherical_triangle(p, N, veach);
+        vec x1 = lp.coord;
+        vec n1 = veach.get_unique_normal_of_facet(lp.s, lp.f);
+        vec wl = (x1 - p).normalized();
+        if (wl.dot_product(N) > 0 && (wl * -1).dot_product(n1) > 0) {
+            intersec_result vis = veach.closet_ray_intersect(p, wl, self);
+            if (vis.isIntersec && vis.s == lp.s && vis.f == lp.f) {
+                BRDF brdf = BRDF::get_brdf_phong(N, wl, wo, kd, ks, ns);
+                if (g_vstrategy == 0 && (g_vflags & V_FIX_NEE_MEASURE)) L_first = lp.I * brdf * (wl.dot_product(N) / lp.prob);
+                else L_first = lp.I * brdf * (wl.dot_product(N) * (wl * -1).dot_product(n1) / (x1 - p).dot_product(x1 - p) / lp.prob);
+            }
+        }
+        if (!roulette_survives(depth)) return L_first + RadianceRGB();
+    } else if (!roulette_survives(depth)) return RadianceRGB();
+
+    if (mis) {
+        lights.prepared_for_lights_spherical_triangle_sampling(p, N, veach);
+        sampledLightPoint lp = lights.lights_spherical_triangle_sampling(p, N, veach);
+        vec wl = (lp.coord - p).normalized();
+        // F10: recursion #1 overwrites the members eval_spherical_triangle_sampling_pdf reads below (Mylight.h:115-120)
+        const bool keep = (g_vflags & V_FIX_STALE_MIS) != 0;
+        std::vector<projectedSphericalTriangle> k_tri;
+        std::vector<double> k_w;
+        std::map<triangle, size_t> k_idx;
+        double k_sum = lights.weights_sum;
+        if (keep) { k_tri = lights.sphericalTriangles; k_w = lights.weights; k_idx = lights.indiceMap; }
+        if (wl.dot_product(N) > 0) {
+            intersec_result hit = veach.closet_ray_intersect(p, wl, self);
+            if (hit.isIntersec) {
+                BRDF brdf = BRDF::get_brdf_phong(N, wl, wo, kd, ks, ns);
+                double phongPdf = BRDF::eval_sample_from_phong_pdf(N, wl, wo, kd, ks, ns);
+                L_first = variant_shade(hit, wl * -1, depth) * brdf * (wl.dot_product(N) / (lp.prob + phongPdf) / P_RR);
+            }
+        }
+        if (keep) { lights.sphericalTriangles.swap(k_tri); lights.weights.swap(k_w); lights.indiceMap.swap(k_idx); lights.weights_sum = k_sum; }
+    }
+
+    RadianceRGB L_second;  // the BRDF-sample branch
+    sampledRay wi = BRDF::sample_from_phong(N, wo, kd, ks, ns);
+    if (wi.dir.dot_product(N) < 0) return L_first + L_second;
+    double pdf = wi.pdf;
+    if (g_vflags & V_FIX_MIXTURE_PDF) pdf = BRDF::eval_sample_from_phong_pdf(N, wi.dir, wo, kd, ks, ns);
+    intersec_result next = veach.closet_ray_intersect(p, wi.dir, self);
+    if (next.isIntersec && !(nee && lights.islight.find(triangle(next.s, next.f)) != lights.islight.end())) {
+        BRDF brdf = BRDF::get_brdf_phong(N, wi.dir, wo, kd, ks, ns);
+        double light_pdf = 0;
+        if (mis) {
+            intersec_result lh = veach.closet_ray_intersect_light_triangle(p, wi.dir, self, lights.islight);
+            if (lh.isIntersec) light_pdf = lights.eval_spherical_triangle_sampling_pdf(triangle(lh.s, lh.f), veach);
+        }
+        L_second = variant_shade(next, wi.dir * -1, depth) * brdf * (wi.dir.dot_product(N) / (pdf + light_pdf) / P_RR);
+    }
+    return L_first + L_second;
+}
+}  // namespace
+
+// ref_render with the estimator above: strategy 0..3 (3 = uniform-area NEE, main.cpp:297), flags = ORACLE_FIX_* bits
+extern "C" void ref_render_variant(const double eye[3], const double w_[3], const double up[3], double pixellen, int W, int H, int i0,
+                                   int i1, int j0, int j1, int spp, int spp_offset, int spp_total, int strategy, int max_depth,
+                                   int flags, uint64_t seed, double* out, uint64_t* counters)
+{
+    g_oracle_max_depth = max_depth;
+    g_vstrategy = strategy; g_vflags = flags;
+    uint64_t v0 = g_oracle_vertices, primary_hits = 0;
+    vec eyev = V3(eye), w = V3(w_);
+    vec N = w.normalized();
+    vec UP = V3(up);
+    vec Vv = N.cross_product(UP).normalized();
+    vec U = Vv.cross_product(N).normalized();
+    matrix3d T = matrix3d(U, Vv, N);
+    const double ci = (H - 1) * 0.5, cj = (W - 1) * 0.5, inv = 1.0 / spp_total;
+    for (int i = i0; i < i1; i++)
+        for (int j = j0; j < j1; j++) {
+            vec delta(-pixellen * (i - ci), pixellen * (j - cj), 0);
+            vec dir = (T * (delta + vec(0, 0, w.norm2()))).normalized();
+            RadianceRGB sum(0, 0, 0);
+            for (int k = 0; k < spp; k++) {
+                oracle_stream_seed(&g_oracle_stream, seed, (uint64_t)i * (uint64_t)W + (uint64_t)j, (uint64_t)(spp_offset + k));
+                intersec_result rs = veach.closet_ray_intersect(eyev, dir, triangle(-1, -1));
+                if (rs.isIntersec) {
+                    primary_hits++;
+                    sum = sum + variant_shade(rs, dir * -1, 0) * inv;
+                }
+            }
+            double* o = out + ((size_t)(i - i0) * (size_t)(j1 - j0) + (size_t)(j - j0)) * 3;
+            o[0] = sum.RGB[0]; o[1] = sum.RGB[1]; o[2] = sum.RGB[2];
+        }
+    if (counters) { counters[0] = g_oracle_vertices - v0; counters[1] = primary_hits; }
+}

@@ -19,6 +19,10 @@ import util  # noqa: E402
 import oracle  # noqa: E402
 
 RENDER = dict(spp=2, max_depth=4, seed=11)
+# (strategy, ORACLE_FIX_* flags) of the estimator variants the GPU is compared with: F10 never reproduced (1), the F9 / F8
+# switches (2, 4), the uniform-area sampler of main.cpp:297 (strategy 3).  Rendered by ref_render_variant on the
+# reference's own objects (oracle/ref_build/ref_driver.cpp).
+VARIANTS = [(3, 0), (3, 4), (1, 4), (0, 2), (0, 4), (0, 6), (2, 1), (2, 5)]
 
 
 def make(name):
@@ -67,6 +71,14 @@ def make(name):
             img, cnt = ref.render(sc.camera, strat, **RENDER)
             out["img%d" % strat] = img
             out["img%d_vertices" % strat] = np.array([cnt["vertices"], cnt["primary_hits"]], np.int64)
+            # the re-hosted estimator with every switch off IS the reference's own shade* (validates the re-hosting)
+            img_v, cnt_v = ref.render_variant(sc.camera, strat, flags=0, **RENDER)
+            assert np.array_equal(img, img_v, equal_nan=True) and cnt == cnt_v, ("re-hosted estimator differs from main.cpp", strat)
+        for strat, flags in VARIANTS:
+            # F10 only shows where recursion #1 changed the survivor set AND the BRDF ray found a light: a few pixels at 24 spp
+            img, cnt = ref.render_variant(sc.camera, strat, flags=flags, **dict(RENDER, spp=24 if strat == 2 else RENDER["spp"]))
+            out["imgv_s%d_f%d" % (strat, flags)] = img
+            out["imgv_s%d_f%d_vertices" % (strat, flags)] = np.array([cnt["vertices"], cnt["primary_hits"]], np.int64)
     path = os.path.join(HERE, name + ".npz")
     np.savez_compressed(path, **out)
     print(name, "->", path, "%.1f KB" % (os.path.getsize(path) / 1024))

@@ -98,8 +98,11 @@ def test_light_only_fp32_trace(scene_name, gpu_scene_of, arrays_of, oracle_of):
     mism = np.mean(p32 != p64)
     assert mism < 5e-3, mism  # FP32 Moeller-Trumbore vs FP64 Cramer: edge hits only
     hit = (p32 == p64) & (p64 >= 0)
-    assert np.max(util.rel_err(b32[hit, 2], b64[hit, 2])) < 1e-3
-    assert np.max(np.abs(b32[hit, :2] - b64[hit, :2])) < 1e-3
+    # t of a grazing hit is ill-conditioned in FP32 (|det| small): bound the bulk tightly, the tail loosely
+    et = util.rel_err(b32[hit, 2], b64[hit, 2])
+    assert np.quantile(et, 0.999) < 1e-4 and et.max() < 5e-2, (np.quantile(et, 0.999), et.max())
+    eb = np.abs(b32[hit, :2] - b64[hit, :2]).max(axis=1)
+    assert np.quantile(eb, 0.999) < 1e-4 and eb.max() < 5e-2, (np.quantile(eb, 0.999), eb.max())
     # FP64 instantiation: bit exact
     pe, be = s.closest(ro, rd, ex, True, api.FP64)
     assert np.array_equal(pe, p64) and np.array_equal(be, b64)
