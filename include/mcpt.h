@@ -30,7 +30,8 @@ typedef enum McptError {
     MCPT_ERR_NO_DEVICE = -3,      /* no CUDA device: there is NO CPU fallback */
     MCPT_ERR_IO = -4,             /* file not found / parse error (host loaders) */
     MCPT_ERR_QUEUE_OVERFLOW = -5, /* MIS path-tree outgrew the ray queue; retry with smaller batch_spp */
-    MCPT_ERR_OOM = -6
+    MCPT_ERR_OOM = -6,
+    MCPT_ERR_NCCL = -7            /* multi-device render: libnccl.so.2 missing, or an NCCL call failed */
 } McptError;
 
 /* Which shade* body runs (main.cpp:269 / 348 / 402).  Same numbering as oracle/mcpt_oracle.h. */
@@ -170,6 +171,24 @@ int mcpt_render(McptScene* scene, const McptCamera* cam, const McptRenderParams*
  * NULL = default) so callers can chain an NCCL reduce; returns after the work is enqueued AND complete. */
 int mcpt_render_device(McptScene* scene, const McptCamera* cam, const McptRenderParams* params, float* d_out_rgb,
                        void* stream, McptStats* stats);
+/* ---- multi-GPU behind the same ABI -------------------------------------------------
+ * The loop shards by samples per pixel: device r of n renders ALL pixels for a contiguous share of the sample indices
+ * [spp_offset, spp_offset + spp) (uniforms are keyed on the global index, so the film does not depend on n beyond the
+ * FP32 order of one sum), normalised by spp_total.  One SAH BVH build; the packed scene is replicated to every device;
+ * one host thread + stream + workspace per device; ONE collective -- ncclReduce(float32, sum, W*H*3) onto devices[0]
+ * over NVLink -- then one device-to-host copy into out_rgb.  NCCL is bound at run time (dlopen libnccl.so.2); without
+ * it these calls return MCPT_ERR_NCCL.  mcpt_multi_upload re-sends the scene blob to every device (e2e timing).
+ * mcpt_render_multi = create + render + destroy, the one-call form of main.cpp:557-588 on n GPUs.
+ * stats: counters summed over devices; ms_* = the slowest device (+ the reduce in ms_total), device-timed. */
+typedef struct McptMulti McptMulti;
+int mcpt_multi_create(const McptSceneDesc* desc, const int32_t* devices, int32_t n, uint32_t build_flags, McptMulti** out);
+int mcpt_multi_device_count(const McptMulti*);
+McptScene* mcpt_multi_scene(McptMulti*, int32_t r); /* replica r (owned by the McptMulti): introspection, mcpt_tonemap */
+int mcpt_multi_upload(McptMulti*);
+int mcpt_multi_render(McptMulti*, const McptCamera* cam, const McptRenderParams* params, float* out_rgb, McptStats* stats);
+void mcpt_multi_destroy(McptMulti*);
+int mcpt_render_multi(const McptSceneDesc* desc, const int32_t* devices, int32_t n, const McptCamera* cam,
+                      const McptRenderParams* params, float* out_rgb, McptStats* stats);
 /* RadianceRGB::tone_mapping (RadianceRGB.cpp:51-67) on the device: rgb8 = clamp(floor(255*(L/Lmax)^g+.5)) */
 int mcpt_tonemap(McptScene* scene, const float* rgb, size_t num_pixels, double max_radiance, double gamma,
                  uint8_t* out_rgb8);

@@ -35,6 +35,8 @@ SYMBOLS = [
     "mcpt_host_scene_camera", "mcpt_host_scene_free", "mcpt_host_bvh_check", "mcpt_scene_create_ex",
     "mcpt_scene_build_info", "mcpt_scene_bvh_check", "mcpt_host_light_tree_check", "mcpt_light_tree_batch",
     "mcpt_scene_light_tree_info", "mcpt_scene_light_tree_nodes", "mcpt_visibility_batch",
+    "mcpt_multi_create", "mcpt_multi_device_count", "mcpt_multi_upload", "mcpt_multi_render", "mcpt_multi_destroy",
+    "mcpt_render_multi", "mcpt_multi_scene",
 ]
 
 
@@ -97,6 +99,11 @@ def load():
     lib.mcpt_host_scene_desc.argtypes = [C.c_void_p]
     lib.mcpt_host_scene_free.argtypes = [C.c_void_p]
     lib.mcpt_scene_destroy.argtypes = [C.c_void_p]
+    lib.mcpt_multi_destroy.argtypes = [C.c_void_p]
+    lib.mcpt_multi_upload.argtypes = [C.c_void_p]
+    lib.mcpt_multi_device_count.argtypes = [C.c_void_p]
+    lib.mcpt_multi_scene.restype = C.c_void_p
+    lib.mcpt_multi_scene.argtypes = [C.c_void_p, C.c_int32]
     _lib = lib
     return lib
 
@@ -189,6 +196,44 @@ def host_light_tree_check(a: SceneArrays):
     out = (C.c_uint32 * 4)()
     _check(lib.mcpt_host_light_tree_check(C.byref(d), out))
     return dict(nodes=out[0], max_depth=out[1], errors=out[2], lights=out[3])
+
+
+class MultiScene:
+    """A scene replicated on several GPUs of this process (mcpt_multi_create): spp sharded inside the library, one NCCL
+    reduce of the films, host film out."""
+
+    def __init__(self, arrays: SceneArrays, devices, build: int = BUILD_HOST_SAH):
+        self.lib = load()
+        d, self._keep = make_desc(arrays)
+        devs = (C.c_int32 * len(devices))(*devices)
+        self.handle = C.c_void_p()
+        self.n = len(devices)
+        _check(self.lib.mcpt_multi_create(C.byref(d), devs, C.c_int32(len(devices)), C.c_uint32(build), C.byref(self.handle)))
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.mcpt_multi_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload(self):
+        _check(self.lib.mcpt_multi_upload(self.handle))
+
+    def render(self, cam: Camera, strategy: int, spp: int, max_depth: int = 0, flags: int = 0, seed: int = 1,
+               spp_offset: int = 0, spp_total: int = 0, batch_spp: int = 0, p_rr: float = 0.0, out=None,
+               leaf_mode: int = LEAF_FAST):
+        if out is None:
+            out = np.zeros((cam.height, cam.width, 3), np.float32)
+        st = Stats()
+        p = Scene._params(None, cam, strategy, spp, max_depth, flags, seed, spp_offset, spp_total, batch_spp, p_rr, leaf_mode)
+        cc = camera_c(cam)
+        _check(self.lib.mcpt_multi_render(self.handle, C.byref(cc), C.byref(p), _p(out), C.byref(st)))
+        return out, st.as_dict()
 
 
 class Scene:

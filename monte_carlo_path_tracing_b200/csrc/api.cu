@@ -4,6 +4,8 @@
 #include <cmath>
 #include <cstring>
 #include <limits>
+#include <memory>
+#include <type_traits>
 #include <numeric>
 #include "bvh_tree.h"
 #include "mcpt_internal.h"
@@ -300,6 +302,43 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
     if (rc != MCPT_OK && s) { mcpt_scene_destroy(s); }
     return rc;
 }
+
+}  // extern "C"
+
+namespace mcpt {
+// A replica of `src` on another device: the host-side description and the packed blob are copied, the device pointers
+// rebased -- no second BVH build (multi.cu).
+McptScene* scene_clone(const McptScene* src, int device)
+{
+    MCPT_CUDA(cudaSetDevice(device));
+    std::unique_ptr<McptScene> s(new McptScene(*src));
+    s->device = device;
+    s->h_blob = nullptr; s->d_blob = nullptr;
+    s->ws = Workspace();
+    for (auto& e : s->ev) e = nullptr;
+    McptScene* raw = s.release();
+    try {
+        MCPT_CUDA(cudaMallocHost(&raw->h_blob, src->blob_bytes));
+        std::memcpy(raw->h_blob, src->h_blob, src->blob_bytes);
+        MCPT_CUDA(cudaMalloc(&raw->d_blob, src->blob_bytes));
+        MCPT_CUDA(cudaMemcpy(raw->d_blob, raw->h_blob, src->blob_bytes, cudaMemcpyHostToDevice));
+        const char* ob = (const char*)src->d_blob;
+        char* nb = (char*)raw->d_blob;
+        auto rebase = [&](auto& ptr) { using T = std::remove_reference_t<decltype(ptr)>; ptr = (T)(nb + ((const char*)ptr - ob)); };
+        DScene& d = raw->d;
+        rebase(d.nodes); rebase(d.nodes4); rebase(d.tris); rebase(d.lnodes); rebase(d.ltris); rebase(d.pverts); rebase(d.pnorms);
+        rebase(d.mats); rebase(d.lights); rebase(d.lsoa); rebase(d.lng64); rebase(d.larea64); rebase(d.crad64);
+        rebase(d.class_begin); rebase(d.class_cdf); rebase(d.tri_cdf); rebase(d.ltree); rebase(d.ltree_leaf);
+        for (int i = 0; i < 6; i++) MCPT_CUDA(cudaEventCreate(&raw->ev[i]));
+    } catch (...) {
+        mcpt_scene_destroy(raw);
+        throw;
+    }
+    return raw;
+}
+}  // namespace mcpt
+
+extern "C" {
 
 void mcpt_scene_destroy(McptScene* s)
 {

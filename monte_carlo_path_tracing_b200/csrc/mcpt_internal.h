@@ -78,6 +78,8 @@ namespace mcpt {
 // render.cu
 void render_device(McptScene* scene, const McptCamera* cam, const McptRenderParams* params, float* d_out_rgb,
                    cudaStream_t stream, McptStats* stats);
+// api.cu: replica of a scene on another device (no second BVH build)
+McptScene* scene_clone(const McptScene* src, int device);
 // render_parity.cu: MCPT_PARITY_FP64
 void render_parity_device(McptScene* scene, const McptCamera* cam, const McptRenderParams* params, float* d_out_rgb,
                           cudaStream_t stream, McptStats* stats);

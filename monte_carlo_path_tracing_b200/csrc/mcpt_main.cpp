@@ -9,7 +9,8 @@
 // Every parameter the reference hard-codes in source is a command-line option.  Uses only include/mcpt.h.
 //
 //   mcpt_render scene.obj scene.xml out.ppm|out.bmp [--spp 10] [--strategy mis|mis_single|nee|nee_uniform|brdf] [--max-depth 0]
-//               [--width W --height H] [--seed 1] [--device 0] [--fix-pdf] [--fix-measure] [--jitter] [--light-tree]
+//               [--width W --height H] [--seed 1] [--device 0] [--gpus N]   (N > 1: spp sharded over devices 0..N-1 inside
+//               the library, one NCCL reduce of the films -- mcpt_multi_*) [--fix-pdf] [--fix-measure] [--jitter] [--light-tree]
 //               [--leaf fast|exact] [--parity]   (MCPT_LEAF_EXACT / MCPT_PARITY_FP64: the reference's FP64 arithmetic)
 //               [--lmax 380 --gamma 0.25] [--pfm out.pfm] [--ref-fov]
 //               [--gpu-bvh] [--every N] [--checkpoint file [--resume]] [--target-rel-error e] [--time-budget seconds]
@@ -99,7 +100,7 @@ int main(int argc, char** argv)
     const char *obj = argv[1], *xml = argv[2], *out = argv[3];
     int spp = 10;                    // main.cpp:567
     int strategy = MCPT_MIS;         // main.cpp:575 calls shade_with_mis as checked in
-    int max_depth = 0, width = 0, height = 0, device = 0, leaf_mode = MCPT_LEAF_FAST;
+    int max_depth = 0, width = 0, height = 0, device = 0, leaf_mode = MCPT_LEAF_FAST, gpus = 1;
     unsigned flags = 0;
     unsigned long long seed = 1;
     double lmax = 380.0, gamma = 0.25;  // main.cpp:583
@@ -133,6 +134,7 @@ int main(int argc, char** argv)
         else if (a == "--height") height = std::atoi(next());
         else if (a == "--seed") seed = std::strtoull(next(), nullptr, 10);
         else if (a == "--device") device = std::atoi(next());
+        else if (a == "--gpus") gpus = std::atoi(next());
         else if (a == "--fix-pdf") flags |= MCPT_FIX_MIXTURE_PDF;
         else if (a == "--fix-measure") flags |= MCPT_FIX_NEE_MEASURE;
         else if (a == "--jitter") flags |= MCPT_JITTER;
@@ -181,7 +183,14 @@ int main(int argc, char** argv)
     cam.pixellen = (ref_fov ? std::tan(cfov / 360.0) : std::tan(cfov * M_PI / 360.0)) * wl / (height * 0.5);
 
     McptScene* scene = nullptr;
-    if (mcpt_scene_create_ex(desc, device, gpu_bvh ? MCPT_BUILD_GPU_LBVH : MCPT_BUILD_HOST_SAH, &scene)) return fail("creating the device scene");
+    McptMulti* multi = nullptr;
+    if (gpus > 1) {
+        std::vector<int32_t> devs(gpus);
+        for (int g = 0; g < gpus; g++) devs[g] = device + g;
+        if (mcpt_multi_create(desc, devs.data(), gpus, gpu_bvh ? MCPT_BUILD_GPU_LBVH : MCPT_BUILD_HOST_SAH, &multi)) return fail("creating the device scenes");
+        scene = mcpt_multi_scene(multi, 0);
+        std::printf("%d devices: spp sharded inside the library, one NCCL reduce of the films\n", gpus);
+    } else if (mcpt_scene_create_ex(desc, device, gpu_bvh ? MCPT_BUILD_GPU_LBVH : MCPT_BUILD_HOST_SAH, &scene)) return fail("creating the device scene");
     uint32_t nodes = 0, leaves = 0, depth = 0;
     double sah = 0, tree_ms = 0, total_ms = 0;
     int32_t builder = 0;
@@ -227,7 +236,7 @@ int main(int argc, char** argv)
         const int n = (int)std::min<uint64_t>((uint64_t)every, (uint64_t)spp - hd.spp_done);
         prm.spp = n; prm.spp_total = n; prm.spp_offset = (int32_t)hd.spp_done;  // film = mean of this batch
         McptStats st;
-        if (mcpt_render(scene, &cam, &prm, film.data(), &st)) return fail("rendering");
+        if (multi ? mcpt_multi_render(multi, &cam, &prm, film.data(), &st) : mcpt_render(scene, &cam, &prm, film.data(), &st)) return fail("rendering");
         double mean_lum = 0, err_acc = 0;
         for (size_t p = 0; p < npix; p++) {
             const double r = film[3 * p], g = film[3 * p + 1], b = film[3 * p + 2];
@@ -298,7 +307,8 @@ int main(int argc, char** argv)
             std::fclose(f);
         } else { std::perror(pfm.c_str()); return 1; }
     }
-    mcpt_scene_destroy(scene);
+    if (multi) mcpt_multi_destroy(multi);
+    else mcpt_scene_destroy(scene);
     mcpt_host_scene_free(hs);
     return 0;
 }
