@@ -10,7 +10,11 @@ BRDF sampling, balance heuristic), no depth cap (the reference has none; Russian
 paths).  One "step" = `--spp-per-step` samples of every pixel on every rank (weak scaling: per-GPU work is
 fixed) followed, for N > 1, by the NCCL reduce of the W*H*3 float film onto rank 0.
 metric = primary Msamples/s = W*H*spp_per_step*N / step time.  Inputs (scene, BVH) are resident in HBM
-for `value`; `e2e` times mcpt_scene_upload (pinned H2D) + mcpt_render (+ film D2H) per step.
+for `value`; `e2e` times the host-buffer C ABI per step: scene upload (pinned H2D) + render + film D2H -- mcpt_scene_upload
++ mcpt_render at N = 1, and at N > 1 mcpt_multi_upload + mcpt_multi_render called by rank 0 alone (one process, spp sharded
+over the N devices INSIDE the library, one ncclReduce; the other ranks have released their GPUs and wait).
+`extra` carries, from the same run: cornell-box config 1 exactly (512x512, 16 spp, depth 5) and at 512 spp, veach-mis
+with MCPT_JITTER, the FAST-vs-EXACT hit-id mismatch rate, and config 3 strong-scaled (interior, 4096 spp / N).
 """
 from __future__ import annotations
 
@@ -155,7 +159,7 @@ def _cpu_worker(args):
         lib.build_grid(cam.eye, 100000)
         render = lambda r0, r1, k: lib.render(cam, STRAT[strategy], 1, max_depth=max_depth, seed=seed, rows=(r0, r1), spp_offset=k, spp_total=1)
     t0 = time.time()
-    samples = vertices = 0
+    samples = vertices = rays = 0
     k = 0
     rows = list(range(wid, cam.height, nw))
     # spread the rows this worker visits over the whole frame
@@ -166,8 +170,9 @@ def _cpu_worker(args):
             _, cnt = render(r, r + 1, k)
             samples += cam.width
             vertices += cnt["vertices"]
+            rays += cnt.get("rays", 0) + cnt.get("light_rays", 0)
             if time.time() - t0 >= budget_s:
-                return samples, vertices, time.time() - t0
+                return samples, vertices, time.time() - t0, rays
         k += 1
 
 
@@ -189,9 +194,12 @@ def cpu_reference_run(stem, cam, strategy, max_depth, budget_s, seed=1, procs=No
     samples = sum(r[0] for r in res)
     vertices = sum(r[1] for r in res)
     busy = max(r[2] for r in res)
+    rays = sum(r[3] for r in res)
     return {"value": samples / busy / 1e6, "unit": "Msamples/s", "cores": nproc, "kind": "reference" if use_ref else "port",
             "sample": "%d primary samples (interleaved full-width rows at 1 spp, %.1f s on %d processes; wall incl. load %.1f s)" % (samples, busy, nproc, wall),
-            "sample_bounces_per_s": vertices / busy, "samples": samples, "seconds": busy}
+            "sample_bounces_per_s": vertices / busy, "Mrays_per_s": rays / busy / 1e6,
+            "rays_counted": "closet_ray_intersect + closet_ray_intersect_light_triangle calls (linker --wrap shims in oracle/ref_build/ref_driver.cpp)",
+            "samples": samples, "seconds": busy}
 
 
 # ---- arms -------------------------------------------------------------------------------------------------------
@@ -242,6 +250,61 @@ def run_reference(args, wl_name, wl):
                                   "sample": "%d steps x %s" % (args.steps, runs[0]["sample"])},
                  "e2e": {"value": v, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
     print(json.dumps(line), flush=True)
+
+
+def shade_flop_constants():
+    """FP32 flops per unit of work of the shading kernels, from the committed ncu capture (profiles/r2_flops.json:
+    thread-level SASS instruction counts by opcode from `ncu --set full --import-source on`, FFMA = 2 flops, FFMA2 = 4,
+    FADD / FMUL = 1, FADD2 / FMUL2 = 2, MUFU = 1, divided by the units the captured launch processed).  Falls back to
+    the hand count of lights.cuh (81 flops + 4 MUFU + ~5 min/max per light and vertex; ~320 per shaded vertex)."""
+    p = os.path.join(ROOT, "profiles", "r2_flops.json")
+    try:
+        j = json.load(open(p))
+        return float(j["flops_per_light_vertex"]), float(j["flops_per_shade_element"]), "ncu: profiles/r2_flops.json"
+    except Exception:
+        return 90.0, 320.0, "hand count (lights.cuh)"
+
+
+def extra_measurements(args, api, torch, rank, world, local, dist):
+    """Side measurements the verdict asks for in the same driver run.  Each is a short, separately timed render; none of
+    them touches the headline numbers.  Returns a dict (rank 0) or None."""
+    out = {}
+    with tempfile.TemporaryDirectory() as td:
+        if world == 1:
+            # cornell-box, BASELINE.json configs[0]: 512x512, 16 spp, depth 5 -- exactly, and at 512 spp per step
+            sc = scenes.cornell_box(width=512, height=512)
+            a = api.load_scene_files(*[sc.write(td) + e for e in (".obj", ".xml")])[0]
+            s = api.Scene(a, local)
+            film = torch.zeros(512 * 512 * 3, dtype=torch.float32, device="cuda")
+            for spp, reps in ((16, 20), (512, 3)):
+                for k in range(3):
+                    s.render_device(sc.camera, api.NEE_UNIFORM, spp, film.data_ptr(), max_depth=5, seed=args.seed, spp_offset=k * spp)
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                v = 0
+                for k in range(reps):
+                    v += s.render_device(sc.camera, api.NEE_UNIFORM, spp, film.data_ptr(), max_depth=5, seed=args.seed, spp_offset=(3 + k) * spp)["vertices"]
+                e1.record()
+                torch.cuda.synchronize()
+                ms = e0.elapsed_time(e1)
+                out["cornell_box_512x512_%dspp_depth5" % spp] = {"Gsample_bounces_per_s": v / ms / 1e6, "Msamples_per_s": 512 * 512 * spp * reps / ms / 1e3,
+                                                                "ms_per_render": ms / reps, "renders": reps}
+            # FAST vs EXACT leaf test: hit-id mismatch rate on 1 M rays leaving random surface points (cornell-box)
+            rng = np.random.default_rng(5)
+            n = 1_000_000
+            prim = rng.integers(0, len(a.material_id), n).astype(np.int32)
+            b = rng.random(n); g = rng.random(n) * (1 - b)
+            v3 = a.positions[prim].astype(np.float64)
+            ro = v3[:, 0] * (1 - b - g)[:, None] + v3[:, 1] * b[:, None] + v3[:, 2] * g[:, None]
+            rd = rng.normal(size=(n, 3)); rd /= np.linalg.norm(rd, axis=1, keepdims=True)
+            pf, _ = s.closest(ro, rd, prim, False, api.FP32)
+            px, _ = s.closest(ro, rd, prim, False, api.FP64)
+            out["fast_vs_exact_hit_id_mismatch"] = {"rate": float(np.mean(pf != px)), "rays": n, "scene": "cornell-box",
+                                                    "what": "k_extend (FP32 Moeller-Trumbore, 4-wide BVH) vs the FP64 Cramer test of Myobj.cpp:165-192"}
+            s.close()
+            del film
+    return out
 
 
 def run_ours(args, wl_name, wl):
@@ -308,28 +371,86 @@ def run_ours(args, wl_name, wl):
     ms = float(ms.item())
     clocks = sampler.stop() if sampler else None
 
+    # ---- the same workload with MCPT_JITTER (extension of F4): no per-pixel sharing of the primary hit and of the first
+    # vertex's light sweep -- the number the no-jitter headline should be read beside
+    side = {}
+    if wl_name == "veach-mis" and not args.no_extras:
+        jkw = dict(kw, flags=kw.get("flags", 0) | api.JITTER)
+        scene.render_device(cam, strategy, S, film.data_ptr(), stream=stream, spp_offset=0, spp_total=S * world, **jkw)
+        sync()
+        j0, j1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        j0.record()
+        jst = scene.render_device(cam, strategy, S, film.data_ptr(), stream=stream, spp_offset=(world + rank) * S, spp_total=S * world, **jkw)
+        mdist.reduce_film(film, 0)
+        j1.record()
+        sync()
+        jms = torch.tensor([j0.elapsed_time(j1)], device="cuda")
+        if world > 1:
+            dist.all_reduce(jms, op=dist.ReduceOp.MAX)
+        side["veach_mis_with_MCPT_JITTER"] = {"Msamples_per_s": npix * S * world / float(jms.item()) / 1e3, "ms_per_step": float(jms.item()),
+                                              "sample_bounces_per_path": jst["vertices"] / max(jst["paths"], 1)}
+
     # ---- e2e through the host-buffer C ABI: scene upload (pinned H2D) + render + film D2H, every step
-    scene.upload(); scene.render(cam, strategy, min(S, 2), **kw)
-    sync()
+    h2d_bytes = scene.device_bytes() * world
     pinned = torch.empty(npix * 3, dtype=torch.float32).pin_memory()
     pinned_np = pinned.numpy()  # the host film buffer the ABI call fills
-    t0 = time.perf_counter()
-    for k in range(args.steps):
-        scene.upload()  # pinned H2D of the whole scene blob (geometry, BVHs, lights, materials)
-        if world == 1:
-            scene.render(cam, strategy, S, spp_offset=(k * world + rank) * S, spp_total=S * world, out=pinned_np, **kw)  # film D2H inside
-        else:
-            # N ranks: the public multi-GPU path -- device film per rank, one NCCL sum, rank 0 reads the film back
-            scene.render_device(cam, strategy, S, film.data_ptr(), stream=stream, spp_offset=(k * world + rank) * S,
-                                spp_total=S * world, **kw)
-            mdist.reduce_film(film, 0)
-            if rank == 0:
-                pinned.copy_(film, non_blocking=False)
-    sync()
-    e2e_s = torch.tensor([time.perf_counter() - t0], device="cuda")
-    if world > 1:
-        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    e2e_s = float(e2e_s.item())
+    e2e_how = "mcpt_scene_upload + mcpt_render"
+    if world == 1:
+        scene.upload(); scene.render(cam, strategy, min(S, 2), **kw)
+        sync()
+        t0 = time.perf_counter()
+        for k in range(args.steps):
+            scene.upload()  # pinned H2D of the whole scene blob (geometry, BVHs, lights, materials)
+            scene.render(cam, strategy, S, spp_offset=k * S, spp_total=S, out=pinned_np, **kw)  # film D2H inside
+        e2e_s = time.perf_counter() - t0
+    else:
+        # N GPUs behind the C ABI (mcpt_multi_*): ONE process drives all devices -- rank 0 calls, the others have released
+        # their GPUs (scene + 80 GB workspace) and wait at the barrier.  spp sharded inside the library, one ncclReduce.
+        e2e_how = "mcpt_multi_upload + mcpt_multi_render (rank 0 drives all %d devices)" % world
+        scene.close()
+        scene = None
+        del film
+        torch.cuda.empty_cache()
+        sync()
+        e2e_s = 0.0
+        if rank == 0:
+            multi = api.MultiScene(arrays, list(range(world)), build=api.BUILD_GPU_LBVH if args.bvh == "gpu" else api.BUILD_HOST_SAH)
+            multi.upload(); multi.render(cam, strategy, min(S, 2) * world, **kw)
+            multi.render(cam, strategy, S * world, out=pinned_np, **kw)
+            t0 = time.perf_counter()
+            for k in range(args.steps):
+                multi.upload()
+                multi.render(cam, strategy, S * world, spp_offset=k * S * world, spp_total=S * world, out=pinned_np, **kw)
+            e2e_s = time.perf_counter() - t0
+            multi.close()
+        sync()
+
+    # ---- config 3 strong-scaled (BASELINE.json configs[2]): interior stand-in, 1280x720, 4096 spp split over the N GPUs
+    if not args.no_extras and wl_name == "veach-mis":
+        with tempfile.TemporaryDirectory() as td3:
+            sc3 = scenes.interior(width=1280, height=720)
+            a3 = api.load_scene_files(*[sc3.write(td3) + e for e in (".obj", ".xml")])[0]
+        s3 = api.Scene(a3, local)
+        film3 = torch.zeros(npix * 3, dtype=torch.float32, device="cuda")
+        off3, cnt3 = mdist.shard_spp(4096, world, rank)
+        s3.render_device(sc3.camera, api.MIS, 8, film3.data_ptr(), stream=stream, seed=args.seed)
+        sync()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record()
+        s3.render_device(sc3.camera, api.MIS, cnt3, film3.data_ptr(), stream=stream, seed=args.seed, spp_offset=off3, spp_total=4096)
+        mdist.reduce_film(film3, 0)
+        c1.record()
+        sync()
+        cms = torch.tensor([c0.elapsed_time(c1)], device="cuda")
+        if world > 1:
+            dist.all_reduce(cms, op=dist.ReduceOp.MAX)
+        side["config3_interior_1280x720_4096spp_strong"] = {"seconds": float(cms.item()) / 1e3, "spp_per_gpu": cnt3, "n_gpus": world,
+                                                            "Msamples_per_s": npix * 4096 / float(cms.item()) / 1e3, "triangles": len(a3.material_id),
+                                                            "scaling": "strong: total work fixed, one NCCL reduce at the end"}
+        s3.close()
+        del film3
+    if not args.no_extras and rank == 0:
+        side.update(extra_measurements(args, api, torch, rank, world, local, dist) or {})
 
     tot = {k: sum(s[k] for s in stats) for k in ("paths", "vertices", "rays_closest", "rays_shadow", "rays_light", "kernel_launches", "bounces")}
     ms_bounce = sum(s["ms_bounce"] for s in stats)
@@ -383,9 +504,19 @@ def run_ours(args, wl_name, wl):
         sweeps = (npix * passes + later * (0.6 if wl["strategy"] == "MIS" else 1.0)) if (sph and not args.light_tree) else 0
         # per light and vertex (lights.cuh light_weight_pair): 10 FADD + 17 FMUL + 27 FFMA (eight dot products, three norms, the
         # Van Oosterom-Strackee denominator, the 8-term atan polynomial) = 81 flops + 4 MUFU + ~5 min/max/select
-        flops = 320.0 * tot["vertices"] + 90.0 * L * sweeps
+        f_light, f_shade, f_src = shade_flop_constants()
+        counted_sweeps = sum(s.get("light_sweeps", 0) for s in stats)   # McptStats.light_sweeps: exact, counted on the device
+        if counted_sweeps and sph and not args.light_tree:
+            sweeps = counted_sweeps
+        Lpad = (L + 63) // 64 * 64
+        flops_sweep = f_light * Lpad * sweeps
+        flops = f_shade * elements + flops_sweep
         flops_per_vertex = flops / max(tot["vertices"], 1)
-        fp32_peak = 148 * 128 * 2 * 1.965e9
+        try:
+            fp32_scalar, fp32_packed = api.measure_fp32(local)
+            fp32_peak, fp32_src = max(fp32_scalar, fp32_packed) * 1e12, "measured: mcpt_measure_fp32 (register-resident FFMA2 chains) %.1f packed / %.1f scalar TFLOP/s" % (fp32_packed, fp32_scalar)
+        except Exception:
+            fp32_peak, fp32_src = 148 * 128 * 2 * 1.965e9, "computed: 148 SMs x 128 lanes x 2 x 1.965 GHz"
         line = base_line(args, wl_name, wl, cam, S)
         if args.light_tree:
             line["config"]["light_selection"] = "MCPT_LIGHT_TREE: O(log L) hierarchy instead of the reference's O(L) loop (not a reference estimator)"
@@ -394,8 +525,8 @@ def run_ours(args, wl_name, wl):
             "value": value, "ms_per_step": ms / args.steps,
             "gpu_launches": int(tot["kernel_launches"]),
             "clocks": clocks,
-            "e2e": {"value": samples / e2e_s / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": scene.device_bytes(),
-                    "d2h_bytes_per_step": npix * 12},
+            "e2e": {"value": samples / e2e_s / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": h2d_bytes,
+                    "d2h_bytes_per_step": npix * 12, "through": e2e_how},
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "traffic_detail": traffic_detail, "peak_source": which,
                          "algorithmic_bytes_per_launch": dom_bytes / dom_launches, "avg_launch_ms": dom_ms / dom_launches,
@@ -407,7 +538,8 @@ def run_ours(args, wl_name, wl):
                                  "the fp32 object is the bound that applies to the light-sampling strategies"},
             "fp32": {"achieved_tflops": flops / (ms * 1e-3) / 1e12, "peak_tflops": fp32_peak / 1e12,
                      "frac": flops / (ms * 1e-3) / fp32_peak, "executed_flops_per_sample_bounce": flops_per_vertex, "lights": L,
-                     "light_table_sweeps": sweeps, "note": "rank 0, whole step; estimate from counted vertices and sweeps"},
+                     "light_table_sweeps": sweeps, "flops_per_light_vertex": f_light, "flops_per_shade_element": f_shade,
+                     "flop_constants": f_src, "peak_source": fp32_src, "note": "rank 0, whole step; sweeps counted on the device (McptStats.light_sweeps)"},
             "extra": {"Msample_bounces_per_s": tot["vertices"] * world / ms / 1e3,
                       "Mrays_per_s": (tot["rays_closest"] + tot["rays_shadow"] + tot["rays_light"]) * world / ms / 1e3,
                       "sample_bounces_per_path": tot["vertices"] / max(tot["paths"], 1),
@@ -415,6 +547,19 @@ def run_ours(args, wl_name, wl):
                       "bvh": bvh_extra, "device_ms_per_step": [round(float(x["ms_total"]), 3) for x in stats],
                       "host_ms_per_step": [round(1e3 * (b - a), 3) for a, b in zip(host_t[:-1], host_t[1:])]},
         })
+        if sph and not args.light_tree and ms_shade >= ms_trace:
+            # the dominant kernels are the light sweeps + shading: FP32-issue-bound (ncu: FMA pipe 66 % busy, 252 GB/s of DRAM), so the
+            # roofline that applies is FP32, against the MEASURED multiply-add ceiling; the HBM reading is kept beside it
+            hbm = dict(line["roofline"])
+            ach = flops / (ms_shade * 1e-3) / 1e12
+            line["roofline"] = {"bound": "fp32", "kernel": dom, "achieved": ach, "peak": fp32_peak / 1e12, "unit": "TFLOP/s",
+                                "frac": ach * 1e12 / fp32_peak, "traffic": traffic, "peak_source": fp32_src,
+                                "algorithmic_flops_per_launch": flops / dom_launches, "avg_launch_ms": dom_ms / dom_launches,
+                                "launches": dom_launches, "kernel_share_of_step": dom_ms / ms, "flop_constants": f_src,
+                                "hbm": hbm,
+                                "note": "bound = fp32: executed FP32 flops of k_lightsel + k_shade (+ k_lightprep's sweeps) per launch over their "
+                                        "device-timed duration, against the measured FFMA ceiling of this GPU; `hbm` holds the byte-roofline view"}
+        line["extra"].update(side)
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_reference_run(stem, cam, wl["strategy"], wl["max_depth"], args.cpu_seconds)
             # the reference as designed is one thread (README.md:418): same rows, one process, a quarter of the budget
@@ -424,7 +569,8 @@ def run_ours(args, wl_name, wl):
             for k in ("samples", "seconds"):
                 line["cpu_baseline"].pop(k, None)
         print(json.dumps(line), flush=True)
-    scene.close()
+    if scene is not None:
+        scene.close()
     if world > 1:
         dist.destroy_process_group()
 
@@ -441,6 +587,7 @@ def main():
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the side measurements (cornell config 1, jitter, config 3, id mismatch)")
     ap.add_argument("--light-tree", action="store_true", help="MCPT_LIGHT_TREE light selection (SURVEY.md 8(f) row 4; not the headline)")
     ap.add_argument("--bvh", default="host", choices=["host", "gpu"], help="scene BVH builder: host SAH (default) or device LBVH")
     args = ap.parse_args()

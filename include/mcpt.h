@@ -139,6 +139,8 @@ typedef struct McptStats {
     float ms_shade;          /* part of ms_bounce spent in k_shade (CUDA events on the launch stream) */
     float ms_trace;          /* part of ms_bounce spent in k_gather + k_extend + k_shadow (+ k_runsum) */
     uint64_t elements;       /* ray-queue elements processed by k_shade, summed over bounces (>= vertices) */
+    uint64_t light_sweeps;   /* vertices for which the whole light table was evaluated (the O(L) loop of Mylight.cpp:329-421):
+                              * once per shadable PIXEL per pass at the first vertex (F4), once per sampling vertex after it */
 } McptStats;
 
 typedef struct McptScene McptScene;
@@ -259,6 +261,9 @@ int mcpt_scene_light_tree_nodes(const McptScene*, float* out_nodes12, int32_t* o
  * with that light's FP32 spherical-triangle weight sA * (R+G+B) (0 = culled at this vertex). */
 int mcpt_light_tree_batch(McptScene*, size_t n, const double* x1, const double* N, const double* u, const int32_t* query_light,
                           int32_t* light, double* prob, double* query_prob, double* query_weight);
+/* FP32 multiply-add ceiling of `device`, measured with register-resident FMA chains (no memory traffic), in TFLOP/s:
+ * three-register scalar FFMA and the packed FFMA2 form the light sweeps use.  bench.py's fp32 roofline denominator. */
+int mcpt_measure_fp32(int device, double* tflops_scalar, double* tflops_packed);
 const char* mcpt_last_error(void);
 int mcpt_version(void);
 int mcpt_device_count(void);

@@ -36,7 +36,7 @@ SYMBOLS = [
     "mcpt_scene_build_info", "mcpt_scene_bvh_check", "mcpt_host_light_tree_check", "mcpt_light_tree_batch",
     "mcpt_scene_light_tree_info", "mcpt_scene_light_tree_nodes", "mcpt_visibility_batch",
     "mcpt_multi_create", "mcpt_multi_device_count", "mcpt_multi_upload", "mcpt_multi_render", "mcpt_multi_destroy",
-    "mcpt_render_multi", "mcpt_multi_scene",
+    "mcpt_render_multi", "mcpt_multi_scene", "mcpt_measure_fp32",
 ]
 
 
@@ -70,7 +70,7 @@ class Stats(C.Structure):
                 ("rays_closest", C.c_uint64), ("rays_shadow", C.c_uint64), ("rays_light", C.c_uint64),
                 ("passes", C.c_uint32), ("bounces", C.c_uint32), ("kernel_launches", C.c_uint32),
                 ("queue_peak", C.c_uint32), ("ms_total", C.c_float), ("ms_bounce", C.c_float), ("ms_other", C.c_float),
-                ("ms_shade", C.c_float), ("ms_trace", C.c_float), ("elements", C.c_uint64)]
+                ("ms_shade", C.c_float), ("ms_trace", C.c_float), ("elements", C.c_uint64), ("light_sweeps", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -196,6 +196,13 @@ def host_light_tree_check(a: SceneArrays):
     out = (C.c_uint32 * 4)()
     _check(lib.mcpt_host_light_tree_check(C.byref(d), out))
     return dict(nodes=out[0], max_depth=out[1], errors=out[2], lights=out[3])
+
+
+def measure_fp32(device: int = 0):
+    """(scalar FFMA, packed FFMA2) FP32 ceilings of the device in TFLOP/s, measured (mcpt_measure_fp32)."""
+    a, b = C.c_double(), C.c_double()
+    _check(load().mcpt_measure_fp32(C.c_int(device), C.byref(a), C.byref(b)))
+    return a.value, b.value
 
 
 class MultiScene:

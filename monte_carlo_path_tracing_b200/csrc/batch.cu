@@ -2,6 +2,7 @@
 // Each runs the same device functions the renderer uses (precision 1 = FP32 instantiation) or their
 // FP64 instantiation in the reference's expression order (precision 0); tests compare both with the
 // oracle (SURVEY.md 8c "Deterministic parity targets").
+#include <algorithm>
 #include <cstring>
 #include "brdf.cuh"
 #include "lights.cuh"
@@ -323,6 +324,29 @@ __global__ void k_pack_ids(size_t n, const int* exclude, const int* light_prim, 
     if (i < n) ids[i] = make_int2(exclude ? exclude[i] : -1, light_prim[i]);
 }
 
+// ---- FP32 ceiling of this device, measured (bench.py's roofline denominator for the shading kernels) ----------------------
+// Register-resident multiply-add chains, 8 independent per thread, no memory traffic.  PACKED = the FFMA2 form the light
+// sweeps use (two FMAs per instruction on a 64-bit register pair); scalar = three-register FFMA.
+template <bool PACKED>
+__global__ void __launch_bounds__(256) k_fp32_peak(float* out, int iters, float b, float c)
+{
+    float2 a[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) a[k] = make_float2(threadIdx.x * 1e-3f + k, threadIdx.x * 2e-3f - k);
+    const float2 bb = make_float2(b, b + 1e-7f), cc = make_float2(c, c - 1e-7f);
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            if (PACKED) a[k] = __ffma2_rn(a[k], bb, cc);
+            else { a[k].x = __fmaf_rn(a[k].x, bb.x, cc.x); a[k].y = __fmaf_rn(a[k].y, bb.y, cc.y); }
+        }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; k++) s += a[k].x + a[k].y;
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 void need(const McptScene* s) { if (!s) throw Error(MCPT_ERR_INVALID, "null scene"); }
 
 }  // namespace
@@ -374,6 +398,39 @@ int mcpt_intersect_batch(McptScene* s, size_t n, const double* ro, const double*
         } else if (n) k_intersect<<<grid_for(n), kBlock>>>(s->d, n, dro.p, drd.p, exclude ? dex.p : nullptr, light_only, precision, dprim.p, dbgt.p);
         finish();
         dprim.to_host(prim); dbgt.to_host(bgt);
+    });
+}
+
+int mcpt_measure_fp32(int device, double* tflops_scalar, double* tflops_packed)
+{
+    return guarded([&] {
+        int ndev = 0;
+        if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); throw Error(MCPT_ERR_NO_DEVICE, "no CUDA device available"); }
+        if (device < 0 || device >= ndev) throw Error(MCPT_ERR_INVALID, "device index out of range");
+        MCPT_CUDA(cudaSetDevice(device));
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        const int grid = sms * 8, iters = 1 << 14;
+        DevBuf<float> out((size_t)grid * 256);
+        cudaEvent_t e0, e1;
+        MCPT_CUDA(cudaEventCreate(&e0)); MCPT_CUDA(cudaEventCreate(&e1));
+        double best[2] = {0, 0};
+        for (int packed = 0; packed < 2; packed++)
+            for (int rep = 0; rep < 4; rep++) {  // first repetition warms up
+                MCPT_CUDA(cudaEventRecord(e0));
+                if (packed) k_fp32_peak<true><<<grid, 256>>>(out.p, iters, 0.999f, 1e-3f);
+                else k_fp32_peak<false><<<grid, 256>>>(out.p, iters, 0.999f, 1e-3f);
+                MCPT_CUDA(cudaEventRecord(e1));
+                MCPT_CUDA(cudaEventSynchronize(e1));
+                float ms = 0.f;
+                cudaEventElapsedTime(&ms, e0, e1);
+                const double flops = 2.0 * 16.0 * (double)iters * (double)grid * 256.0;  // 16 FMAs per thread per iteration
+                if (rep) best[packed] = std::max(best[packed], flops / (ms * 1e-3) / 1e12);
+            }
+        cudaEventDestroy(e0); cudaEventDestroy(e1);
+        MCPT_CUDA(cudaGetLastError());
+        if (tflops_scalar) *tflops_scalar = best[0];
+        if (tflops_packed) *tflops_packed = best[1];
     });
 }
 

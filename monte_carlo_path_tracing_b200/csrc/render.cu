@@ -44,7 +44,7 @@ constexpr int kBlk = 128;             // threads per block (4 warps; a warp owns
 constexpr unsigned kFull = 0xffffffffu;
 constexpr size_t kTargetSlots = 128u << 20;  // auto batch: up to 128 Mi path slots in flight per pass (memory permitting)
 
-enum { CNT_VERTICES = 0, CNT_RAYS, CNT_SHADOW, CNT_LIGHTRAYS, CNT_PRIMARY_HITS, CNT_OVERFLOW, CNT_N };
+enum { CNT_VERTICES = 0, CNT_RAYS, CNT_SHADOW, CNT_LIGHTRAYS, CNT_PRIMARY_HITS, CNT_OVERFLOW, CNT_SWEEPS, CNT_N };
 
 struct Queue {
     float4* org;   // o.xyz | exclude prim (int bits)          (Myobj.cpp:417 rotri)
@@ -283,7 +283,7 @@ __global__ void __launch_bounds__(kBlk) k_primary_exact(DScene s, DCamera cam, i
 // shade_with_mis's roulette, main.cpp:429-437, already ended it); wsum_pix[pixel] = weights_sum.
 __global__ void __launch_bounds__(kBlk, 5) k_lightprep(DScene s, DCamera cam, const float4* __restrict__ primary_hit, int npix,
                                                     int batch_spp, int sample_base, uint64_t seed, float p_rr, int rr_first,
-                                                    int max_depth, int use_cdf, int2* sel, float* wsum_pix)
+                                                    int max_depth, int use_cdf, int2* sel, float* wsum_pix, unsigned long long* counters)
 {
     extern __shared__ float sm_prep[];
     const int lane = threadIdx.x & 31;
@@ -292,6 +292,7 @@ __global__ void __launch_bounds__(kBlk, 5) k_lightprep(DScene s, DCamera cam, co
     const int warp = (blockIdx.x * kBlk + threadIdx.x) >> 5, nwarps = (gridDim.x * kBlk) >> 5;
     const bool rr_forced = max_depth > 0 && 1 >= max_depth;
     const int K = s.Lpad >> 5;
+    unsigned c_sweeps = 0;
     for (int pair = warp; 2 * pair < npix; pair += nwarps) {
         f3 X[2], Nn[2];
         bool shad[2];
@@ -312,6 +313,7 @@ __global__ void __launch_bounds__(kBlk, 5) k_lightprep(DScene s, DCamera cam, co
         }
         float part[2] = {0.f, 0.f}, incl[2] = {0.f, 0.f}, total[2] = {0.f, 0.f};
         if (shad[0] || shad[1]) {
+            c_sweeps += (unsigned)shad[0] + (unsigned)shad[1];
             if (!shad[0]) { X[0] = X[1]; Nn[0] = Nn[1]; }
             if (!shad[1]) { X[1] = X[0]; Nn[1] = Nn[0]; }
             warp_light_partial<2>(s, X, Nn, part, use_cdf ? cdf : nullptr);
@@ -375,6 +377,7 @@ __global__ void __launch_bounds__(kBlk, 5) k_lightprep(DScene s, DCamera cam, co
         }
         __syncwarp();  // the next pair overwrites cdf / sinc
     }
+    if (lane == 0 && c_sweeps) atomicAdd(counters + CNT_SWEEPS, (unsigned long long)c_sweeps);  // vertices whose light table was swept
 }
 
 // ---- light selection at the later vertices ---------------------------------------------------------------------
@@ -611,7 +614,7 @@ __global__ void __launch_bounds__(kBlk, (STRAT == MCPT_MIS && !EXACT) ? 5 : MCPT
     const DScene& s = a.s;
     const int lane = threadIdx.x & 31;
     const unsigned below = (1u << lane) - 1u;
-    unsigned c_vert = 0, c_lrays = 0, c_phits = 0;
+    unsigned c_vert = 0, c_lrays = 0, c_phits = 0, c_sweeps = 0;
     const int nchunks = (a.in_count + kChunk - 1) / kChunk;
     const int depth = a.bounce + 1;
     const bool rr_forced = a.max_depth > 0 && depth >= a.max_depth;
@@ -692,6 +695,8 @@ __global__ void __launch_bounds__(kBlk, (STRAT == MCPT_MIS && !EXACT) ? 5 : MCPT
             n_list += __popc(mk_);
         }
         __syncwarp();
+        // the listed entries of a later bounce are exactly the vertices k_lightsel swept the light table for (warp-uniform count)
+        if (kSph && !FIRST && !(a.flags & MCPT_LIGHT_TREE)) c_sweeps += (unsigned)n_list;
 
         // ==== phase B: the listed entries, 32 at a time ===================================================================
         int emitted = 0;
@@ -917,6 +922,7 @@ __global__ void __launch_bounds__(kBlk, (STRAT == MCPT_MIS && !EXACT) ? 5 : MCPT
         if (c_vert) atomicAdd(a.counters + CNT_VERTICES, (unsigned long long)c_vert);
         if (c_lrays) atomicAdd(a.counters + CNT_LIGHTRAYS, (unsigned long long)c_lrays);
         if (c_phits) atomicAdd(a.counters + CNT_PRIMARY_HITS, (unsigned long long)c_phits);
+        if (c_sweeps) atomicAdd(a.counters + CNT_SWEEPS, (unsigned long long)c_sweeps);
     }
 }
 
@@ -1386,7 +1392,7 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
             const size_t npairs = (npix + 1) / 2;
             const int pgrid = (int)std::min<size_t>((npairs + kBlk / 32 - 1) / (kBlk / 32), (size_t)sms * std::max(1, pbps));
             k_lightprep<<<pgrid, kBlk, dyn, st>>>(scene->d, dc, primary, (int)npix, b, a.sample_base, prm->seed, p_rr, (tree || single) ? 1 : 0,
-                                                  prm->max_depth, use_cdf, sel, wsum_pix);
+                                                  prm->max_depth, use_cdf, sel, wsum_pix, d_counters);
             MCPT_CUDA(cudaGetLastError());
             S.kernel_launches++;
         }
@@ -1479,6 +1485,7 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
     S.rays_shadow = h_counters[CNT_SHADOW];
     S.rays_light = h_counters[CNT_LIGHTRAYS];
     S.primary_hits = h_counters[CNT_PRIMARY_HITS];
+    S.light_sweeps = h_counters[CNT_SWEEPS];
     overflow = h_counters[CNT_OVERFLOW] != 0;
     S.ms_total = ms_total; S.ms_bounce = ms_bounce; S.ms_other = ms_total - ms_bounce;
     S.ms_shade = ms_shade; S.ms_trace = ms_bounce - ms_shade;

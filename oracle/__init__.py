@@ -151,11 +151,11 @@ class RefLib(_Probes):
         W, H = cam.width, cam.height
         i0, i1 = rows or (0, H)
         j0, j1 = cols or (0, W)
-        out = np.zeros((i1 - i0, j1 - j0, 3)); cnt = (C.c_uint64 * 2)()
+        out = np.zeros((i1 - i0, j1 - j0, 3)); cnt = (C.c_uint64 * 4)()
         e, w, u, pl = camera_args(cam)
         self.lib.ref_render(e, w, u, pl, W, H, i0, i1, j0, j1, spp, spp_offset, spp_total or spp, strategy, max_depth,
                             C.c_uint64(seed), _p(out), cnt)
-        return out, dict(vertices=cnt[0], primary_hits=cnt[1])
+        return out, dict(vertices=cnt[0], primary_hits=cnt[1], rays=cnt[2], light_rays=cnt[3])
 
 
     def render_variant(self, cam, strategy, spp, max_depth=0, flags=0, seed=1, rows=None, cols=None, spp_offset=0, spp_total=None):
@@ -164,11 +164,11 @@ class RefLib(_Probes):
         W, H = cam.width, cam.height
         i0, i1 = rows or (0, H)
         j0, j1 = cols or (0, W)
-        out = np.zeros((i1 - i0, j1 - j0, 3)); cnt = (C.c_uint64 * 2)()
+        out = np.zeros((i1 - i0, j1 - j0, 3)); cnt = (C.c_uint64 * 4)()
         e, w, u, pl = camera_args(cam)
         self.lib.ref_render_variant(e, w, u, pl, W, H, i0, i1, j0, j1, spp, spp_offset, spp_total or spp, strategy, max_depth,
                                     flags, C.c_uint64(seed), _p(out), cnt)
-        return out, dict(vertices=cnt[0], primary_hits=cnt[1])
+        return out, dict(vertices=cnt[0], primary_hits=cnt[1], rays=cnt[2], light_rays=cnt[3])
 
 
 class OracleLib(_Probes):

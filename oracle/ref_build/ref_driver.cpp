@@ -27,6 +27,20 @@ RadianceRGB shade(intersec_result point, vec wo);
 RadianceRGB shade_with_brdf(intersec_result point, vec wo);
 RadianceRGB shade_with_mis(intersec_result point, vec wo);
 
+// ---- ray counters without touching the reference: the linker's --wrap (oracle/Makefile) sends every call that main.o
+// and this file make to Myobj::closet_ray_intersect / closet_ray_intersect_light_triangle (Myobj.cpp:334-622) through
+// the two functions below, which count and then call the real, unmodified definitions in Myobj.o.
+static uint64_t g_ref_rays = 0, g_ref_light_rays = 0;
+typedef std::map<triangle, RadianceRGB> islight_map;
+intersec_result real_closest(Myobj*, vec, vec, triangle) asm("__real__ZN5Myobj20closet_ray_intersectE3vecS0_8triangle");
+intersec_result wrap_closest(Myobj*, vec, vec, triangle) asm("__wrap__ZN5Myobj20closet_ray_intersectE3vecS0_8triangle");
+intersec_result real_closest_light(Myobj*, vec, vec, triangle, islight_map&)
+    asm("__real__ZN5Myobj35closet_ray_intersect_light_triangleE3vecS0_8triangleRSt3mapIS1_11RadianceRGBSt4lessIS1_ESaISt4pairIKS1_S3_EEE");
+intersec_result wrap_closest_light(Myobj*, vec, vec, triangle, islight_map&)
+    asm("__wrap__ZN5Myobj35closet_ray_intersect_light_triangleE3vecS0_8triangleRSt3mapIS1_11RadianceRGBSt4lessIS1_ESaISt4pairIKS1_S3_EEE");
+intersec_result wrap_closest(Myobj* self, vec o, vec d, triangle t) { ++g_ref_rays; return real_closest(self, o, d, t); }
+intersec_result wrap_closest_light(Myobj* self, vec o, vec d, triangle t, islight_map& m) { ++g_ref_light_rays; return real_closest_light(self, o, d, t, m); }
+
 oracle_stream g_oracle_stream;
 int g_oracle_depth = 0;
 int g_oracle_max_depth = 0;
@@ -280,6 +294,7 @@ void ref_render(const double eye[3], const double w_[3], const double up[3], dou
 {
     g_oracle_max_depth = max_depth;
     uint64_t v0 = g_oracle_vertices, primary_hits = 0;
+    const uint64_t r0 = g_ref_rays, l0 = g_ref_light_rays;
     vec eyev = V3(eye), w = V3(w_);
     // main.cpp:548-553
     vec N = w.normalized();
@@ -314,6 +329,8 @@ void ref_render(const double eye[3], const double w_[3], const double up[3], dou
     if (counters) {
         counters[0] = g_oracle_vertices - v0;  // non-emissive vertices shaded (RR engines built)
         counters[1] = primary_hits;
+        counters[2] = g_ref_rays - r0;         // closet_ray_intersect calls (camera, extension, visibility rays)
+        counters[3] = g_ref_light_rays - l0;   // closet_ray_intersect_light_triangle calls (main.cpp:484)
     }
 }
 
@@ -423,6 +440,7 @@ extern "C" void ref_render_variant(const double eye[3], const double w_[3], cons
     g_oracle_max_depth = max_depth;
     g_vstrategy = strategy; g_vflags = flags;
     uint64_t v0 = g_oracle_vertices, primary_hits = 0;
+    const uint64_t r0 = g_ref_rays, l0 = g_ref_light_rays;
     vec eyev = V3(eye), w = V3(w_);
     vec N = w.normalized();
     vec UP = V3(up);
@@ -446,5 +464,5 @@ extern "C" void ref_render_variant(const double eye[3], const double w_[3], cons
             double* o = out + ((size_t)(i - i0) * (size_t)(j1 - j0) + (size_t)(j - j0)) * 3;
             o[0] = sum.RGB[0]; o[1] = sum.RGB[1]; o[2] = sum.RGB[2];
         }
-    if (counters) { counters[0] = g_oracle_vertices - v0; counters[1] = primary_hits; }
+    if (counters) { counters[0] = g_oracle_vertices - v0; counters[1] = primary_hits; counters[2] = g_ref_rays - r0; counters[3] = g_ref_light_rays - l0; }
 }

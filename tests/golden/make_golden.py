@@ -71,6 +71,8 @@ def make(name):
             img, cnt = ref.render(sc.camera, strat, **RENDER)
             out["img%d" % strat] = img
             out["img%d_vertices" % strat] = np.array([cnt["vertices"], cnt["primary_hits"]], np.int64)
+            # closet_ray_intersect / closet_ray_intersect_light_triangle calls, counted by the linker --wrap shims of ref_driver.cpp
+            out["img%d_rays" % strat] = np.array([cnt["rays"], cnt["light_rays"]], np.int64)
             # the re-hosted estimator with every switch off IS the reference's own shade* (validates the re-hosting)
             img_v, cnt_v = ref.render_variant(sc.camera, strat, flags=0, **RENDER)
             assert np.array_equal(img, img_v, equal_nan=True) and cnt == cnt_v, ("re-hosted estimator differs from main.cpp", strat)

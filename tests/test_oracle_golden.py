@@ -100,6 +100,7 @@ def test_images_bit_identical_to_reference(scene_name, strategy, golden, oracle_
     img, cnt = oracle_of(scene_name).render(cam, strategy, spp=2, max_depth=4, flags=0, seed=11)
     assert np.array_equal(img, g["img%d" % strategy], equal_nan=True)
     assert [cnt["vertices"], cnt["primary_hits"]] == g["img%d_vertices" % strategy].tolist()
+    assert [cnt["rays"], cnt["light_rays"]] == g["img%d_rays" % strategy].tolist()  # same rays traced, one for one
     assert np.nanmax(img) > 0
 
 
