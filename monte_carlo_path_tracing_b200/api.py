@@ -15,7 +15,7 @@ import numpy as np
 from .scenes import Camera, SceneArrays
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libmcpt.so")
+LIB_PATH = os.environ.get("MCPT_LIB") or os.path.join(HERE, "libmcpt.so")  # MCPT_LIB: an A/B build variant (tools/)
 CSRC = os.path.join(HERE, "csrc")
 
 NEE_SPHERICAL, BRDF_ONLY, MIS, NEE_UNIFORM, MIS_SINGLE = 0, 1, 2, 3, 4

@@ -2,6 +2,8 @@
 #include <chrono>
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <memory>
@@ -17,7 +19,7 @@ void set_last_error(const std::string& msg) { g_last_error = msg; }
 
 namespace {
 struct BlobLayout {
-    size_t off_nodes, off_nodes4, off_tris, off_lnodes, off_ltris, off_pverts, off_pnorms, off_mats, off_lights, off_lsoa, off_lng64, off_larea64,
+    size_t off_nodes, off_nodes4, off_tris, off_nodes8, off_tris8, off_lnodes, off_ltris, off_pverts, off_pnorms, off_mats, off_lights, off_lsoa, off_lng64, off_larea64,
         off_crad64, off_class_begin, off_class_cdf, off_tri_cdf, off_ltree, off_ltree_leaf, total;
 };
 size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -171,8 +173,10 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
             }
             s->ltree = build_light_tree(s->positions.data(), s->light_prim.data(), s->geom_normals.data(), s->light_area.data(), lsum.data(), L);
         }
-        if (s->bvh.max_depth4 * 3 + 1 > (uint32_t)kBvhStackDepth)
-            throw Error(MCPT_ERR_INVALID, "scene BVH is too deep for the traversal stack (degenerate geometry?)");
+        if (s->bvh.max_depth4 * 3 + 1 > (uint32_t)kBvhStackDepth || s->bvh.max_depth + 1 > (uint32_t)kBvhStackDepth)
+            throw Error(MCPT_ERR_INVALID, "scene BVH is too deep for the traversal stack (the builders fall back to median splits well before: corrupt input?)");
+        if (s->lbvh.max_depth + 1 > (uint32_t)kBvhStackDepth)
+            throw Error(MCPT_ERR_INVALID, "light BVH is too deep for the traversal stack");
         s->extent = std::max({s->bvh.hi[0] - s->bvh.lo[0], s->bvh.hi[1] - s->bvh.lo[1], s->bvh.hi[2] - s->bvh.lo[2], 1e-30f});
 
         // pack the blob
@@ -182,6 +186,8 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
         B.off_nodes = place(s->bvh.nodes.size() * sizeof(BvhNode));
         B.off_nodes4 = place(s->bvh.nodes4.size() * sizeof(f4));
         B.off_tris = place(s->bvh.tris.size() * sizeof(f4));
+        B.off_nodes8 = place(s->bvh.nodes8.size() * sizeof(f4));
+        B.off_tris8 = place(s->bvh.tris8.size() * sizeof(f4));
         B.off_lnodes = place(s->lbvh.nodes.size() * sizeof(BvhNode));
         B.off_ltris = place(s->lbvh.tris.size() * sizeof(f4));
         B.off_pverts = place((size_t)P * 3 * 16);
@@ -206,6 +212,8 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
         std::memcpy(hb + B.off_nodes, s->bvh.nodes.data(), s->bvh.nodes.size() * sizeof(BvhNode));
         std::memcpy(hb + B.off_nodes4, s->bvh.nodes4.data(), s->bvh.nodes4.size() * sizeof(f4));
         std::memcpy(hb + B.off_tris, s->bvh.tris.data(), s->bvh.tris.size() * sizeof(f4));
+        std::memcpy(hb + B.off_nodes8, s->bvh.nodes8.data(), s->bvh.nodes8.size() * sizeof(f4));
+        std::memcpy(hb + B.off_tris8, s->bvh.tris8.data(), s->bvh.tris8.size() * sizeof(f4));
         std::memcpy(hb + B.off_lnodes, s->lbvh.nodes.data(), s->lbvh.nodes.size() * sizeof(BvhNode));
         std::memcpy(hb + B.off_ltris, s->lbvh.tris.data(), s->lbvh.tris.size() * sizeof(f4));
         if (L) {
@@ -284,6 +292,13 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
         DScene& d = s->d;
         d.nodes = (const float4*)(db + B.off_nodes); d.tris = (const float4*)(db + B.off_tris);
         d.nodes4 = (const float4*)(db + B.off_nodes4);
+        d.nodes8 = (const float4*)(db + B.off_nodes8); d.tris8 = (const float4*)(db + B.off_tris8);
+        // Which wide layout the trace kernels walk.  The compressed 8-wide nodes halve the bytes and loads per visit, which is
+        // what bounds incoherent rays through a large tree (L1 pipeline); on small scenes the byte decoding costs more ALU work
+        // than the loads it saves.  MCPT_BVH8=0/1 overrides the size rule (A/B measurements).
+        d.use8 = P >= 32768 ? 1 : 0;
+        if (const char* e = std::getenv("MCPT_BVH8")) d.use8 = std::atoi(e) != 0;
+        if (s->bvh.max_depth8 + 2 > (uint32_t)kBvh8StackDepth || s->bvh.nodes8.empty()) d.use8 = 0;
         d.lnodes = (const float4*)(db + B.off_lnodes); d.ltris = (const float4*)(db + B.off_ltris);
         d.pverts = (const float4*)(db + B.off_pverts); d.pnorms = (const float4*)(db + B.off_pnorms);
         d.mats = (const float4*)(db + B.off_mats); d.lights = (const float4*)(db + B.off_lights);
@@ -326,7 +341,7 @@ McptScene* scene_clone(const McptScene* src, int device)
         char* nb = (char*)raw->d_blob;
         auto rebase = [&](auto& ptr) { using T = std::remove_reference_t<decltype(ptr)>; ptr = (T)(nb + ((const char*)ptr - ob)); };
         DScene& d = raw->d;
-        rebase(d.nodes); rebase(d.nodes4); rebase(d.tris); rebase(d.lnodes); rebase(d.ltris); rebase(d.pverts); rebase(d.pnorms);
+        rebase(d.nodes); rebase(d.nodes4); rebase(d.tris); rebase(d.nodes8); rebase(d.tris8); rebase(d.lnodes); rebase(d.ltris); rebase(d.pverts); rebase(d.pnorms);
         rebase(d.mats); rebase(d.lights); rebase(d.lsoa); rebase(d.lng64); rebase(d.larea64); rebase(d.crad64);
         rebase(d.class_begin); rebase(d.class_cdf); rebase(d.tri_cdf); rebase(d.ltree); rebase(d.ltree_leaf);
         for (int i = 0; i < 6; i++) MCPT_CUDA(cudaEventCreate(&raw->ev[i]));
@@ -463,6 +478,79 @@ static uint32_t check_bvh(const mcpt::Bvh& b, const float* positions, uint32_t n
         }
         for (int32_t id : ids) if (seen4[id] != 1) errors++;
         if (b.max_depth4 > b.max_depth + 1 || b.max_depth4 * 3 + 1 > (uint32_t)kBvhStackDepth) errors++;
+    }
+    // the compressed 8-wide collapse (bvh.h, nodes8 / tris8): every prim in exactly one slot, every triangle inside its slot's
+    // DEQUANTISED box (p + q * 2^e evaluated in float, as the traversal does), every inner child's node box inside its slot's box
+    if (!ids.empty()) {
+        uint32_t cat[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        const uint32_t e_before = errors;
+        std::vector<uint32_t> seen8(num_prims, 0);
+        struct Item8 { uint32_t node; float lo[3], hi[3]; uint32_t depth; };
+        std::vector<Item8> st8;
+        st8.push_back(Item8{0, {-inf, -inf, -inf}, {inf, inf, inf}, 1});
+        uint32_t depth8 = 0;
+        while (!st8.empty()) {
+            const Item8 it = st8.back();
+            st8.pop_back();
+            depth8 = std::max(depth8, it.depth);
+            if ((size_t)it.node * 5 + 4 >= b.nodes8.size()) { errors++; continue; }
+            const f4* N = &b.nodes8[(size_t)it.node * 5];
+            uint32_t w[20];
+            std::memcpy(w, N, 80);
+            const float p[3] = {N[0].x, N[0].y, N[0].z};
+            float scale[3];
+            for (int a = 0; a < 3; a++) { const uint32_t e = ((w[3] >> (8 * a)) & 255u) << 23; std::memcpy(&scale[a], &e, 4); }
+            const uint32_t imask = w[3] >> 24, child_base = w[4], tri_base = w[5];
+            const uint8_t* meta = (const uint8_t*)&w[6];
+            const uint8_t* q = (const uint8_t*)&w[8];  // qlo.x[8] qlo.y[8] qlo.z[8] qhi.x[8] qhi.y[8] qhi.z[8]
+            for (int a = 0; a < 3; a++)
+                if (p[a] < it.lo[a] - 1e-3f * std::fabs(it.lo[a]) - 1e-6f) { errors++; cat[0]++; }
+            uint32_t inner_seen = 0;
+            for (int sl = 0; sl < 8; sl++) {
+                const uint32_t m = meta[sl];
+                if (m == 0) { if ((imask >> sl) & 1u) errors++; continue; }
+                float lo[3], hi[3];
+                for (int a = 0; a < 3; a++) { lo[a] = p[a] + (float)q[8 * a + sl] * scale[a]; hi[a] = p[a] + (float)q[24 + 8 * a + sl] * scale[a]; }
+                for (int a = 0; a < 3; a++)
+                    // a slot box may overhang the box its node got in the parent by one quantisation step (outward rounding on
+                    // a finer grid); what the traversal relies on is checked below: triangles lie inside EVERY ancestor's box
+                    if (lo[a] > hi[a] || hi[a] > it.hi[a] + 1.01f * scale[a] + 1e-3f * std::fabs(it.hi[a]) + 1e-6f) { errors++; cat[1]++; }
+                const bool inner = (m & 0x18u) == 0x18u;
+                if (inner != (((imask >> sl) & 1u) != 0)) errors++;
+                if (inner) {
+                    if ((m >> 5) != 1u || (m & 7u) != (uint32_t)sl) errors++;
+                    Item8 c;
+                    c.node = child_base + inner_seen++; c.depth = it.depth + 1;
+                    for (int a = 0; a < 3; a++) { c.lo[a] = std::max(lo[a], it.lo[a]); c.hi[a] = std::min(hi[a], it.hi[a]); }  // intersection of the ancestors' boxes
+                    st8.push_back(c);
+                } else {
+                    const uint32_t bits = m >> 5, off = m & 31u;
+                    const uint32_t cnt = bits == 1 ? 1 : bits == 3 ? 2 : bits == 7 ? 3 : 0;
+                    if (cnt == 0 || off + cnt > 24) { errors++; continue; }
+                    for (uint32_t i = 0; i < cnt; i++) {
+                        const size_t t = (size_t)tri_base + off + i;
+                        if (t * 3 + 2 >= b.tris8.size()) { errors++; continue; }
+                        int32_t prim;
+                        std::memcpy(&prim, &b.tris8[3 * t].w, 4);
+                        if (prim < 0 || (uint32_t)prim >= num_prims) { errors++; continue; }
+                        seen8[prim]++;
+                        for (int v = 0; v < 3; v++) {
+                            const f4& pt = b.tris8[3 * t + v];
+                            const float* src = positions + (size_t)prim * 9 + 3 * v;
+                            if (pt.x != src[0] || pt.y != src[1] || pt.z != src[2]) errors++;
+                            const float c[3] = {pt.x, pt.y, pt.z};
+                            for (int a = 0; a < 3; a++)
+                                if (c[a] < std::max(lo[a], it.lo[a]) || c[a] > std::min(hi[a], it.hi[a])) { errors++; cat[2]++; }
+                        }
+                    }
+                }
+            }
+        }
+        for (int32_t id : ids) if (seen8[id] != 1) { errors++; cat[3]++; }
+        if (depth8 != b.max_depth8 || b.max_depth8 + 2 > (uint32_t)kBvh8StackDepth) { errors++; cat[4]++; }
+        if (b.tris8.size() != b.tris.size()) { errors++; cat[5]++; }
+        if (errors != e_before && std::getenv("MCPT_DEBUG_BVH8"))
+            std::fprintf(stderr, "nodes8 check: origin %u, slot box %u, triangle outside %u, seen %u, depth %u (%u vs %u), size %u\n", cat[0], cat[1], cat[2], cat[3], cat[4], depth8, b.max_depth8, cat[5]);
     }
     uint32_t total = 0;
     for (uint32_t v : seen) total += v;

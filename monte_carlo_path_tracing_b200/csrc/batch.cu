@@ -75,24 +75,6 @@ __global__ void __launch_bounds__(kBlock) k_intersect(DScene s, size_t n, const 
     }
 }
 
-// The renderer's own traversal (k_extend: trace_stream over the 4-wide BVH, dynamic refill, majority-vote step)
-// on explicit rays, so that the FP32 parity tests exercise the production code path.
-__global__ void __launch_bounds__(kBlock) k_intersect_stream(DScene s, int n, const double* ro, const double* rd, const int* exclude,
-                                                             int* counter, int* prim, double* bgt)
-{
-    __shared__ int stack[kStackSm * kBlock];
-    trace_stream<false>(
-        s.nodes4, s.tris, s.tmin, n, counter, stack + threadIdx.x, kBlock,
-        [&](int i, f3& o, f3& d, int& ex, float& tmax, int& init_prim) {
-            o = to_f3(ld3(ro, i)); d = to_f3(ld3(rd, i));
-            ex = exclude ? exclude[i] : -1; tmax = 3.0e38f; init_prim = -1;
-        },
-        [&](int i, const Hit& h) {
-            prim[i] = h.prim;
-            bgt[3 * i] = h.prim >= 0 ? h.b : 0; bgt[3 * i + 1] = h.prim >= 0 ? h.g : 0; bgt[3 * i + 2] = h.prim >= 0 ? h.t : 0;
-        });
-}
-
 // ---- Phong -----------------------------------------------------------------------------------------------
 template <class T> __device__ __forceinline__ PhongMat<T> ldmat(const double* kd, const double* ks, const double* ns, size_t i)
 {
@@ -390,11 +372,14 @@ int mcpt_intersect_batch(McptScene* s, size_t n, const double* ro, const double*
             trace_rays_device(s, (int)n, org.p, dir.p, MCPT_LEAF_EXACT, hit.p);
             k_unpack_hits<<<grid_for(n), kBlock>>>(n, hit.p, dprim.p, dbgt.p);
         } else if (n && precision == 1 && !light_only) {
+            // the renderer's own trace kernel (render.cu: k_extend over the 4-wide BVH, or k_extend8 over the compressed 8-wide
+            // BVH, whichever this scene uses) on the FP32 roundings of the rays
             if (n > (size_t)1 << 30) throw Error(MCPT_ERR_INVALID, "too many rays in one batch");
-            DevBuf<int> cursor(1);
-            MCPT_CUDA(cudaMemset(cursor.p, 0, sizeof(int)));
-            k_intersect_stream<<<(unsigned)std::min<size_t>(grid_for(n), 148 * 8), kBlock>>>(s->d, (int)n, dro.p, drd.p, exclude ? dex.p : nullptr,
-                                                                                          cursor.p, dprim.p, dbgt.p);
+            DevBuf<float4> org(n), dir(n), hit(n);
+            k_pack_rays<<<grid_for(n), kBlock>>>(n, dro.p, drd.p, exclude ? dex.p : nullptr, org.p, dir.p);
+            MCPT_CUDA(cudaGetLastError());
+            trace_rays_device(s, (int)n, org.p, dir.p, MCPT_LEAF_FAST, hit.p);
+            k_unpack_hits<<<grid_for(n), kBlock>>>(n, hit.p, dprim.p, dbgt.p);
         } else if (n) k_intersect<<<grid_for(n), kBlock>>>(s->d, n, dro.p, drd.p, exclude ? dex.p : nullptr, light_only, precision, dprim.p, dbgt.p);
         finish();
         dprim.to_host(prim); dbgt.to_host(bgt);

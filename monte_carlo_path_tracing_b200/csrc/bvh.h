@@ -20,6 +20,19 @@
 //   q0 = lo.x[4], q1 = hi.x[4], q2 = lo.y[4], q3 = hi.y[4], q4 = lo.z[4], q5 = hi.z[4], q6 = child[4] (int bits,
 //   same inner / leaf encoding as above; unused slots hold kBvhNoChild and an inverted box).  Half the levels of the binary tree
 //   means half as many dependent node fetches per ray, which is what bounds incoherent rays in a deep BVH.
+//
+// nodes8 / tris8: the same tree once more as a COMPRESSED 8-WIDE BVH for large scenes (layout after Ylitie, Karras, Laine,
+// "Efficient Incoherent Ray Traversal on GPUs Through Compressed Wide BVHs", HPG 2017; restated here from the paper):
+// 80 B per node, five 16-byte vectors, against 2 x 112 B for the two levels of 4-wide nodes it replaces --
+//   v0 = origin p (3 floats) | ex, ey, ez (IEEE exponent bytes of the per-axis quantisation step), imask (slots that hold an inner node)
+//   v1 = child_base (index of the first inner child in nodes8), tri_base (first triangle of this node in tris8),
+//        meta[8]: per slot  0 = empty,  inner: 0b001_11sss (low 5 bits = 24 + slot),  leaf: unary triangle count in the top
+//        3 bits (0b001, 0b011, 0b111 = 1, 2, 3 triangles) | offset of its first triangle from tri_base in the low 5 (0..23)
+//   v2 = qlo.x[8] qlo.y[8],  v3 = qlo.z[8] qhi.x[8],  v4 = qhi.y[8] qhi.z[8]   child boxes as bytes: p + q * 2^e, rounded outward
+// Inner children are stored consecutively from child_base in slot order.  A child sits in the slot whose sign pattern
+// (bit a set = towards -axis a) best matches its offset from the node centre, so a ray with direction-sign octant `oct`
+// meets the slots in roughly front-to-back order when it takes them by descending (slot ^ oct) -- no distance sort.
+// tris8 holds every triangle once more, grouped by node8 (a node's <= 24 leaf triangles are contiguous), 48 B each.
 #pragma once
 #include <cstdint>
 #include <vector>
@@ -35,7 +48,9 @@ struct Bvh {
     std::vector<BvhNode> nodes;  // nodes[0] is the root (always an inner node)
     std::vector<f4> nodes4;      // 7 per 4-wide node; nodes4[0..6] is the root
     std::vector<f4> tris;        // 3 per triangle, leaf order
-    uint32_t num_leaves = 0, max_depth = 0, max_depth4 = 0;
+    std::vector<f4> nodes8;      // 5 per compressed 8-wide node; nodes8[0..4] is the root
+    std::vector<f4> tris8;       // 3 per triangle, grouped by 8-wide node
+    uint32_t num_leaves = 0, max_depth = 0, max_depth4 = 0, max_depth8 = 0;
     double sah_cost = 0;
     float lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};  // bounds of everything inside
 };
@@ -43,6 +58,8 @@ struct Bvh {
 constexpr int kBvhMaxLeaf = 4;
 constexpr int32_t kBvhNoChild = INT32_MIN;  // child word of an unused nodes4 slot (its box is inverted, too)
 constexpr int kBvhStackDepth = 64;  // traversal stack entries; the builder falls back to median splits to stay below
+constexpr int kBvh8StackDepth = 32; // node-group entries of the 8-wide traversal: at most one pending group per level
+static_assert(kBvhMaxLeaf <= 6, "emit_wide8 splits a leaf into two slots of at most 3 triangles");
 
 // positions: [P][3][3] floats; prims: the subset to build over (ids kept as triangle payload).
 Bvh build_bvh(const float* positions, const int32_t* prims, size_t count);

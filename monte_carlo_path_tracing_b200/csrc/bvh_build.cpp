@@ -152,6 +152,160 @@ void emit_wide(const std::vector<TmpNode>& tmp, int32_t root, float tiny, Bvh& o
     }
 }
 
+// Collapse the binary tree into compressed 8-wide nodes (bvh.h, nodes8 / tris8).
+void emit_wide8(const float* positions, const std::vector<TmpNode>& tmp, const std::vector<int32_t>& order, int32_t root, float tiny, Bvh& out)
+{
+    struct Kid { Box box; int32_t tmp_idx; uint32_t first, count; bool leaf; };  // leaf: triangles order[first .. first + count), count <= 3
+    auto tri_box = [&](uint32_t first, uint32_t count) {
+        Box b; b.reset();
+        for (uint32_t i = first; i < first + count; i++) for (int k = 0; k < 3; k++) b.grow(positions + (size_t)order[i] * 9 + 3 * k);
+        return b;
+    };
+    auto make_kid = [&](int32_t t) {
+        Kid k; k.box = tmp[t].box; k.tmp_idx = t; k.first = tmp[t].first; k.count = tmp[t].count; k.leaf = tmp[t].left < 0;
+        return k;
+    };
+    struct Item { int32_t tmp_idx, out_idx; uint32_t depth; };
+    std::vector<Item> todo;
+    auto alloc = [&](int n) { int32_t i = (int32_t)(out.nodes8.size() / 5); out.nodes8.resize(out.nodes8.size() + 5 * (size_t)n, f4{0, 0, 0, 0}); return i; };
+    todo.push_back({root, alloc(1), 1});
+    while (!todo.empty()) {
+        const Item it = todo.back();
+        todo.pop_back();
+        out.max_depth8 = std::max(out.max_depth8, it.depth);
+        Kid kids[8];
+        int nk = 0;
+        if (tmp[it.tmp_idx].left < 0) kids[nk++] = make_kid(it.tmp_idx);  // lone leaf root
+        else { kids[nk++] = make_kid(tmp[it.tmp_idx].left); kids[nk++] = make_kid(tmp[it.tmp_idx].right); }
+        // open the inner child with the largest surface area while eight slots still hold everything; a leaf of more than 3
+        // triangles needs two slots (it is split in two below: a slot addresses at most 3 triangles)
+        auto need = [&](int32_t t) { return (tmp[t].left < 0 && tmp[t].count > 3) ? 2 : 1; };
+        int total = 0;
+        for (int k = 0; k < nk; k++) total += need(kids[k].tmp_idx);
+        for (;;) {
+            int best = -1;
+            float best_area = -1.f;
+            for (int k = 0; k < nk; k++) {
+                if (kids[k].leaf) continue;
+                const int after = total - 1 + need(tmp[kids[k].tmp_idx].left) + need(tmp[kids[k].tmp_idx].right);
+                if (after <= 8 && kids[k].box.half_area() > best_area) { best = k; best_area = kids[k].box.half_area(); }
+            }
+            if (best < 0) break;
+            const int32_t open = kids[best].tmp_idx;
+            total += need(tmp[open].left) + need(tmp[open].right) - 1;
+            kids[best] = make_kid(tmp[open].left);
+            kids[nk++] = make_kid(tmp[open].right);
+        }
+        for (int k = 0, n0 = nk; k < n0; k++) {
+            if (!kids[k].leaf || kids[k].count <= 3) continue;
+            const Kid whole = kids[k];
+            const uint32_t h = whole.count / 2;
+            Kid a = whole, b = whole;
+            a.count = h; a.box = tri_box(a.first, a.count);
+            b.first = whole.first + h; b.count = whole.count - h; b.box = tri_box(b.first, b.count);
+            kids[k] = a; kids[nk++] = b;
+        }
+        // node box, origin, per-axis exponent
+        Box nb; nb.reset();
+        Box padded[8];
+        for (int k = 0; k < nk; k++) {
+            float lo[3], hi[3];
+            pad_box(kids[k].box, tiny, lo, hi);
+            for (int a = 0; a < 3; a++) { padded[k].lo[a] = lo[a]; padded[k].hi[a] = hi[a]; }
+            nb.grow(padded[k]);
+        }
+        int ex[3];
+        float scale[3];
+        for (int a = 0; a < 3; a++) {
+            const float ext = std::max(nb.hi[a] - nb.lo[a], 1e-30f);
+            int e = (int)std::ceil(std::log2(ext / 255.0f));
+            // q = ceil((hi - p) / 2^e) must fit 255 with the rounding of the division
+            while (std::ceil((nb.hi[a] - nb.lo[a]) / std::ldexp(1.0f, e)) > 255.0f) e++;
+            e = std::max(-126, std::min(127, e));
+            ex[a] = e + 127;
+            scale[a] = std::ldexp(1.0f, e);
+        }
+        // slots: greedy assignment of children to the sign octants of their offset from the node centre
+        int slot_of[8], kid_in[8];
+        for (int k = 0; k < 8; k++) { slot_of[k] = -1; kid_in[k] = -1; }
+        {
+            float c0[3];
+            for (int a = 0; a < 3; a++) c0[a] = 0.5f * (nb.lo[a] + nb.hi[a]);
+            float cost[8][8];
+            for (int k = 0; k < nk; k++)
+                for (int sl = 0; sl < 8; sl++) {
+                    float d = 0.f;
+                    for (int a = 0; a < 3; a++) {
+                        const float off = 0.5f * (kids[k].box.lo[a] + kids[k].box.hi[a]) - c0[a];
+                        d += ((sl >> a) & 1) ? -off : off;
+                    }
+                    cost[k][sl] = d;
+                }
+            for (int n = 0; n < nk; n++) {
+                int bk = -1, bs = -1;
+                float bc = -std::numeric_limits<float>::infinity();
+                for (int k = 0; k < nk; k++) {
+                    if (slot_of[k] >= 0) continue;
+                    for (int sl = 0; sl < 8; sl++)
+                        if (kid_in[sl] < 0 && cost[k][sl] > bc) { bc = cost[k][sl]; bk = k; bs = sl; }
+                }
+                slot_of[bk] = bs; kid_in[bs] = bk;
+            }
+        }
+        // children: inner ones get consecutive nodes in slot order; leaf triangles are appended to tris8
+        uint32_t imask = 0;
+        int n_inner = 0;
+        for (int sl = 0; sl < 8; sl++) if (kid_in[sl] >= 0 && !kids[kid_in[sl]].leaf) { imask |= 1u << sl; n_inner++; }
+        const int32_t child_base = n_inner ? alloc(n_inner) : 0;
+        const uint32_t tri_base = (uint32_t)(out.tris8.size() / 3);
+        uint8_t meta[8], q[6][8];
+        int inner_seen = 0;
+        uint32_t tri_off = 0;
+        for (int sl = 0; sl < 8; sl++) {
+            meta[sl] = 0;
+            for (int r = 0; r < 6; r++) q[r][sl] = r < 3 ? 255 : 0;  // inverted box: never entered
+            const int k = kid_in[sl];
+            if (k < 0) continue;
+            for (int a = 0; a < 3; a++) {
+                float ql = std::floor((padded[k].lo[a] - nb.lo[a]) / scale[a]);
+                float qh = std::ceil((padded[k].hi[a] - nb.lo[a]) / scale[a]);
+                ql = std::max(0.f, std::min(255.f, ql)); qh = std::max(0.f, std::min(255.f, qh));
+                // outward in the arithmetic the traversal uses (p + q * 2^e in float)
+                while (ql > 0.f && nb.lo[a] + ql * scale[a] > padded[k].lo[a]) ql -= 1.f;
+                while (qh < 255.f && nb.lo[a] + qh * scale[a] < padded[k].hi[a]) qh += 1.f;
+                q[a][sl] = (uint8_t)ql; q[3 + a][sl] = (uint8_t)qh;
+            }
+            if (kids[k].leaf) {
+                meta[sl] = (uint8_t)((((1u << kids[k].count) - 1u) << 5) | tri_off);
+                for (uint32_t i = kids[k].first; i < kids[k].first + kids[k].count; i++) {
+                    const int32_t prim = order[i];
+                    const float* v = positions + (size_t)prim * 9;
+                    f4 a = {v[0], v[1], v[2], 0.f};
+                    std::memcpy(&a.w, &prim, 4);
+                    out.tris8.push_back(a);
+                    out.tris8.push_back(f4{v[3], v[4], v[5], 0.f});
+                    out.tris8.push_back(f4{v[6], v[7], v[8], 0.f});
+                }
+                tri_off += kids[k].count;
+            } else {
+                meta[sl] = (uint8_t)((1u << 5) | (24u + (uint32_t)sl));
+                todo.push_back({kids[k].tmp_idx, child_base + inner_seen, it.depth + 1});
+                inner_seen++;
+            }
+        }
+        auto pack4 = [](const uint8_t* b) { uint32_t u = (uint32_t)b[0] | ((uint32_t)b[1] << 8) | ((uint32_t)b[2] << 16) | ((uint32_t)b[3] << 24); float f; std::memcpy(&f, &u, 4); return f; };
+        const uint8_t eb[4] = {(uint8_t)ex[0], (uint8_t)ex[1], (uint8_t)ex[2], (uint8_t)imask};
+        float cb, tb;
+        std::memcpy(&cb, &child_base, 4); std::memcpy(&tb, &tri_base, 4);
+        f4* N = &out.nodes8[(size_t)it.out_idx * 5];
+        N[0] = f4{nb.lo[0], nb.lo[1], nb.lo[2], pack4(eb)};
+        N[1] = f4{cb, tb, pack4(meta), pack4(meta + 4)};
+        N[2] = f4{pack4(q[0]), pack4(q[0] + 4), pack4(q[1]), pack4(q[1] + 4)};
+        N[3] = f4{pack4(q[2]), pack4(q[2] + 4), pack4(q[3]), pack4(q[3] + 4)};
+        N[4] = f4{pack4(q[4]), pack4(q[4] + 4), pack4(q[5]), pack4(q[5] + 4)};
+    }
+}
+
 }  // namespace
 
 // Tree -> the two traversal layouts of bvh.h.  Walks the tree from the root, so nodes a builder left unreachable
@@ -204,6 +358,7 @@ void emit_bvh(const float* positions, const BvhTree& T, Bvh& out)
         out.num_leaves = 1;
         out.sah_cost = kCostTrav + tmp[root].count * kCostTri;
         emit_wide(tmp, root, tiny, out);
+        emit_wide8(positions, tmp, T.order, root, tiny, out);
         return;
     }
     const double root_area = std::max(tmp[root].box.half_area(), 1e-30f);
@@ -239,6 +394,7 @@ void emit_bvh(const float* positions, const BvhTree& T, Bvh& out)
     }
     out.sah_cost = sah;
     emit_wide(tmp, root, tiny, out);
+    emit_wide8(positions, tmp, T.order, root, tiny, out);
 }
 
 bool build_tree_host(const float* positions, const int32_t* prims, size_t count, BvhTree& T)

@@ -944,6 +944,46 @@ __global__ void __launch_bounds__(kBlk) k_extend(DScene s, const float4* __restr
         [&](int i, const Hit& h) { hit[i] = make_float4(__int_as_float(h.prim), h.b, h.g, h.t); });
 }
 
+// the same over the compressed 8-wide BVH (traverse.cuh: trace_stream8), chosen per scene (DScene.use8)
+__global__ void __launch_bounds__(kBlk) k_extend8(DScene s, const float4* __restrict__ org, const float4* __restrict__ dir,
+                                                  const int* __restrict__ n_ptr, int* counter, float4* hit)
+{
+    __shared__ uint2 stack[kStack8Sm * kBlk];
+    const int n = *n_ptr;
+    trace_stream8<false>(
+        s.nodes8, s.tris8, s.tmin, n, counter, stack + threadIdx.x, kBlk,
+        [&](int i, f3& o, f3& d, int& exclude, float& tmax, int& init_prim) {
+            const float4 qo = org[i], qd = dir[i];
+            o = to_f3(qo); d = to_f3(qd);
+            exclude = __float_as_int(qo.w); tmax = 3.0e38f; init_prim = -1;
+        },
+        [&](int i, const Hit& h) { hit[i] = make_float4(__int_as_float(h.prim), h.b, h.g, h.t); });
+}
+
+__global__ void __launch_bounds__(kBlk) k_shadow8(DScene s, const ShadowQueue sq, int* counter, float4* Lacc, unsigned long long* counters)
+{
+    __shared__ uint2 stack[kStack8Sm * kBlk];
+    const int n = *sq.count;
+    if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(counters + CNT_SHADOW, (unsigned long long)n);
+    trace_stream8<true>(
+        s.nodes8, s.tris8, s.tmin, n, counter, stack + threadIdx.x, kBlk,
+        [&](int i, f3& o, f3& d, int& exclude, float& tmax, int& init_prim) {
+            const float4 qo = sq.org[i], qd = sq.dir[i];
+            const int2 id = sq.ids[i];
+            o = to_f3(qo); d = to_f3(qd);
+            exclude = id.x; tmax = qo.w; init_prim = id.y;
+        },
+        [&](int i, const Hit& h) {
+            if (h.prim == sq.ids[i].y) {
+                const float4 c = sq.ctr[i];
+                const int slot = __float_as_int(sq.dir[i].w);
+                float4 L = Lacc[slot];
+                L.x += c.x; L.y += c.y; L.z += c.z;
+                Lacc[slot] = L;
+            }
+        });
+}
+
 // k_shadow: the visibility test of main.cpp:309-311 -- "the closest hit along wl IS the sampled light triangle" -- as
 // an any-hit search for something that beats the light point under the closest-hit order; survivors add their
 // pending contribution to the slot's accumulator (each slot has at most one visibility ray per bounce).
@@ -1045,19 +1085,25 @@ __global__ void k_runsum(const float4* __restrict__ contrib, int n, float4* Lacc
     }
 }
 
-// film accumulation (main.cpp:566,575-576,582): the pixel's owner thread sums its slots of this pass
-__global__ void k_accumulate(const float4* __restrict__ Lacc, int npix, int batch_spp, float4* image, int first_pass)
+// film accumulation (main.cpp:566,575-576,582): the pixel's owner thread adds its samples of this pass to the running
+// sum ONE BY ONE, in sample order -- the reference's `sum = sum + I` -- with Kahan compensation carried in `comp` from
+// pass to pass.  The sequence of operations does not depend on where the pass boundaries fall, so a film is bit-identical
+// for every batch_spp (and across an overflow retry), and 1024+ spp lose nothing to FP32 accumulation.
+__global__ void k_accumulate(const float4* __restrict__ Lacc, int npix, int batch_spp, float4* image, float4* comp, int first_pass)
 {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= npix) return;
-    float sx = 0.f, sy = 0.f, sz = 0.f;
+    float4 s = first_pass ? make_float4(0.f, 0.f, 0.f, 0.f) : image[p];
+    float4 c = first_pass ? make_float4(0.f, 0.f, 0.f, 0.f) : comp[p];
     for (int k = 0; k < batch_spp; k++) {
         const float4 v = Lacc[(size_t)k * npix + p];
-        sx += v.x; sy += v.y; sz += v.z;
+        float y, t;
+        y = __fsub_rn(v.x, c.x); t = __fadd_rn(s.x, y); c.x = __fsub_rn(__fsub_rn(t, s.x), y); s.x = t;
+        y = __fsub_rn(v.y, c.y); t = __fadd_rn(s.y, y); c.y = __fsub_rn(__fsub_rn(t, s.y), y); s.y = t;
+        y = __fsub_rn(v.z, c.z); t = __fadd_rn(s.z, y); c.z = __fsub_rn(__fsub_rn(t, s.z), y); s.z = t;
     }
-    float4 o = first_pass ? make_float4(0.f, 0.f, 0.f, 0.f) : image[p];
-    o.x += sx; o.y += sy; o.z += sz;
-    image[p] = o;
+    image[p] = s;
+    comp[p] = c;
 }
 
 __global__ void k_finalize(const float4* __restrict__ image, int npix, float inv_spp, int accumulate, float* out_rgb)
@@ -1153,6 +1199,7 @@ void trace_rays_device(McptScene* scene, int n, const float4* d_org, const float
     if (e == cudaSuccess) {
         const int grid = std::min(148 * 8, (n + kBlk - 1) / kBlk);
         if (leaf_mode == MCPT_LEAF_EXACT) k_extend_exact<<<grid, kBlk>>>(scene->d, d_org, d_dir, d_small, d_hit);
+        else if (scene->d.use8) k_extend8<<<grid, kBlk>>>(scene->d, d_org, d_dir, d_small, d_small + 1, d_hit);
         else k_extend<<<grid, kBlk>>>(scene->d, d_org, d_dir, d_small, d_small + 1, d_hit);
         e = cudaGetLastError();
         if (e == cudaSuccess) e = cudaDeviceSynchronize();
@@ -1181,6 +1228,7 @@ void visibility_device(McptScene* scene, int n, const float4* d_org, const float
         k_vis_prepare<<<(n + 255) / 256, 256>>>(scene->d, n, d_org, d_dir, d_ids, exact, sq, Lacc, d_visible);
         const int grid = std::min(148 * 8, (n + kBlk - 1) / kBlk);
         if (exact) k_shadow_exact<<<grid, kBlk>>>(scene->d, sq, Lacc, (unsigned long long*)(small + 8));
+        else if (scene->d.use8) k_shadow8<<<grid, kBlk>>>(scene->d, sq, small + 1, Lacc, (unsigned long long*)(small + 8));
         else k_shadow<<<grid, kBlk>>>(scene->d, sq, small + 1, Lacc, (unsigned long long*)(small + 8));
         k_vis_finish<<<(n + 255) / 256, 256>>>(n, Lacc, d_visible);
         e = cudaGetLastError();
@@ -1219,7 +1267,7 @@ struct QueueOverflow { int batch; };  // thrown by render_wavefront when the MIS
 
 // One attempt at the whole call.  tree_factor: capacity of the MIS path-tree queues in entries per path slot (x 1/100).
 void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderParams* prm, float* d_out_rgb, cudaStream_t st,
-                      McptStats* stats, int tree_factor)
+                      McptStats* stats, int tree_factor, size_t pretend_cap)
 {
     const bool dbg_timing = std::getenv("MCPT_DEBUG_TIMING") != nullptr;
     const auto dbg_t0 = std::chrono::steady_clock::now();
@@ -1258,7 +1306,7 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
     batch = std::min(batch, prm->spp);
     const size_t slots = npix * (size_t)batch;
     if (slots > (1u << 30)) throw Error(MCPT_ERR_INVALID, "batch_spp * pixels too large");
-    const size_t cap = tree ? std::max(slots * (size_t)tree_factor / 100, slots + 1) : slots;
+    const size_t cap = tree ? std::max(slots * (size_t)tree_factor / 100, slots + 1) : slots;  // never below the first bounce's own queue
     if (cap > (1u << 30)) throw Error(MCPT_ERR_INVALID, "batch_spp * pixels too large for the path-tree queue");
     const size_t chunks = (cap + kChunk - 1) / kChunk + 1;
     const bool single = prm->strategy == MCPT_MIS_SINGLE;
@@ -1275,7 +1323,7 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
         o_q[q][0] = place(qn[q] * 16); o_q[q][1] = place(qn[q] * 16); o_q[q][2] = place(qn[q] * 16);
         o_q[q][3] = place(tree ? qn[q] * 8 : 16);
     }
-    const size_t o_lacc = place(slots * 16), o_contrib = place(tree ? cap * 16 : 16), o_ph = place(npix * 16), o_img = place(npix * 16);
+    const size_t o_lacc = place(slots * 16), o_contrib = place(tree ? cap * 16 : 16), o_ph = place(npix * 16), o_img = place(npix * 16), o_comp = place(npix * 16);
     const size_t groups = (chunks + kGroup - 1) / kGroup;
     const size_t o_counts = place(chunks * 4), o_small = place(256 + groups * 4);
     const size_t o_sel = place(sph ? slots * 8 : 16), o_wsum = place(sph ? npix * 4 : 16), o_sel4 = place(sph ? cap * 16 : 16);
@@ -1301,6 +1349,7 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
     float4* contrib = (float4*)(base + o_contrib);
     float4* primary = (float4*)(base + o_ph);
     float4* image = (float4*)(base + o_img);
+    float4* comp = (float4*)(base + o_comp);
     int* counts = (int*)(base + o_counts);
     int2* sel = (int2*)(base + o_sel);
     float* wsum_pix = (float*)(base + o_wsum);
@@ -1345,9 +1394,15 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
               : prm->strategy == MCPT_MIS_SINGLE  ? bounce_blocks_per_sm<MCPT_MIS_SINGLE>()
                                                   : bounce_blocks_per_sm<MCPT_NEE_UNIFORM>();
     const int max_grid = sms * bps;
+    const bool use8 = scene->d.use8 != 0;
     int ebps = 1, sbps = 1;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ebps, k_extend, kBlk, 0);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sbps, k_shadow, kBlk, 0);
+    if (use8) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ebps, k_extend8, kBlk, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sbps, k_shadow8, kBlk, 0);
+    } else {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ebps, k_extend, kBlk, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sbps, k_shadow, kBlk, 0);
+    }
     const int ext_grid = sms * std::max(1, ebps), sh_grid = sms * std::max(1, sbps);
     int lbps = 1;
     if (prm->strategy == MCPT_MIS) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&lbps, k_lightsel<MCPT_MIS>, kBlk, 0);
@@ -1401,6 +1456,7 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
             k_raygen<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(dc, (int)npix, count, a.sample_base, prm->seed, Q[0], tree ? 1 : 0, Lacc, d_count);
             MCPT_CUDA(cudaMemsetAsync(d_ticket, 0, 32, st));
             if (exact) k_extend_exact<<<std::min(ext_grid, (count + kBlk - 1) / kBlk), kBlk, 0, st>>>(scene->d, Q[0].org, Q[0].dir, d_count, hit);
+            else if (use8) k_extend8<<<std::min(ext_grid, (count + kBlk - 1) / kBlk), kBlk, 0, st>>>(scene->d, Q[0].org, Q[0].dir, d_count, d_ext_cursor, hit);
             else k_extend<<<std::min(ext_grid, (count + kBlk - 1) / kBlk), kBlk, 0, st>>>(scene->d, Q[0].org, Q[0].dir, d_count, d_ext_cursor, hit);
             MCPT_CUDA(cudaGetLastError());
             S.kernel_launches += 2;
@@ -1429,14 +1485,16 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
             S.elements += (uint64_t)count;
             const bool last = prm->max_depth > 0 && bounce + 1 >= prm->max_depth + 1;  // vertices deeper than max_depth never spawn
             if (!last) {
-                k_gather<<<ngroups, 256, 0, st>>>(Q[1], Q[0], counts, d_groupsum, nch, (int)stride, (int)cap, tree ? 1 : 0, d_count, d_counters);
+                k_gather<<<ngroups, 256, 0, st>>>(Q[1], Q[0], counts, d_groupsum, nch, (int)stride, (int)(pretend_cap ? std::min(cap, pretend_cap) : cap), tree ? 1 : 0, d_count, d_counters);
                 const int eg = std::min(ext_grid, (count * (tree ? 2 : 1) + kBlk - 1) / kBlk);
                 if (exact) k_extend_exact<<<eg, kBlk, 0, st>>>(scene->d, Q[0].org, Q[0].dir, d_count, hit);
+                else if (use8) k_extend8<<<eg, kBlk, 0, st>>>(scene->d, Q[0].org, Q[0].dir, d_count, d_ext_cursor, hit);
                 else k_extend<<<eg, kBlk, 0, st>>>(scene->d, Q[0].org, Q[0].dir, d_count, d_ext_cursor, hit);
                 S.kernel_launches += 2;
             }
             if (nee) {
                 if (exact) k_shadow_exact<<<std::min(sh_grid, (count + kBlk - 1) / kBlk), kBlk, 0, st>>>(scene->d, SQ, Lacc, d_counters);
+                else if (use8) k_shadow8<<<std::min(sh_grid, (count + kBlk - 1) / kBlk), kBlk, 0, st>>>(scene->d, SQ, d_sh_cursor, Lacc, d_counters);
                 else k_shadow<<<std::min(sh_grid, (count + kBlk - 1) / kBlk), kBlk, 0, st>>>(scene->d, SQ, d_sh_cursor, Lacc, d_counters);
                 S.kernel_launches++;
             }
@@ -1465,7 +1523,7 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
             if (count < 0) throw QueueOverflow{batch};  // k_gather: the tree outgrew the queue; nothing of this call has reached d_out_rgb yet
             S.rays_closest += (uint64_t)count;
         }
-        k_accumulate<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(Lacc, (int)npix, b, image, pass == 0);
+        k_accumulate<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(Lacc, (int)npix, b, image, comp, pass == 0);
         S.kernel_launches++;
         done += b;
         pass++;
@@ -1500,18 +1558,22 @@ void render_device(McptScene* scene, const McptCamera* cam, const McptRenderPara
     if (prm->flags & MCPT_PARITY_FP64) { render_parity_device(scene, cam, prm, d_out_rgb, st, stats); return; }
     // shade_with_mis grows a path TREE (F6).  Its queues hold 3 entries per path slot, which the reference scenes never
     // fill; a scene that does (light samples mostly occluded, so both children of most vertices live on) is retried here
-    // with half the pass and twice the room per slot -- same memory, and bit-identical films, because nothing depends on
-    // the pass size.  MCPT_TREE_FACTOR (percent, testing only) sets the first attempt's room.
+    // with half the pass and twice the room per slot -- same memory, and a bit-identical film, because nothing depends on
+    // the pass size (per-slot radiance is computed inside a pass, the film adds the samples one by one in sample order).  MCPT_TREE_FACTOR (percent, testing only) sets the first attempt's room.
     int factor = 300;
     if (const char* e = std::getenv("MCPT_TREE_FACTOR")) { const int v = std::atoi(e); if (v > 100) factor = v; }
+    // testing only: pretend the queue of the FIRST attempt holds no more than this many entries, so that the retry path runs
+    size_t pretend = 0;
+    if (const char* e = std::getenv("MCPT_TEST_OVERFLOW_ABOVE")) { const long v = std::atol(e); if (v > 0) pretend = (size_t)v; }
     McptRenderParams p = *prm;
     for (;;) {
         try {
-            render_wavefront(scene, cam, &p, d_out_rgb, st, stats, factor);
+            render_wavefront(scene, cam, &p, d_out_rgb, st, stats, factor, pretend);
             return;
         } catch (const QueueOverflow& q) {
             if (factor >= 9600) throw Error(MCPT_ERR_QUEUE_OVERFLOW, "MIS path tree outgrew the ray queue at 96 entries per path slot");
             factor *= 2;
+            pretend = 0;
             p.batch_spp = std::max(1, q.batch / 2);
         }
     }

@@ -3,6 +3,8 @@
 // HBM layout (everything 16-byte vectors, read through the read-only path):
 //   nodes / tris, lnodes / ltris : the two BVHs of bvh.h (whole scene; emissive triangles only)
 //   nodes4 [N4][7] float4 : the scene BVH collapsed to 4-wide nodes (bvh.h) for k_extend / k_shadow
+//   nodes8 [N8][5] float4, tris8 [P][3] float4 : the same tree as a compressed 8-wide BVH (80 B nodes, byte boxes) with its
+//                          own node-grouped copy of the triangles; the trace kernels use it for large scenes (use8)
 //   pverts [P][3] float4 : prim-order vertices; v0.w = material id bits, v1.w = light index bits (-1 = not a light)
 //   pnorms [P][3] float4 : prim-order vertex normals (shading normal = normalised barycentric blend,
 //                          main.cpp:273-274)
@@ -25,6 +27,8 @@ struct DScene {
     const float4* nodes;
     const float4* nodes4;  // the scene BVH collapsed to 4-wide nodes (bvh.h), what the trace kernels traverse
     const float4* tris;
+    const float4* nodes8;  // compressed 8-wide BVH of the scene (bvh.h), traversed instead of nodes4 when use8 != 0
+    const float4* tris8;   // the triangles once more, grouped by 8-wide node
     const float4* lnodes;
     const float4* ltris;
     const float4* pverts;
@@ -41,6 +45,7 @@ struct DScene {
     const float4* ltree;        // [2L-1][3] light hierarchy nodes (light_tree.h), node 0 = root
     const int32_t* ltree_leaf;  // [L] leaf node of each light
     int32_t P, L, C, M, Lpad;
+    int32_t use8;  // trace kernels walk nodes8 / tris8 (large scenes) instead of nodes4 / tris
     float tmin;  // FP32 leaf test: reject t < tmin (scene-scale aware stand-in for the reference's 1e-8)
 };
 

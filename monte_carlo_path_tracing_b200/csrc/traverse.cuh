@@ -80,16 +80,19 @@ struct TStack {
     int sp;
     int local[kStackLocal];
     __device__ __forceinline__ void init(int* base, int stride_) { sm = base; stride = stride_; sp = 0; }
+    // A tree deeper than the stack is refused at scene creation (api.cu); should an entry ever not fit, it is DROPPED --
+    // the traversal then ends early instead of popping a bogus node and walking the tree again from the root.
     __device__ __forceinline__ void push(int v)
     {
         if (sp < kStackSm) sm[sp * stride] = v;
         else if (sp < kBvhStackDepth) local[sp - kStackSm] = v;
+        else return;
         sp++;
     }
     __device__ __forceinline__ int pop()
     {
         sp--;
-        return sp < kStackSm ? sm[sp * stride] : (sp < kBvhStackDepth ? local[sp - kStackSm] : 0);
+        return sp < kStackSm ? sm[sp * stride] : local[sp - kStackSm];
     }
 };
 
@@ -347,6 +350,172 @@ __device__ __forceinline__ void trace_stream(const float4* __restrict__ nodes, c
                     if (st.sp == 0) done = true;
                     else node = st.pop();
                 }
+            }
+            if (done) {
+                store(idx, best);
+                active = false;
+            }
+            const unsigned m = __ballot_sync(full, active);
+            if (m == 0u || (more && __popc(m) < kRefill)) break;
+        }
+    }
+}
+
+// ---- compressed 8-wide BVH (bvh.h: nodes8 / tris8): the same ray-stream tracer for large scenes ---------------------------
+// One node visit = five 16-byte loads (80 B) for eight children, against 2 x seven for the two levels of 4-wide nodes it
+// replaces: the trace kernels on the 1 M-triangle soup were bound by the L1 pipeline (98.8 % busy: every divergent LDG.128
+// of a warp costs 32 wavefronts), so bytes and loads per visit are what counts.  Child boxes are bytes on the node's own
+// grid (p + q * 2^e); the slab test runs on them directly: t = q * (2^e / d) + (p - o) / d, one FMA per plane after the
+// byte-to-float conversion.  Children are visited in octant order (slot ^ ray octant, highest first) taken straight from
+// the bit positions of the hit mask -- no distance sort.  State per lane: a node group G = (first child node, hit bits
+// 24..31 | inner-child mask) and a triangle group T = (first triangle, hit bits 0..23); the stack holds node groups.
+constexpr int kStack8Sm = 6;
+struct TStack8 {
+    uint2* sm;
+    int stride, sp;
+    uint2 local[kBvh8StackDepth - kStack8Sm];
+    __device__ __forceinline__ void init(uint2* base, int stride_) { sm = base; stride = stride_; sp = 0; }
+    __device__ __forceinline__ void push(uint2 v)
+    {
+        if (sp < kStack8Sm) sm[sp * stride] = v;
+        else if (sp < kBvh8StackDepth) local[sp - kStack8Sm] = v;
+        else return;
+        sp++;
+    }
+    __device__ __forceinline__ uint2 pop()
+    {
+        sp--;
+        return sp < kStack8Sm ? sm[sp * stride] : local[sp - kStack8Sm];
+    }
+};
+
+// byte i of w as a float.  MCPT_BYTE_MAGIC: one PRMT drops the byte into the mantissa of 2^23 and one FADD takes 2^23
+// off again (both full rate) instead of the I2F conversion.
+#ifndef MCPT_BYTE_MAGIC
+#define MCPT_BYTE_MAGIC 0
+#endif
+__device__ __forceinline__ float byte_f(unsigned w, int i)
+{
+#if MCPT_BYTE_MAGIC
+    return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7650u + (unsigned)i)) - 8388608.0f;
+#else
+    return (float)((w >> (8 * i)) & 0xffu);
+#endif
+}
+
+template <bool ANY, class Load, class Store>
+__device__ __forceinline__ void trace_stream8(const float4* __restrict__ nodes8, const float4* __restrict__ tris8, float tmin, int n,
+                                              int* counter, uint2* stack_sm, int stack_stride, Load load, Store store)
+{
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    TStack8 st;
+    st.init(stack_sm, stack_stride);
+    bool active = false, more = true;
+    int idx = -1, exclude = -1;
+    f3 o = mk<float>(0.f, 0.f, 0.f), d = mk<float>(0.f, 0.f, 1.f), id = d, ood = o;
+    unsigned oct = 0;
+    uint2 G = make_uint2(0u, 0u), T = make_uint2(0u, 0u);
+    Hit best;
+    best.prim = -1; best.b = best.g = 0.f; best.t = 0.f;
+    for (;;) {
+        const unsigned act = __ballot_sync(full, active);
+        if (more && __popc(act) < kRefill) {
+            const unsigned idle = ~act;
+            int base = 0;
+            if (lane == 0) base = atomicAdd(counter, __popc(idle));
+            base = __shfl_sync(full, base, 0);
+            if (!active) {
+                const int my = base + __popc(idle & ((1u << lane) - 1u));
+                if (my < n) {
+                    float tmax;
+                    int init_prim;
+                    idx = my;
+                    load(idx, o, d, exclude, tmax, init_prim);
+                    id = mk<float>(safe_rcp(d.x), safe_rcp(d.y), safe_rcp(d.z));
+                    ood = mk<float>(o.x * id.x, o.y * id.y, o.z * id.z);
+                    oct = (id.x < 0.f ? 1u : 0u) | (id.y < 0.f ? 2u : 0u) | (id.z < 0.f ? 4u : 0u);
+                    best.prim = init_prim; best.b = 0.f; best.g = 0.f; best.t = tmax;
+                    st.sp = 0;
+                    G = make_uint2(0u, 0x80000000u);  // the root as a group of one: node 0, no siblings
+                    T = make_uint2(0u, 0u);
+                    active = true;
+                }
+            }
+            if (base + __popc(idle) >= n) more = false;
+        }
+        if (!__any_sync(full, active)) {
+            if (!more) break;
+            continue;
+        }
+        for (;;) {
+            // invariant: an active lane has triangles waiting in T or inner hits waiting in G.  Majority vote as in trace_stream.
+            const bool at_leaf = active && T.y != 0u, at_inner = active && T.y == 0u;
+            const unsigned mi = __ballot_sync(full, at_inner), ml = __ballot_sync(full, at_leaf);
+            bool done = false;
+            if (__popc(mi) >= __popc(ml)) {
+                if (at_inner) {
+                    // nearest pending child of G in octant order = highest hit bit
+                    const unsigned hits = G.y & 0xff000000u;
+                    const int b = 31 - __clz(hits);
+                    const unsigned imask = G.y & 0xffu;
+                    G.y &= ~(1u << b);
+                    if (G.y & 0xff000000u) st.push(G);
+                    const unsigned slot = (unsigned)(b - 24) ^ oct;
+                    const unsigned nidx = G.x + __popc(imask & ((1u << slot) - 1u));
+                    const float4* q = nodes8 + 5 * (size_t)nidx;
+                    const float4 n0 = __ldg(q), n1 = __ldg(q + 1), n2 = __ldg(q + 2), n3 = __ldg(q + 3), n4 = __ldg(q + 4);
+                    const unsigned w3 = __float_as_uint(n0.w);
+                    const float sx = __uint_as_float((w3 & 0xffu) << 23) * id.x, sy = __uint_as_float(((w3 >> 8) & 0xffu) << 23) * id.y,
+                                sz = __uint_as_float(((w3 >> 16) & 0xffu) << 23) * id.z;
+                    const float bx = __fmaf_rn(n0.x, id.x, -ood.x), by = __fmaf_rn(n0.y, id.y, -ood.y), bz = __fmaf_rn(n0.z, id.z, -ood.z);
+                    unsigned hitmask = 0u;
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        const unsigned meta4 = __float_as_uint(h ? n1.w : n1.z);
+                        const unsigned inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+                        const unsigned inner_mask4 = (inner4 >> 4) * 0xffu;
+                        const unsigned bit4 = (meta4 ^ ((oct * 0x01010101u) & inner_mask4)) & 0x1f1f1f1fu;
+                        const unsigned cnt4 = (meta4 >> 5) & 0x07070707u;
+                        const unsigned qlx = __float_as_uint(h ? n2.y : n2.x), qly = __float_as_uint(h ? n2.w : n2.z), qlz = __float_as_uint(h ? n3.y : n3.x);
+                        const unsigned qhx = __float_as_uint(h ? n3.w : n3.z), qhy = __float_as_uint(h ? n4.y : n4.x), qhz = __float_as_uint(h ? n4.w : n4.z);
+                        const unsigned nx = (oct & 1u) ? qhx : qlx, fx = (oct & 1u) ? qlx : qhx;
+                        const unsigned ny = (oct & 2u) ? qhy : qly, fy = (oct & 2u) ? qly : qhy;
+                        const unsigned nz = (oct & 4u) ? qhz : qlz, fz = (oct & 4u) ? qlz : qhz;
+#pragma unroll
+                        for (int i = 0; i < 4; i++) {
+                            const float tn = fmaxf(fmaxf(__fmaf_rn(byte_f(nx, i), sx, bx), __fmaf_rn(byte_f(ny, i), sy, by)),
+                                                   fmaxf(__fmaf_rn(byte_f(nz, i), sz, bz), 0.f));
+                            const float tf = fminf(fminf(__fmaf_rn(byte_f(fx, i), sx, bx), __fmaf_rn(byte_f(fy, i), sy, by)),
+                                                   fminf(__fmaf_rn(byte_f(fz, i), sz, bz), best.t));
+                            if (tn <= tf) hitmask |= ((cnt4 >> (8 * i)) & 0xffu) << ((bit4 >> (8 * i)) & 0xffu);
+                        }
+                    }
+                    G = make_uint2(__float_as_uint(n1.x), (hitmask & 0xff000000u) | (w3 >> 24));
+                    T = make_uint2(__float_as_uint(n1.y), hitmask & 0x00ffffffu);
+                }
+            } else if (at_leaf) {
+                while (T.y) {
+                    const int bit = __ffs(T.y) - 1;
+                    T.y &= T.y - 1u;
+                    const float4* tp = tris8 + 3 * (size_t)(T.x + (unsigned)bit);
+                    const float4 v0 = __ldg(tp);
+                    const int prim = __float_as_int(v0.w);
+                    if (prim == exclude) continue;
+                    const float4 v1 = __ldg(tp + 1), v2 = __ldg(tp + 2);
+                    float be, ga, tt;
+                    if (tri_test_fast(o, d, to_f3(v0), to_f3(v1), to_f3(v2), tmin, &be, &ga, &tt)) {
+                        if (tt < best.t || (tt == best.t && (unsigned)prim < (unsigned)best.prim)) {
+                            best.prim = prim; best.b = be; best.g = ga; best.t = tt;
+                            if (ANY) { done = true; break; }
+                        }
+                    }
+                }
+            }
+            // restore the invariant: nothing waiting here -> next group from the stack, or the ray is finished
+            if (active && !done && T.y == 0u && !(G.y & 0xff000000u)) {
+                if (st.sp == 0) done = true;
+                else G = st.pop();
             }
             if (done) {
                 store(idx, best);

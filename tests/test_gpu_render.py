@@ -89,7 +89,7 @@ def test_full_size_properties(cornell_full):
     again, _ = s.render(cam, api.NEE_UNIFORM, 16, **kw)
     assert np.array_equal(full, again)  # deterministic: counter-based RNG, atomic-free accumulation
     small_batch, _ = s.render(cam, api.NEE_UNIFORM, 16, batch_spp=3, **kw)
-    assert np.allclose(full, small_batch, rtol=1e-5, atol=1e-6)  # only the FP32 summation order differs
+    assert np.array_equal(full, small_batch)  # the film adds its samples one by one in sample order, whatever the pass size
     # spp sharding: samples [0,8) and [8,16) rendered separately, each normalised by the global 16
     lo, _ = s.render(cam, api.NEE_UNIFORM, 8, spp_offset=0, spp_total=16, **kw)
     hi, _ = s.render(cam, api.NEE_UNIFORM, 8, spp_offset=8, spp_total=16, **kw)
@@ -421,8 +421,9 @@ def test_reference_side_binding_is_a_drop_in(scene_name, strategy, scene_files, 
     _, cam = arrays_of(scene_name)
     a_pfm, b_pfm, b_ppm, a_ppm = tmp_path / "ref.pfm", tmp_path / "own.pfm", tmp_path / "own.ppm", tmp_path / "ref.ppm"
     common = ["--spp", "8", "--strategy", strategy, "--seed", "3", "--max-depth", "6"]
-    r = subprocess.run([exe, stem + ".obj", stem + ".xml", str(a_pfm), "--ppm", str(a_ppm)] + common, capture_output=True, text=True, timeout=300)
-    assert r.returncode == 0, r.stdout + r.stderr
+    # bytes, not text: the reference's loaders print GBK-encoded banners (Myobj.cpp:12,26-27)
+    r = subprocess.run([exe, stem + ".obj", stem + ".xml", str(a_pfm), "--ppm", str(a_ppm)] + common, capture_output=True, timeout=300)
+    assert r.returncode == 0, (r.stdout + r.stderr).decode(errors="replace")
     r = subprocess.run([drv, stem + ".obj", stem + ".xml", str(b_ppm), "--pfm", str(b_pfm), "--every", "8"] + common,
                        capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout + r.stderr
@@ -432,7 +433,9 @@ def test_reference_side_binding_is_a_drop_in(scene_name, strategy, scene_files, 
     hdr = ("P6\n%d %d\n255\n" % (cam.width, cam.height)).encode()
     pa = np.frombuffer(a_ppm.read_bytes()[len(hdr):], np.uint8).astype(int)
     pb = np.frombuffer(b_ppm.read_bytes()[len(hdr):], np.uint8).astype(int)
-    assert np.array_equal(pa, pb)
+    # same formula, FP64 pow from two libraries (glibc / CUDA): a value within an ulp of a rounding boundary may land on
+    # either side of floor(255 x + 0.5)
+    assert np.abs(pa - pb).max() <= 1 and np.mean(pa != pb) < 1e-3
 
 
 def test_multi_abi_on_one_device_equals_render(scene_name, gpu_scene_of, arrays_of):
@@ -484,15 +487,16 @@ def test_multi_gpu_render_behind_the_c_abi(scene_name, scene_files, tmp_path, gp
 
 
 def test_mis_queue_overflow_is_retried_inside_the_library(gpu_scene_of, arrays_of, monkeypatch):
-    """shade_with_mis grows a path tree (F6).  With room for only 1.05 entries per path slot (MCPT_TREE_FACTOR, testing
-    only) the first attempt overflows; the library halves the pass, doubles the room and retries until it fits -- the
-    caller sees the same film as with the default 3 entries per slot, bit for bit (nothing depends on the pass size)."""
+    """shade_with_mis grows a path tree (F6).  When it outgrows its queue (here the first attempt is told its queue ends
+    after 1000 entries, MCPT_TEST_OVERFLOW_ABOVE, testing only) the library abandons the pass, halves it, doubles the
+    room per path slot and renders again -- the caller sees the same film as without the overflow, bit for bit
+    (nothing depends on the pass size)."""
     _, cam = arrays_of("cornell-box")
     s = gpu_scene_of("cornell-box")
     ref, st0 = s.render(cam, api.MIS, 16, max_depth=6, seed=12)
-    monkeypatch.setenv("MCPT_TREE_FACTOR", "105")
+    monkeypatch.setenv("MCPT_TEST_OVERFLOW_ABOVE", "1000")
     img, st = s.render(cam, api.MIS, 16, max_depth=6, seed=12)
-    monkeypatch.delenv("MCPT_TREE_FACTOR")
+    monkeypatch.delenv("MCPT_TEST_OVERFLOW_ABOVE")
     assert np.array_equal(img, ref)
     assert st["vertices"] == st0["vertices"] and st["passes"] > st0["passes"]
 
