@@ -36,7 +36,7 @@ SYMBOLS = [
     "mcpt_scene_build_info", "mcpt_scene_bvh_check", "mcpt_host_light_tree_check", "mcpt_light_tree_batch",
     "mcpt_scene_light_tree_info", "mcpt_scene_light_tree_nodes", "mcpt_visibility_batch",
     "mcpt_multi_create", "mcpt_multi_device_count", "mcpt_multi_upload", "mcpt_multi_render", "mcpt_multi_destroy",
-    "mcpt_render_multi", "mcpt_multi_scene", "mcpt_measure_fp32",
+    "mcpt_render_multi", "mcpt_multi_scene", "mcpt_measure_fp32", "mcpt_scene_trace_layout",
 ]
 
 
@@ -330,6 +330,12 @@ class Scene:
         t = C.c_double(); a = C.c_double(); b = C.c_int32()
         _check(self.lib.mcpt_scene_build_info(self.handle, C.byref(t), C.byref(a), C.byref(b)))
         return dict(tree_ms=t.value, total_ms=a.value, builder=b.value)
+
+    def trace_layout(self):
+        """Wide BVH layout the trace kernels use for this scene (4 or 8) and the calibration times (ms) of both."""
+        w = C.c_int32(); ms = (C.c_float * 2)()
+        _check(self.lib.mcpt_scene_trace_layout(self.handle, C.byref(w), ms))
+        return dict(width=w.value, calib_ms_bvh4=ms[0], calib_ms_bvh8=ms[1])
 
     def bvh_check(self) -> int:
         """violations found in the scene BVH this scene holds (0 = sound)"""

@@ -80,6 +80,15 @@ int mcpt_scene_create(const McptSceneDesc* desc, int device, McptScene** out)
     return mcpt_scene_create_ex(desc, device, MCPT_BUILD_HOST_SAH, out);
 }
 
+int mcpt_scene_trace_layout(const McptScene* s, int32_t* width, float calib_ms[2])
+{
+    return guarded([&] {
+        if (!s) throw Error(MCPT_ERR_INVALID, "null scene");
+        if (width) *width = s->d.use8 ? 8 : 4;
+        if (calib_ms) { calib_ms[0] = s->calib_ms[0]; calib_ms[1] = s->calib_ms[1]; }
+    });
+}
+
 int mcpt_scene_build_info(const McptScene* s, double* tree_ms, double* total_ms, int32_t* builder)
 {
     return guarded([&] {
@@ -293,12 +302,7 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
         d.nodes = (const float4*)(db + B.off_nodes); d.tris = (const float4*)(db + B.off_tris);
         d.nodes4 = (const float4*)(db + B.off_nodes4);
         d.nodes8 = (const float4*)(db + B.off_nodes8); d.tris8 = (const float4*)(db + B.off_tris8);
-        // Which wide layout the trace kernels walk.  The compressed 8-wide nodes halve the bytes and loads per visit, which is
-        // what bounds incoherent rays through a large tree (L1 pipeline); on small scenes the byte decoding costs more ALU work
-        // than the loads it saves.  MCPT_BVH8=0/1 overrides the size rule (A/B measurements).
-        d.use8 = P >= 32768 ? 1 : 0;
-        if (const char* e = std::getenv("MCPT_BVH8")) d.use8 = std::atoi(e) != 0;
-        if (s->bvh.max_depth8 + 2 > (uint32_t)kBvh8StackDepth || s->bvh.nodes8.empty()) d.use8 = 0;
+        d.use8 = 0;
         d.lnodes = (const float4*)(db + B.off_lnodes); d.ltris = (const float4*)(db + B.off_ltris);
         d.pverts = (const float4*)(db + B.off_pverts); d.pnorms = (const float4*)(db + B.off_pnorms);
         d.mats = (const float4*)(db + B.off_mats); d.lights = (const float4*)(db + B.off_lights);
@@ -311,6 +315,12 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
         d.tmin = s->extent * 1e-6f;
         MCPT_CUDA(cudaMemcpy(s->d_blob, s->h_blob, B.total, cudaMemcpyHostToDevice));
         for (int i = 0; i < 6; i++) MCPT_CUDA(cudaEventCreate(&s->ev[i]));
+        // Which wide layout the trace kernels walk: measured on this scene (render.cu: calibrate_trace_layout) unless the
+        // 8-wide tree is too deep for its stack or MCPT_BVH8=0/1 forces the choice (A/B measurements, tests).
+        if (s->bvh.max_depth8 + 2 <= (uint32_t)kBvh8StackDepth && !s->bvh.nodes8.empty()) {
+            if (const char* e = std::getenv("MCPT_BVH8")) d.use8 = std::atoi(e) != 0;
+            else calibrate_trace_layout(s);
+        }
         s->build_total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
         *out = s;
     });

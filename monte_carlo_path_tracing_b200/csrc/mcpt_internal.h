@@ -70,6 +70,7 @@ struct McptScene {
     size_t blob_bytes = 0;
     mcpt::DScene d{};      // device pointers into d_blob
     float extent = 1.f;    // largest scene dimension
+    float calib_ms[2] = {0.f, 0.f};  // time of the layout calibration batch through the 4-wide / compressed 8-wide BVH (0: not run)
     mcpt::Workspace ws;
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
@@ -83,6 +84,8 @@ McptScene* scene_clone(const McptScene* src, int device);
 // render_parity.cu: MCPT_PARITY_FP64
 void render_parity_device(McptScene* scene, const McptCamera* cam, const McptRenderParams* params, float* d_out_rgb,
                           cudaStream_t stream, McptStats* stats);
+// render.cu: times a batch of rays through both wide layouts and sets d.use8
+void calibrate_trace_layout(McptScene* scene);
 // render.cu test hooks: the production trace kernels (k_extend / k_extend_exact, k_shadow / k_shadow_exact) on explicit rays
 void trace_rays_device(McptScene* scene, int n, const float4* d_org, const float4* d_dir, int leaf_mode, float4* d_hit);
 void visibility_device(McptScene* scene, int n, const float4* d_org, const float4* d_dir, const int2* d_ids, int leaf_mode, int* d_visible);

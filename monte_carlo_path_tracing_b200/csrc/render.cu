@@ -1238,6 +1238,66 @@ void visibility_device(McptScene* scene, int n, const float4* d_org, const float
     MCPT_CUDA(e);
 }
 
+// ---- which wide BVH layout the trace kernels walk for this scene: measured, not guessed -----------------------------------
+// The compressed 8-wide nodes need fewer and smaller loads per visit but more ALU work (byte decoding, no distance sort):
+// they win where the 4-wide traversal is bound by the L1 pipeline (1 M-triangle soup +26 %, Cornell box +17 %) and lose
+// where it is bound by the ALU pipe (veach-mis, interior: -5 %).  Both layouts return identical hits, so the choice is
+// free: scene creation traces 512 Ki rays leaving random surface points into the hemisphere of their shading normal (what
+// the bounce rays of a render look like) through both kernels and keeps the faster.
+namespace {
+__global__ void k_calib_rays(DScene s, int n, float4* org, float4* dir)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const Rng4 a = rng_draw4(0x5eedu, (uint32_t)i, 0u, 1u, 0u), b = rng_draw4(0x5eedu, (uint32_t)i, 0u, 1u, 1u);
+    const int prim = min(s.P - 1, (int)(a.u[0] * (float)s.P));
+    const float be = 1.f - sqrtf(1.f - a.u[1]), ga = (1.f - be) * a.u[2];
+    const f3 p = to_f3(__ldg(s.pverts + 3 * prim)) * (1.f - be - ga) + to_f3(__ldg(s.pverts + 3 * prim + 1)) * be + to_f3(__ldg(s.pverts + 3 * prim + 2)) * ga;
+    const f3 nn = to_f3(__ldg(s.pnorms + 3 * prim)) * (1.f - be - ga) + to_f3(__ldg(s.pnorms + 3 * prim + 1)) * be + to_f3(__ldg(s.pnorms + 3 * prim + 2)) * ga;
+    const float z = 1.f - 2.f * b.u[0], r = sqrtf(fmaxf(0.f, 1.f - z * z)), phi = 6.2831853f * b.u[1];
+    f3 w = mk<float>(r * cosf(phi), r * sinf(phi), z);
+    if (dot(w, nn) < 0.f) w = -w;  // uniform over the hemisphere of the shading normal
+    org[i] = make_float4(p.x, p.y, p.z, __int_as_float(prim));
+    dir[i] = make_float4(w.x, w.y, w.z, __int_as_float(i));
+}
+}  // namespace
+
+void calibrate_trace_layout(McptScene* scene)
+{
+    scene->calib_ms[0] = scene->calib_ms[1] = 0.f;
+    const int n = 512 << 10;
+    char* buf = nullptr;
+    MCPT_CUDA(cudaMalloc((void**)&buf, (size_t)n * 48 + 64));
+    float4 *org = (float4*)buf, *dir = org + n, *hit = dir + n;
+    int* small = (int*)(hit + n);  // [0] n, [1] cursor
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    cudaError_t err = cudaEventCreate(&e0);
+    if (err == cudaSuccess) err = cudaEventCreate(&e1);
+    if (err == cudaSuccess) {
+        k_calib_rays<<<(n + 255) / 256, 256>>>(scene->d, n, org, dir);
+        const int grid = std::min(148 * 8, (n + kBlk - 1) / kBlk);
+        for (int rep = 0; rep < 3 && err == cudaSuccess; rep++)  // repetition 0 warms the caches
+            for (int w = 0; w < 2 && err == cudaSuccess; w++) {
+                const int init[2] = {n, 0};
+                err = cudaMemcpy(small, init, 8, cudaMemcpyHostToDevice);
+                cudaEventRecord(e0);
+                if (w) k_extend8<<<grid, kBlk>>>(scene->d, org, dir, small, small + 1, hit);
+                else k_extend<<<grid, kBlk>>>(scene->d, org, dir, small, small + 1, hit);
+                cudaEventRecord(e1);
+                if (err == cudaSuccess) err = cudaEventSynchronize(e1);
+                float ms = 0.f;
+                cudaEventElapsedTime(&ms, e0, e1);
+                if (rep) scene->calib_ms[w] = rep == 1 ? ms : std::min(scene->calib_ms[w], ms);
+            }
+        if (err == cudaSuccess) err = cudaGetLastError();
+    }
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    cudaFree(buf);
+    MCPT_CUDA(err);
+    scene->d.use8 = scene->calib_ms[1] < scene->calib_ms[0] ? 1 : 0;
+}
+
 void workspace_free(Workspace& ws)
 {
     if (ws.base) cudaFree(ws.base);

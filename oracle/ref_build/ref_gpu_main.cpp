@@ -22,7 +22,10 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <execinfo.h>
 #include <iostream>
+#include <signal.h>
+#include <unistd.h>
 #include <string>
 #include <vector>
 
@@ -84,8 +87,20 @@ static int upload_scene(Myobj& veach, Mylight& lights, int device, McptSceneDesc
     return mcpt_scene_create(&d, device, scene);  // the library copies everything; the vectors may die here
 }
 
+static void on_crash(int sig)
+{
+    void* frames[64];
+    const int n = backtrace(frames, 64);
+    const char msg[] = "ref_gpu_main: fatal signal, backtrace:\n";
+    if (write(2, msg, sizeof msg - 1) < 0) {}
+    backtrace_symbols_fd(frames, n, 2);
+    _exit(128 + sig);
+}
+
 int main(int argc, char** argv)
 {
+    signal(SIGSEGV, on_crash);
+    signal(SIGABRT, on_crash);
     if (argc < 4) { std::fprintf(stderr, "usage: %s scene.obj scene.xml out.pfm [options]\n", argv[0]); return 2; }
     int spp = 10, strategy = MCPT_MIS, max_depth = 0, leaf = MCPT_LEAF_FAST, gpus = 1;  // main.cpp:567,575
     unsigned flags = 0;
