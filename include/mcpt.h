@@ -161,9 +161,11 @@ enum { MCPT_BUILD_HOST_SAH = 0, MCPT_BUILD_GPU_LBVH = 1 };
 int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_flags, McptScene** out);
 int mcpt_scene_build_info(const McptScene*, double* tree_ms, double* total_ms, int32_t* builder);
 /* Which wide BVH the trace kernels walk for this scene -- 4 (112 B nodes, distance-sorted children) or 8 (compressed 80 B
- * nodes, octant order; csrc/bvh.h) -- and the time in ms of the 512 Ki-ray calibration batch through each at scene creation
- * (0, 0 when MCPT_BVH8 forced the choice).  Hits and films are identical for both. */
-int mcpt_scene_trace_layout(const McptScene*, int32_t* width, float calib_ms[2]);
+ * nodes, octant order; csrc/bvh.h).  Hits and films are identical for both, so the library measures: calib_ms = time of
+ * a 512 Ki-ray batch of random surface rays through each layout at scene creation (the first guess), render_ms = time of
+ * both kernels on the first bounce of >= 256 Ki real rays of the first render, which settles it (0, 0: not measured --
+ * MCPT_BVH8=0/1 forced the choice, or no such bounce yet). */
+int mcpt_scene_trace_layout(const McptScene*, int32_t* width, float calib_ms[2], float render_ms[2]);
 void mcpt_scene_destroy(McptScene* scene);
 /* bytes of scene data resident on the device / re-upload them (used by the e2e timing) */
 size_t mcpt_scene_device_bytes(const McptScene* scene);

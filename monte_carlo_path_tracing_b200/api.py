@@ -333,9 +333,9 @@ class Scene:
 
     def trace_layout(self):
         """Wide BVH layout the trace kernels use for this scene (4 or 8) and the calibration times (ms) of both."""
-        w = C.c_int32(); ms = (C.c_float * 2)()
-        _check(self.lib.mcpt_scene_trace_layout(self.handle, C.byref(w), ms))
-        return dict(width=w.value, calib_ms_bvh4=ms[0], calib_ms_bvh8=ms[1])
+        w = C.c_int32(); ms = (C.c_float * 2)(); rs = (C.c_float * 2)()
+        _check(self.lib.mcpt_scene_trace_layout(self.handle, C.byref(w), ms, rs))
+        return dict(width=w.value, calib_ms_bvh4=ms[0], calib_ms_bvh8=ms[1], first_bounce_ms_bvh4=rs[0], first_bounce_ms_bvh8=rs[1])
 
     def bvh_check(self) -> int:
         """violations found in the scene BVH this scene holds (0 = sound)"""

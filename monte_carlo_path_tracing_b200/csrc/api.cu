@@ -80,12 +80,13 @@ int mcpt_scene_create(const McptSceneDesc* desc, int device, McptScene** out)
     return mcpt_scene_create_ex(desc, device, MCPT_BUILD_HOST_SAH, out);
 }
 
-int mcpt_scene_trace_layout(const McptScene* s, int32_t* width, float calib_ms[2])
+int mcpt_scene_trace_layout(const McptScene* s, int32_t* width, float calib_ms[2], float render_ms[2])
 {
     return guarded([&] {
         if (!s) throw Error(MCPT_ERR_INVALID, "null scene");
         if (width) *width = s->d.use8 ? 8 : 4;
         if (calib_ms) { calib_ms[0] = s->calib_ms[0]; calib_ms[1] = s->calib_ms[1]; }
+        if (render_ms) { render_ms[0] = s->render_ms[0]; render_ms[1] = s->render_ms[1]; }
     });
 }
 
@@ -319,7 +320,7 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
         // 8-wide tree is too deep for its stack or MCPT_BVH8=0/1 forces the choice (A/B measurements, tests).
         if (s->bvh.max_depth8 + 2 <= (uint32_t)kBvh8StackDepth && !s->bvh.nodes8.empty()) {
             if (const char* e = std::getenv("MCPT_BVH8")) d.use8 = std::atoi(e) != 0;
-            else calibrate_trace_layout(s);
+            else { calibrate_trace_layout(s); s->layout_free = true; }
         }
         s->build_total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
         *out = s;

@@ -71,6 +71,9 @@ struct McptScene {
     mcpt::DScene d{};      // device pointers into d_blob
     float extent = 1.f;    // largest scene dimension
     float calib_ms[2] = {0.f, 0.f};  // time of the layout calibration batch through the 4-wide / compressed 8-wide BVH (0: not run)
+    float render_ms[2] = {0.f, 0.f}; // the same two kernels timed on the first large bounce of the first render (0: not yet)
+    bool layout_free = false;        // the layout is the library's to choose (not forced by MCPT_BVH8, 8-wide tree usable)
+    bool layout_final = false;       // settled on real rays
     mcpt::Workspace ws;
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };

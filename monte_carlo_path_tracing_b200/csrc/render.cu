@@ -1242,8 +1242,9 @@ void visibility_device(McptScene* scene, int n, const float4* d_org, const float
 // The compressed 8-wide nodes need fewer and smaller loads per visit but more ALU work (byte decoding, no distance sort):
 // they win where the 4-wide traversal is bound by the L1 pipeline (1 M-triangle soup +26 %, Cornell box +17 %) and lose
 // where it is bound by the ALU pipe (veach-mis, interior: -5 %).  Both layouts return identical hits, so the choice is
-// free: scene creation traces 512 Ki rays leaving random surface points into the hemisphere of their shading normal (what
-// the bounce rays of a render look like) through both kernels and keeps the faster.
+// free: scene creation traces 512 Ki rays leaving random surface points -- half into the hemisphere of their shading normal,
+// half towards random points on the lights, the two kinds of rays a render's bounces make -- through both kernels and keeps
+// the faster.
 namespace {
 __global__ void k_calib_rays(DScene s, int n, float4* org, float4* dir)
 {
@@ -1257,6 +1258,14 @@ __global__ void k_calib_rays(DScene s, int n, float4* org, float4* dir)
     const float z = 1.f - 2.f * b.u[0], r = sqrtf(fmaxf(0.f, 1.f - z * z)), phi = 6.2831853f * b.u[1];
     f3 w = mk<float>(r * cosf(phi), r * sinf(phi), z);
     if (dot(w, nn) < 0.f) w = -w;  // uniform over the hemisphere of the shading normal
+    if ((i & 1) && s.L > 0) {      // every other ray: towards a random point of a random light triangle (light-sample / visibility rays)
+        const int l = min(s.L - 1, (int)(a.u[3] * (float)s.L));
+        const float lb = 1.f - sqrtf(1.f - b.u[2]), lg = (1.f - lb) * b.u[3];
+        const f3 t = to_f3(__ldg(s.lights + 5 * l)) * (1.f - lb - lg) + to_f3(__ldg(s.lights + 5 * l + 1)) * lb + to_f3(__ldg(s.lights + 5 * l + 2)) * lg;
+        const f3 dl = t - p;
+        const float d2 = dot(dl, dl);
+        if (d2 > 0.f) w = dl * rsqrtf(d2);
+    }
     org[i] = make_float4(p.x, p.y, p.z, __int_as_float(prim));
     dir[i] = make_float4(w.x, w.y, w.z, __int_as_float(i));
 }
@@ -1454,16 +1463,17 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
               : prm->strategy == MCPT_MIS_SINGLE  ? bounce_blocks_per_sm<MCPT_MIS_SINGLE>()
                                                   : bounce_blocks_per_sm<MCPT_NEE_UNIFORM>();
     const int max_grid = sms * bps;
-    const bool use8 = scene->d.use8 != 0;
-    int ebps = 1, sbps = 1;
-    if (use8) {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ebps, k_extend8, kBlk, 0);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sbps, k_shadow8, kBlk, 0);
-    } else {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ebps, k_extend, kBlk, 0);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sbps, k_shadow, kBlk, 0);
-    }
-    const int ext_grid = sms * std::max(1, ebps), sh_grid = sms * std::max(1, sbps);
+    bool use8 = scene->d.use8 != 0;
+    int ebps = 1, sbps = 1, ebps8 = 1, sbps8 = 1;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ebps8, k_extend8, kBlk, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sbps8, k_shadow8, kBlk, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ebps, k_extend, kBlk, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sbps, k_shadow, kBlk, 0);
+    const int ext_grid4 = sms * std::max(1, ebps), sh_grid4 = sms * std::max(1, sbps), ext_grid8 = sms * std::max(1, ebps8), sh_grid8 = sms * std::max(1, sbps8);
+    int ext_grid = use8 ? ext_grid8 : ext_grid4, sh_grid = use8 ? sh_grid8 : sh_grid4;
+    // The layout guess of scene creation (random rays) is settled on the first real bounce: the rays a render makes are
+    // more coherent than the calibration batch, which shifts the balance towards the 4-wide nodes on some scenes (interior).
+    cudaEvent_t evm[3] = {nullptr, nullptr, nullptr};
     int lbps = 1;
     if (prm->strategy == MCPT_MIS) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&lbps, k_lightsel<MCPT_MIS>, kBlk, 0);
     else if (prm->strategy == MCPT_NEE_SPHERICAL) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&lbps, k_lightsel<MCPT_NEE_SPHERICAL>, kBlk, 0);
@@ -1484,7 +1494,7 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
         S.rays_closest += npix;
     }
     float ms_bounce = 0.f, ms_shade = 0.f;
-    bool overflow = false;
+    bool overflow = false, measuring = false;
     int done = 0, pass = 0;
     while (done < prm->spp) {
         const int b = std::min(batch, prm->spp - done);
@@ -1547,7 +1557,19 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
             if (!last) {
                 k_gather<<<ngroups, 256, 0, st>>>(Q[1], Q[0], counts, d_groupsum, nch, (int)stride, (int)(pretend_cap ? std::min(cap, pretend_cap) : cap), tree ? 1 : 0, d_count, d_counters);
                 const int eg = std::min(ext_grid, (count * (tree ? 2 : 1) + kBlk - 1) / kBlk);
-                if (exact) k_extend_exact<<<eg, kBlk, 0, st>>>(scene->d, Q[0].org, Q[0].dir, d_count, hit);
+                measuring = !exact && scene->layout_free && !scene->layout_final && count >= (1 << 18);
+                if (measuring) {
+                    // both layouts on the same queue (identical hits): time them, keep the faster from here on
+                    for (auto& e : evm) if (!e) MCPT_CUDA(cudaEventCreate(&e));
+                    const int need = (count * (tree ? 2 : 1) + kBlk - 1) / kBlk;
+                    MCPT_CUDA(cudaEventRecord(evm[0], st));
+                    k_extend<<<std::min(ext_grid4, need), kBlk, 0, st>>>(scene->d, Q[0].org, Q[0].dir, d_count, d_ext_cursor, hit);
+                    MCPT_CUDA(cudaEventRecord(evm[1], st));
+                    MCPT_CUDA(cudaMemsetAsync(d_ext_cursor, 0, 4, st));
+                    k_extend8<<<std::min(ext_grid8, need), kBlk, 0, st>>>(scene->d, Q[0].org, Q[0].dir, d_count, d_ext_cursor, hit);
+                    MCPT_CUDA(cudaEventRecord(evm[2], st));
+                    S.kernel_launches++;
+                } else if (exact) k_extend_exact<<<eg, kBlk, 0, st>>>(scene->d, Q[0].org, Q[0].dir, d_count, hit);
                 else if (use8) k_extend8<<<eg, kBlk, 0, st>>>(scene->d, Q[0].org, Q[0].dir, d_count, d_ext_cursor, hit);
                 else k_extend<<<eg, kBlk, 0, st>>>(scene->d, Q[0].org, Q[0].dir, d_count, d_ext_cursor, hit);
                 S.kernel_launches += 2;
@@ -1566,6 +1588,18 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
             MCPT_CUDA(cudaEventRecord(scene->ev[3], st));
             if (!last) MCPT_CUDA(cudaMemcpyAsync((void*)h_count, d_count, 4, cudaMemcpyDeviceToHost, st));
             MCPT_CUDA(cudaStreamSynchronize(st));
+            if (measuring) {
+                float t4 = 0.f, t8 = 0.f;
+                cudaEventElapsedTime(&t4, evm[0], evm[1]);
+                cudaEventElapsedTime(&t8, evm[1], evm[2]);
+                scene->render_ms[0] = t4; scene->render_ms[1] = t8;
+                use8 = t8 < t4;
+                scene->d.use8 = use8 ? 1 : 0;
+                a.s.use8 = scene->d.use8;
+                scene->layout_final = true;
+                ext_grid = use8 ? ext_grid8 : ext_grid4; sh_grid = use8 ? sh_grid8 : sh_grid4;
+                measuring = false;
+            }
             float ms = 0.f;
             cudaEventElapsedTime(&ms, scene->ev[2], scene->ev[3]);
             ms_bounce += ms;
@@ -1580,7 +1614,7 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
             S.bounces++;
             if (last) break;
             count = *h_count;
-            if (count < 0) throw QueueOverflow{batch};  // k_gather: the tree outgrew the queue; nothing of this call has reached d_out_rgb yet
+            if (count < 0) { for (auto& e : evm) if (e) cudaEventDestroy(e); throw QueueOverflow{batch}; }  // k_gather: the tree outgrew the queue; nothing of this call has reached d_out_rgb yet
             S.rays_closest += (uint64_t)count;
         }
         k_accumulate<<<(unsigned)((npix + 255) / 256), 256, 0, st>>>(Lacc, (int)npix, b, image, comp, pass == 0);
@@ -1607,6 +1641,7 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
     overflow = h_counters[CNT_OVERFLOW] != 0;
     S.ms_total = ms_total; S.ms_bounce = ms_bounce; S.ms_other = ms_total - ms_bounce;
     S.ms_shade = ms_shade; S.ms_trace = ms_bounce - ms_shade;
+    for (auto& e : evm) if (e) cudaEventDestroy(e);
     if (stats) *stats = S;
     if (overflow) throw QueueOverflow{batch};
 }
