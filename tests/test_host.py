@@ -53,6 +53,17 @@ def test_abi_struct_layouts_match_header(tmp_path):
             assert int(got["%s.%s" % (cname, f)]) == getattr(ct, f).offset, (cname, f)
 
 
+def test_integration_md_quotes_the_binding_verbatim():
+    """INTEGRATION.md section 2 IS oracle/ref_build/ref_gpu_main.cpp, the reference-side binding that is compiled against
+    the unmodified reference objects and run by tests/test_gpu_render.py -- not a sketch that can rot."""
+    md = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    src = open(os.path.join(ROOT, "oracle", "ref_build", "ref_gpu_main.cpp")).read()
+    a = md.index("<!-- BEGIN ref_gpu_main.cpp (verbatim) -->")
+    b = md.index("<!-- END ref_gpu_main.cpp -->")
+    quoted = md[a:b].split("```cpp\n", 1)[1].rsplit("```", 1)[0]
+    assert quoted == src
+
+
 @pytest.mark.skipif(os.path.exists("/dev/nvidiactl"), reason="a GPU is present")
 def test_no_gpu_fails_loudly(arrays_of):
     """No CUDA device -> MCPT_ERR_NO_DEVICE (or a CUDA error), never a silent CPU path."""
