@@ -353,6 +353,7 @@ def run_ours(args, wl_name, wl):
         step(k)
     sync()
     bvh_extra["trace_layout"] = scene.trace_layout()  # settled on the first real bounce of the warm-up
+    bvh_extra["light_lists"] = scene.light_lists()
     sampler = ClockSampler(local) if rank == 0 else None
     if sampler:
         sampler.start()
@@ -510,7 +511,12 @@ def run_ours(args, wl_name, wl):
         if counted_sweeps and sph and not args.light_tree:
             sweeps = counted_sweeps
         Lpad = (L + 63) // 64 * 64
-        flops_sweep = f_light * Lpad * sweeps
+        # (light, vertex) weights the sweeps evaluated: counted on the device (McptStats.light_evals) -- the padded table per
+        # sweep, or the per-primitive survivor lists (csrc/light_lists.h) where the scene has them
+        light_evals = sum(s.get("light_evals", 0) for s in stats) if (sph and not args.light_tree) else 0
+        if not light_evals:
+            light_evals = Lpad * sweeps
+        flops_sweep = f_light * light_evals
         flops = f_shade * elements + flops_sweep
         flops_per_vertex = flops / max(tot["vertices"], 1)
         try:
@@ -539,7 +545,8 @@ def run_ours(args, wl_name, wl):
                                  "the fp32 object is the bound that applies to the light-sampling strategies"},
             "fp32": {"achieved_tflops": flops / (ms * 1e-3) / 1e12, "peak_tflops": fp32_peak / 1e12,
                      "frac": flops / (ms * 1e-3) / fp32_peak, "executed_flops_per_sample_bounce": flops_per_vertex, "lights": L,
-                     "light_table_sweeps": sweeps, "flops_per_light_vertex": f_light, "flops_per_shade_element": f_shade,
+                     "light_table_sweeps": sweeps, "light_weight_evaluations": light_evals,
+                     "evaluations_per_sweep": light_evals / max(sweeps, 1), "flops_per_light_vertex": f_light, "flops_per_shade_element": f_shade,
                      "flop_constants": f_src, "peak_source": fp32_src, "note": "rank 0, whole step; sweeps counted on the device (McptStats.light_sweeps)"},
             "extra": {"Msample_bounces_per_s": tot["vertices"] * world / ms / 1e3,
                       "Mrays_per_s": (tot["rays_closest"] + tot["rays_shadow"] + tot["rays_light"]) * world / ms / 1e3,

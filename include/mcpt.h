@@ -141,6 +141,8 @@ typedef struct McptStats {
     uint64_t elements;       /* ray-queue elements processed by k_shade, summed over bounces (>= vertices) */
     uint64_t light_sweeps;   /* vertices for which the whole light table was evaluated (the O(L) loop of Mylight.cpp:329-421):
                               * once per shadable PIXEL per pass at the first vertex (F4), once per sampling vertex after it */
+    uint64_t light_evals;    /* (light, vertex) spherical-triangle weights those sweeps evaluated: light_sweeps x the padded table
+                              * length, or less when the sweeps run over per-primitive survivor lists (csrc/light_lists.h) */
 } McptStats;
 
 typedef struct McptScene McptScene;
@@ -166,6 +168,19 @@ int mcpt_scene_build_info(const McptScene*, double* tree_ms, double* total_ms, i
  * both kernels on the first bounce of >= 256 Ki real rays of the first render, which settles it (0, 0: not measured --
  * MCPT_BVH8=0/1 forced the choice, or no such bounce yet). */
 int mcpt_scene_trace_layout(const McptScene*, int32_t* width, float calib_ms[2], float render_ms[2]);
+/* Per-primitive survivor lists of the O(L) spherical-triangle light selection (csrc/light_lists.h): for every non-emissive
+ * primitive the lights that are NOT culled (Mylight.cpp:178-197: vertex behind the light / light below the horizon) at
+ * every point of it.  The sweeps evaluate the list instead of the table: identical weights and probabilities, about half
+ * the evaluations on veach-mis.  lists = 0: not in use for this scene (few lights, too many primitives, MCPT_LIGHT_LISTS=0);
+ * mean_fraction = mean list length / lights. */
+int mcpt_scene_light_lists(const McptScene*, uint32_t* lists, uint64_t* entries, double* mean_fraction, double* build_ms);
+/* The list of primitive `prim` as light indices (ascending; padding dropped): *count entries written to out_lights
+ * (capacity num_lights).  *count = -1 when the primitive has no list (emissive, or lists not in use). */
+int mcpt_scene_light_list_of_prim(const McptScene*, uint32_t prim, int32_t* out_lights, int32_t* count);
+/* Host-only (no GPU): build the lists for `desc` and write them as a membership matrix, mask[prim * num_lights + light] =
+ * 1 when the light is on the primitive's list (all 0 for emissive primitives).  out3 = {lists, longest padded list,
+ * 1000 x mean fraction}; lists = 0: the builder declined (see above), mask untouched. */
+int mcpt_host_light_lists(const McptSceneDesc* desc, uint8_t* mask, uint32_t out3[3]);
 void mcpt_scene_destroy(McptScene* scene);
 /* bytes of scene data resident on the device / re-upload them (used by the e2e timing) */
 size_t mcpt_scene_device_bytes(const McptScene* scene);

@@ -36,7 +36,7 @@ SYMBOLS = [
     "mcpt_scene_build_info", "mcpt_scene_bvh_check", "mcpt_host_light_tree_check", "mcpt_light_tree_batch",
     "mcpt_scene_light_tree_info", "mcpt_scene_light_tree_nodes", "mcpt_visibility_batch",
     "mcpt_multi_create", "mcpt_multi_device_count", "mcpt_multi_upload", "mcpt_multi_render", "mcpt_multi_destroy",
-    "mcpt_render_multi", "mcpt_multi_scene", "mcpt_measure_fp32", "mcpt_scene_trace_layout",
+    "mcpt_render_multi", "mcpt_multi_scene", "mcpt_measure_fp32", "mcpt_scene_trace_layout", "mcpt_scene_light_lists", "mcpt_scene_light_list_of_prim", "mcpt_host_light_lists",
 ]
 
 
@@ -70,7 +70,7 @@ class Stats(C.Structure):
                 ("rays_closest", C.c_uint64), ("rays_shadow", C.c_uint64), ("rays_light", C.c_uint64),
                 ("passes", C.c_uint32), ("bounces", C.c_uint32), ("kernel_launches", C.c_uint32),
                 ("queue_peak", C.c_uint32), ("ms_total", C.c_float), ("ms_bounce", C.c_float), ("ms_other", C.c_float),
-                ("ms_shade", C.c_float), ("ms_trace", C.c_float), ("elements", C.c_uint64), ("light_sweeps", C.c_uint64)]
+                ("ms_shade", C.c_float), ("ms_trace", C.c_float), ("elements", C.c_uint64), ("light_sweeps", C.c_uint64), ("light_evals", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -196,6 +196,19 @@ def host_light_tree_check(a: SceneArrays):
     out = (C.c_uint32 * 4)()
     _check(lib.mcpt_host_light_tree_check(C.byref(d), out))
     return dict(nodes=out[0], max_depth=out[1], errors=out[2], lights=out[3])
+
+
+def host_light_lists(a: SceneArrays):
+    """Per-primitive survivor lists of the light sweeps (csrc/light_lists.h) built on the host, as a [P, L] membership
+    matrix (no GPU needed); None when the builder declines (few lights, too many primitives)."""
+    lib = load()
+    d, keep = make_desc(a)
+    mask = np.zeros((len(a.positions), len(a.light_prim)), np.uint8)
+    out = (C.c_uint32 * 3)()
+    _check(lib.mcpt_host_light_lists(C.byref(d), _p(mask), out))
+    if out[0] == 0:
+        return None
+    return dict(mask=mask.astype(bool), lists=out[0], max_len=out[1], mean_fraction=out[2] / 1000.0)
 
 
 def measure_fp32(device: int = 0):
@@ -336,6 +349,18 @@ class Scene:
         w = C.c_int32(); ms = (C.c_float * 2)(); rs = (C.c_float * 2)()
         _check(self.lib.mcpt_scene_trace_layout(self.handle, C.byref(w), ms, rs))
         return dict(width=w.value, calib_ms_bvh4=ms[0], calib_ms_bvh8=ms[1], first_bounce_ms_bvh4=rs[0], first_bounce_ms_bvh8=rs[1])
+
+    def light_lists(self):
+        """Per-primitive survivor lists of the light sweeps (csrc/light_lists.h); lists == 0: not in use for this scene."""
+        n = C.c_uint32(); e = C.c_uint64(); f = C.c_double(); ms = C.c_double()
+        _check(self.lib.mcpt_scene_light_lists(self.handle, C.byref(n), C.byref(e), C.byref(f), C.byref(ms)))
+        return dict(lists=n.value, entries=e.value, mean_fraction=f.value, build_ms=ms.value)
+
+    def light_list_of_prim(self, prim: int):
+        """light indices on the survivor list of `prim`, or None when it has no list"""
+        out = np.zeros(max(1, len(self.arrays.light_prim)), np.int32); n = C.c_int32()
+        _check(self.lib.mcpt_scene_light_list_of_prim(self.handle, C.c_uint32(prim), _p(out), C.byref(n)))
+        return None if n.value < 0 else out[:n.value].copy()
 
     def bvh_check(self) -> int:
         """violations found in the scene BVH this scene holds (0 = sound)"""

@@ -12,6 +12,7 @@
 #include "bvh_tree.h"
 #include "mcpt_internal.h"
 #include "light_tree.h"
+#include "light_lists.h"
 
 namespace mcpt {
 static thread_local std::string g_last_error;
@@ -20,7 +21,7 @@ void set_last_error(const std::string& msg) { g_last_error = msg; }
 namespace {
 struct BlobLayout {
     size_t off_nodes, off_nodes4, off_tris, off_nodes8, off_tris8, off_lnodes, off_ltris, off_pverts, off_pnorms, off_mats, off_lights, off_lsoa, off_lng64, off_larea64,
-        off_crad64, off_class_begin, off_class_cdf, off_tri_cdf, off_ltree, off_ltree_leaf, total;
+        off_crad64, off_class_begin, off_class_cdf, off_tri_cdf, off_ltree, off_ltree_leaf, off_llist, off_lrange, off_prim_list, total;
 };
 size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
@@ -87,6 +88,39 @@ int mcpt_scene_trace_layout(const McptScene* s, int32_t* width, float calib_ms[2
         if (width) *width = s->d.use8 ? 8 : 4;
         if (calib_ms) { calib_ms[0] = s->calib_ms[0]; calib_ms[1] = s->calib_ms[1]; }
         if (render_ms) { render_ms[0] = s->render_ms[0]; render_ms[1] = s->render_ms[1]; }
+    });
+}
+
+int mcpt_scene_light_lists(const McptScene* s, uint32_t* lists, uint64_t* entries, double* mean_fraction, double* build_ms)
+{
+    return guarded([&] {
+        if (!s) throw Error(MCPT_ERR_INVALID, "null scene");
+        if (lists) *lists = s->nlists;
+        if (entries) *entries = s->list_entries;
+        if (mean_fraction) *mean_fraction = s->list_fraction;
+        if (build_ms) *build_ms = s->list_build_ms;
+    });
+}
+
+int mcpt_scene_light_list_of_prim(const McptScene* s, uint32_t prim, int32_t* out_lights, int32_t* count)
+{
+    return guarded([&] {
+        if (!s || !count) throw Error(MCPT_ERR_INVALID, "null argument");
+        if (prim >= s->P) throw Error(MCPT_ERR_INVALID, "prim out of range");
+        *count = -1;
+        if (!s->nlists) return;
+        const char* hb = (const char*)s->h_blob;
+        const char* db = (const char*)s->d_blob;
+        const int32_t id = ((const int32_t*)(hb + ((const char*)s->d.prim_list - db)))[prim];
+        if (id < 0) return;
+        const int32_t* rg = (const int32_t*)(hb + ((const char*)s->d.lrange - db)) + 2 * (size_t)id;
+        const uint32_t* e = (const uint32_t*)(hb + ((const char*)s->d.llist - db)) + rg[0];
+        int32_t n = 0;
+        for (int32_t k = 0; k < rg[1]; k++) {
+            const int32_t l = (int32_t)(((e[k] >> 7) << 5) + (e[k] & 31));  // lights.cuh lsoa_light
+            if (l < (int32_t)s->L) { if (out_lights) out_lights[n] = l; n++; }
+        }
+        *count = n;
     });
 }
 
@@ -204,7 +238,15 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
         B.off_pnorms = place((size_t)P * 3 * 16);
         B.off_mats = place((size_t)Mn * 2 * 16);
         B.off_lights = place((size_t)L * 5 * 16);
-        const uint32_t Lpad = (L + 63) / 64 * 64;
+        std::vector<int32_t> light_of_prim(P, -1);
+        for (uint32_t l = 0; l < L; l++) light_of_prim[s->light_prim[l]] = (int32_t)l;
+        // per-primitive survivor lists of the light sweeps (light_lists.h); their padding entries point at a padding light of
+        // the table, so a table that is full to the last block gets one more block when (and only when) lists are in use
+        uint32_t Lpad = (L + 63) / 64 * 64;
+        LightLists lists = build_light_lists(s->positions.data(), s->normals.data(), light_of_prim.data(), P, s->light_prim.data(),
+                                             s->geom_normals.data(), s->light_area.data(), L, Lpad > L ? Lpad : Lpad + 64);
+        if (lists.nlists && Lpad == L) Lpad += 64;
+        s->nlists = lists.nlists; s->list_max = lists.max_len; s->list_entries = lists.entries.size(); s->list_fraction = lists.mean_fraction; s->list_build_ms = lists.build_ms;
         B.off_lsoa = place((size_t)Lpad * 4 * 16);
         B.off_lng64 = place((size_t)L * 3 * 8);
         B.off_larea64 = place((size_t)L * 8);
@@ -214,6 +256,9 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
         B.off_tri_cdf = place((size_t)L * 4);
         B.off_ltree = place(s->ltree.nodes.size() * sizeof(f4));
         B.off_ltree_leaf = place((size_t)L * 4);
+        B.off_llist = place(lists.entries.size() * 4);
+        B.off_lrange = place(lists.range.size() * 4);
+        B.off_prim_list = place(lists.nlists ? (size_t)P * 4 : 0);
         B.total = o;
         s->blob_bytes = B.total;
         MCPT_CUDA(cudaMallocHost(&s->h_blob, B.total));
@@ -230,8 +275,11 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
             std::memcpy(hb + B.off_ltree, s->ltree.nodes.data(), s->ltree.nodes.size() * sizeof(f4));
             std::memcpy(hb + B.off_ltree_leaf, s->ltree.leaf_of_light.data(), (size_t)L * 4);
         }
-        std::vector<int32_t> light_of_prim(P, -1);
-        for (uint32_t l = 0; l < L; l++) light_of_prim[s->light_prim[l]] = (int32_t)l;
+        if (lists.nlists) {
+            std::memcpy(hb + B.off_llist, lists.entries.data(), lists.entries.size() * 4);
+            std::memcpy(hb + B.off_lrange, lists.range.data(), lists.range.size() * 4);
+            std::memcpy(hb + B.off_prim_list, lists.prim_list.data(), (size_t)P * 4);
+        }
         f4* pv = (f4*)(hb + B.off_pverts);
         f4* pn = (f4*)(hb + B.off_pnorms);
         for (uint32_t p = 0; p < P; p++) {
@@ -312,6 +360,8 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
         d.crad64 = (const double*)(db + B.off_crad64); d.class_begin = (const int32_t*)(db + B.off_class_begin);
         d.class_cdf = (const float*)(db + B.off_class_cdf); d.tri_cdf = (const float*)(db + B.off_tri_cdf);
         d.ltree = (const float4*)(db + B.off_ltree); d.ltree_leaf = (const int32_t*)(db + B.off_ltree_leaf);
+        d.llist = (const uint32_t*)(db + B.off_llist); d.lrange = (const int2*)(db + B.off_lrange);
+        d.prim_list = (const int32_t*)(db + B.off_prim_list); d.nlists = (int32_t)lists.nlists; d.list_max = (int32_t)lists.max_len;
         d.P = (int32_t)P; d.L = (int32_t)L; d.C = (int32_t)C; d.M = (int32_t)Mn;
         d.tmin = s->extent * 1e-6f;
         MCPT_CUDA(cudaMemcpy(s->d_blob, s->h_blob, B.total, cudaMemcpyHostToDevice));
@@ -355,6 +405,7 @@ McptScene* scene_clone(const McptScene* src, int device)
         rebase(d.nodes); rebase(d.nodes4); rebase(d.tris); rebase(d.nodes8); rebase(d.tris8); rebase(d.lnodes); rebase(d.ltris); rebase(d.pverts); rebase(d.pnorms);
         rebase(d.mats); rebase(d.lights); rebase(d.lsoa); rebase(d.lng64); rebase(d.larea64); rebase(d.crad64);
         rebase(d.class_begin); rebase(d.class_cdf); rebase(d.tri_cdf); rebase(d.ltree); rebase(d.ltree_leaf);
+        rebase(d.llist); rebase(d.lrange); rebase(d.prim_list);
         for (int i = 0; i < 6; i++) MCPT_CUDA(cudaEventCreate(&raw->ev[i]));
     } catch (...) {
         mcpt_scene_destroy(raw);
@@ -606,6 +657,42 @@ int mcpt_host_light_tree_check(const McptSceneDesc* desc, uint32_t out4[4])
         }
         const LightTree T = build_light_tree(desc->positions, desc->light_prim, gn.data(), area.data(), lsum.data(), L);
         out4[0] = T.num_nodes; out4[1] = T.max_depth; out4[2] = check_light_tree(T, desc->positions, desc->light_prim, gn.data(), L); out4[3] = L;
+    });
+}
+
+int mcpt_host_light_lists(const McptSceneDesc* desc, uint8_t* mask, uint32_t out3[3])
+{
+    return guarded([&] {
+        validate(desc);
+        if (!mask || !out3) throw Error(MCPT_ERR_INVALID, "null argument");
+        const uint32_t P = desc->num_prims, L = desc->num_lights;
+        std::vector<double> gn((size_t)P * 3, 0.0), area(L);
+        std::vector<int32_t> light_of_prim(P, -1);
+        for (uint32_t l = 0; l < L; l++) {
+            const int32_t p = desc->light_prim[l];
+            light_of_prim[p] = (int32_t)l;
+            const dvec g = unique_normal(desc->positions + (size_t)p * 9, desc->normals + (size_t)p * 9);
+            for (int c = 0; c < 3; c++) gn[(size_t)p * 3 + c] = g[c];
+            const float* v = desc->positions + (size_t)p * 9;
+            double e1[3], e2[3];
+            for (int c = 0; c < 3; c++) { e1[c] = (double)v[3 + c] - v[c]; e2[c] = (double)v[6 + c] - v[c]; }
+            const double n[3] = {e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0]};
+            area[l] = 0.5 * std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+        }
+        const uint32_t Lpad = (L + 63) / 64 * 64;
+        const LightLists R = build_light_lists(desc->positions, desc->normals, light_of_prim.data(), P, desc->light_prim, gn.data(), area.data(), L,
+                                               Lpad > L ? Lpad : Lpad + 64);
+        out3[0] = R.nlists; out3[1] = R.max_len; out3[2] = (uint32_t)(1000.0 * R.mean_fraction + 0.5);
+        if (!R.nlists) return;
+        std::memset(mask, 0, (size_t)P * L);
+        for (uint32_t p = 0; p < P; p++) {
+            const int32_t id = R.prim_list[p];
+            if (id < 0) continue;
+            for (int32_t k = 0; k < R.range[2 * id + 1]; k++) {
+                const uint32_t e = R.entries[(size_t)R.range[2 * id] + k], l = ((e >> 7) << 5) + (e & 31);
+                if (l < L) mask[(size_t)p * L + l] = 1;
+            }
+        }
     });
 }
 

@@ -159,11 +159,15 @@ __device__ __forceinline__ float light_weight_soa(float4 p0, float4 p1, float4 p
 // lsoa is blocked by 32 lights: [Lpad / 32][4 planes][32] float4, so one pointer with constant offsets serves a sweep
 __host__ __device__ __forceinline__ int lsoa_index(int l) { return ((l >> 5) << 7) + (l & 31); }
 
-__device__ __forceinline__ float light_weight_fast(const DScene& s, int l, f3 x1, f3 n)
+__host__ __device__ __forceinline__ int lsoa_light(int off) { return ((off >> 7) << 5) + (off & 31); }  // inverse of lsoa_index
+
+// weight of the light at lsoa offset `off` (what the survivor lists of light_lists.h store)
+__device__ __forceinline__ float light_weight_at(const DScene& s, int off, f3 x1, f3 n)
 {
-    const float4* P = s.lsoa + lsoa_index(l);
+    const float4* P = s.lsoa + off;
     return light_weight_soa(__ldg(P), __ldg(P + 32), __ldg(P + 64), __ldg(P + 96), x1, n);
 }
+__device__ __forceinline__ float light_weight_fast(const DScene& s, int l, f3 x1, f3 n) { return light_weight_at(s, lsoa_index(l), x1, n); }
 
 // ---- packed FP32 (sm_100 FFMA2 / FADD2 / FMUL2) --------------------------------------------------------------
 // Blackwell issues ONE instruction for two independent FP32 operations on a 64-bit register pair, and any operand
@@ -254,6 +258,36 @@ __device__ __forceinline__ void warp_light_partial(const DScene& s, const f3 (&x
 #pragma unroll
         for (int h = 0; h < V / 2; h++) acc[h] = __fadd2_rn(acc[h], light_weight_pair(a0, a1, a2, a3, vp[h]));
         if (V == 2 && cdf) { cdf[l] = acc[0].x; cdf[s.Lpad + l] = acc[0].y; }
+    }
+#pragma unroll
+    for (int h = 0; h < V / 2; h++) { part[2 * h] = acc[h].x; part[2 * h + 1] = acc[h].y; }
+}
+
+// The same sweep over a survivor list (light_lists.h) instead of the whole table: `list` holds n lsoa offsets (n a multiple
+// of 32, padded with a weight-0 light), lane k takes entries k, k + 32, ...  The lights a list leaves out are culled at
+// every vertex of the primitive it belongs to, i.e. they would have added exact zeros.  cdf (optional): running
+// sums by list POSITION, cdf[v * cdf_stride + k].
+template <int V>
+__device__ __forceinline__ void warp_light_partial_list(const DScene& s, const uint32_t* __restrict__ list, int n, const f3 (&x1)[V],
+                                                        const f3 (&nn)[V], float (&part)[V], float* cdf = nullptr, int cdf_stride = 0)
+{
+    static_assert(V == 2 || V == 4, "the sweep is packed over vertex pairs");
+    const int lane = threadIdx.x & 31;
+    VertexPair2 vp[V / 2];
+    float2 acc[V / 2];
+#pragma unroll
+    for (int h = 0; h < V / 2; h++) { vp[h] = make_vertex2(x1[2 * h], nn[2 * h], x1[2 * h + 1], nn[2 * h + 1]); acc[h] = make_float2(0.f, 0.f); }
+    const uint32_t* __restrict__ E = list + lane;
+#pragma unroll kSweepUnroll
+    for (int k = lane; k < n; k += 32, E += 32) {
+        const float4* __restrict__ P = s.lsoa + __ldg(E);
+        const float4 a0 = __ldg(P), a1 = __ldg(P + 32), a2 = __ldg(P + 64), a3 = __ldg(P + 96);
+#pragma unroll
+        for (int h = 0; h < V / 2; h++) acc[h] = __fadd2_rn(acc[h], light_weight_pair(a0, a1, a2, a3, vp[h]));
+        if (cdf) {
+#pragma unroll
+            for (int h = 0; h < V / 2; h++) { cdf[(2 * h) * cdf_stride + k] = acc[h].x; cdf[(2 * h + 1) * cdf_stride + k] = acc[h].y; }
+        }
     }
 #pragma unroll
     for (int h = 0; h < V / 2; h++) { part[2 * h] = acc[h].x; part[2 * h + 1] = acc[h].y; }

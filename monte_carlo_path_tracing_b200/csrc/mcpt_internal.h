@@ -62,6 +62,10 @@ struct McptScene {
     std::vector<double> light_area;    // [L]
     mcpt::Bvh bvh, lbvh;
     mcpt::LightTree ltree;  // light hierarchy of MCPT_LIGHT_TREE
+    uint32_t list_max = 0;  // longest padded list
+    uint32_t nlists = 0;    // per-primitive survivor lists of the light sweeps (light_lists.h); 0 = not in use
+    size_t list_entries = 0;
+    double list_fraction = 0, list_build_ms = 0;
     double build_tree_ms = 0, build_total_ms = 0;  // scene BVH: tree construction / whole scene_create
     int32_t builder = 0;                           // MCPT_BUILD_*
     // one packed, pinned host image of everything the kernels read + its device twin

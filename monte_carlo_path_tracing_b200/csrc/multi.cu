@@ -225,7 +225,7 @@ int mcpt_multi_render(McptMulti* m, const McptCamera* cam, const McptRenderParam
             for (int r = 0; r < n; r++) {
                 const McptStats& s = slots[r].st;
                 S.paths += s.paths; S.primary_hits += s.primary_hits; S.vertices += s.vertices; S.rays_closest += s.rays_closest;
-                S.rays_shadow += s.rays_shadow; S.rays_light += s.rays_light; S.elements += s.elements; S.light_sweeps += s.light_sweeps;
+                S.rays_shadow += s.rays_shadow; S.rays_light += s.rays_light; S.elements += s.elements; S.light_sweeps += s.light_sweeps; S.light_evals += s.light_evals;
                 S.passes += s.passes; S.bounces += s.bounces; S.kernel_launches += s.kernel_launches;
                 S.queue_peak = std::max(S.queue_peak, s.queue_peak);
                 // device time of the call = the slowest device (they run side by side) + the reduce

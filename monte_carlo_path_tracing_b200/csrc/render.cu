@@ -44,7 +44,7 @@ constexpr int kBlk = 128;             // threads per block (4 warps; a warp owns
 constexpr unsigned kFull = 0xffffffffu;
 constexpr size_t kTargetSlots = 128u << 20;  // auto batch: up to 128 Mi path slots in flight per pass (memory permitting)
 
-enum { CNT_VERTICES = 0, CNT_RAYS, CNT_SHADOW, CNT_LIGHTRAYS, CNT_PRIMARY_HITS, CNT_OVERFLOW, CNT_SWEEPS, CNT_N };
+enum { CNT_VERTICES = 0, CNT_RAYS, CNT_SHADOW, CNT_LIGHTRAYS, CNT_PRIMARY_HITS, CNT_OVERFLOW, CNT_SWEEPS, CNT_EVALS, CNT_N };
 
 struct Queue {
     float4* org;   // o.xyz | exclude prim (int bits)          (Myobj.cpp:417 rotri)
@@ -76,6 +76,10 @@ struct BounceArgs {
     int* counts;               // [chunks] children staged by each chunk
     int* groupsum;             // [chunks / kGroup] sums of counts, filled with one integer atomic per chunk
     int* ticket;               // chunk ticket counter
+    int* skey;                 // [capacity] survivor list of the vertex of in-queue ray i that samples a light, -1 otherwise (k_lsel_classify)
+    int* sorted;               // [capacity + 4 nlists] those queue indices grouped by list, runs padded to whole groups with -1
+    int* lhist;                // [nlists] vertices per list, then (k_lsel_offsets) the scatter cursors
+    int* ngroups;              // [1] groups of kSelV sorted entries
     unsigned long long* counters;
     uint64_t seed;
     int in_count, capacity, npix, batch_spp, sample_base, bounce, max_depth;
@@ -112,7 +116,10 @@ __device__ __forceinline__ f3 camera_dir(const DCamera& c, int pixel, float di, 
 struct LightPick { int light; float w; };
 
 // `part` = this lane's partial sum, `incl` its inclusive scan over lanes, `total` the sum over all lanes.
-__device__ __forceinline__ LightPick warp_light_pick(const DScene& s, f3 X, f3 Nn, float part, float incl, float total, float uu)
+// LIST: the sweep ran over a survivor list of n lsoa offsets (light_lists.h); otherwise over the whole table (n = s.L).
+template <bool LIST>
+__device__ __forceinline__ LightPick warp_light_pick(const DScene& s, const uint32_t* __restrict__ list, int n, f3 X, f3 Nn, float part,
+                                                     float incl, float total, float uu)
 {
     const int lane = threadIdx.x & 31;
     LightPick r;
@@ -126,24 +133,25 @@ __device__ __forceinline__ LightPick warp_light_pick(const DScene& s, f3 X, f3 N
     float running = 0.f;
     int last_l = -1;
     float last_w = 0.f;
-    for (int k0 = 0; j + 32 * k0 < s.L && r.light < 0; k0 += 32) {
-        const int l = j + 32 * (k0 + lane);
-        const float w = (l < s.L) ? light_weight_fast(s, l, X, Nn) : 0.f;
+    for (int k0 = 0; j + 32 * k0 < n && r.light < 0; k0 += 32) {
+        const int pos = j + 32 * (k0 + lane);
+        const int off = pos < n ? (LIST ? (int)__ldg(list + pos) : lsoa_index(pos)) : -1;
+        const float w = (off >= 0) ? light_weight_at(s, off, X, Nn) : 0.f;
         float wi = w;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             float t = __shfl_up_sync(kFull, wi, o);
             if (lane >= o) wi += t;
         }
-        const unsigned pos = __ballot_sync(kFull, w > 0.f);
+        const unsigned pos_m = __ballot_sync(kFull, w > 0.f);
         const unsigned hit = __ballot_sync(kFull, w > 0.f && running + wi >= rem);
         if (hit) {
             const int f = __ffs(hit) - 1;
-            r.light = j + 32 * (k0 + f);
+            r.light = lsoa_light(__shfl_sync(kFull, off, f));
             r.w = __shfl_sync(kFull, w, f);
-        } else if (pos) {
-            const int f = 31 - __clz(pos);
-            last_l = j + 32 * (k0 + f);
+        } else if (pos_m) {
+            const int f = 31 - __clz(pos_m);
+            last_l = lsoa_light(__shfl_sync(kFull, off, f));
             last_w = __shfl_sync(kFull, w, f);
         }
         running += __shfl_sync(kFull, wi, 31);
@@ -291,11 +299,12 @@ __global__ void __launch_bounds__(kBlk, 5) k_lightprep(DScene s, DCamera cam, co
     float* sinc = cdf + 2 * s.Lpad;                                  // [2][32] inclusive scan of the lane totals
     const int warp = (blockIdx.x * kBlk + threadIdx.x) >> 5, nwarps = (gridDim.x * kBlk) >> 5;
     const bool rr_forced = max_depth > 0 && 1 >= max_depth;
-    const int K = s.Lpad >> 5;
     unsigned c_sweeps = 0;
+    unsigned c_evals = 0;  // in units of 32 (every sweep length is a multiple of 32)
     for (int pair = warp; 2 * pair < npix; pair += nwarps) {
         f3 X[2], Nn[2];
         bool shad[2];
+        int lid[2] = {-1, -1};
 #pragma unroll
         for (int v = 0; v < 2; v++) {
             const int pixel = 2 * pair + v;
@@ -308,15 +317,27 @@ __global__ void __launch_bounds__(kBlk, 5) k_lightprep(DScene s, DCamera cam, co
                     const Vertex vx = make_vertex(s, prim, ph.y, ph.z, -camera_dir(cam, pixel, 0.f, 0.f));
                     shad[v] = vx.front && vx.light < 0;
                     X[v] = vx.p; Nn[v] = vx.N;
+                    if (shad[v] && s.nlists) lid[v] = __ldg(s.prim_list + prim);
                 }
             }
         }
+        // the sweep runs over the survivor list of the pixels' primitive (light_lists.h) when both pixels share one --
+        // neighbouring pixels mostly do -- and over the whole table otherwise; n = entries swept (a multiple of 32)
+        if (!shad[0]) lid[0] = lid[1];
+        if (!shad[1]) lid[1] = lid[0];
+        const bool by_list = s.nlists && lid[0] >= 0 && lid[0] == lid[1];
+        const uint32_t* list = nullptr;
+        int n = s.Lpad;
+        if (by_list) { const int2 rg = __ldg(s.lrange + lid[0]); list = s.llist + rg.x; n = rg.y; }
+        const int K = n >> 5;
         float part[2] = {0.f, 0.f}, incl[2] = {0.f, 0.f}, total[2] = {0.f, 0.f};
         if (shad[0] || shad[1]) {
             c_sweeps += (unsigned)shad[0] + (unsigned)shad[1];
+            c_evals += (unsigned)(n >> 5) * ((unsigned)shad[0] + (unsigned)shad[1]);
             if (!shad[0]) { X[0] = X[1]; Nn[0] = Nn[1]; }
             if (!shad[1]) { X[1] = X[0]; Nn[1] = Nn[0]; }
-            warp_light_partial<2>(s, X, Nn, part, use_cdf ? cdf : nullptr);
+            if (by_list) warp_light_partial_list<2>(s, list, n, X, Nn, part, use_cdf ? cdf : nullptr, s.Lpad);
+            else warp_light_partial<2>(s, X, Nn, part, use_cdf ? cdf : nullptr);
 #pragma unroll
             for (int v = 0; v < 2; v++) {
                 incl[v] = warp_scan_incl(part[v]);
@@ -343,7 +364,7 @@ __global__ void __launch_bounds__(kBlk, 5) k_lightprep(DScene s, DCamera cam, co
                 int mine = -1;
                 float wmine = 0.f;
                 if (use_cdf) {
-                    if (need) {
+                    if (need && K > 0) {
                         const float* si = sinc + 32 * v;
                         const float target = fmaxf(u, 1e-7f) * total[v];
                         int j = 0;  // first lane whose inclusive total reaches the target
@@ -357,10 +378,12 @@ __global__ void __launch_bounds__(kBlk, 5) k_lightprep(DScene s, DCamera cam, co
                             const int mid = (lo + hi) >> 1;
                             if (col[32 * mid] < rem) lo = mid + 1; else hi = mid;
                         }
-                        mine = j + 32 * lo;
+                        const int pos = j + 32 * lo;  // position in the sweep: list entry or table index
+                        const int off = by_list ? (int)__ldg(list + pos) : lsoa_index(pos);
+                        mine = lsoa_light(off);
                         // the CDF difference only SELECTS; the weight handed on (sA = w / Lsum feeds arvo_direct) is
                         // re-evaluated, bit-identical to the sweep's and to what warp_light_pick returns at later vertices
-                        wmine = (mine < s.L) ? light_weight_fast(s, mine, X[v], Nn[v]) : 0.f;
+                        wmine = (mine < s.L) ? light_weight_at(s, off, X[v], Nn[v]) : 0.f;
                         if (!(wmine > 0.f) || mine >= s.L) mine = -1;
                     }
                 } else {
@@ -368,7 +391,9 @@ __global__ void __launch_bounds__(kBlk, 5) k_lightprep(DScene s, DCamera cam, co
                     while (todo) {
                         const int src = __ffs(todo) - 1;
                         todo &= todo - 1;
-                        const LightPick pk = warp_light_pick(s, X[v], Nn[v], part[v], incl[v], total[v], __shfl_sync(kFull, u, src));
+                        const float us = __shfl_sync(kFull, u, src);
+                        const LightPick pk = by_list ? warp_light_pick<true>(s, list, n, X[v], Nn[v], part[v], incl[v], total[v], us)
+                                                     : warp_light_pick<false>(s, nullptr, s.L, X[v], Nn[v], part[v], incl[v], total[v], us);
                         if (lane == src) { mine = pk.light; wmine = pk.w; }
                     }
                 }
@@ -377,7 +402,10 @@ __global__ void __launch_bounds__(kBlk, 5) k_lightprep(DScene s, DCamera cam, co
         }
         __syncwarp();  // the next pair overwrites cdf / sinc
     }
-    if (lane == 0 && c_sweeps) atomicAdd(counters + CNT_SWEEPS, (unsigned long long)c_sweeps);  // vertices whose light table was swept
+    if (lane == 0 && c_sweeps) {
+        atomicAdd(counters + CNT_SWEEPS, (unsigned long long)c_sweeps);  // vertices whose light table was swept
+        atomicAdd(counters + CNT_EVALS, (unsigned long long)c_evals * 32);  // (light, vertex) weights evaluated for them
+    }
 }
 
 // ---- light selection at the later vertices ---------------------------------------------------------------------
@@ -407,18 +435,20 @@ __global__ void __launch_bounds__(kBlk, MCPT_SEL_MINBLK) k_lightsel(const Bounce
     f3 PX = mk<float>(0.f, 0.f, 0.f), PN = mk<float>(0.f, 0.f, 1.f);
     float Pu = 0.f;
     int Pi = -1;
+    unsigned c_evals = 0;  // in units of 32
     auto sweep_pair = [&](f3 X0, f3 N0, float u0, int i0, bool two, f3 X1, f3 N1, float u1, int i1) {
         f3 X[2] = {X0, two ? X1 : X0}, Nn[2] = {N0, two ? N1 : N0};
         const float uu[2] = {u0, u1};
         const int ii[2] = {i0, i1};
         float part[2];
         warp_light_partial<2>(s, X, Nn, part);
+        c_evals += (unsigned)(s.Lpad >> 5) * (two ? 2u : 1u);
 #pragma unroll
         for (int v = 0; v < 2; v++) {
             if (v == 1 && !two) break;
             const float incl = warp_scan_incl(part[v]);
             const float total = __shfl_sync(kFull, incl, 31);
-            const LightPick pk = warp_light_pick(s, X[v], Nn[v], part[v], incl, total, uu[v]);
+            const LightPick pk = warp_light_pick<false>(s, nullptr, s.L, X[v], Nn[v], part[v], incl, total, uu[v]);
             if (lane == 0) a.sel4[ii[v]] = make_float4(__int_as_float(pk.light), pk.w, total, 0.f);
         }
     };
@@ -487,6 +517,232 @@ __global__ void __launch_bounds__(kBlk, MCPT_SEL_MINBLK) k_lightsel(const Bounce
         }
     }
     if (pend) sweep_pair(PX, PN, Pu, Pi, false, PX, PN, Pu, Pi);
+    if (lane == 0 && c_evals) atomicAdd(a.counters + CNT_EVALS, (unsigned long long)c_evals * 32);
+}
+
+// ---- the same selection over per-primitive survivor lists (light_lists.h) ---------------------------------------------
+// About half of the lights are culled at EVERY vertex of a given primitive (they face away from all of it, or lie below its
+// horizon everywhere): the scene carries, per primitive, the list of the others.  A sweep over the list instead of the
+// table halves the evaluations -- but a packed sweep serves a group of vertices with ONE list, so the vertices that sample
+// a light are first grouped by list:
+//   k_lsel_classify   per queue entry: does its vertex sample a light (same decisions as k_lightsel)?  key[i] = its list,
+//                     histogram of the lists (one atomic per distinct list per warp)
+//   k_lsel_offsets    one block: exclusive scan of the counts, each rounded up to whole groups of kSelV; the slack is
+//                     filled with -1
+//   k_lsel_scatter    queue indices into their list's run (order inside a run is whatever the atomics give: the result
+//                     for a vertex depends on its own list only, never on its neighbours in the group)
+//   k_lightsel_sorted persistent warps, one group of kSelV vertices of one list per ticket: rebuild the vertices, sweep
+//                     the list for all of them at once (the loads of a light serve 2 x kSelV/2 packed evaluations),
+//                     scan, pick, sel4[i]
+// Weights, weights_sum and probabilities are those of the full sweep up to the order of the FP32 additions.
+#ifndef MCPT_SEL_V
+#define MCPT_SEL_V 4
+#endif
+constexpr int kSelV = MCPT_SEL_V;
+
+// the vertex of in-queue ray i if it samples a light: the decisions k_shade takes before light sampling, repeated
+template <int STRAT>
+__device__ __forceinline__ bool sel_vertex(const BounceArgs& a, int i, bool rr_forced, bool want_u, f3* p, f3* N, float* u, int* prim_out)
+{
+    constexpr bool kTree = (STRAT == MCPT_MIS);
+    const float4 qh = a.hit[i];
+    const int prim = __float_as_int(qh.x);
+    if (prim < 0) return false;
+    const float4 qd = a.in.dir[i];
+    const Vertex v = make_vertex(a.s, prim, qh.y, qh.z, -to_f3(qd));
+    if (!(v.front && v.light < 0)) return false;
+    const int slot = __float_as_int(qd.w);
+    const uint32_t pixel = (uint32_t)(slot % a.npix), sample = (uint32_t)(a.sample_base + slot / a.npix);
+    uint64_t node = (uint64_t)a.bounce + 1;
+    if (kTree) { const uint2 nd = a.in.node[i]; node = ((uint64_t)nd.y << 32) | nd.x; }
+    // MIS (both forms): roulette before any sampling (main.cpp:429-437); NEE samples the light first (:300-316)
+    if (kTree || STRAT == MCPT_MIS_SINGLE)
+        if (rr_forced || rng_draw4(a.seed, pixel, sample, node, 0).u[0] > a.p_rr) return false;
+    if (want_u) *u = rng_draw4(a.seed, pixel, sample, node, 1).u[0];
+    *p = v.p; *N = v.N; *prim_out = prim;
+    return true;
+}
+
+template <int STRAT>
+__global__ void __launch_bounds__(256) k_lsel_classify(const BounceArgs a)
+{
+    const bool rr_forced = a.max_depth > 0 && a.bounce + 1 >= a.max_depth;
+    const int lane = threadIdx.x & 31;
+    for (int base = (blockIdx.x * 256 + threadIdx.x) & ~31; base < a.in_count; base += gridDim.x * 256) {
+        const int i = base + lane;
+        int k = -1;
+        if (i < a.in_count) {
+            f3 p, N;
+            float u;
+            int prim;
+            if (sel_vertex<STRAT>(a, i, rr_forced, false, &p, &N, &u, &prim)) k = __ldg(a.s.prim_list + prim);
+            else a.sel4[i] = make_float4(__int_as_float(-1), 0.f, 0.f, 0.f);
+            a.skey[i] = k;
+        }
+        const unsigned act = __ballot_sync(kFull, k >= 0);
+        if (k >= 0) {
+            const unsigned peers = __match_any_sync(act, k);
+            if (lane == __ffs(peers) - 1) atomicAdd(a.lhist + k, __popc(peers));
+        }
+    }
+}
+
+__global__ void __launch_bounds__(1024) k_lsel_offsets(int* __restrict__ hist, int nlists, int* __restrict__ sorted, int* __restrict__ ngroups)
+{
+    __shared__ int s_warp[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int per = (nlists + 1023) / 1024, l0 = tid * per, l1 = min(nlists, l0 + per);
+    int mine = 0;
+    for (int l = l0; l < l1; l++) mine += (hist[l] + kSelV - 1) / kSelV * kSelV;
+    int incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(kFull, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        int w = s_warp[lane], wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int t = __shfl_up_sync(kFull, wi, o);
+            if (lane >= o) wi += t;
+        }
+        s_warp[lane] = wi - w;
+        if (lane == 31) *ngroups = wi / kSelV;
+    }
+    __syncthreads();
+    int at = s_warp[warp] + incl - mine;
+    for (int l = l0; l < l1; l++) {
+        const int c = hist[l], padded = (c + kSelV - 1) / kSelV * kSelV;
+        hist[l] = at;  // from here on: the scatter cursor of list l
+        for (int k = c; k < padded; k++) sorted[at + k] = -1;
+        at += padded;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_lsel_scatter(const BounceArgs a)
+{
+    const int lane = threadIdx.x & 31;
+    for (int base = (blockIdx.x * 256 + threadIdx.x) & ~31; base < a.in_count; base += gridDim.x * 256) {
+        const int i = base + lane;
+        const int k = i < a.in_count ? a.skey[i] : -1;
+        const unsigned act = __ballot_sync(kFull, k >= 0);
+        if (k >= 0) {
+            const unsigned peers = __match_any_sync(act, k);
+            const int leader = __ffs(peers) - 1;
+            int at = 0;
+            if (lane == leader) at = atomicAdd(a.lhist + k, __popc(peers));
+            at = __shfl_sync(peers, at, leader);
+            a.sorted[at + __popc(peers & ((1u << lane) - 1u))] = i;
+        }
+    }
+}
+
+// One ticket = 32 sorted entries = 32 / kSelV groups: all lanes rebuild one vertex each, then the groups are swept one
+// after the other.  With `cdf_stride` > 0 (dynamic shared memory, kSelV x cdf_stride floats per warp) the sweep leaves the
+// running sums of every lane's column behind, and lane v picks vertex v's light by bisection of its column -- one weight
+// re-evaluated per vertex instead of a second warp-wide pass (warp_light_pick) per vertex.
+template <int STRAT>
+__global__ void __launch_bounds__(kBlk, kSelV == 4 ? 4 : MCPT_SEL_MINBLK) k_lightsel_sorted(const BounceArgs a, int* cursor, int cdf_stride)
+{
+    extern __shared__ float sm_sel[];
+    const DScene& s = a.s;
+    const int lane = threadIdx.x & 31;
+    float* cdf = sm_sel + (threadIdx.x >> 5) * (kSelV * cdf_stride);
+    const int ngroups = *a.ngroups;
+    const int ntickets = (ngroups * kSelV + 31) >> 5;
+    const bool rr_forced = a.max_depth > 0 && a.bounce + 1 >= a.max_depth;
+    unsigned c_evals = 0;  // in units of 32
+    int next = 0;
+    if (lane == 0) next = atomicAdd(cursor, 1);
+    for (;;) {
+        const int t = __shfl_sync(kFull, next, 0);
+        if (t >= ntickets) break;
+        if (lane == 0) next = atomicAdd(cursor, 1);
+        const int e = 32 * t + lane;
+        int i = e < ngroups * kSelV ? a.sorted[e] : -1;
+        f3 p = mk<float>(0.f, 0.f, 0.f), N = mk<float>(0.f, 0.f, 1.f);
+        float u = 0.f;
+        int prim = 0, lid = 0;
+        if (i >= 0) {
+            if (sel_vertex<STRAT>(a, i, rr_forced, true, &p, &N, &u, &prim)) lid = __ldg(s.prim_list + prim);
+            else i = -1;  // cannot happen: k_lsel_classify took the same decisions
+        }
+#pragma unroll 1
+        for (int g0 = 0; g0 < 32; g0 += kSelV) {
+            const int i0 = __shfl_sync(kFull, i, g0);  // the first entry of a group always exists (k_lsel_offsets)
+            if (i0 < 0) continue;
+            const int2 rg = __ldg(s.lrange + __shfl_sync(kFull, lid, g0));
+            const uint32_t* list = s.llist + rg.x;
+            f3 X[kSelV], Nn[kSelV];
+            float uu[kSelV];
+            int ii[kSelV];
+            int nvalid = 0;
+#pragma unroll
+            for (int v = 0; v < kSelV; v++) {
+                ii[v] = __shfl_sync(kFull, i, g0 + v);
+                const int src = ii[v] >= 0 ? g0 + v : g0;
+                X[v] = mk<float>(__shfl_sync(kFull, p.x, src), __shfl_sync(kFull, p.y, src), __shfl_sync(kFull, p.z, src));
+                Nn[v] = mk<float>(__shfl_sync(kFull, N.x, src), __shfl_sync(kFull, N.y, src), __shfl_sync(kFull, N.z, src));
+                uu[v] = __shfl_sync(kFull, u, src);
+                nvalid += ii[v] >= 0;
+            }
+            float part[kSelV];
+            warp_light_partial_list<kSelV>(s, list, rg.y, X, Nn, part, cdf_stride ? cdf : nullptr, cdf_stride);
+            c_evals += (unsigned)(rg.y >> 5) * (unsigned)nvalid;
+            if (cdf_stride) {
+                // lane v resolves vertex v: lane totals -> lane j, then bisection of lane j's column of running sums
+                __syncwarp();
+                const int K = rg.y >> 5;
+                int my_i = -1, my_j = 0;
+                float my_rem = 0.f, my_total = 0.f;
+                f3 mX = X[0], mN = Nn[0];
+#pragma unroll
+                for (int v = 0; v < kSelV; v++) {
+                    const float incl = warp_scan_incl(part[v]);
+                    const float total = __shfl_sync(kFull, incl, 31);
+                    const float target = fmaxf(uu[v], 1e-7f) * total;
+                    const unsigned nz = __ballot_sync(kFull, part[v] > 0.f);
+                    const unsigned ge = __ballot_sync(kFull, incl >= target && part[v] > 0.f);
+                    const int j = ge ? (__ffs(ge) - 1) : (nz ? 31 - __clz(nz) : 0);
+                    const float rem = target - (__shfl_sync(kFull, incl, j) - __shfl_sync(kFull, part[v], j));
+                    if (lane == v) { my_i = ii[v]; my_j = j; my_rem = rem; my_total = total; mX = X[v]; mN = Nn[v]; }
+                }
+                if (lane < kSelV && my_i >= 0) {
+                    int light = -1;
+                    float w = 0.f;
+                    if (my_total > 0.f && K > 0) {
+                        const float* col = cdf + lane * cdf_stride + my_j;  // col[32 m]: running sum of lane j's entries
+                        const float rem = fminf(my_rem, col[32 * (K - 1)]);
+                        int lo = 0, hi = K - 1;
+                        while (lo < hi) {
+                            const int mid = (lo + hi) >> 1;
+                            if (col[32 * mid] < rem) lo = mid + 1; else hi = mid;
+                        }
+                        const int off = (int)__ldg(list + my_j + 32 * lo);
+                        // the running sums only SELECT; the weight handed on is evaluated again, bit-identical to the sweep's
+                        w = light_weight_at(s, off, mX, mN);
+                        light = lsoa_light(off);
+                        if (!(w > 0.f) || light >= s.L) { light = -1; w = 0.f; }
+                    }
+                    a.sel4[my_i] = make_float4(__int_as_float(light), w, my_total, 0.f);
+                }
+                __syncwarp();  // the next group overwrites the columns
+            } else {
+#pragma unroll
+                for (int v = 0; v < kSelV; v++) {
+                    if (ii[v] < 0) continue;
+                    const float incl = warp_scan_incl(part[v]);
+                    const float total = __shfl_sync(kFull, incl, 31);
+                    const LightPick pk = warp_light_pick<true>(s, list, rg.y, X[v], Nn[v], part[v], incl, total, uu[v]);
+                    if (lane == 0) a.sel4[ii[v]] = make_float4(__int_as_float(pk.light), pk.w, total, 0.f);
+                }
+            }
+        }
+    }
+    if (lane == 0 && c_evals) atomicAdd(a.counters + CNT_EVALS, (unsigned long long)c_evals * 32);
 }
 
 // ---- light selection through the light hierarchy (MCPT_LIGHT_TREE) ------------------------------------------------
@@ -1137,6 +1393,25 @@ int launch_bounce(bool first, bool exact, const BounceArgs& a, int grid, int sel
     }
     if constexpr (kSph) {
         if (a.flags & MCPT_LIGHT_TREE) k_lighttree<STRAT><<<std::max(1, std::min((a.in_count + 255) / 256, 148 * 8)), 256, 0, st>>>(a);
+        else if (a.s.nlists > 0 && a.s.L > kSerialLights) {
+            // survivor lists: group the sampling vertices by list, then sweep list by list (k_lsel_* above)
+            const int cgrid = std::max(1, std::min((a.in_count + 255) / 256, 148 * 16));
+            cudaMemsetAsync(a.lhist, 0, (size_t)a.s.nlists * 4, st);
+            k_lsel_classify<STRAT><<<cgrid, 256, 0, st>>>(a);
+            k_lsel_offsets<<<1, 1024, 0, st>>>(a.lhist, a.s.nlists, a.sorted, a.ngroups);
+            k_lsel_scatter<<<cgrid, 256, 0, st>>>(a);
+            // running-sum columns in shared memory (kSelV x list_max floats per warp) while >= 3 blocks per SM still fit
+            const size_t dyn = (size_t)(kBlk / 32) * kSelV * (size_t)a.s.list_max * sizeof(float);
+            const bool use_cdf = dyn > 0 && dyn <= 64 * 1024;
+            if (use_cdf && dyn > 48 * 1024) cudaFuncSetAttribute(k_lightsel_sorted<STRAT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+            int sb = 1;
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sb, k_lightsel_sorted<STRAT>, kBlk, use_cdf ? dyn : 0);
+            const int sgrid = std::min(std::max(1, (a.in_count + 127) / 128), 148 * std::max(1, sb));
+            k_lightsel_sorted<STRAT><<<sgrid, kBlk, use_cdf ? dyn : 0, st>>>(a, sel_cursor, use_cdf ? a.s.list_max : 0);
+            if (exact) k_shade<STRAT, false, true><<<grid, kBlk, 0, st>>>(a);
+            else k_shade<STRAT, false, false><<<grid, kBlk, 0, st>>>(a);
+            return 5;
+        }
         else k_lightsel<STRAT><<<std::min(grid, sel_grid), kBlk, 0, st>>>(a, sel_cursor);
     }
     if (exact) k_shade<STRAT, false, true><<<grid, kBlk, 0, st>>>(a);
@@ -1367,7 +1642,7 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
             else cudaGetLastError();
         }
         if (scene->ws.mem_budget) {
-            const size_t per_slot = tree ? 224 + (size_t)155 * tree_factor / 100 : 224;  // bytes of queues + staging + hit + accumulators per path slot
+            const size_t per_slot = (tree ? 224 + (size_t)155 * tree_factor / 100 : 224) + (scene->d.nlists > 0 ? (tree ? (size_t)8 * tree_factor / 100 : 8) : 0);  // bytes of queues + staging + hit + accumulators per path slot
             target = std::min(target, std::max<size_t>(npix, scene->ws.mem_budget / 2 / per_slot));
         }
     }
@@ -1396,6 +1671,9 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
     const size_t groups = (chunks + kGroup - 1) / kGroup;
     const size_t o_counts = place(chunks * 4), o_small = place(256 + groups * 4);
     const size_t o_sel = place(sph ? slots * 8 : 16), o_wsum = place(sph ? npix * 4 : 16), o_sel4 = place(sph ? cap * 16 : 16);
+    const bool lists = sph && scene->d.nlists > 0 && scene->d.L > kSerialLights && !(prm->flags & MCPT_LIGHT_TREE);
+    const size_t nl = lists ? (size_t)scene->d.nlists : 0;
+    const size_t o_skey = place(lists ? cap * 4 : 16), o_sorted = place(lists ? (cap + 4 * nl) * 4 : 16), o_lhist = place(nl * 4 + 16);
     const bool nee = prm->strategy == MCPT_NEE_SPHERICAL || prm->strategy == MCPT_NEE_UNIFORM || prm->strategy == MCPT_MIS_SINGLE;  // queues visibility rays
     const size_t o_hit = place(cap * 16);
     const size_t sqn = nee ? cap : 1;
@@ -1502,6 +1780,7 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
         a.s = scene->d; a.cam = dc;
         a.Lacc = Lacc; a.contrib = contrib; a.primary_hit = primary; a.sel = sel; a.wsum_pix = wsum_pix; a.sel4 = sel4; a.counts = counts; a.groupsum = d_groupsum; a.ticket = d_ticket;
         a.hit = hit; a.sq = SQ;
+        a.skey = (int*)(base + o_skey); a.sorted = (int*)(base + o_sorted); a.lhist = (int*)(base + o_lhist); a.ngroups = a.lhist + nl;
         a.counters = d_counters; a.seed = prm->seed; a.capacity = (int)cap; a.npix = (int)npix; a.batch_spp = b;
         a.sample_base = prm->spp_offset + done; a.max_depth = prm->max_depth; a.flags = prm->flags; a.p_rr = p_rr;
         int count = (int)(npix * (size_t)b);
@@ -1638,6 +1917,7 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
     S.rays_light = h_counters[CNT_LIGHTRAYS];
     S.primary_hits = h_counters[CNT_PRIMARY_HITS];
     S.light_sweeps = h_counters[CNT_SWEEPS];
+    S.light_evals = h_counters[CNT_EVALS];
     overflow = h_counters[CNT_OVERFLOW] != 0;
     S.ms_total = ms_total; S.ms_bounce = ms_bounce; S.ms_other = ms_total - ms_bounce;
     S.ms_shade = ms_shade; S.ms_trace = ms_bounce - ms_shade;

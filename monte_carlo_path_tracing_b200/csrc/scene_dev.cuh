@@ -15,6 +15,7 @@
 //                          the O(L) spherical-triangle weight loop (lights.cuh); Lpad = L rounded up to 64
 //   lng64 [L][3], larea64 [L], crad64 [C][3] : FP64 originals for the parity entry points
 //   ltree [2L-1][3] float4, ltree_leaf [L] : light hierarchy of MCPT_LIGHT_TREE (light_tree.h)
+//   llist, lrange [nlists], prim_list [P] : per-primitive survivor lists of the O(L) sweeps (light_lists.h)
 //   class_begin [C+1], class_cdf [C], tri_cdf [L] : the two discrete distributions of
 //                          select_a_point_from_lights (Mylight.cpp:112-135) as normalised cumulative tables
 #pragma once
@@ -44,6 +45,11 @@ struct DScene {
     const float* tri_cdf;
     const float4* ltree;        // [2L-1][3] light hierarchy nodes (light_tree.h), node 0 = root
     const int32_t* ltree_leaf;  // [L] leaf node of each light
+    const uint32_t* llist;      // per-primitive survivor lists of the light sweeps (light_lists.h): lsoa offsets
+    const int2* lrange;         // [nlists] first entry | padded count (multiple of 32)
+    const int32_t* prim_list;   // [P] list of each primitive, -1 for emissive ones
+    int32_t nlists;             // 0: no lists, the sweeps evaluate the whole table
+    int32_t list_max;           // longest padded list (entries)
     int32_t P, L, C, M, Lpad;
     int32_t use8;  // trace kernels walk nodes8 / tris8 (large scenes) instead of nodes4 / tris
     float tmin;  // FP32 leaf test: reject t < tmin (scene-scale aware stand-in for the reference's 1e-8)

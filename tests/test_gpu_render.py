@@ -41,9 +41,9 @@ def test_image_matches_oracle(scene_name, case, gpu_scene_of, oracle_of, arrays_
     img, st = gpu_scene_of(scene_name).render(cam, strat, spp, max_depth=DEPTH, flags=gflags, seed=3)
     assert np.isfinite(img).all()
     a = np.nan_to_num(a); b = np.nan_to_num(b)
-    noise = util.rmse(a, b)
+    noise = util.rmse_trimmed(a, b)
     ref = 0.5 * (a + b)
-    err = util.rmse(img, a)
+    err = util.rmse_trimmed(img, a)
     assert noise > 0
     # + the float32 rounding of the output image (directly visible emitters are ~1e2 brighter than the rest)
     assert err <= 1.5 * noise + 2e-7 * ref.max(), (err, noise)
