@@ -236,6 +236,24 @@ int mcpt_intersect_batch(McptScene*, size_t n, const double* ro, const double* r
  * misses the light triangle itself (the renderer queues no visibility ray then). */
 int mcpt_visibility_batch(McptScene*, size_t n, const double* ro, const double* rd, const int32_t* exclude,
                           const int32_t* light_prim, int leaf_mode, int32_t* visible);
+/* The same test for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  The call allocates nothing
+ * and frees nothing -- no cudaMalloc / cudaFree, no allocating library routine: the scratch mcpt_visibility_batch allocates
+ * per call (visibility-ray queue, per-ray accumulators, counters: 72 bytes per ray) lives in one fixed device array inside
+ * the library, sized for MCPT_NOALLOC_MAX_RAYS rays (4.5 MiB on every GPU that loads libmcpt.so, until the process exits).
+ * Inputs and outputs are the CALLER'S DEVICE buffers on the scene's device, in the layout the render queues use:
+ *   d_org [n] float4 = origin xyz | unused,   d_dir [n] float4 = unit direction xyz | unused,
+ *   d_ids [n] int2 = prim the origin lies on (excluded, -1 none) | light prim aimed at (must be < num_prims),
+ *   d_visible [n] int32 out = 1 / 0 / -1 as above.
+ * n > MCPT_NOALLOC_MAX_RAYS returns MCPT_ERR_INVALID (mcpt_last_error names the limit); n = 0 is a no-op.  The kernels are
+ * launched on `stream` (a cudaStream_t; NULL = the default stream) and the call returns WITHOUT synchronising: the results
+ * are there once the stream reaches that point.  All calls on one GPU share the scratch array, which keeps the previous
+ * call's contents (the call clears what must start at zero itself): calls in one stream are ordered and safe, calls that
+ * overlap on the GPU (two streams, two host threads) race and must be serialised by the caller.  The array's address is
+ * resolved once per device (cudaGetSymbolAddress) on the first call for that device. */
+#define MCPT_NOALLOC_MAX_RAYS 65536
+int mcpt_visibility_noalloc(McptScene*, size_t n, const void* d_org, const void* d_dir, const void* d_ids, int leaf_mode,
+                            void* d_visible, void* stream);
 /* BRDF::get_brdf_phong / sample_from_phong / eval_sample_from_phong_pdf (BRDF.cpp:17-132) */
 int mcpt_phong_eval_batch(McptScene*, size_t n, const double* N, const double* wi, const double* wr,
                           const double* kd, const double* ks, const double* ns, int precision, double* rgb);

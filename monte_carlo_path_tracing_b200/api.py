@@ -36,8 +36,11 @@ SYMBOLS = [
     "mcpt_scene_build_info", "mcpt_scene_bvh_check", "mcpt_host_light_tree_check", "mcpt_light_tree_batch",
     "mcpt_scene_light_tree_info", "mcpt_scene_light_tree_nodes", "mcpt_visibility_batch",
     "mcpt_multi_create", "mcpt_multi_device_count", "mcpt_multi_upload", "mcpt_multi_render", "mcpt_multi_destroy",
-    "mcpt_render_multi", "mcpt_multi_scene", "mcpt_measure_fp32", "mcpt_scene_trace_layout", "mcpt_scene_light_lists", "mcpt_scene_light_list_of_prim", "mcpt_host_light_lists",
+    "mcpt_render_multi", "mcpt_multi_scene", "mcpt_measure_fp32", "mcpt_scene_trace_layout", "mcpt_scene_light_lists", "mcpt_scene_light_list_of_prim", "mcpt_host_light_lists", "mcpt_visibility_noalloc",
 ]
+
+
+NOALLOC_MAX_RAYS = 65536  # include/mcpt.h MCPT_NOALLOC_MAX_RAYS
 
 
 class McptError(RuntimeError):
@@ -400,6 +403,13 @@ class Scene:
         vis = np.zeros(n, np.int32)
         _check(self.lib.mcpt_visibility_batch(self.handle, C.c_size_t(n), _p(ro), _p(rd), _p(ex), _p(lp), int(leaf_mode), _p(vis)))
         return vis
+
+    def visibility_noalloc(self, d_org: int, d_dir: int, d_ids: int, n: int, d_visible: int, leaf_mode=LEAF_FAST, stream: int = 0):
+        """mcpt_visibility_noalloc: the same test on the caller's DEVICE buffers (raw pointers: float4 org, float4 dir,
+        int2 exclude | light prim, int32 visible out), scratch in a fixed array inside the library -- no allocation,
+        at most NOALLOC_MAX_RAYS rays, launched on ``stream`` without a synchronise."""
+        _check(self.lib.mcpt_visibility_noalloc(self.handle, C.c_size_t(n), C.c_void_p(d_org), C.c_void_p(d_dir), C.c_void_p(d_ids),
+                                                int(leaf_mode), C.c_void_p(d_visible), C.c_void_p(stream)))
 
     def brdf_eval(self, N, wi, wr, kd, ks, ns, precision=FP64):
         N, wi, wr, kd, ks, ns = map(_f64, (N, wi, wr, kd, ks, ns))

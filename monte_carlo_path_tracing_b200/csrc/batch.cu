@@ -445,6 +445,17 @@ int mcpt_visibility_batch(McptScene* s, size_t n, const double* ro, const double
     });
 }
 
+int mcpt_visibility_noalloc(McptScene* s, size_t n, const void* d_org, const void* d_dir, const void* d_ids, int leaf_mode, void* d_visible,
+                            void* stream)
+{
+    return guarded([&] {
+        need(s);
+        if (leaf_mode != MCPT_LEAF_FAST && leaf_mode != MCPT_LEAF_EXACT) throw Error(MCPT_ERR_INVALID, "unknown leaf_mode");
+        if (n && (!d_org || !d_dir || !d_ids || !d_visible)) throw Error(MCPT_ERR_INVALID, "null argument");
+        visibility_noalloc_device(s, n, (const float4*)d_org, (const float4*)d_dir, (const int2*)d_ids, leaf_mode, (int*)d_visible, (cudaStream_t)stream);
+    });
+}
+
 int mcpt_phong_eval_batch(McptScene* s, size_t n, const double* N, const double* wi, const double* wr, const double* kd,
                           const double* ks, const double* ns, int precision, double* rgb)
 {

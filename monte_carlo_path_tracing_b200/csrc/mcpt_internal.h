@@ -96,6 +96,9 @@ void calibrate_trace_layout(McptScene* scene);
 // render.cu test hooks: the production trace kernels (k_extend / k_extend_exact, k_shadow / k_shadow_exact) on explicit rays
 void trace_rays_device(McptScene* scene, int n, const float4* d_org, const float4* d_dir, int leaf_mode, float4* d_hit);
 void visibility_device(McptScene* scene, int n, const float4* d_org, const float4* d_dir, const int2* d_ids, int leaf_mode, int* d_visible);
+// render.cu: the same visibility test with its scratch in a fixed file-scope device array (no allocation; launches on `stream`, no sync)
+void visibility_noalloc_device(McptScene* scene, size_t n, const float4* d_org, const float4* d_dir, const int2* d_ids, int leaf_mode,
+                               int* d_visible, cudaStream_t stream);
 void tonemap_device(McptScene* scene, const float* rgb, size_t n, double max_radiance, double gamma, uint8_t* out);
 void workspace_free(Workspace& ws);
 }  // namespace mcpt

@@ -31,6 +31,8 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <mutex>
+#include <string>
 #include "brdf.cuh"
 #include "lights.cuh"
 #include "mcpt_internal.h"
@@ -1511,6 +1513,63 @@ void visibility_device(McptScene* scene, int n, const float4* d_org, const float
     }
     cudaFree(buf);
     MCPT_CUDA(e);
+}
+
+// ---- the same visibility test without any allocation (mcpt_visibility_noalloc, include/mcpt.h) ---------------------------
+// For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it): the scratch
+// visibility_device allocates per call -- the visibility-ray queue k_shadow consumes, the per-ray accumulators, the queue
+// length / ticket / counter words -- lives in ONE file-scope device array of a fixed size, 72 bytes per ray for at most
+// MCPT_NOALLOC_MAX_RAYS rays (4.5 MiB, held by every GPU that loads the library until exit).  In host code the array's name
+// is only a stand-in for the symbol; its device address is looked up once per device with cudaGetSymbolAddress, with that
+// device current, and that pointer is what the kernels get.  Every call on a device shares the array and finds the last
+// call's contents in it: the words that must start at zero are cleared on the stream first, everything else is written
+// before it is read.  Two calls that overlap on one GPU (different streams) race on it.
+namespace {
+constexpr size_t kNoAllocBytes = (size_t)MCPT_NOALLOC_MAX_RAYS * (16 * 4 + 8) + 256;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
+constexpr int kNoAllocMaxDevices = 64;
+void* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+std::mutex g_noalloc_mutex;
+
+char* noalloc_scratch(int device)
+{
+    if (device < 0 || device >= kNoAllocMaxDevices) throw Error(MCPT_ERR_INVALID, "device index beyond the no-allocation scratch table");
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[device]) {
+        void* p = nullptr;
+        MCPT_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));  // the caller made `device` current
+        if (!p) throw Error(MCPT_ERR_CUDA, "cudaGetSymbolAddress returned a null scratch address");
+        g_noalloc_ptr[device] = p;
+    }
+    return (char*)g_noalloc_ptr[device];
+}
+}  // namespace
+
+void visibility_noalloc_device(McptScene* scene, size_t n, const float4* d_org, const float4* d_dir, const int2* d_ids, int leaf_mode,
+                               int* d_visible, cudaStream_t st)
+{
+    if (n > (size_t)MCPT_NOALLOC_MAX_RAYS)
+        throw Error(MCPT_ERR_INVALID, "mcpt_visibility_noalloc: " + std::to_string(n) + " rays exceed the fixed scratch of MCPT_NOALLOC_MAX_RAYS = " +
+                                          std::to_string(MCPT_NOALLOC_MAX_RAYS) + " rays; split the batch or use mcpt_visibility_batch");
+    if (n == 0) return;
+    MCPT_CUDA(cudaSetDevice(scene->device));
+    char* buf = noalloc_scratch(scene->device);
+    const size_t N = (size_t)MCPT_NOALLOC_MAX_RAYS;  // fixed carve-up, whatever n is
+    ShadowQueue sq;
+    sq.org = (float4*)buf; sq.dir = sq.org + N; sq.ctr = sq.dir + N;
+    float4* Lacc = sq.ctr + N;
+    sq.ids = (int2*)(Lacc + N);
+    int* small = (int*)(sq.ids + N);  // [0] count, [1] cursor, [8..] counters
+    sq.count = small;
+    MCPT_CUDA(cudaMemsetAsync(small, 0, 256, st));  // what must start at zero; Lacc[i] and visible[i] are written by k_vis_prepare
+    const int ni = (int)n, exact = leaf_mode == MCPT_LEAF_EXACT;
+    k_vis_prepare<<<(ni + 255) / 256, 256, 0, st>>>(scene->d, ni, d_org, d_dir, d_ids, exact, sq, Lacc, d_visible);
+    const int grid = std::min(148 * 8, (ni + kBlk - 1) / kBlk);
+    if (exact) k_shadow_exact<<<grid, kBlk, 0, st>>>(scene->d, sq, Lacc, (unsigned long long*)(small + 8));
+    else if (scene->d.use8) k_shadow8<<<grid, kBlk, 0, st>>>(scene->d, sq, small + 1, Lacc, (unsigned long long*)(small + 8));
+    else k_shadow<<<grid, kBlk, 0, st>>>(scene->d, sq, small + 1, Lacc, (unsigned long long*)(small + 8));
+    k_vis_finish<<<(ni + 255) / 256, 256, 0, st>>>(ni, Lacc, d_visible);
+    MCPT_CUDA(cudaGetLastError());
 }
 
 // ---- which wide BVH layout the trace kernels walk for this scene: measured, not guessed -----------------------------------
