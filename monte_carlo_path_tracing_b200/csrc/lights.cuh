@@ -278,9 +278,12 @@ __device__ __forceinline__ void warp_light_partial_list(const DScene& s, const u
 #pragma unroll
     for (int h = 0; h < V / 2; h++) { vp[h] = make_vertex2(x1[2 * h], nn[2 * h], x1[2 * h + 1], nn[2 * h + 1]); acc[h] = make_float2(0.f, 0.f); }
     const uint32_t* __restrict__ E = list + lane;
+    // the entry of the NEXT iteration is fetched one iteration ahead: the light's four loads depend on it (veach-mis: +2.4 %)
+    uint32_t e_next = n > 0 ? __ldg(E) : 0u;
 #pragma unroll kSweepUnroll
     for (int k = lane; k < n; k += 32, E += 32) {
-        const float4* __restrict__ P = s.lsoa + __ldg(E);
+        const float4* __restrict__ P = s.lsoa + e_next;
+        if (k + 32 < n) e_next = __ldg(E + 32);
         const float4 a0 = __ldg(P), a1 = __ldg(P + 32), a2 = __ldg(P + 64), a3 = __ldg(P + 96);
 #pragma unroll
         for (int h = 0; h < V / 2; h++) acc[h] = __fadd2_rn(acc[h], light_weight_pair(a0, a1, a2, a3, vp[h]));
