@@ -117,7 +117,7 @@ int mcpt_scene_light_list_of_prim(const McptScene* s, uint32_t prim, int32_t* ou
         const uint32_t* e = (const uint32_t*)(hb + ((const char*)s->d.llist - db)) + rg[0];
         int32_t n = 0;
         for (int32_t k = 0; k < rg[1]; k++) {
-            const int32_t l = (int32_t)(((e[k] >> 7) << 5) + (e[k] & 31));  // lights.cuh lsoa_light
+            const int32_t l = (int32_t)((e[k] / (uint32_t)kLsoaBlock) * 32 + (e[k] % (uint32_t)kLsoaBlock));  // lights.cuh lsoa_light
             if (l < (int32_t)s->L) { if (out_lights) out_lights[n] = l; n++; }
         }
         *count = n;
@@ -247,7 +247,7 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
                                              s->geom_normals.data(), s->light_area.data(), L, Lpad > L ? Lpad : Lpad + 64);
         if (lists.nlists && Lpad == L) Lpad += 64;
         s->nlists = lists.nlists; s->list_max = lists.max_len; s->list_entries = lists.entries.size(); s->list_fraction = lists.mean_fraction; s->list_build_ms = lists.build_ms;
-        B.off_lsoa = place((size_t)Lpad * 4 * 16);
+        B.off_lsoa = place((size_t)Lpad * kLsoaPlanes * 16);
         B.off_lng64 = place((size_t)L * 3 * 8);
         B.off_larea64 = place((size_t)L * 8);
         B.off_crad64 = place((size_t)C * 3 * 8);
@@ -306,8 +306,8 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
         float* tcdf = (float*)(hb + B.off_tri_cdf);
         for (uint32_t c = 0; c < C * 3; c++) crd[c] = s->class_radiance[c];
         f4* so = (f4*)(hb + B.off_lsoa);
-        auto sidx = [](uint32_t l, int plane) { return (size_t)(l >> 5) * 128 + (size_t)plane * 32 + (l & 31); };  // lights.cuh lsoa_index
-        for (uint32_t l = L; l < Lpad; l++) so[sidx(l, 2)].w = std::numeric_limits<float>::infinity();  // padding: always culled
+        auto sidx = [](uint32_t l, int plane) { return (size_t)(l >> 5) * kLsoaBlock + (size_t)plane * 32 + (l & 31); };  // lights.cuh lsoa_index
+        for (uint32_t l = L; l < Lpad; l++) so[sidx(l, MCPT_EDGE_FORM ? 4 : 2)].w = std::numeric_limits<float>::infinity();  // padding: always culled
         for (uint32_t l = 0; l < L; l++) {
             int32_t prim = s->light_prim[l], cls = s->light_class[l];
             const float* v = &s->positions[(size_t)prim * 9];
@@ -322,8 +322,20 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
             std::memcpy(&lt[5 * l + 1].w, &cls, 4);
             const double a2 = 2.0 * s->light_area[l];
             so[sidx(l, 0)] = f4{v[0], v[1], v[2], 0.f};
+#if MCPT_EDGE_FORM
+            // edges from the first vertex and their three dot products, rounded once from FP64 (lights.cuh: light_weight_pair)
+            double e1[3], e2[3], d11 = 0, d22 = 0, d12 = 0;
+            for (int c = 0; c < 3; c++) {
+                e1[c] = (double)(float)((double)v[3 + c] - (double)v[c]); e2[c] = (double)(float)((double)v[6 + c] - (double)v[c]);
+                d11 += e1[c] * e1[c]; d22 += e2[c] * e2[c]; d12 += e1[c] * e2[c];
+            }
+            so[sidx(l, 1)] = f4{(float)e1[0], (float)e1[1], (float)e1[2], 0.f};
+            so[sidx(l, 2)] = f4{(float)e2[0], (float)e2[1], (float)e2[2], 0.f};
+            so[sidx(l, 4)] = f4{(float)d11, (float)d22, (float)d12, (float)(1e-8 * a2)};
+#else
             so[sidx(l, 1)] = f4{v[3], v[4], v[5], 0.f};
             so[sidx(l, 2)] = f4{v[6], v[7], v[8], (float)(1e-8 * a2)};
+#endif
             so[sidx(l, 3)] = f4{-(float)(g[0] * a2), -(float)(g[1] * a2), -(float)(g[2] * a2), 2.0f * (float)(r[0] + r[1] + r[2])};
             for (int c = 0; c < 3; c++) lng[3 * l + c] = g[c];
             lar[l] = s->light_area[l];

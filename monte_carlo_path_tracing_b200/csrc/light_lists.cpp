@@ -15,7 +15,7 @@ constexpr uint32_t kMinLights = 33;            // <= 32 lights: k_lightsel's per
 constexpr uint64_t kMaxPairs = 48ull << 20;    // primitive x light tests done on the host at scene creation
 constexpr uint32_t kMaxLists = 1u << 16;       // distinct lists the counting sort of k_lsel_* is sized for
 constexpr uint64_t kMaxEntries = 24ull << 20;  // 96 MB of list entries
-inline uint32_t lsoa_offset(uint32_t l) { return ((l >> 5) << 7) + (l & 31); }  // lights.cuh lsoa_index
+inline uint32_t lsoa_offset(uint32_t l) { return (l >> 5) * (uint32_t)kLsoaBlock + (l & 31); }  // lights.cuh lsoa_index
 }  // namespace
 
 LightLists build_light_lists(const float* positions, const float* normals, const int32_t* light_of_prim, uint32_t P,

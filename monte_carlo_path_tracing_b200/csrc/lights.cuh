@@ -4,6 +4,7 @@
 #pragma once
 #include "device_math.cuh"
 #include "scene_dev.cuh"
+#include "light_lists.h"
 
 namespace mcpt {
 
@@ -135,6 +136,37 @@ __device__ __forceinline__ float dot_rn(float ax, float ay, float az, float bx, 
 {
     return __fmaf_rn(az, bz, __fmaf_rn(ay, by, __fmul_rn(ax, bx)));
 }
+#if MCPT_EDGE_FORM
+// Edge form: with e1 = v1 - v0, e2 = v2 - v0 (precomputed per light, with e1.e1, e2.e2, e1.e2) and a = v0 - x1, the
+// other two corner vectors are b = a + e1, c = a + e2, so
+//   a.b = a.a + a.e1,  a.c = a.a + a.e2,  b.c = a.a + a.e1 + a.e2 + e1.e2,  b.b = a.a + 2 a.e1 + e1.e1,  c.c likewise:
+// three dot products (a.a, a.e1, a.e2) and eight additions stand for the six subtractions and five dot products of the
+// direct form -- 47 instead of 54 packed FP32 operations per light and vertex pair.  The horizon cull needs
+// n.b = n.a + n.e1 and n.c = n.a + n.e2 only when the first vertex does not settle it.  p4 = e1.e1 | e2.e2 | e1.e2 | threshold.
+__device__ __forceinline__ float light_weight_soa(float4 p0, float4 p1, float4 p2, float4 p3, float4 p4, f3 x1, f3 n)
+{
+    const float ax = __fadd_rn(p0.x, -x1.x), ay = __fadd_rn(p0.y, -x1.y), az = __fadd_rn(p0.z, -x1.z);
+    const float num = dot_rn(p3.x, p3.y, p3.z, ax, ay, az);            // 2 area * (ng . (x1 - v0)), :178-185
+    const float ha = dot_rn(n.x, n.y, n.z, ax, ay, az);
+    const float hb = __fadd_rn(ha, dot_rn(n.x, n.y, n.z, p1.x, p1.y, p1.z)), hc = __fadd_rn(ha, dot_rn(n.x, n.y, n.z, p2.x, p2.y, p2.z));
+    const bool up = ha >= 1e-8f || fmaxf(hb, hc) >= 1e-8f;             // :187-197
+    const float aa = dot_rn(ax, ay, az, ax, ay, az);
+    const float ae1 = dot_rn(ax, ay, az, p1.x, p1.y, p1.z), ae2 = dot_rn(ax, ay, az, p2.x, p2.y, p2.z);
+    const float ab = __fadd_rn(aa, ae1), ac = __fadd_rn(aa, ae2);
+    const float bb = __fmaf_rn(2.f, ae1, __fadd_rn(aa, p4.x)), cc = __fmaf_rn(2.f, ae2, __fadd_rn(aa, p4.y));
+    const float bc = __fadd_rn(__fadd_rn(ab, ae2), p4.z);
+    const float la = __fmul_rn(aa, rsqrtf(aa)), lb = __fmul_rn(bb, rsqrtf(bb)), lc = __fmul_rn(cc, rsqrtf(cc));
+    float den = __fmul_rn(__fmul_rn(la, lb), lc);
+    den = __fmaf_rn(ab, lc, den);
+    den = __fmaf_rn(ac, lb, den);
+    den = __fmaf_rn(bc, la, den);
+    const float ad = fabsf(den);
+    const float q = __fmul_rn(fminf(ad, num), rcp_fast(fmaxf(ad, num)));
+    const float w = __fmul_rn(atan2_fix(atan_unit(q), num, den), p3.w);
+    const bool ok = num >= p4.w && up && w < CUDART_INF_F;  // w < inf also rejects NaN; w == 0 adds nothing
+    return ok ? w : 0.f;
+}
+#else
 __device__ __forceinline__ float light_weight_soa(float4 p0, float4 p1, float4 p2, float4 p3, f3 x1, f3 n)
 {
     const float ax = __fadd_rn(p0.x, -x1.x), ay = __fadd_rn(p0.y, -x1.y), az = __fadd_rn(p0.z, -x1.z);
@@ -155,17 +187,22 @@ __device__ __forceinline__ float light_weight_soa(float4 p0, float4 p1, float4 p
     const bool ok = num >= p2.w && hmax >= 1e-8f && w < CUDART_INF_F;  // w < inf also rejects NaN; w == 0 adds nothing
     return ok ? w : 0.f;
 }
+#endif
 
-// lsoa is blocked by 32 lights: [Lpad / 32][4 planes][32] float4, so one pointer with constant offsets serves a sweep
-__host__ __device__ __forceinline__ int lsoa_index(int l) { return ((l >> 5) << 7) + (l & 31); }
+// lsoa is blocked by 32 lights: [Lpad / 32][kLsoaPlanes][32] float4, so one pointer with constant offsets serves a sweep
+__host__ __device__ __forceinline__ int lsoa_index(int l) { return (l >> 5) * kLsoaBlock + (l & 31); }
 
-__host__ __device__ __forceinline__ int lsoa_light(int off) { return ((off >> 7) << 5) + (off & 31); }  // inverse of lsoa_index
+__host__ __device__ __forceinline__ int lsoa_light(int off) { return (off / kLsoaBlock) * 32 + (off % kLsoaBlock); }  // inverse of lsoa_index
 
 // weight of the light at lsoa offset `off` (what the survivor lists of light_lists.h store)
 __device__ __forceinline__ float light_weight_at(const DScene& s, int off, f3 x1, f3 n)
 {
     const float4* P = s.lsoa + off;
+#if MCPT_EDGE_FORM
+    return light_weight_soa(__ldg(P), __ldg(P + 32), __ldg(P + 64), __ldg(P + 96), __ldg(P + 128), x1, n);
+#else
     return light_weight_soa(__ldg(P), __ldg(P + 32), __ldg(P + 64), __ldg(P + 96), x1, n);
+#endif
 }
 __device__ __forceinline__ float light_weight_fast(const DScene& s, int l, f3 x1, f3 n) { return light_weight_at(s, lsoa_index(l), x1, n); }
 
@@ -190,8 +227,71 @@ __device__ __forceinline__ VertexPair2 make_vertex2(f3 xa, f3 na, f3 xb, f3 nb)
     v.nx = make_float2(na.x, nb.x); v.ny = make_float2(na.y, nb.y); v.nz = make_float2(na.z, nb.z);
     return v;
 }
-__device__ __forceinline__ float2 light_weight_pair(float4 p0, float4 p1, float4 p2, float4 p3, const VertexPair2& v)
+#if MCPT_EDGE_FORM
+struct LightRec { float4 p0, p1, p2, p3, p4; };
+__device__ __forceinline__ LightRec load_light_rec(const float4* __restrict__ P)
 {
+    LightRec r;
+    r.p0 = __ldg(P); r.p1 = __ldg(P + 32); r.p2 = __ldg(P + 64); r.p3 = __ldg(P + 96); r.p4 = __ldg(P + 128);
+    return r;
+}
+__device__ __forceinline__ float2 light_weight_pair(const LightRec& L, const VertexPair2& v)
+{
+    const float4 p1 = L.p1, p2 = L.p2, p3 = L.p3, p4 = L.p4;
+    const float2 ax = __fadd2_rn(bc2(L.p0.x), v.mx), ay = __fadd2_rn(bc2(L.p0.y), v.my), az = __fadd2_rn(bc2(L.p0.z), v.mz);
+    const float2 num = dot2_rn(bc2(p3.x), bc2(p3.y), bc2(p3.z), ax, ay, az);
+    // horizon cull (:187-197): the light counts iff ANY of its vertices is above the vertex's tangent plane.  The first
+    // vertex alone settles that for nearly every light; the other two are only looked at when some lane needs them
+    // (all 32 lanes are here together: the sweeps have warp-uniform trip counts).
+    const float2 ha = dot2_rn(v.nx, v.ny, v.nz, ax, ay, az);
+    bool up0 = ha.x >= 1e-8f, up1 = ha.y >= 1e-8f;
+    if (__any_sync(0xffffffffu, !(up0 && up1))) {
+        const float2 hb = __fadd2_rn(ha, dot2_rn(v.nx, v.ny, v.nz, bc2(p1.x), bc2(p1.y), bc2(p1.z)));
+        const float2 hc = __fadd2_rn(ha, dot2_rn(v.nx, v.ny, v.nz, bc2(p2.x), bc2(p2.y), bc2(p2.z)));
+        up0 = up0 || fmaxf(hb.x, hc.x) >= 1e-8f;
+        up1 = up1 || fmaxf(hb.y, hc.y) >= 1e-8f;
+    }
+    const float2 aa = dot2_rn(ax, ay, az, ax, ay, az);
+    const float2 ae1 = dot2_rn(ax, ay, az, bc2(p1.x), bc2(p1.y), bc2(p1.z)), ae2 = dot2_rn(ax, ay, az, bc2(p2.x), bc2(p2.y), bc2(p2.z));
+    const float2 ab = __fadd2_rn(aa, ae1), ac = __fadd2_rn(aa, ae2);
+    const float2 bb = __ffma2_rn(bc2(2.f), ae1, __fadd2_rn(aa, bc2(p4.x))), cc = __ffma2_rn(bc2(2.f), ae2, __fadd2_rn(aa, bc2(p4.y)));
+    const float2 bcd = __fadd2_rn(__fadd2_rn(ab, ae2), bc2(p4.z));
+    const float2 la = __fmul2_rn(aa, make_float2(rsqrtf(aa.x), rsqrtf(aa.y)));
+    const float2 lb = __fmul2_rn(bb, make_float2(rsqrtf(bb.x), rsqrtf(bb.y)));
+    const float2 lc = __fmul2_rn(cc, make_float2(rsqrtf(cc.x), rsqrtf(cc.y)));
+    float2 den = __fmul2_rn(__fmul2_rn(la, lb), lc);
+    den = __ffma2_rn(ab, lc, den);
+    den = __ffma2_rn(ac, lb, den);
+    den = __ffma2_rn(bcd, la, den);
+    const float adx = fabsf(den.x), ady = fabsf(den.y);
+    const float2 q = __fmul2_rn(make_float2(fminf(adx, num.x), fminf(ady, num.y)),
+                                make_float2(rcp_fast(fmaxf(adx, num.x)), rcp_fast(fmaxf(ady, num.y))));
+    const float2 s = __fmul2_rn(q, q);
+    float2 p = bc2(MCPT_ATAN_C0);
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C1));
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C2));
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C3));
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C4));
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C5));
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C6));
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C7));
+    const float2 r = __ffma2_rn(q, __fmul2_rn(p, s), q);
+    const float2 w = __fmul2_rn(make_float2(atan2_fix(r.x, num.x, den.x), atan2_fix(r.y, num.y, den.y)), bc2(p3.w));
+    const bool ok0 = num.x >= p4.w && up0 && w.x < CUDART_INF_F;
+    const bool ok1 = num.y >= p4.w && up1 && w.y < CUDART_INF_F;
+    return make_float2(ok0 ? w.x : 0.f, ok1 ? w.y : 0.f);
+}
+#else
+struct LightRec { float4 p0, p1, p2, p3; };
+__device__ __forceinline__ LightRec load_light_rec(const float4* __restrict__ P)
+{
+    LightRec r;
+    r.p0 = __ldg(P); r.p1 = __ldg(P + 32); r.p2 = __ldg(P + 64); r.p3 = __ldg(P + 96);
+    return r;
+}
+__device__ __forceinline__ float2 light_weight_pair(const LightRec& L, const VertexPair2& v)
+{
+    const float4 p0 = L.p0, p1 = L.p1, p2 = L.p2, p3 = L.p3;
     const float2 ax = __fadd2_rn(bc2(p0.x), v.mx), ay = __fadd2_rn(bc2(p0.y), v.my), az = __fadd2_rn(bc2(p0.z), v.mz);
     const float2 bx = __fadd2_rn(bc2(p1.x), v.mx), by = __fadd2_rn(bc2(p1.y), v.my), bz = __fadd2_rn(bc2(p1.z), v.mz);
     const float2 cx = __fadd2_rn(bc2(p2.x), v.mx), cy = __fadd2_rn(bc2(p2.y), v.my), cz = __fadd2_rn(bc2(p2.z), v.mz);
@@ -232,6 +332,7 @@ __device__ __forceinline__ float2 light_weight_pair(float4 p0, float4 p1, float4
     const bool ok1 = num.y >= p2.w && up1 && w.y < CUDART_INF_F;
     return make_float2(ok0 ? w.x : 0.f, ok1 ? w.y : 0.f);
 }
+#endif
 
 // Per-lane partial sums, over this lane's lights (l = lane, lane + 32, ...), of the weights seen from V = 2 or 4
 // vertices (one packed evaluation per light and vertex pair: the four 16-byte loads of a light serve all).  With `cdf` (shared memory,
@@ -253,10 +354,10 @@ __device__ __forceinline__ void warp_light_partial(const DScene& s, const f3 (&x
     for (int h = 0; h < V / 2; h++) { vp[h] = make_vertex2(x1[2 * h], n[2 * h], x1[2 * h + 1], n[2 * h + 1]); acc[h] = make_float2(0.f, 0.f); }
     const float4* __restrict__ P = s.lsoa + lane;
 #pragma unroll kSweepUnroll
-    for (int l = lane; l < s.Lpad; l += 32, P += 128) {  // Lpad is a multiple of 64
-        const float4 a0 = __ldg(P), a1 = __ldg(P + 32), a2 = __ldg(P + 64), a3 = __ldg(P + 96);
+    for (int l = lane; l < s.Lpad; l += 32, P += kLsoaBlock) {  // Lpad is a multiple of 64
+        const LightRec rec = load_light_rec(P);
 #pragma unroll
-        for (int h = 0; h < V / 2; h++) acc[h] = __fadd2_rn(acc[h], light_weight_pair(a0, a1, a2, a3, vp[h]));
+        for (int h = 0; h < V / 2; h++) acc[h] = __fadd2_rn(acc[h], light_weight_pair(rec, vp[h]));
         if (V == 2 && cdf) { cdf[l] = acc[0].x; cdf[s.Lpad + l] = acc[0].y; }
     }
 #pragma unroll
@@ -284,9 +385,9 @@ __device__ __forceinline__ void warp_light_partial_list(const DScene& s, const u
     for (int k = lane; k < n; k += 32, E += 32) {
         const float4* __restrict__ P = s.lsoa + e_next;
         if (k + 32 < n) e_next = __ldg(E + 32);
-        const float4 a0 = __ldg(P), a1 = __ldg(P + 32), a2 = __ldg(P + 64), a3 = __ldg(P + 96);
+        const LightRec rec = load_light_rec(P);
 #pragma unroll
-        for (int h = 0; h < V / 2; h++) acc[h] = __fadd2_rn(acc[h], light_weight_pair(a0, a1, a2, a3, vp[h]));
+        for (int h = 0; h < V / 2; h++) acc[h] = __fadd2_rn(acc[h], light_weight_pair(rec, vp[h]));
         if (cdf) {
 #pragma unroll
             for (int h = 0; h < V / 2; h++) { cdf[(2 * h) * cdf_stride + k] = acc[h].x; cdf[(2 * h + 1) * cdf_stride + k] = acc[h].y; }
