@@ -307,7 +307,7 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
         for (uint32_t c = 0; c < C * 3; c++) crd[c] = s->class_radiance[c];
         f4* so = (f4*)(hb + B.off_lsoa);
         auto sidx = [](uint32_t l, int plane) { return (size_t)(l >> 5) * kLsoaBlock + (size_t)plane * 32 + (l & 31); };  // lights.cuh lsoa_index
-        for (uint32_t l = L; l < Lpad; l++) so[sidx(l, MCPT_EDGE_FORM ? 4 : 2)].w = std::numeric_limits<float>::infinity();  // padding: always culled
+        for (uint32_t l = L; l < Lpad; l++) so[sidx(l, 4)].w = std::numeric_limits<float>::infinity();  // padding: always culled
         for (uint32_t l = 0; l < L; l++) {
             int32_t prim = s->light_prim[l], cls = s->light_class[l];
             const float* v = &s->positions[(size_t)prim * 9];
@@ -322,7 +322,6 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
             std::memcpy(&lt[5 * l + 1].w, &cls, 4);
             const double a2 = 2.0 * s->light_area[l];
             so[sidx(l, 0)] = f4{v[0], v[1], v[2], 0.f};
-#if MCPT_EDGE_FORM
             // edges from the first vertex and their three dot products, rounded once from FP64 (lights.cuh: light_weight_pair)
             double e1[3], e2[3], d11 = 0, d22 = 0, d12 = 0;
             for (int c = 0; c < 3; c++) {
@@ -332,10 +331,6 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
             so[sidx(l, 1)] = f4{(float)e1[0], (float)e1[1], (float)e1[2], 0.f};
             so[sidx(l, 2)] = f4{(float)e2[0], (float)e2[1], (float)e2[2], 0.f};
             so[sidx(l, 4)] = f4{(float)d11, (float)d22, (float)d12, (float)(1e-8 * a2)};
-#else
-            so[sidx(l, 1)] = f4{v[3], v[4], v[5], 0.f};
-            so[sidx(l, 2)] = f4{v[6], v[7], v[8], (float)(1e-8 * a2)};
-#endif
             so[sidx(l, 3)] = f4{-(float)(g[0] * a2), -(float)(g[1] * a2), -(float)(g[2] * a2), 2.0f * (float)(r[0] + r[1] + r[2])};
             for (int c = 0; c < 3; c++) lng[3 * l + c] = g[c];
             lar[l] = s->light_area[l];

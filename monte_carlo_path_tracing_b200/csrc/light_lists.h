@@ -25,12 +25,8 @@
 namespace mcpt {
 
 // Layout of the SoA light table `lsoa` the sweeps read (lights.cuh, filled in api.cu): blocks of 32 lights, kLsoaPlanes
-// float4 planes per block.  MCPT_EDGE_FORM = 1: v0 | e1 = v1 - v0 | e2 = v2 - v0 | -2 area ng, 2 Lsum | e1.e1, e2.e2, e1.e2,
-// cull threshold; 0: v0 | v1 | v2, threshold | -2 area ng, 2 Lsum.
-#ifndef MCPT_EDGE_FORM
-#define MCPT_EDGE_FORM 1
-#endif
-constexpr int kLsoaPlanes = MCPT_EDGE_FORM ? 5 : 4;
+// float4 planes per block: v0 | e1 = v1 - v0 | e2 = v2 - v0 | -2 area ng, 2 Lsum | e1.e1, e2.e2, e1.e2, cull threshold.
+constexpr int kLsoaPlanes = 5;
 constexpr int kLsoaBlock = 32 * kLsoaPlanes;  // float4 per block of 32 lights
 
 struct LightLists {

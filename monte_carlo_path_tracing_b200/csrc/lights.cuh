@@ -88,10 +88,10 @@ __device__ __forceinline__ V3<T> arvo_sample(const SphTri<T>& st, T xi1, T xi2)
 // where a,b,c = vertices - x1.  a.(b x c) = (v0-x1).((v1-v0) x (v2-v0)) = 2 area * ng.(v0-x1) has no
 // cancellation, so tiny lights keep full FP32 relative accuracy where alpha+beta+gamma-pi has none.
 //
-// The loop reads the SoA table `lsoa` (scene_dev.cuh): four float4 planes per block of 32 lights, so a warp's 32
-// lanes fetch 32 consecutive 16-byte vectors per plane (4 x 512 B, fully coalesced, one pointer + constant offsets):
-//   plane0 = v0 | -, plane1 = v1 | -, plane2 = v2 | cull threshold 1e-8 * 2 area,
-//   plane3 = -Ns = -2 area * ng | 2 Lsum;  padding entries have threshold = +inf and evaluate to 0.
+// The loop reads the SoA table `lsoa` (scene_dev.cuh, light_lists.h): five float4 planes per block of 32 lights, so a
+// warp's 32 lanes fetch 32 consecutive 16-byte vectors per plane (5 x 512 B, fully coalesced, one pointer + constant offsets):
+//   plane0 = v0, plane1 = e1 = v1 - v0, plane2 = e2 = v2 - v0, plane3 = -Ns = -2 area * ng | 2 Lsum,
+//   plane4 = e1.e1 | e2.e2 | e1.e2 | cull threshold 1e-8 * 2 area;  padding entries have threshold = +inf and evaluate to 0.
 // Branch-free on purpose.
 
 // atan(q) for q in [0,1]: Abramowitz & Stegun 4.4.49, |error| <= 2e-8; exact to first order as q -> 0
@@ -122,6 +122,9 @@ __device__ __forceinline__ float rcp_fast(float x)  // MUFU.RCP
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
+// |v| from v.v as x * MUFU.RSQ(x).  MUFU.SQRT would save the (packed) multiply but measured slower: veach-mis 1663 instead
+// of 1697 Msamples/s -- the sweep is co-limited by the special-function unit (8 MUFU per light and vertex pair).
+__device__ __forceinline__ float len_fast(float x) { return __fmul_rn(x, rsqrtf(x)); }
 // the octant fix-ups of atan2(y, x) for y > 0 (result in (0, pi)), given r = atan(min/max) of (|x|, y)
 __device__ __forceinline__ float atan2_fix(float r, float y, float x)
 {
@@ -136,7 +139,6 @@ __device__ __forceinline__ float dot_rn(float ax, float ay, float az, float bx, 
 {
     return __fmaf_rn(az, bz, __fmaf_rn(ay, by, __fmul_rn(ax, bx)));
 }
-#if MCPT_EDGE_FORM
 // Edge form: with e1 = v1 - v0, e2 = v2 - v0 (precomputed per light, with e1.e1, e2.e2, e1.e2) and a = v0 - x1, the
 // other two corner vectors are b = a + e1, c = a + e2, so
 //   a.b = a.a + a.e1,  a.c = a.a + a.e2,  b.c = a.a + a.e1 + a.e2 + e1.e2,  b.b = a.a + 2 a.e1 + e1.e1,  c.c likewise:
@@ -155,39 +157,17 @@ __device__ __forceinline__ float light_weight_soa(float4 p0, float4 p1, float4 p
     const float ab = __fadd_rn(aa, ae1), ac = __fadd_rn(aa, ae2);
     const float bb = __fmaf_rn(2.f, ae1, __fadd_rn(aa, p4.x)), cc = __fmaf_rn(2.f, ae2, __fadd_rn(aa, p4.y));
     const float bc = __fadd_rn(__fadd_rn(ab, ae2), p4.z);
-    const float la = __fmul_rn(aa, rsqrtf(aa)), lb = __fmul_rn(bb, rsqrtf(bb)), lc = __fmul_rn(cc, rsqrtf(cc));
+    const float la = len_fast(aa), lb = len_fast(bb), lc = len_fast(cc);
     float den = __fmul_rn(__fmul_rn(la, lb), lc);
     den = __fmaf_rn(ab, lc, den);
     den = __fmaf_rn(ac, lb, den);
     den = __fmaf_rn(bc, la, den);
     const float ad = fabsf(den);
     const float q = __fmul_rn(fminf(ad, num), rcp_fast(fmaxf(ad, num)));
-    const float w = __fmul_rn(atan2_fix(atan_unit(q), num, den), p3.w);
-    const bool ok = num >= p4.w && up && w < CUDART_INF_F;  // w < inf also rejects NaN; w == 0 adds nothing
-    return ok ? w : 0.f;
+    const float h = atan2_fix(atan_unit(q), num, den);        // half the solid angle
+    const bool ok = num >= p4.w && up && h < CUDART_INF_F;    // h < inf also rejects NaN; 0 adds nothing
+    return ok ? __fmul_rn(h, p3.w) : 0.f;
 }
-#else
-__device__ __forceinline__ float light_weight_soa(float4 p0, float4 p1, float4 p2, float4 p3, f3 x1, f3 n)
-{
-    const float ax = __fadd_rn(p0.x, -x1.x), ay = __fadd_rn(p0.y, -x1.y), az = __fadd_rn(p0.z, -x1.z);
-    const float bx = __fadd_rn(p1.x, -x1.x), by = __fadd_rn(p1.y, -x1.y), bz = __fadd_rn(p1.z, -x1.z);
-    const float cx = __fadd_rn(p2.x, -x1.x), cy = __fadd_rn(p2.y, -x1.y), cz = __fadd_rn(p2.z, -x1.z);
-    const float num = dot_rn(p3.x, p3.y, p3.z, ax, ay, az);            // 2 area * (ng . (x1 - v0)), :178-185
-    const float hmax = fmaxf(dot_rn(n.x, n.y, n.z, ax, ay, az),
-                             fmaxf(dot_rn(n.x, n.y, n.z, bx, by, bz), dot_rn(n.x, n.y, n.z, cx, cy, cz)));  // :187-197
-    const float aa = dot_rn(ax, ay, az, ax, ay, az), bb = dot_rn(bx, by, bz, bx, by, bz), cc = dot_rn(cx, cy, cz, cx, cy, cz);
-    const float la = __fmul_rn(aa, rsqrtf(aa)), lb = __fmul_rn(bb, rsqrtf(bb)), lc = __fmul_rn(cc, rsqrtf(cc));
-    float den = __fmul_rn(__fmul_rn(la, lb), lc);
-    den = __fmaf_rn(dot_rn(ax, ay, az, bx, by, bz), lc, den);
-    den = __fmaf_rn(dot_rn(ax, ay, az, cx, cy, cz), lb, den);
-    den = __fmaf_rn(dot_rn(bx, by, bz, cx, cy, cz), la, den);
-    const float ad = fabsf(den);
-    const float q = __fmul_rn(fminf(ad, num), rcp_fast(fmaxf(ad, num)));
-    const float w = __fmul_rn(atan2_fix(atan_unit(q), num, den), p3.w);
-    const bool ok = num >= p2.w && hmax >= 1e-8f && w < CUDART_INF_F;  // w < inf also rejects NaN; w == 0 adds nothing
-    return ok ? w : 0.f;
-}
-#endif
 
 // lsoa is blocked by 32 lights: [Lpad / 32][kLsoaPlanes][32] float4, so one pointer with constant offsets serves a sweep
 __host__ __device__ __forceinline__ int lsoa_index(int l) { return (l >> 5) * kLsoaBlock + (l & 31); }
@@ -198,11 +178,7 @@ __host__ __device__ __forceinline__ int lsoa_light(int off) { return (off / kLso
 __device__ __forceinline__ float light_weight_at(const DScene& s, int off, f3 x1, f3 n)
 {
     const float4* P = s.lsoa + off;
-#if MCPT_EDGE_FORM
     return light_weight_soa(__ldg(P), __ldg(P + 32), __ldg(P + 64), __ldg(P + 96), __ldg(P + 128), x1, n);
-#else
-    return light_weight_soa(__ldg(P), __ldg(P + 32), __ldg(P + 64), __ldg(P + 96), x1, n);
-#endif
 }
 __device__ __forceinline__ float light_weight_fast(const DScene& s, int l, f3 x1, f3 n) { return light_weight_at(s, lsoa_index(l), x1, n); }
 
@@ -214,6 +190,7 @@ __device__ __forceinline__ float light_weight_fast(const DScene& s, int l, f3 x1
 // polynomial constants are broadcast operands.  Only min/max, the three reciprocal square roots, the reciprocal
 // (MUFU) and the final selects stay scalar.  Same operations in the same order as light_weight_soa.
 __device__ __forceinline__ float2 bc2(float a) { return make_float2(a, a); }
+__device__ __forceinline__ float2 len2_fast(float2 x) { return __fmul2_rn(x, make_float2(rsqrtf(x.x), rsqrtf(x.y))); }
 __device__ __forceinline__ float2 dot2_rn(float2 ax, float2 ay, float2 az, float2 bx, float2 by, float2 bz)
 {
     return __ffma2_rn(az, bz, __ffma2_rn(ay, by, __fmul2_rn(ax, bx)));
@@ -227,7 +204,6 @@ __device__ __forceinline__ VertexPair2 make_vertex2(f3 xa, f3 na, f3 xb, f3 nb)
     v.nx = make_float2(na.x, nb.x); v.ny = make_float2(na.y, nb.y); v.nz = make_float2(na.z, nb.z);
     return v;
 }
-#if MCPT_EDGE_FORM
 struct LightRec { float4 p0, p1, p2, p3, p4; };
 __device__ __forceinline__ LightRec load_light_rec(const float4* __restrict__ P)
 {
@@ -256,9 +232,7 @@ __device__ __forceinline__ float2 light_weight_pair(const LightRec& L, const Ver
     const float2 ab = __fadd2_rn(aa, ae1), ac = __fadd2_rn(aa, ae2);
     const float2 bb = __ffma2_rn(bc2(2.f), ae1, __fadd2_rn(aa, bc2(p4.x))), cc = __ffma2_rn(bc2(2.f), ae2, __fadd2_rn(aa, bc2(p4.y)));
     const float2 bcd = __fadd2_rn(__fadd2_rn(ab, ae2), bc2(p4.z));
-    const float2 la = __fmul2_rn(aa, make_float2(rsqrtf(aa.x), rsqrtf(aa.y)));
-    const float2 lb = __fmul2_rn(bb, make_float2(rsqrtf(bb.x), rsqrtf(bb.y)));
-    const float2 lc = __fmul2_rn(cc, make_float2(rsqrtf(cc.x), rsqrtf(cc.y)));
+    const float2 la = len2_fast(aa), lb = len2_fast(bb), lc = len2_fast(cc);
     float2 den = __fmul2_rn(__fmul2_rn(la, lb), lc);
     den = __ffma2_rn(ab, lc, den);
     den = __ffma2_rn(ac, lb, den);
@@ -276,63 +250,17 @@ __device__ __forceinline__ float2 light_weight_pair(const LightRec& L, const Ver
     p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C6));
     p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C7));
     const float2 r = __ffma2_rn(q, __fmul2_rn(p, s), q);
-    const float2 w = __fmul2_rn(make_float2(atan2_fix(r.x, num.x, den.x), atan2_fix(r.y, num.y, den.y)), bc2(p3.w));
-    const bool ok0 = num.x >= p4.w && up0 && w.x < CUDART_INF_F;
-    const bool ok1 = num.y >= p4.w && up1 && w.y < CUDART_INF_F;
-    return make_float2(ok0 ? w.x : 0.f, ok1 ? w.y : 0.f);
+    // half the solid angle, 0 where the light is culled; the caller multiplies by 2 Lsum and accumulates in one FFMA2
+    const float hx = atan2_fix(r.x, num.x, den.x), hy = atan2_fix(r.y, num.y, den.y);
+    const bool ok0 = num.x >= p4.w && up0 && hx < CUDART_INF_F;
+    const bool ok1 = num.y >= p4.w && up1 && hy < CUDART_INF_F;
+    return make_float2(ok0 ? hx : 0.f, ok1 ? hy : 0.f);
 }
-#else
-struct LightRec { float4 p0, p1, p2, p3; };
-__device__ __forceinline__ LightRec load_light_rec(const float4* __restrict__ P)
+// acc += weight of light L seen from the two vertices of v (weight = half solid angle x 2 Lsum)
+__device__ __forceinline__ float2 light_weight_pair_acc(const LightRec& L, const VertexPair2& v, float2 acc)
 {
-    LightRec r;
-    r.p0 = __ldg(P); r.p1 = __ldg(P + 32); r.p2 = __ldg(P + 64); r.p3 = __ldg(P + 96);
-    return r;
+    return __ffma2_rn(light_weight_pair(L, v), bc2(L.p3.w), acc);
 }
-__device__ __forceinline__ float2 light_weight_pair(const LightRec& L, const VertexPair2& v)
-{
-    const float4 p0 = L.p0, p1 = L.p1, p2 = L.p2, p3 = L.p3;
-    const float2 ax = __fadd2_rn(bc2(p0.x), v.mx), ay = __fadd2_rn(bc2(p0.y), v.my), az = __fadd2_rn(bc2(p0.z), v.mz);
-    const float2 bx = __fadd2_rn(bc2(p1.x), v.mx), by = __fadd2_rn(bc2(p1.y), v.my), bz = __fadd2_rn(bc2(p1.z), v.mz);
-    const float2 cx = __fadd2_rn(bc2(p2.x), v.mx), cy = __fadd2_rn(bc2(p2.y), v.my), cz = __fadd2_rn(bc2(p2.z), v.mz);
-    const float2 num = dot2_rn(bc2(p3.x), bc2(p3.y), bc2(p3.z), ax, ay, az);
-    // horizon cull (:187-197): the light counts iff ANY of its vertices is above the vertex's tangent plane.  The first
-    // vertex alone settles that for nearly every light; the other two are only looked at when some lane needs them
-    // (all 32 lanes are here together: the sweeps have warp-uniform trip counts).
-    const float2 ha = dot2_rn(v.nx, v.ny, v.nz, ax, ay, az);
-    bool up0 = ha.x >= 1e-8f, up1 = ha.y >= 1e-8f;
-    if (__any_sync(0xffffffffu, !(up0 && up1))) {
-        const float2 hb = dot2_rn(v.nx, v.ny, v.nz, bx, by, bz), hc = dot2_rn(v.nx, v.ny, v.nz, cx, cy, cz);
-        up0 = up0 || fmaxf(hb.x, hc.x) >= 1e-8f;
-        up1 = up1 || fmaxf(hb.y, hc.y) >= 1e-8f;
-    }
-    const float2 aa = dot2_rn(ax, ay, az, ax, ay, az), bb = dot2_rn(bx, by, bz, bx, by, bz), cc = dot2_rn(cx, cy, cz, cx, cy, cz);
-    const float2 la = __fmul2_rn(aa, make_float2(rsqrtf(aa.x), rsqrtf(aa.y)));
-    const float2 lb = __fmul2_rn(bb, make_float2(rsqrtf(bb.x), rsqrtf(bb.y)));
-    const float2 lc = __fmul2_rn(cc, make_float2(rsqrtf(cc.x), rsqrtf(cc.y)));
-    float2 den = __fmul2_rn(__fmul2_rn(la, lb), lc);
-    den = __ffma2_rn(dot2_rn(ax, ay, az, bx, by, bz), lc, den);
-    den = __ffma2_rn(dot2_rn(ax, ay, az, cx, cy, cz), lb, den);
-    den = __ffma2_rn(dot2_rn(bx, by, bz, cx, cy, cz), la, den);
-    const float adx = fabsf(den.x), ady = fabsf(den.y);
-    const float2 q = __fmul2_rn(make_float2(fminf(adx, num.x), fminf(ady, num.y)),
-                                make_float2(rcp_fast(fmaxf(adx, num.x)), rcp_fast(fmaxf(ady, num.y))));
-    const float2 s = __fmul2_rn(q, q);
-    float2 p = bc2(MCPT_ATAN_C0);
-    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C1));
-    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C2));
-    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C3));
-    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C4));
-    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C5));
-    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C6));
-    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C7));
-    const float2 r = __ffma2_rn(q, __fmul2_rn(p, s), q);
-    const float2 w = __fmul2_rn(make_float2(atan2_fix(r.x, num.x, den.x), atan2_fix(r.y, num.y, den.y)), bc2(p3.w));
-    const bool ok0 = num.x >= p2.w && up0 && w.x < CUDART_INF_F;
-    const bool ok1 = num.y >= p2.w && up1 && w.y < CUDART_INF_F;
-    return make_float2(ok0 ? w.x : 0.f, ok1 ? w.y : 0.f);
-}
-#endif
 
 // Per-lane partial sums, over this lane's lights (l = lane, lane + 32, ...), of the weights seen from V = 2 or 4
 // vertices (one packed evaluation per light and vertex pair: the four 16-byte loads of a light serve all).  With `cdf` (shared memory,
@@ -357,7 +285,7 @@ __device__ __forceinline__ void warp_light_partial(const DScene& s, const f3 (&x
     for (int l = lane; l < s.Lpad; l += 32, P += kLsoaBlock) {  // Lpad is a multiple of 64
         const LightRec rec = load_light_rec(P);
 #pragma unroll
-        for (int h = 0; h < V / 2; h++) acc[h] = __fadd2_rn(acc[h], light_weight_pair(rec, vp[h]));
+        for (int h = 0; h < V / 2; h++) acc[h] = light_weight_pair_acc(rec, vp[h], acc[h]);
         if (V == 2 && cdf) { cdf[l] = acc[0].x; cdf[s.Lpad + l] = acc[0].y; }
     }
 #pragma unroll
@@ -387,7 +315,7 @@ __device__ __forceinline__ void warp_light_partial_list(const DScene& s, const u
         if (k + 32 < n) e_next = __ldg(E + 32);
         const LightRec rec = load_light_rec(P);
 #pragma unroll
-        for (int h = 0; h < V / 2; h++) acc[h] = __fadd2_rn(acc[h], light_weight_pair(rec, vp[h]));
+        for (int h = 0; h < V / 2; h++) acc[h] = light_weight_pair_acc(rec, vp[h], acc[h]);
         if (cdf) {
 #pragma unroll
             for (int h = 0; h < V / 2; h++) { cdf[(2 * h) * cdf_stride + k] = acc[h].x; cdf[(2 * h + 1) * cdf_stride + k] = acc[h].y; }

@@ -646,8 +646,11 @@ __global__ void __launch_bounds__(256) k_lsel_scatter(const BounceArgs a)
 // after the other.  With `cdf_stride` > 0 (dynamic shared memory, kSelV x cdf_stride floats per warp) the sweep leaves the
 // running sums of every lane's column behind, and lane v picks vertex v's light by bisection of its column -- one weight
 // re-evaluated per vertex instead of a second warp-wide pass (warp_light_pick) per vertex.
+#ifndef MCPT_SORTED_MINBLK
+#define MCPT_SORTED_MINBLK (kSelV == 4 ? 4 : MCPT_SEL_MINBLK)
+#endif
 template <int STRAT>
-__global__ void __launch_bounds__(kBlk, kSelV == 4 ? 4 : MCPT_SEL_MINBLK) k_lightsel_sorted(const BounceArgs a, int* cursor, int cdf_stride)
+__global__ void __launch_bounds__(kBlk, MCPT_SORTED_MINBLK) k_lightsel_sorted(const BounceArgs a, int* cursor, int cdf_stride)
 {
     extern __shared__ float sm_sel[];
     const DScene& s = a.s;
@@ -1384,6 +1387,9 @@ __global__ void k_tonemap(const float* __restrict__ rgb, size_t n3, double A, do
     out[i] = (uint8_t)(v > 255 ? 255 : (v < 0 ? 0 : v));
 }
 
+// experiment knob (tools/diag/overlap_probe.py): resident blocks per SM of the persistent kernels divided by this, so that
+// two renders on two streams can share the SMs
+static int g_grid_div = 1;
 template <int STRAT>
 int launch_bounce(bool first, bool exact, const BounceArgs& a, int grid, int sel_grid, int* sel_cursor, cudaStream_t st)
 {
@@ -1408,7 +1414,7 @@ int launch_bounce(bool first, bool exact, const BounceArgs& a, int grid, int sel
             if (use_cdf && dyn > 48 * 1024) cudaFuncSetAttribute(k_lightsel_sorted<STRAT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
             int sb = 1;
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sb, k_lightsel_sorted<STRAT>, kBlk, use_cdf ? dyn : 0);
-            const int sgrid = std::min(std::max(1, (a.in_count + 127) / 128), 148 * std::max(1, sb));
+            const int sgrid = std::min(std::max(1, (a.in_count + 127) / 128), 148 * std::max(1, sb / g_grid_div));
             k_lightsel_sorted<STRAT><<<sgrid, kBlk, use_cdf ? dyn : 0, st>>>(a, sel_cursor, use_cdf ? a.s.list_max : 0);
             if (exact) k_shade<STRAT, false, true><<<grid, kBlk, 0, st>>>(a);
             else k_shade<STRAT, false, false><<<grid, kBlk, 0, st>>>(a);
@@ -1799,14 +1805,16 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
               : prm->strategy == MCPT_MIS         ? bounce_blocks_per_sm<MCPT_MIS>()
               : prm->strategy == MCPT_MIS_SINGLE  ? bounce_blocks_per_sm<MCPT_MIS_SINGLE>()
                                                   : bounce_blocks_per_sm<MCPT_NEE_UNIFORM>();
-    const int max_grid = sms * bps;
+    if (const char* e = std::getenv("MCPT_GRID_DIV")) g_grid_div = std::max(1, std::atoi(e));
+    const int gdiv = g_grid_div;
+    const int max_grid = sms * std::max(1, bps / gdiv);
     bool use8 = scene->d.use8 != 0;
     int ebps = 1, sbps = 1, ebps8 = 1, sbps8 = 1;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ebps8, k_extend8, kBlk, 0);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sbps8, k_shadow8, kBlk, 0);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ebps, k_extend, kBlk, 0);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sbps, k_shadow, kBlk, 0);
-    const int ext_grid4 = sms * std::max(1, ebps), sh_grid4 = sms * std::max(1, sbps), ext_grid8 = sms * std::max(1, ebps8), sh_grid8 = sms * std::max(1, sbps8);
+    const int ext_grid4 = sms * std::max(1, ebps / gdiv), sh_grid4 = sms * std::max(1, sbps / gdiv), ext_grid8 = sms * std::max(1, ebps8 / gdiv), sh_grid8 = sms * std::max(1, sbps8 / gdiv);
     int ext_grid = use8 ? ext_grid8 : ext_grid4, sh_grid = use8 ? sh_grid8 : sh_grid4;
     // The layout guess of scene creation (random rays) is settled on the first real bounce: the rays a render makes are
     // more coherent than the calibration batch, which shifts the balance towards the 4-wide nodes on some scenes (interior).
@@ -1815,7 +1823,7 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
     if (prm->strategy == MCPT_MIS) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&lbps, k_lightsel<MCPT_MIS>, kBlk, 0);
     else if (prm->strategy == MCPT_NEE_SPHERICAL) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&lbps, k_lightsel<MCPT_NEE_SPHERICAL>, kBlk, 0);
     else if (prm->strategy == MCPT_MIS_SINGLE) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&lbps, k_lightsel<MCPT_MIS_SINGLE>, kBlk, 0);
-    const int sel_grid = sms * std::max(1, lbps);
+    const int sel_grid = sms * std::max(1, lbps / gdiv);
 
     McptStats S;
     std::memset(&S, 0, sizeof S);
@@ -1853,7 +1861,7 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
             int pbps = 1;
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pbps, k_lightprep, kBlk, dyn);
             const size_t npairs = (npix + 1) / 2;
-            const int pgrid = (int)std::min<size_t>((npairs + kBlk / 32 - 1) / (kBlk / 32), (size_t)sms * std::max(1, pbps));
+            const int pgrid = (int)std::min<size_t>((npairs + kBlk / 32 - 1) / (kBlk / 32), (size_t)sms * std::max(1, pbps / gdiv));
             k_lightprep<<<pgrid, kBlk, dyn, st>>>(scene->d, dc, primary, (int)npix, b, a.sample_base, prm->seed, p_rr, (tree || single) ? 1 : 0,
                                                   prm->max_depth, use_cdf, sel, wsum_pix, d_counters);
             MCPT_CUDA(cudaGetLastError());
