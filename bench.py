@@ -349,6 +349,16 @@ def run_ours(args, wl_name, wl):
             dist.barrier()
             torch.cuda.synchronize()
 
+    # A second, host-side group: while rank 0 drives all N devices through mcpt_multi_* (the e2e leg) the other ranks must
+    # wait on the CPU.  An NCCL barrier is a kernel that spins on the waiting rank's GPU, and a GPU shared by two processes is
+    # time-sliced between them: measured at N = 2, it halved the rate of the device rank 0 was rendering on.
+    cpu_group = dist.new_group(backend="gloo") if world > 1 else None
+
+    def host_barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier(group=cpu_group)
+
     for k in range(args.warmup):
         step(k)
     sync()
@@ -413,7 +423,7 @@ def run_ours(args, wl_name, wl):
         scene = None
         del film
         torch.cuda.empty_cache()
-        sync()
+        host_barrier()
         e2e_s = 0.0
         if rank == 0:
             multi = api.MultiScene(arrays, list(range(world)), build=api.BUILD_GPU_LBVH if args.bvh == "gpu" else api.BUILD_HOST_SAH)
@@ -425,7 +435,7 @@ def run_ours(args, wl_name, wl):
                 multi.render(cam, strategy, S * world, spp_offset=k * S * world, spp_total=S * world, out=pinned_np, **kw)
             e2e_s = time.perf_counter() - t0
             multi.close()
-        sync()
+        host_barrier()
 
     # ---- config 3 strong-scaled (BASELINE.json configs[2]): interior stand-in, 1280x720, 4096 spp split over the N GPUs
     if not args.no_extras and wl_name == "veach-mis":
