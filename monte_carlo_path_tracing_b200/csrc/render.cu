@@ -861,6 +861,15 @@ constexpr int kChunk = 256;  // queue entries per warp ticket / staging window (
 #endif
 // EXACT (MCPT_LEAF_EXACT): the two ray/triangle tests k_shade makes itself -- the sampled light point's distance and the
 // MIS light-only ray -- go through the reference's FP64 test like every other ray of the render.
+#ifndef MCPT_SHADE_PREFETCH
+#define MCPT_SHADE_PREFETCH 1
+#endif
+#ifndef MCPT_PREFETCH_AHEAD
+#define MCPT_PREFETCH_AHEAD 512
+#endif
+constexpr int kPrefetchAhead = MCPT_PREFETCH_AHEAD;
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 template <int STRAT, bool FIRST, bool EXACT>
 __global__ void __launch_bounds__(kBlk, (STRAT == MCPT_MIS && !EXACT) ? 5 : MCPT_SHADE_MINBLK) k_shade(const BounceArgs a)
 {
@@ -886,6 +895,19 @@ __global__ void __launch_bounds__(kBlk, (STRAT == MCPT_MIS && !EXACT) ? 5 : MCPT
         const int chunk = __shfl_sync(kFull, next, 0);
         if (chunk >= nchunks) break;
         if (lane == 0) next = atomicAdd(a.ticket, 1);  // prefetch the next ticket behind this chunk's work
+#if MCPT_SHADE_PREFETCH
+        if (!FIRST) {
+            // phase A is a dependent chain per 32 entries (queue record -> vertex gather -> accumulator) at 20 warps per SM:
+            // bound by DRAM latency (ncu: 10 of 15 warp-cycles per issue on the long scoreboard).  Whoever takes the chunk
+            // kPrefetchAhead tickets from here (a few microseconds away) finds its queue records in L2: one line per lane and array.
+            const int pc = chunk + kPrefetchAhead;
+            if (pc < nchunks) {
+                const size_t e = (size_t)pc * kChunk + 8 * (size_t)lane;
+                prefetch_l2(a.in.dir + e); prefetch_l2(a.hit + e); prefetch_l2(a.in.thr + e);
+                if (kTree && lane < 16) prefetch_l2(a.in.node + (size_t)pc * kChunk + 16 * (size_t)lane);
+            }
+        }
+#endif
 
         // ==== phase A: classify every entry, write its accumulator, list the ones that sample ===========================
         int n_list = 0;
