@@ -87,6 +87,7 @@ struct BounceArgs {
     int in_count, capacity, npix, batch_spp, sample_base, bounce, max_depth;
     uint32_t flags;
     float p_rr;
+    int by_lists;              // this bounce's light selection runs over the survivor lists (k_lsel_*): skey[] is valid
 };
 
 // ---- small helpers --------------------------------------------------------------------------------------
@@ -541,6 +542,14 @@ __global__ void __launch_bounds__(kBlk, MCPT_SEL_MINBLK) k_lightsel(const Bounce
 #define MCPT_SEL_V 4
 #endif
 constexpr int kSelV = MCPT_SEL_V;
+// Every list's run is kept as kSelSub sub-runs with a histogram bin and a scatter cursor each, chosen by the 32-entry group
+// an entry sits in: the cursor atomics of k_lsel_classify / k_lsel_scatter all go to one word per list, and a handful of
+// lists (the floor under the lights) take a large share of the vertices -- same-address atomics serialise in L2.
+#ifndef MCPT_SEL_SUB
+#define MCPT_SEL_SUB 8
+#endif
+constexpr int kSelSub = MCPT_SEL_SUB;
+__device__ __forceinline__ int sel_bin(int list, int i) { return list * kSelSub + ((i >> 5) & (kSelSub - 1)); }
 
 // the vertex of in-queue ray i if it samples a light: the decisions k_shade takes before light sampling, repeated
 template <int STRAT>
@@ -578,13 +587,12 @@ __global__ void __launch_bounds__(256) k_lsel_classify(const BounceArgs a)
             float u;
             int prim;
             if (sel_vertex<STRAT>(a, i, rr_forced, false, &p, &N, &u, &prim)) k = __ldg(a.s.prim_list + prim);
-            else a.sel4[i] = make_float4(__int_as_float(-1), 0.f, 0.f, 0.f);
-            a.skey[i] = k;
+            a.skey[i] = k;  // -1: no light drawn here; k_shade looks at the key before it trusts sel4[i] (16 bytes less written per entry)
         }
         const unsigned act = __ballot_sync(kFull, k >= 0);
         if (k >= 0) {
             const unsigned peers = __match_any_sync(act, k);
-            if (lane == __ffs(peers) - 1) atomicAdd(a.lhist + k, __popc(peers));
+            if (lane == __ffs(peers) - 1) atomicAdd(a.lhist + sel_bin(k, base), __popc(peers));
         }
     }
 }
@@ -626,18 +634,34 @@ __global__ void __launch_bounds__(1024) k_lsel_offsets(int* __restrict__ hist, i
 
 __global__ void __launch_bounds__(256) k_lsel_scatter(const BounceArgs a)
 {
+    // Two dependent round trips per 32 entries (the key from DRAM, then the cursor atomic from L2) at 13 % issue-active: four
+    // groups of 32 are in flight per warp, all keys loaded before the first vote, all atomics issued before the first store.
+    constexpr int kU = 4;
     const int lane = threadIdx.x & 31;
-    for (int base = (blockIdx.x * 256 + threadIdx.x) & ~31; base < a.in_count; base += gridDim.x * 256) {
-        const int i = base + lane;
-        const int k = i < a.in_count ? a.skey[i] : -1;
-        const unsigned act = __ballot_sync(kFull, k >= 0);
-        if (k >= 0) {
-            const unsigned peers = __match_any_sync(act, k);
-            const int leader = __ffs(peers) - 1;
-            int at = 0;
-            if (lane == leader) at = atomicAdd(a.lhist + k, __popc(peers));
-            at = __shfl_sync(peers, at, leader);
-            a.sorted[at + __popc(peers & ((1u << lane) - 1u))] = i;
+    const int warp = (blockIdx.x * 256 + threadIdx.x) >> 5, nwarps = (gridDim.x * 256) >> 5;
+    for (int base = warp * 32 * kU; base < a.in_count; base += nwarps * 32 * kU) {
+        int k[kU], at[kU], rank[kU];
+#pragma unroll
+        for (int u = 0; u < kU; u++) {
+            const int i = base + 32 * u + lane;
+            k[u] = i < a.in_count ? a.skey[i] : -1;
+        }
+#pragma unroll
+        for (int u = 0; u < kU; u++) {
+            const unsigned act = __ballot_sync(kFull, k[u] >= 0);
+            at[u] = 0; rank[u] = 0;
+            if (k[u] >= 0) {
+                const unsigned peers = __match_any_sync(act, k[u]);
+                const int leader = __ffs(peers) - 1;
+                if (lane == leader) at[u] = atomicAdd(a.lhist + sel_bin(k[u], base + 32 * u), __popc(peers));
+                rank[u] = (leader << 8) | __popc(peers & ((1u << lane) - 1u));
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kU; u++) {
+            // every lane takes part in the shuffle; only the keyed ones use what they get
+            const int base_at = __shfl_sync(kFull, at[u], rank[u] >> 8);
+            if (k[u] >= 0) a.sorted[base_at + (rank[u] & 255)] = base + 32 * u + lane;
         }
     }
 }
@@ -1051,7 +1075,7 @@ __global__ void __launch_bounds__(kBlk, (STRAT == MCPT_MIS && !EXACT) ? 5 : MCPT
                     const int2 v = a.sel[slot];
                     chosen = v.x; wch = __int_as_float(v.y);
                     wsum = a.wsum_pix[pixel];
-                } else {      // drawn by k_lightsel / k_lighttree
+                } else if (!a.by_lists || a.skey[i] >= 0) {  // drawn by k_lightsel / k_lightsel_sorted / k_lighttree
                     const float4 v = a.sel4[i];
                     chosen = __float_as_int(v.x); wch = v.y; wsum = v.z;
                 }
@@ -1423,12 +1447,12 @@ int launch_bounce(bool first, bool exact, const BounceArgs& a, int grid, int sel
     }
     if constexpr (kSph) {
         if (a.flags & MCPT_LIGHT_TREE) k_lighttree<STRAT><<<std::max(1, std::min((a.in_count + 255) / 256, 148 * 8)), 256, 0, st>>>(a);
-        else if (a.s.nlists > 0 && a.s.L > kSerialLights) {
+        else if (a.by_lists) {
             // survivor lists: group the sampling vertices by list, then sweep list by list (k_lsel_* above)
             const int cgrid = std::max(1, std::min((a.in_count + 255) / 256, 148 * 16));
-            cudaMemsetAsync(a.lhist, 0, (size_t)a.s.nlists * 4, st);
+            cudaMemsetAsync(a.lhist, 0, (size_t)a.s.nlists * kSelSub * 4, st);
             k_lsel_classify<STRAT><<<cgrid, 256, 0, st>>>(a);
-            k_lsel_offsets<<<1, 1024, 0, st>>>(a.lhist, a.s.nlists, a.sorted, a.ngroups);
+            k_lsel_offsets<<<1, 1024, 0, st>>>(a.lhist, a.s.nlists * kSelSub, a.sorted, a.ngroups);
             k_lsel_scatter<<<cgrid, 256, 0, st>>>(a);
             // running-sum columns in shared memory (kSelV x list_max floats per warp) while >= 3 blocks per SM still fit
             const size_t dyn = (size_t)(kBlk / 32) * kSelV * (size_t)a.s.list_max * sizeof(float);
@@ -1760,7 +1784,7 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
     const size_t o_sel = place(sph ? slots * 8 : 16), o_wsum = place(sph ? npix * 4 : 16), o_sel4 = place(sph ? cap * 16 : 16);
     const bool lists = sph && scene->d.nlists > 0 && scene->d.L > kSerialLights && !(prm->flags & MCPT_LIGHT_TREE);
     const size_t nl = lists ? (size_t)scene->d.nlists : 0;
-    const size_t o_skey = place(lists ? cap * 4 : 16), o_sorted = place(lists ? (cap + 4 * nl) * 4 : 16), o_lhist = place(nl * 4 + 16);
+    const size_t o_skey = place(lists ? cap * 4 : 16), o_sorted = place(lists ? (cap + kSelV * kSelSub * nl) * 4 : 16), o_lhist = place(nl * kSelSub * 4 + 16);
     const bool nee = prm->strategy == MCPT_NEE_SPHERICAL || prm->strategy == MCPT_NEE_UNIFORM || prm->strategy == MCPT_MIS_SINGLE;  // queues visibility rays
     const size_t o_hit = place(cap * 16);
     const size_t sqn = nee ? cap : 1;
@@ -1869,9 +1893,10 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
         a.s = scene->d; a.cam = dc;
         a.Lacc = Lacc; a.contrib = contrib; a.primary_hit = primary; a.sel = sel; a.wsum_pix = wsum_pix; a.sel4 = sel4; a.counts = counts; a.groupsum = d_groupsum; a.ticket = d_ticket;
         a.hit = hit; a.sq = SQ;
-        a.skey = (int*)(base + o_skey); a.sorted = (int*)(base + o_sorted); a.lhist = (int*)(base + o_lhist); a.ngroups = a.lhist + nl;
+        a.skey = (int*)(base + o_skey); a.sorted = (int*)(base + o_sorted); a.lhist = (int*)(base + o_lhist); a.ngroups = a.lhist + nl * kSelSub;
         a.counters = d_counters; a.seed = prm->seed; a.capacity = (int)cap; a.npix = (int)npix; a.batch_spp = b;
         a.sample_base = prm->spp_offset + done; a.max_depth = prm->max_depth; a.flags = prm->flags; a.p_rr = p_rr;
+        a.by_lists = lists ? 1 : 0;
         int count = (int)(npix * (size_t)b);
         a.in = Q[0]; a.out = Q[1];
         if (sph && !jitter) {
