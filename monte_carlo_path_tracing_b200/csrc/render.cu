@@ -46,7 +46,7 @@ constexpr int kBlk = 128;             // threads per block (4 warps; a warp owns
 constexpr unsigned kFull = 0xffffffffu;
 constexpr size_t kTargetSlots = 128u << 20;  // auto batch: up to 128 Mi path slots in flight per pass (memory permitting)
 
-enum { CNT_VERTICES = 0, CNT_RAYS, CNT_SHADOW, CNT_LIGHTRAYS, CNT_PRIMARY_HITS, CNT_OVERFLOW, CNT_SWEEPS, CNT_EVALS, CNT_N };
+enum { CNT_VERTICES = 0, CNT_RAYS, CNT_SHADOW, CNT_LIGHTRAYS, CNT_PRIMARY_HITS, CNT_OVERFLOW, CNT_SWEEPS, CNT_EVALS, CNT_SQ_HOLES, CNT_N };
 
 struct Queue {
     float4* org;   // o.xyz | exclude prim (int bits)          (Myobj.cpp:417 rotri)
@@ -182,6 +182,10 @@ __device__ __forceinline__ float warp_scan_incl(float v)
 // atomic per warp: commutative, so the result is deterministic).  k_gather then turns group sums + counts into
 // exact offsets and moves the chunk windows into the dense queue, preserving input order -- which keeps all
 // rays of one path-tree adjacent (k_runsum) without any warp ever waiting for another.
+#ifndef MCPT_SQ_GRAB
+#define MCPT_SQ_GRAB 256
+#endif
+constexpr int kSqGrab = MCPT_SQ_GRAB;  // visibility-queue slots a warp of k_shade reserves per atomic
 constexpr int kSerialLights = 32;  // at or below: per-lane light loop in k_lightsel instead of the warp-cooperative sweep
 constexpr int kGroup = 64;    // chunks per k_gather block (16 Ki queue entries; threads 0..63 scan one chunk count each)
 
@@ -913,6 +917,9 @@ __global__ void __launch_bounds__(kBlk, (STRAT == MCPT_MIS && !EXACT) ? 5 : MCPT
     const int depth = a.bounce + 1;
     const bool rr_forced = a.max_depth > 0 && depth >= a.max_depth;
 
+    // visibility-ray queue: the warp reserves kSqGrab slots at a time (one atomic on the queue's one counter per kSqGrab
+    // records instead of one per 32 entries) and hands them out batch by batch; what is left at the end is marked as holes
+    int sq_rb = 0, sq_re = 0;
     int next = 0;
     if (lane == 0) next = atomicAdd(a.ticket, 1);
     for (;;) {
@@ -1203,11 +1210,18 @@ __global__ void __launch_bounds__(kBlk, (STRAT == MCPT_MIS && !EXACT) ? 5 : MCPT
             // Lacc[slot] += contribution needs no ordering), one atomic per warp
             const unsigned ms = __ballot_sync(kFull, sh_need);
             if (ms) {
-                int base = 0;
-                if (lane == 0) base = atomicAdd(a.sq.count, __popc(ms));
-                base = __shfl_sync(kFull, base, 0);
+                const int m = __popc(ms), have = sq_re - sq_rb;
+                int nb = 0;
+                if (have < m) {  // the batch runs over the end of the reservation: the overflow goes to the head of a new one
+                    if (lane == 0) nb = atomicAdd(a.sq.count, kSqGrab);
+                    nb = __shfl_sync(kFull, nb, 0);
+                }
+                const int r = __popc(ms & ((1u << lane) - 1u));
+                const int dst_ = r < have ? sq_rb + r : nb + (r - have);
+                if (have < m) { sq_rb = nb + (m - have); sq_re = nb + kSqGrab; }
+                else sq_rb += m;
                 if (sh_need) {
-                    const int dst = base + __popc(ms & ((1u << lane) - 1u));
+                    const int dst = dst_;
                     a.sq.org[dst] = make_float4(p.x, p.y, p.z, sh_t);
                     a.sq.dir[dst] = make_float4(sh_d.x, sh_d.y, sh_d.z, __int_as_float(slot));
                     a.sq.ctr[dst] = make_float4(sh_c.x, sh_c.y, sh_c.z, 0.f);
@@ -1221,6 +1235,14 @@ __global__ void __launch_bounds__(kBlk, (STRAT == MCPT_MIS && !EXACT) ? 5 : MCPT
             if (emitted) atomicAdd(a.groupsum + chunk / kGroup, emitted);
         }
         __syncwarp();  // the next chunk overwrites the list
+    }
+    if (kShadow && sq_re > sq_rb) {  // the unused tail of the last reservation: holes k_shadow skips (light prim -2, tmax < 0)
+        for (int j = sq_rb + lane; j < sq_re; j += 32) {
+            a.sq.org[j] = make_float4(0.f, 0.f, 0.f, -1.f);
+            a.sq.dir[j] = make_float4(0.f, 0.f, 1.f, __int_as_float(0));
+            a.sq.ids[j] = make_int2(-2, -2);
+        }
+        if (lane == 0) atomicAdd(a.counters + CNT_SQ_HOLES, (unsigned long long)(sq_re - sq_rb));
     }
     // warp-level counter reduction: one atomic per counter per warp
     c_vert = __reduce_add_sync(kFull, c_vert);
@@ -1281,7 +1303,7 @@ __global__ void __launch_bounds__(kBlk) k_shadow8(DScene s, const ShadowQueue sq
             exclude = id.x; tmax = qo.w; init_prim = id.y;
         },
         [&](int i, const Hit& h) {
-            if (h.prim == sq.ids[i].y) {
+            if (h.prim >= 0 && h.prim == sq.ids[i].y) {  // (holes of the queue carry light prim -2)
                 const float4 c = sq.ctr[i];
                 const int slot = __float_as_int(sq.dir[i].w);
                 float4 L = Lacc[slot];
@@ -1308,7 +1330,7 @@ __global__ void __launch_bounds__(kBlk) k_shadow(DScene s, const ShadowQueue sq,
             exclude = id.x; tmax = qo.w; init_prim = id.y;
         },
         [&](int i, const Hit& h) {
-            if (h.prim == sq.ids[i].y) {
+            if (h.prim >= 0 && h.prim == sq.ids[i].y) {  // (holes of the queue carry light prim -2)
                 const float4 c = sq.ctr[i];
                 const int slot = __float_as_int(sq.dir[i].w);
                 float4 L = Lacc[slot];
@@ -1342,6 +1364,7 @@ __global__ void __launch_bounds__(kBlk) k_shadow_exact(DScene s, const ShadowQue
     for (int i = blockIdx.x * kBlk + threadIdx.x; i < n; i += gridDim.x * kBlk) {
         const float4 qo = sq.org[i], qd = sq.dir[i];
         const int2 id = sq.ids[i];
+        if (id.y < 0) continue;  // a hole of the queue (k_shade's unused reservation)
         const HitD h = trace_exact<false>(s.nodes, s.tris, to_d3(qo), to_d3(qd), id.x, 1.7976931348623157e308, stack + threadIdx.x, kBlk);
         if (h.prim == id.y) {  // main.cpp:309-311
             const float4 c = sq.ctr[i];
@@ -1767,6 +1790,14 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
     const bool single = prm->strategy == MCPT_MIS_SINGLE;
     const bool sph = prm->strategy == MCPT_NEE_SPHERICAL || prm->strategy == MCPT_MIS || single;
 
+    int dev = scene->device, sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    int bps = prm->strategy == MCPT_NEE_SPHERICAL ? bounce_blocks_per_sm<MCPT_NEE_SPHERICAL>()
+              : prm->strategy == MCPT_BRDF_ONLY   ? bounce_blocks_per_sm<MCPT_BRDF_ONLY>()
+              : prm->strategy == MCPT_MIS         ? bounce_blocks_per_sm<MCPT_MIS>()
+              : prm->strategy == MCPT_MIS_SINGLE  ? bounce_blocks_per_sm<MCPT_MIS_SINGLE>()
+                                                  : bounce_blocks_per_sm<MCPT_NEE_UNIFORM>();
+    const size_t sq_warps = (size_t)sms * bps * (kBlk / 32);
     // workspace carve-up
     size_t off = 0;
     auto place = [&](size_t bytes) { size_t at = off; off = (off + bytes + 255) & ~(size_t)255; return at; };
@@ -1787,7 +1818,8 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
     const size_t o_skey = place(lists ? cap * 4 : 16), o_sorted = place(lists ? (cap + kSelV * kSelSub * nl) * 4 : 16), o_lhist = place(nl * kSelSub * 4 + 16);
     const bool nee = prm->strategy == MCPT_NEE_SPHERICAL || prm->strategy == MCPT_NEE_UNIFORM || prm->strategy == MCPT_MIS_SINGLE;  // queues visibility rays
     const size_t o_hit = place(cap * 16);
-    const size_t sqn = nee ? cap : 1;
+    // every resident warp of k_shade may leave one partly used reservation behind
+    const size_t sqn = nee ? cap + (size_t)sq_warps * kSqGrab : 1;
     const size_t o_sq[4] = {place(sqn * 16), place(sqn * 16), place(sqn * 16), place(sqn * 8)};
     Workspace& ws = scene->ws;
     if (ws.bytes < off) {
@@ -1844,13 +1876,6 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
         dc.W = W; dc.H = H;
     }
 
-    int dev = scene->device, sms = 148;
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    int bps = prm->strategy == MCPT_NEE_SPHERICAL ? bounce_blocks_per_sm<MCPT_NEE_SPHERICAL>()
-              : prm->strategy == MCPT_BRDF_ONLY   ? bounce_blocks_per_sm<MCPT_BRDF_ONLY>()
-              : prm->strategy == MCPT_MIS         ? bounce_blocks_per_sm<MCPT_MIS>()
-              : prm->strategy == MCPT_MIS_SINGLE  ? bounce_blocks_per_sm<MCPT_MIS_SINGLE>()
-                                                  : bounce_blocks_per_sm<MCPT_NEE_UNIFORM>();
     if (const char* e = std::getenv("MCPT_GRID_DIV")) g_grid_div = std::max(1, std::atoi(e));
     const int gdiv = g_grid_div;
     const int max_grid = sms * std::max(1, bps / gdiv);
@@ -2027,7 +2052,7 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
     cudaEventElapsedTime(&ms_total, scene->ev[0], scene->ev[1]);
     S.passes = (uint32_t)pass;
     S.vertices = h_counters[CNT_VERTICES];
-    S.rays_shadow = h_counters[CNT_SHADOW];
+    S.rays_shadow = h_counters[CNT_SHADOW] - h_counters[CNT_SQ_HOLES];  // the queue length counts k_shade's unused reservations
     S.rays_light = h_counters[CNT_LIGHTRAYS];
     S.primary_hits = h_counters[CNT_PRIMARY_HITS];
     S.light_sweeps = h_counters[CNT_SWEEPS];
