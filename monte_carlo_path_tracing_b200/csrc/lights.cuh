@@ -262,6 +262,55 @@ __device__ __forceinline__ float2 light_weight_pair_acc(const LightRec& L, const
     return __ffma2_rn(light_weight_pair(L, v), bc2(L.p3.w), acc);
 }
 
+// The transposed packing for scenes with few lights (k_lightsel's per-lane loop): TWO LIGHTS against one vertex per
+// instruction.  L = 17 float2 (light 2j | light 2j+1) in the order v0.xyz, e1.xyz, e2.xyz, q.xyz, 2 Lsum, e1.e1, e2.e2, e1.e2,
+// threshold (kLightPairFields; staged in shared memory by the kernel, every lane reads the same pair: broadcast).  The same
+// operations in the same order as light_weight_soa, so the two weights equal light_weight_fast's bit for bit.  The horizon
+// branch is per lane here (the lanes of a warp hold different vertices).
+constexpr int kLightPairFields = 17;
+__device__ __forceinline__ float2 light_weight_2lights(const float2* __restrict__ L, f3 x1, f3 n)
+{
+    const float2 mx = bc2(-x1.x), my = bc2(-x1.y), mz = bc2(-x1.z), nx = bc2(n.x), ny = bc2(n.y), nz = bc2(n.z);
+    const float2 e1x = L[3], e1y = L[4], e1z = L[5], e2x = L[6], e2y = L[7], e2z = L[8];
+    const float2 ax = __fadd2_rn(L[0], mx), ay = __fadd2_rn(L[1], my), az = __fadd2_rn(L[2], mz);
+    const float2 num = dot2_rn(L[9], L[10], L[11], ax, ay, az);
+    const float2 ha = dot2_rn(nx, ny, nz, ax, ay, az);
+    bool up0 = ha.x >= 1e-8f, up1 = ha.y >= 1e-8f;
+    if (!(up0 && up1)) {
+        const float2 hb = __fadd2_rn(ha, dot2_rn(nx, ny, nz, e1x, e1y, e1z)), hc = __fadd2_rn(ha, dot2_rn(nx, ny, nz, e2x, e2y, e2z));
+        up0 = up0 || fmaxf(hb.x, hc.x) >= 1e-8f;
+        up1 = up1 || fmaxf(hb.y, hc.y) >= 1e-8f;
+    }
+    const float2 aa = dot2_rn(ax, ay, az, ax, ay, az);
+    const float2 ae1 = dot2_rn(ax, ay, az, e1x, e1y, e1z), ae2 = dot2_rn(ax, ay, az, e2x, e2y, e2z);
+    const float2 ab = __fadd2_rn(aa, ae1), ac = __fadd2_rn(aa, ae2);
+    const float2 bb = __ffma2_rn(bc2(2.f), ae1, __fadd2_rn(aa, L[13])), cc = __ffma2_rn(bc2(2.f), ae2, __fadd2_rn(aa, L[14]));
+    const float2 bcd = __fadd2_rn(__fadd2_rn(ab, ae2), L[15]);
+    const float2 la = len2_fast(aa), lb = len2_fast(bb), lc = len2_fast(cc);
+    float2 den = __fmul2_rn(__fmul2_rn(la, lb), lc);
+    den = __ffma2_rn(ab, lc, den);
+    den = __ffma2_rn(ac, lb, den);
+    den = __ffma2_rn(bcd, la, den);
+    const float adx = fabsf(den.x), ady = fabsf(den.y);
+    const float2 q = __fmul2_rn(make_float2(fminf(adx, num.x), fminf(ady, num.y)),
+                                make_float2(rcp_fast(fmaxf(adx, num.x)), rcp_fast(fmaxf(ady, num.y))));
+    const float2 s = __fmul2_rn(q, q);
+    float2 p = bc2(MCPT_ATAN_C0);
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C1));
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C2));
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C3));
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C4));
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C5));
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C6));
+    p = __ffma2_rn(p, s, bc2(MCPT_ATAN_C7));
+    const float2 r = __ffma2_rn(q, __fmul2_rn(p, s), q);
+    const float hx = atan2_fix(r.x, num.x, den.x), hy = atan2_fix(r.y, num.y, den.y);
+    const bool ok0 = num.x >= L[16].x && up0 && hx < CUDART_INF_F;
+    const bool ok1 = num.y >= L[16].y && up1 && hy < CUDART_INF_F;
+    const float2 w = __fmul2_rn(make_float2(hx, hy), L[12]);
+    return make_float2(ok0 ? w.x : 0.f, ok1 ? w.y : 0.f);
+}
+
 // Per-lane partial sums, over this lane's lights (l = lane, lane + 32, ...), of the weights seen from V = 2 or 4
 // vertices (one packed evaluation per light and vertex pair: the four 16-byte loads of a light serve all).  With `cdf` (shared memory,
 // [2][Lpad] floats) every running partial is also stored: cdf[v][l] = sum of the lane's weights up to and

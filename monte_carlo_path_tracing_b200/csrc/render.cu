@@ -434,6 +434,24 @@ __global__ void __launch_bounds__(kBlk, MCPT_SEL_MINBLK) k_lightsel(const Bounce
     const int lane = threadIdx.x & 31;
     const int nchunks = (a.in_count + 31) >> 5;
     const bool rr_forced = a.max_depth > 0 && a.bounce + 1 >= a.max_depth;
+    // few lights: the table as pairs of lights in shared memory for the packed per-lane loop below (light_weight_2lights)
+    __shared__ float2 sm_lp[(kSerialLights / 2) * kLightPairFields];
+    if (s.L <= kSerialLights) {
+        const int npairs = (s.L + 1) >> 1;
+        for (int t = threadIdx.x; t < npairs * kLightPairFields; t += kBlk) {
+            const int j = t / kLightPairFields, f = t - j * kLightPairFields;
+            // field f of a light record: planes 0..2 xyz, plane 3 xyzw, plane 4 xyzw (lights.cuh); light L is a padding light (weight 0)
+            const int plane = f < 9 ? f / 3 : (f < 13 ? 3 : 4), comp = f < 9 ? f % 3 : (f < 13 ? f - 9 : f - 13);
+            float v[2];
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const float4 r = __ldg(s.lsoa + lsoa_index(2 * j + h) + 32 * plane);
+                v[h] = comp == 0 ? r.x : comp == 1 ? r.y : comp == 2 ? r.z : r.w;
+            }
+            sm_lp[t] = make_float2(v[0], v[1]);
+        }
+        __syncthreads();
+    }
     // Warp path: a sweep serves two vertices, and only ~1 queue entry in 9 needs one at the second bounce of veach-mis
     // (3.6 per chunk of 32), so pairing inside a chunk would leave every other chunk with a half-empty sweep.  The odd
     // vertex is carried (warp-uniform registers) and paired with the first one of the next chunk; results are written
@@ -496,14 +514,20 @@ __global__ void __launch_bounds__(kBlk, MCPT_SEL_MINBLK) k_lightsel(const Bounce
             float wsum = 0.f, wch = 0.f;
             if (need) {
                 float uu = fminf(u, 0.99999994f);
-                for (int l = 0; l < s.L; l++) {
-                    const float w = light_weight_fast(s, l, p, N);
-                    if (w > 0.f) {
-                        wsum += w;
-                        const float pr = __fdividef(w, wsum);
-                        if (uu < pr) { chosen = l; wch = w; uu = __fdividef(uu, pr); }
-                        else uu = __fdividef(uu - pr, 1.f - pr);
-                        uu = fminf(fmaxf(uu, 0.f), 0.99999994f);
+                for (int l = 0; l < s.L; l += 2) {
+                    // lights l and l + 1 in one packed evaluation (bit-identical to light_weight_fast), then the two
+                    // reservoir steps in table order
+                    const float2 w2 = light_weight_2lights(sm_lp + (l >> 1) * kLightPairFields, p, N);
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        const float w = h ? w2.y : w2.x;
+                        if (w > 0.f && l + h < s.L) {
+                            wsum += w;
+                            const float pr = __fdividef(w, wsum);
+                            if (uu < pr) { chosen = l + h; wch = w; uu = __fdividef(uu, pr); }
+                            else uu = __fdividef(uu - pr, 1.f - pr);
+                            uu = fminf(fmaxf(uu, 0.f), 0.99999994f);
+                        }
                     }
                 }
             }
