@@ -143,6 +143,8 @@ typedef struct McptStats {
                               * once per shadable PIXEL per pass at the first vertex (F4), once per sampling vertex after it */
     uint64_t light_evals;    /* (light, vertex) spherical-triangle weights those sweeps evaluated: light_sweeps x the padded table
                               * length, or less when the sweeps run over per-primitive survivor lists (csrc/light_lists.h) */
+    float ms_sweep;          /* part of ms_shade spent in the light-sweep kernel alone (k_lightsel / k_lightsel_sorted / k_lighttree) */
+    float ms_prep;           /* k_lightprep: the first-vertex sweeps, once per pixel and pass (part of ms_other) */
 } McptStats;
 
 typedef struct McptScene McptScene;

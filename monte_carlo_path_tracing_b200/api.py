@@ -73,7 +73,8 @@ class Stats(C.Structure):
                 ("rays_closest", C.c_uint64), ("rays_shadow", C.c_uint64), ("rays_light", C.c_uint64),
                 ("passes", C.c_uint32), ("bounces", C.c_uint32), ("kernel_launches", C.c_uint32),
                 ("queue_peak", C.c_uint32), ("ms_total", C.c_float), ("ms_bounce", C.c_float), ("ms_other", C.c_float),
-                ("ms_shade", C.c_float), ("ms_trace", C.c_float), ("elements", C.c_uint64), ("light_sweeps", C.c_uint64), ("light_evals", C.c_uint64)]
+                ("ms_shade", C.c_float), ("ms_trace", C.c_float), ("elements", C.c_uint64), ("light_sweeps", C.c_uint64), ("light_evals", C.c_uint64),
+                ("ms_sweep", C.c_float), ("ms_prep", C.c_float)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -372,7 +372,7 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
         d.P = (int32_t)P; d.L = (int32_t)L; d.C = (int32_t)C; d.M = (int32_t)Mn;
         d.tmin = s->extent * 1e-6f;
         MCPT_CUDA(cudaMemcpy(s->d_blob, s->h_blob, B.total, cudaMemcpyHostToDevice));
-        for (int i = 0; i < 6; i++) MCPT_CUDA(cudaEventCreate(&s->ev[i]));
+        for (int i = 0; i < 10; i++) MCPT_CUDA(cudaEventCreate(&s->ev[i]));
         // Which wide layout the trace kernels walk: measured on this scene (render.cu: calibrate_trace_layout) unless the
         // 8-wide tree is too deep for its stack or MCPT_BVH8=0/1 forces the choice (A/B measurements, tests).
         if (s->bvh.max_depth8 + 2 <= (uint32_t)kBvh8StackDepth && !s->bvh.nodes8.empty()) {
@@ -413,7 +413,7 @@ McptScene* scene_clone(const McptScene* src, int device)
         rebase(d.mats); rebase(d.lights); rebase(d.lsoa); rebase(d.lng64); rebase(d.larea64); rebase(d.crad64);
         rebase(d.class_begin); rebase(d.class_cdf); rebase(d.tri_cdf); rebase(d.ltree); rebase(d.ltree_leaf);
         rebase(d.llist); rebase(d.lrange); rebase(d.prim_list);
-        for (int i = 0; i < 6; i++) MCPT_CUDA(cudaEventCreate(&raw->ev[i]));
+        for (int i = 0; i < 10; i++) MCPT_CUDA(cudaEventCreate(&raw->ev[i]));
     } catch (...) {
         mcpt_scene_destroy(raw);
         throw;
@@ -431,7 +431,7 @@ void mcpt_scene_destroy(McptScene* s)
     workspace_free(s->ws);
     if (s->d_blob) cudaFree(s->d_blob);
     if (s->h_blob) cudaFreeHost(s->h_blob);
-    for (int i = 0; i < 6; i++)
+    for (int i = 0; i < 10; i++)
         if (s->ev[i]) cudaEventDestroy(s->ev[i]);
     delete s;
 }

@@ -79,7 +79,7 @@ struct McptScene {
     bool layout_free = false;        // the layout is the library's to choose (not forced by MCPT_BVH8, 8-wide tree usable)
     bool layout_final = false;       // settled on real rays
     mcpt::Workspace ws;
-    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 
 namespace mcpt {

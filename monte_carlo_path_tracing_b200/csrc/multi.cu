@@ -231,6 +231,7 @@ int mcpt_multi_render(McptMulti* m, const McptCamera* cam, const McptRenderParam
                 // device time of the call = the slowest device (they run side by side) + the reduce
                 S.ms_total = std::max(S.ms_total, s.ms_total); S.ms_bounce = std::max(S.ms_bounce, s.ms_bounce);
                 S.ms_shade = std::max(S.ms_shade, s.ms_shade); S.ms_trace = std::max(S.ms_trace, s.ms_trace);
+                S.ms_sweep = std::max(S.ms_sweep, s.ms_sweep); S.ms_prep = std::max(S.ms_prep, s.ms_prep);
             }
             S.ms_total += ms_reduce;
             S.ms_other = S.ms_total - S.ms_bounce;

@@ -1484,7 +1484,7 @@ __global__ void k_tonemap(const float* __restrict__ rgb, size_t n3, double A, do
 // two renders on two streams can share the SMs
 static int g_grid_div = 1;
 template <int STRAT>
-int launch_bounce(bool first, bool exact, const BounceArgs& a, int grid, int sel_grid, int* sel_cursor, cudaStream_t st)
+int launch_bounce(bool first, bool exact, const BounceArgs& a, int grid, int sel_grid, int* sel_cursor, cudaStream_t st, cudaEvent_t ev_sweep0, cudaEvent_t ev_sweep1)
 {
     constexpr bool kSph = (STRAT == MCPT_NEE_SPHERICAL || STRAT == MCPT_MIS || STRAT == MCPT_MIS_SINGLE);
     if (first) {
@@ -1493,7 +1493,11 @@ int launch_bounce(bool first, bool exact, const BounceArgs& a, int grid, int sel
         return 1;
     }
     if constexpr (kSph) {
-        if (a.flags & MCPT_LIGHT_TREE) k_lighttree<STRAT><<<std::max(1, std::min((a.in_count + 255) / 256, 148 * 8)), 256, 0, st>>>(a);
+        if (a.flags & MCPT_LIGHT_TREE) {
+            cudaEventRecord(ev_sweep0, st);
+            k_lighttree<STRAT><<<std::max(1, std::min((a.in_count + 255) / 256, 148 * 8)), 256, 0, st>>>(a);
+            cudaEventRecord(ev_sweep1, st);
+        }
         else if (a.by_lists) {
             // survivor lists: group the sampling vertices by list, then sweep list by list (k_lsel_* above)
             const int cgrid = std::max(1, std::min((a.in_count + 255) / 256, 148 * 16));
@@ -1508,12 +1512,18 @@ int launch_bounce(bool first, bool exact, const BounceArgs& a, int grid, int sel
             int sb = 1;
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sb, k_lightsel_sorted<STRAT>, kBlk, use_cdf ? dyn : 0);
             const int sgrid = std::min(std::max(1, (a.in_count + 127) / 128), 148 * std::max(1, sb / g_grid_div));
+            cudaEventRecord(ev_sweep0, st);
             k_lightsel_sorted<STRAT><<<sgrid, kBlk, use_cdf ? dyn : 0, st>>>(a, sel_cursor, use_cdf ? a.s.list_max : 0);
+            cudaEventRecord(ev_sweep1, st);
             if (exact) k_shade<STRAT, false, true><<<grid, kBlk, 0, st>>>(a);
             else k_shade<STRAT, false, false><<<grid, kBlk, 0, st>>>(a);
             return 5;
         }
-        else k_lightsel<STRAT><<<std::min(grid, sel_grid), kBlk, 0, st>>>(a, sel_cursor);
+        else {
+            cudaEventRecord(ev_sweep0, st);
+            k_lightsel<STRAT><<<std::min(grid, sel_grid), kBlk, 0, st>>>(a, sel_cursor);
+            cudaEventRecord(ev_sweep1, st);
+        }
     }
     if (exact) k_shade<STRAT, false, true><<<grid, kBlk, 0, st>>>(a);
     else k_shade<STRAT, false, false><<<grid, kBlk, 0, st>>>(a);
@@ -1933,7 +1943,8 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
         S.kernel_launches++;
         S.rays_closest += npix;
     }
-    float ms_bounce = 0.f, ms_shade = 0.f;
+    float ms_bounce = 0.f, ms_shade = 0.f, ms_sweep = 0.f, ms_prep = 0.f;
+    bool prep_timed = false;
     bool overflow = false, measuring = false;
     int done = 0, pass = 0;
     while (done < prm->spp) {
@@ -1958,8 +1969,11 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pbps, k_lightprep, kBlk, dyn);
             const size_t npairs = (npix + 1) / 2;
             const int pgrid = (int)std::min<size_t>((npairs + kBlk / 32 - 1) / (kBlk / 32), (size_t)sms * std::max(1, pbps / gdiv));
+            MCPT_CUDA(cudaEventRecord(scene->ev[8], st));
             k_lightprep<<<pgrid, kBlk, dyn, st>>>(scene->d, dc, primary, (int)npix, b, a.sample_base, prm->seed, p_rr, (tree || single) ? 1 : 0,
                                                   prm->max_depth, use_cdf, sel, wsum_pix, d_counters);
+            MCPT_CUDA(cudaEventRecord(scene->ev[9], st));
+            prep_timed = true;
             MCPT_CUDA(cudaGetLastError());
             S.kernel_launches++;
         }
@@ -1985,11 +1999,11 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
             const bool first = bounce == 0 && !jitter;
             int nl = 1;
             switch (prm->strategy) {
-                case MCPT_NEE_SPHERICAL: nl = launch_bounce<MCPT_NEE_SPHERICAL>(first, exact, a, grid, sel_grid, d_sel_cursor, st); break;
-                case MCPT_BRDF_ONLY: nl = launch_bounce<MCPT_BRDF_ONLY>(first, exact, a, grid, sel_grid, d_sel_cursor, st); break;
-                case MCPT_MIS: nl = launch_bounce<MCPT_MIS>(first, exact, a, grid, sel_grid, d_sel_cursor, st); break;
-                case MCPT_MIS_SINGLE: nl = launch_bounce<MCPT_MIS_SINGLE>(first, exact, a, grid, sel_grid, d_sel_cursor, st); break;
-                default: nl = launch_bounce<MCPT_NEE_UNIFORM>(first, exact, a, grid, sel_grid, d_sel_cursor, st); break;
+                case MCPT_NEE_SPHERICAL: nl = launch_bounce<MCPT_NEE_SPHERICAL>(first, exact, a, grid, sel_grid, d_sel_cursor, st, scene->ev[6], scene->ev[7]); break;
+                case MCPT_BRDF_ONLY: nl = launch_bounce<MCPT_BRDF_ONLY>(first, exact, a, grid, sel_grid, d_sel_cursor, st, scene->ev[6], scene->ev[7]); break;
+                case MCPT_MIS: nl = launch_bounce<MCPT_MIS>(first, exact, a, grid, sel_grid, d_sel_cursor, st, scene->ev[6], scene->ev[7]); break;
+                case MCPT_MIS_SINGLE: nl = launch_bounce<MCPT_MIS_SINGLE>(first, exact, a, grid, sel_grid, d_sel_cursor, st, scene->ev[6], scene->ev[7]); break;
+                default: nl = launch_bounce<MCPT_NEE_UNIFORM>(first, exact, a, grid, sel_grid, d_sel_cursor, st, scene->ev[6], scene->ev[7]); break;
             }
             MCPT_CUDA(cudaGetLastError());
             MCPT_CUDA(cudaEventRecord(scene->ev[4], st));
@@ -2047,6 +2061,15 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
             ms_bounce += ms;
             cudaEventElapsedTime(&ms, scene->ev[2], scene->ev[4]);
             ms_shade += ms;
+            if (sph && !first) {  // the light-sweep kernel of this bounce alone
+                float msw = 0.f;
+                if (cudaEventElapsedTime(&msw, scene->ev[6], scene->ev[7]) == cudaSuccess) ms_sweep += msw; else cudaGetLastError();
+            }
+            if (prep_timed) {  // k_lightprep of this pass (it finished before the first bounce did)
+                float mp = 0.f;
+                if (cudaEventElapsedTime(&mp, scene->ev[8], scene->ev[9]) == cudaSuccess) ms_prep += mp; else cudaGetLastError();
+                prep_timed = false;
+            }
             if (dbg_timing) {
                 float mb = 0.f;
                 cudaEventElapsedTime(&mb, scene->ev[2], scene->ev[3]);
@@ -2084,6 +2107,7 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
     overflow = h_counters[CNT_OVERFLOW] != 0;
     S.ms_total = ms_total; S.ms_bounce = ms_bounce; S.ms_other = ms_total - ms_bounce;
     S.ms_shade = ms_shade; S.ms_trace = ms_bounce - ms_shade;
+    S.ms_sweep = ms_sweep; S.ms_prep = ms_prep;
     for (auto& e : evm) if (e) cudaEventDestroy(e);
     if (stats) *stats = S;
     if (overflow) throw QueueOverflow{batch};

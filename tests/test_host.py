@@ -33,7 +33,7 @@ def test_abi_struct_layouts_match_header(tmp_path):
     """ctypes mirrors of the PODs have the sizes AND field offsets the C compiler gives include/mcpt.h."""
     assert C.sizeof(api.CameraC) == 10 * 8
     assert C.sizeof(api.RenderParams) == 4 * 8 + 8 + 4 + 4 + 4 + 4
-    assert C.sizeof(api.Stats) == 6 * 8 + 4 * 4 + 5 * 4 + 4 + 8 + 8 + 8  # 5 floats, 4 bytes of padding, elements, light_sweeps, light_evals
+    assert C.sizeof(api.Stats) == 6 * 8 + 4 * 4 + 5 * 4 + 4 + 8 + 8 + 8 + 2 * 4  # 5 floats, 4 bytes of padding, elements, light_sweeps, light_evals, ms_sweep, ms_prep
     assert C.sizeof(api.SceneDesc) == 5 * 4 + 4 + 10 * 8
     structs = {"McptCamera": api.CameraC, "McptRenderParams": api.RenderParams, "McptStats": api.Stats, "McptSceneDesc": api.SceneDesc}
     lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "mcpt.h"', 'int main(void){']
