@@ -345,7 +345,10 @@ __device__ __forceinline__ void warp_light_partial(const DScene& s, const f3 (&x
 // of 32, padded with a weight-0 light), lane k takes entries k, k + 32, ...  The lights a list leaves out are culled at
 // every vertex of the primitive it belongs to, i.e. they would have added exact zeros.  cdf (optional): running
 // sums by list POSITION, cdf[v * cdf_stride + k].
-template <int V>
+// SUB > 1: only every SUB-th running sum of a lane's column is kept (after list positions SUB-1, 2 SUB-1, ... of the lane), at
+// cdf[v * cdf_stride + 32 m + lane] for the m-th checkpoint: the picker bisects the checkpoints and re-evaluates the <= SUB
+// weights of one group (k_lightsel_sorted).  A quarter of the shared memory leaves the light table room in L1.
+template <int V, int SUB = 1>
 __device__ __forceinline__ void warp_light_partial_list(const DScene& s, const uint32_t* __restrict__ list, int n, const f3 (&x1)[V],
                                                         const f3 (&nn)[V], float (&part)[V], float* cdf = nullptr, int cdf_stride = 0)
 {
@@ -366,8 +369,14 @@ __device__ __forceinline__ void warp_light_partial_list(const DScene& s, const u
 #pragma unroll
         for (int h = 0; h < V / 2; h++) acc[h] = light_weight_pair_acc(rec, vp[h], acc[h]);
         if (cdf) {
+            if (SUB == 1) {
 #pragma unroll
-            for (int h = 0; h < V / 2; h++) { cdf[(2 * h) * cdf_stride + k] = acc[h].x; cdf[(2 * h + 1) * cdf_stride + k] = acc[h].y; }
+                for (int h = 0; h < V / 2; h++) { cdf[(2 * h) * cdf_stride + k] = acc[h].x; cdf[(2 * h + 1) * cdf_stride + k] = acc[h].y; }
+            } else if (((k >> 5) & (SUB - 1)) == SUB - 1) {
+                const int at = ((k >> 5) / SUB << 5) + lane;
+#pragma unroll
+                for (int h = 0; h < V / 2; h++) { cdf[(2 * h) * cdf_stride + at] = acc[h].x; cdf[(2 * h + 1) * cdf_stride + at] = acc[h].y; }
+            }
         }
     }
 #pragma unroll

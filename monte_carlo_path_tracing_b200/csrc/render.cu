@@ -577,6 +577,11 @@ constexpr int kSelV = MCPT_SEL_V;
 #define MCPT_SEL_SUB 8
 #endif
 constexpr int kSelSub = MCPT_SEL_SUB;
+// running-sum checkpoints kept per lane column in k_lightsel_sorted: every kCdfSub-th list position (power of two; 1 = all)
+#ifndef MCPT_CDF_SUB
+#define MCPT_CDF_SUB 8
+#endif
+constexpr int kCdfSub = MCPT_CDF_SUB;
 __device__ __forceinline__ int sel_bin(int list, int i) { return list * kSelSub + ((i >> 5) & (kSelSub - 1)); }
 
 // the vertex of in-queue ray i if it samples a light: the decisions k_shade takes before light sampling, repeated
@@ -699,7 +704,7 @@ __global__ void __launch_bounds__(256) k_lsel_scatter(const BounceArgs a)
 // running sums of every lane's column behind, and lane v picks vertex v's light by bisection of its column -- one weight
 // re-evaluated per vertex instead of a second warp-wide pass (warp_light_pick) per vertex.
 #ifndef MCPT_SORTED_MINBLK
-#define MCPT_SORTED_MINBLK (kSelV == 4 ? 4 : MCPT_SEL_MINBLK)
+#define MCPT_SORTED_MINBLK (kSelV == 4 ? 6 : MCPT_SEL_MINBLK)
 #endif
 template <int STRAT>
 __global__ void __launch_bounds__(kBlk, MCPT_SORTED_MINBLK) k_lightsel_sorted(const BounceArgs a, int* cursor, int cdf_stride)
@@ -747,12 +752,14 @@ __global__ void __launch_bounds__(kBlk, MCPT_SORTED_MINBLK) k_lightsel_sorted(co
                 nvalid += ii[v] >= 0;
             }
             float part[kSelV];
-            warp_light_partial_list<kSelV>(s, list, rg.y, X, Nn, part, cdf_stride ? cdf : nullptr, cdf_stride);
+            warp_light_partial_list<kSelV, kCdfSub>(s, list, rg.y, X, Nn, part, cdf_stride ? cdf : nullptr, cdf_stride);
             c_evals += (unsigned)(rg.y >> 5) * (unsigned)nvalid;
             if (cdf_stride) {
-                // lane v resolves vertex v: lane totals -> lane j, then bisection of lane j's column of running sums
+                // lanes kCdfSub v .. kCdfSub v + kCdfSub - 1 resolve vertex v: lane totals -> lane column j, bisection of the
+                // column's checkpoints -> one group of kCdfSub list positions, whose weights the lanes re-evaluate (one each,
+                // bit-identical to the sweep's) and the first lane of the group walks
                 __syncwarp();
-                const int K = rg.y >> 5;
+                const int K = rg.y >> 5, M = K / kCdfSub;
                 int my_i = -1, my_j = 0;
                 float my_rem = 0.f, my_total = 0.f;
                 f3 mX = X[0], mN = Nn[0];
@@ -765,26 +772,54 @@ __global__ void __launch_bounds__(kBlk, MCPT_SORTED_MINBLK) k_lightsel_sorted(co
                     const unsigned ge = __ballot_sync(kFull, incl >= target && part[v] > 0.f);
                     const int j = ge ? (__ffs(ge) - 1) : (nz ? 31 - __clz(nz) : 0);
                     const float rem = target - (__shfl_sync(kFull, incl, j) - __shfl_sync(kFull, part[v], j));
-                    if (lane == v) { my_i = ii[v]; my_j = j; my_rem = rem; my_total = total; mX = X[v]; mN = Nn[v]; }
+                    if (lane / kCdfSub == v) { my_i = ii[v]; my_j = j; my_rem = rem; my_total = total; mX = X[v]; mN = Nn[v]; }
                 }
-                if (lane < kSelV && my_i >= 0) {
-                    int light = -1;
-                    float w = 0.f;
-                    if (my_total > 0.f && K > 0) {
-                        const float* col = cdf + lane * cdf_stride + my_j;  // col[32 m]: running sum of lane j's entries
-                        const float rem = fminf(my_rem, col[32 * (K - 1)]);
-                        int lo = 0, hi = K - 1;
-                        while (lo < hi) {
-                            const int mid = (lo + hi) >> 1;
-                            if (col[32 * mid] < rem) lo = mid + 1; else hi = mid;
-                        }
-                        const int off = (int)__ldg(list + my_j + 32 * lo);
-                        // the running sums only SELECT; the weight handed on is evaluated again, bit-identical to the sweep's
-                        w = light_weight_at(s, off, mX, mN);
-                        light = lsoa_light(off);
-                        if (!(w > 0.f) || light >= s.L) { light = -1; w = 0.f; }
+                const int t = lane & (kCdfSub - 1);
+                const bool mine = lane < kSelV * kCdfSub && my_i >= 0 && my_total > 0.f && K > 0;
+                float w = 0.f, start = 0.f;
+                int off = 0;
+                if (mine) {
+                    const float* col = cdf + (lane / kCdfSub) * cdf_stride + my_j;  // col[32 m]: running sum after the lane's position kCdfSub m + kCdfSub - 1
+                    int lo = 0, hi = M;                                             // first checkpoint >= rem; M: the tail group
+                    while (lo < hi) {
+                        const int mid = (lo + hi) >> 1;
+                        if (col[32 * mid] < my_rem) lo = mid + 1; else hi = mid;
                     }
-                    a.sel4[my_i] = make_float4(__int_as_float(light), w, my_total, 0.f);
+                    start = lo ? col[32 * (lo - 1)] : 0.f;
+                    const int it = kCdfSub * lo + t;
+                    if (it < K) {
+                        off = (int)__ldg(list + my_j + 32 * it);
+                        w = light_weight_at(s, off, mX, mN);
+                        if (!(w > 0.f) || lsoa_light(off) >= s.L) w = 0.f;
+                    }
+                }
+                // the first lane of each group collects the group's weights (all lanes shuffle) and walks them in list order
+                float wg[kCdfSub];
+                int og[kCdfSub];
+#pragma unroll
+                for (int q = 0; q < kCdfSub; q++) { wg[q] = __shfl_down_sync(kFull, w, q); og[q] = __shfl_down_sync(kFull, off, q); }
+                if (lane < kSelV * kCdfSub && t == 0 && my_i >= 0) {
+                    int light = -1;
+                    float wsel = 0.f, acc = start;
+                    bool found = false;
+#pragma unroll
+                    for (int q = 0; q < kCdfSub; q++) {
+                        if (wg[q] > 0.f && !found) {
+                            acc += wg[q];
+                            light = lsoa_light(og[q]); wsel = wg[q];  // the last survivor so far: the fallback against rounding
+                            found = acc >= my_rem;
+                        }
+                    }
+                    if (light < 0 && mine) {
+                        // rounding put the target past the last positive weight of the column's tail: take the column's last
+                        // survivor (rare: a backwards scan of the lane's positions)
+                        for (int it = K - 1; it >= 0 && light < 0; it--) {
+                            const int o2 = (int)__ldg(list + my_j + 32 * it);
+                            const float w2 = light_weight_at(s, o2, mX, mN);
+                            if (w2 > 0.f && lsoa_light(o2) < s.L) { light = lsoa_light(o2); wsel = w2; }
+                        }
+                    }
+                    a.sel4[my_i] = make_float4(__int_as_float(light), wsel, my_total, 0.f);
                 }
                 __syncwarp();  // the next group overwrites the columns
             } else {
@@ -1506,14 +1541,15 @@ int launch_bounce(bool first, bool exact, const BounceArgs& a, int grid, int sel
             k_lsel_offsets<<<1, 1024, 0, st>>>(a.lhist, a.s.nlists * kSelSub, a.sorted, a.ngroups);
             k_lsel_scatter<<<cgrid, 256, 0, st>>>(a);
             // running-sum columns in shared memory (kSelV x list_max floats per warp) while >= 3 blocks per SM still fit
-            const size_t dyn = (size_t)(kBlk / 32) * kSelV * (size_t)a.s.list_max * sizeof(float);
+            const int cdf_stride = ((a.s.list_max / 32 + kCdfSub - 1) / kCdfSub) * 32;  // checkpoints per column x 32 lanes
+            const size_t dyn = (size_t)(kBlk / 32) * kSelV * (size_t)cdf_stride * sizeof(float);
             const bool use_cdf = dyn > 0 && dyn <= 64 * 1024;
             if (use_cdf && dyn > 48 * 1024) cudaFuncSetAttribute(k_lightsel_sorted<STRAT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
             int sb = 1;
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sb, k_lightsel_sorted<STRAT>, kBlk, use_cdf ? dyn : 0);
             const int sgrid = std::min(std::max(1, (a.in_count + 127) / 128), 148 * std::max(1, sb / g_grid_div));
             cudaEventRecord(ev_sweep0, st);
-            k_lightsel_sorted<STRAT><<<sgrid, kBlk, use_cdf ? dyn : 0, st>>>(a, sel_cursor, use_cdf ? a.s.list_max : 0);
+            k_lightsel_sorted<STRAT><<<sgrid, kBlk, use_cdf ? dyn : 0, st>>>(a, sel_cursor, use_cdf ? cdf_stride : 0);
             cudaEventRecord(ev_sweep1, st);
             if (exact) k_shade<STRAT, false, true><<<grid, kBlk, 0, st>>>(a);
             else k_shade<STRAT, false, false><<<grid, kBlk, 0, st>>>(a);
