@@ -359,6 +359,7 @@ int mcpt_scene_create_ex(const McptSceneDesc* desc, int device, uint32_t build_f
         d.nodes4 = (const float4*)(db + B.off_nodes4);
         d.nodes8 = (const float4*)(db + B.off_nodes8); d.tris8 = (const float4*)(db + B.off_tris8);
         d.use8 = 0;
+        d.refill4 = kRefill4; d.refill8 = kRefill8;
         d.lnodes = (const float4*)(db + B.off_lnodes); d.ltris = (const float4*)(db + B.off_ltris);
         d.pverts = (const float4*)(db + B.off_pverts); d.pnorms = (const float4*)(db + B.off_pnorms);
         d.mats = (const float4*)(db + B.off_mats); d.lights = (const float4*)(db + B.off_lights);

@@ -1323,7 +1323,7 @@ __global__ void __launch_bounds__(kBlk) k_extend(DScene s, const float4* __restr
     __shared__ int stack[kStackSm * kBlk];
     const int n = *n_ptr;
     trace_stream<false>(
-        s.nodes4, s.tris, s.tmin, n, counter, stack + threadIdx.x, kBlk,
+        s.nodes4, s.tris, s.tmin, n, counter, stack + threadIdx.x, kBlk, s.refill4,
         [&](int i, f3& o, f3& d, int& exclude, float& tmax, int& init_prim) {
             const float4 qo = org[i], qd = dir[i];
             o = to_f3(qo); d = to_f3(qd);
@@ -1339,7 +1339,7 @@ __global__ void __launch_bounds__(kBlk) k_extend8(DScene s, const float4* __rest
     __shared__ uint2 stack[kStack8Sm * kBlk];
     const int n = *n_ptr;
     trace_stream8<false>(
-        s.nodes8, s.tris8, s.tmin, n, counter, stack + threadIdx.x, kBlk,
+        s.nodes8, s.tris8, s.tmin, n, counter, stack + threadIdx.x, kBlk, s.refill8,
         [&](int i, f3& o, f3& d, int& exclude, float& tmax, int& init_prim) {
             const float4 qo = org[i], qd = dir[i];
             o = to_f3(qo); d = to_f3(qd);
@@ -1354,7 +1354,7 @@ __global__ void __launch_bounds__(kBlk) k_shadow8(DScene s, const ShadowQueue sq
     const int n = *sq.count;
     if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(counters + CNT_SHADOW, (unsigned long long)n);
     trace_stream8<true>(
-        s.nodes8, s.tris8, s.tmin, n, counter, stack + threadIdx.x, kBlk,
+        s.nodes8, s.tris8, s.tmin, n, counter, stack + threadIdx.x, kBlk, s.refill8,
         [&](int i, f3& o, f3& d, int& exclude, float& tmax, int& init_prim) {
             const float4 qo = sq.org[i], qd = sq.dir[i];
             const int2 id = sq.ids[i];
@@ -1381,7 +1381,7 @@ __global__ void __launch_bounds__(kBlk) k_shadow(DScene s, const ShadowQueue sq,
     const int n = *sq.count;
     if (blockIdx.x == 0 && threadIdx.x == 0 && n) atomicAdd(counters + CNT_SHADOW, (unsigned long long)n);
     trace_stream<true>(
-        s.nodes4, s.tris, s.tmin, n, counter, stack + threadIdx.x, kBlk,
+        s.nodes4, s.tris, s.tmin, n, counter, stack + threadIdx.x, kBlk, s.refill4,
         [&](int i, f3& o, f3& d, int& exclude, float& tmax, int& init_prim) {
             const float4 qo = sq.org[i], qd = sq.dir[i];
             const int2 id = sq.ids[i];
@@ -1959,7 +1959,7 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
     int ext_grid = use8 ? ext_grid8 : ext_grid4, sh_grid = use8 ? sh_grid8 : sh_grid4;
     // The layout guess of scene creation (random rays) is settled on the first real bounce: the rays a render makes are
     // more coherent than the calibration batch, which shifts the balance towards the 4-wide nodes on some scenes (interior).
-    cudaEvent_t evm[3] = {nullptr, nullptr, nullptr};
+    cudaEvent_t evm[4] = {nullptr, nullptr, nullptr, nullptr};
     int lbps = 1;
     if (prm->strategy == MCPT_MIS) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&lbps, k_lightsel<MCPT_MIS>, kBlk, 0);
     else if (prm->strategy == MCPT_NEE_SPHERICAL) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&lbps, k_lightsel<MCPT_NEE_SPHERICAL>, kBlk, 0);
@@ -2054,13 +2054,19 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
                     // both layouts on the same queue (identical hits): time them, keep the faster from here on
                     for (auto& e : evm) if (!e) MCPT_CUDA(cudaEventCreate(&e));
                     const int need = (count * (tree ? 2 : 1) + kBlk - 1) / kBlk;
+                    // ... and the 8-wide kernel at the two ends of its refill-threshold range (bvh.h: kRefill8Lo / kRefill8Hi)
+                    DScene d_lo = scene->d, d_hi = scene->d;
+                    d_lo.refill8 = kRefill8Lo; d_hi.refill8 = kRefill8Hi;
                     MCPT_CUDA(cudaEventRecord(evm[0], st));
                     k_extend<<<std::min(ext_grid4, need), kBlk, 0, st>>>(scene->d, Q[0].org, Q[0].dir, d_count, d_ext_cursor, hit);
                     MCPT_CUDA(cudaEventRecord(evm[1], st));
                     MCPT_CUDA(cudaMemsetAsync(d_ext_cursor, 0, 4, st));
-                    k_extend8<<<std::min(ext_grid8, need), kBlk, 0, st>>>(scene->d, Q[0].org, Q[0].dir, d_count, d_ext_cursor, hit);
+                    k_extend8<<<std::min(ext_grid8, need), kBlk, 0, st>>>(d_lo, Q[0].org, Q[0].dir, d_count, d_ext_cursor, hit);
                     MCPT_CUDA(cudaEventRecord(evm[2], st));
-                    S.kernel_launches++;
+                    MCPT_CUDA(cudaMemsetAsync(d_ext_cursor, 0, 4, st));
+                    k_extend8<<<std::min(ext_grid8, need), kBlk, 0, st>>>(d_hi, Q[0].org, Q[0].dir, d_count, d_ext_cursor, hit);
+                    MCPT_CUDA(cudaEventRecord(evm[3], st));
+                    S.kernel_launches += 2;
                 } else if (exact) k_extend_exact<<<eg, kBlk, 0, st>>>(scene->d, Q[0].org, Q[0].dir, d_count, hit);
                 else if (use8) k_extend8<<<eg, kBlk, 0, st>>>(scene->d, Q[0].org, Q[0].dir, d_count, d_ext_cursor, hit);
                 else k_extend<<<eg, kBlk, 0, st>>>(scene->d, Q[0].org, Q[0].dir, d_count, d_ext_cursor, hit);
@@ -2081,13 +2087,16 @@ void render_wavefront(McptScene* scene, const McptCamera* cam, const McptRenderP
             if (!last) MCPT_CUDA(cudaMemcpyAsync((void*)h_count, d_count, 4, cudaMemcpyDeviceToHost, st));
             MCPT_CUDA(cudaStreamSynchronize(st));
             if (measuring) {
-                float t4 = 0.f, t8 = 0.f;
+                float t4 = 0.f, t8lo = 0.f, t8hi = 0.f;
                 cudaEventElapsedTime(&t4, evm[0], evm[1]);
-                cudaEventElapsedTime(&t8, evm[1], evm[2]);
+                cudaEventElapsedTime(&t8lo, evm[1], evm[2]);
+                cudaEventElapsedTime(&t8hi, evm[2], evm[3]);
+                const float t8 = std::min(t8lo, t8hi);
                 scene->render_ms[0] = t4; scene->render_ms[1] = t8;
+                scene->d.refill8 = t8hi < t8lo ? kRefill8Hi : kRefill8Lo;
                 use8 = t8 < t4;
                 scene->d.use8 = use8 ? 1 : 0;
-                a.s.use8 = scene->d.use8;
+                a.s.use8 = scene->d.use8; a.s.refill8 = scene->d.refill8;
                 scene->layout_final = true;
                 ext_grid = use8 ? ext_grid8 : ext_grid4; sh_grid = use8 ? sh_grid8 : sh_grid4;
                 measuring = false;

@@ -52,6 +52,7 @@ struct DScene {
     int32_t list_max;           // longest padded list (entries)
     int32_t P, L, C, M, Lpad;
     int32_t use8;  // trace kernels walk nodes8 / tris8 (large scenes) instead of nodes4 / tris
+    int32_t refill4, refill8;  // ray-stream tracers: idle lanes fetch new rays when fewer than this many lanes of the warp are traversing
     float tmin;  // FP32 leaf test: reject t < tmin (scene-scale aware stand-in for the reference's 1e-8)
 };
 

@@ -231,18 +231,17 @@ __device__ __forceinline__ HitD trace_exact(const float4* __restrict__ nodes, co
 
 // ---- ray-stream tracing with dynamic refill ---------------------------------------------------------------
 // The wavefront trace kernels (k_extend: closest hit, k_shadow: any hit) run persistent warps over a compact
-// array of rays.  A lane keeps its ray until the traversal ends; when fewer than kRefill lanes of the warp are
+// array of rays.  A lane keeps its ray until the traversal ends; when fewer than `refill` lanes of the warp (bvh.h: kRefill4 / kRefill8) are
 // still traversing, the idle lanes pull the next rays of the stream (one atomicAdd per refill, ballot/popc
 // ranks) instead of waiting for the slowest ray of their original group of 32 -- incoherent rays through a
 // deep BVH differ by an order of magnitude in node visits.  Results are written by ray index, so the order in
 // which rays finish is irrelevant.
 //   load(idx, o, d, exclude, tmax, init_prim)   fetches ray idx
 //   store(idx, hit)                             consumes its result
-constexpr int kRefill = 20;
 
 template <bool ANY, class Load, class Store>
 __device__ __forceinline__ void trace_stream(const float4* __restrict__ nodes, const float4* __restrict__ tris, float tmin, int n,
-                                             int* counter, int* stack_sm, int stack_stride, Load load, Store store)
+                                             int* counter, int* stack_sm, int stack_stride, int refill, Load load, Store store)
 {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -256,7 +255,7 @@ __device__ __forceinline__ void trace_stream(const float4* __restrict__ nodes, c
     best.prim = -1; best.b = best.g = 0.f; best.t = 0.f;
     for (;;) {
         const unsigned act = __ballot_sync(full, active);
-        if (more && __popc(act) < kRefill) {
+        if (more && __popc(act) < refill) {
             const unsigned idle = ~act;
             int base = 0;
             if (lane == 0) base = atomicAdd(counter, __popc(idle));
@@ -356,7 +355,7 @@ __device__ __forceinline__ void trace_stream(const float4* __restrict__ nodes, c
                 active = false;
             }
             const unsigned m = __ballot_sync(full, active);
-            if (m == 0u || (more && __popc(m) < kRefill)) break;
+            if (m == 0u || (more && __popc(m) < refill)) break;
         }
     }
 }
@@ -405,7 +404,7 @@ __device__ __forceinline__ float byte_f(unsigned w, int i)
 
 template <bool ANY, class Load, class Store>
 __device__ __forceinline__ void trace_stream8(const float4* __restrict__ nodes8, const float4* __restrict__ tris8, float tmin, int n,
-                                              int* counter, uint2* stack_sm, int stack_stride, Load load, Store store)
+                                              int* counter, uint2* stack_sm, int stack_stride, int refill, Load load, Store store)
 {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -420,7 +419,7 @@ __device__ __forceinline__ void trace_stream8(const float4* __restrict__ nodes8,
     best.prim = -1; best.b = best.g = 0.f; best.t = 0.f;
     for (;;) {
         const unsigned act = __ballot_sync(full, active);
-        if (more && __popc(act) < kRefill) {
+        if (more && __popc(act) < refill) {
             const unsigned idle = ~act;
             int base = 0;
             if (lane == 0) base = atomicAdd(counter, __popc(idle));
@@ -522,7 +521,7 @@ __device__ __forceinline__ void trace_stream8(const float4* __restrict__ nodes8,
                 active = false;
             }
             const unsigned m = __ballot_sync(full, active);
-            if (m == 0u || (more && __popc(m) < kRefill)) break;
+            if (m == 0u || (more && __popc(m) < refill)) break;
         }
     }
 }
