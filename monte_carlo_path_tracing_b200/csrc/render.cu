@@ -944,7 +944,7 @@ struct Child { f3 o, d, thr; int exclude; uint64_t node; float misw; };
 // later bounces, 17.8 at the first).
 constexpr int kChunk = 256;  // queue entries per warp ticket / staging window (128: veach-mis 1378 instead of 1399 Msamples/s)
 #ifndef MCPT_SHADE_MINBLK
-#define MCPT_SHADE_MINBLK 1
+#define MCPT_SHADE_MINBLK 6
 #endif
 // EXACT (MCPT_LEAF_EXACT): the two ray/triangle tests k_shade makes itself -- the sampled light point's distance and the
 // MIS light-only ray -- go through the reference's FP64 test like every other ray of the render.
