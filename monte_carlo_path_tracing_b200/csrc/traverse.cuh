@@ -368,7 +368,10 @@ __device__ __forceinline__ void trace_stream(const float4* __restrict__ nodes, c
 // byte-to-float conversion.  Children are visited in octant order (slot ^ ray octant, highest first) taken straight from
 // the bit positions of the hit mask -- no distance sort.  State per lane: a node group G = (first child node, hit bits
 // 24..31 | inner-child mask) and a triangle group T = (first triangle, hit bits 0..23); the stack holds node groups.
-constexpr int kStack8Sm = 6;
+#ifndef MCPT_STACK8_SM
+#define MCPT_STACK8_SM 6
+#endif
+constexpr int kStack8Sm = MCPT_STACK8_SM;
 struct TStack8 {
     uint2* sm;
     int stride, sp;
