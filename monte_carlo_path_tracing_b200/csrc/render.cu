@@ -477,6 +477,34 @@ __global__ void __launch_bounds__(kBlk, MCPT_SEL_MINBLK) k_lightsel(const Bounce
             if (lane == 0) a.sel4[ii[v]] = make_float4(__int_as_float(pk.light), pk.w, total, 0.f);
         }
     };
+    // few lights: up to 63 waiting vertices per warp (position | uniform, normal | queue index)
+    __shared__ float4 sm_wait[(kBlk / 32) * 64 * 2];
+    float4* wbuf = sm_wait + (threadIdx.x >> 5) * 128;
+    int q_n = 0;
+    // one vertex per lane: the whole (short) table, two lights per packed evaluation (bit-identical to light_weight_fast),
+    // selection in the same pass by weighted reservoir sampling with ONE recycled uniform -- P(l) = w_l / weights_sum exactly
+    auto serial_pick = [&](const float4* e) {
+        const float4 e0 = e[0], e1 = e[1];
+        const f3 p = mk<float>(e0.x, e0.y, e0.z), N = mk<float>(e1.x, e1.y, e1.z);
+        int chosen = -1;
+        float wsum = 0.f, wch = 0.f;
+        float uu = fminf(e0.w, 0.99999994f);
+        for (int l = 0; l < s.L; l += 2) {
+            const float2 w2 = light_weight_2lights(sm_lp + (l >> 1) * kLightPairFields, p, N);
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const float w = h ? w2.y : w2.x;
+                if (w > 0.f && l + h < s.L) {
+                    wsum += w;
+                    const float pr = __fdividef(w, wsum);
+                    if (uu < pr) { chosen = l + h; wch = w; uu = __fdividef(uu, pr); }
+                    else uu = __fdividef(uu - pr, 1.f - pr);
+                    uu = fminf(fmaxf(uu, 0.f), 0.99999994f);
+                }
+            }
+        }
+        a.sel4[__float_as_int(e1.w)] = make_float4(__int_as_float(chosen), wch, wsum, 0.f);
+    };
     int next = 0;
     if (lane == 0) next = atomicAdd(cursor, 1);
     for (;;) {
@@ -508,30 +536,22 @@ __global__ void __launch_bounds__(kBlk, MCPT_SEL_MINBLK) k_lightsel(const Bounce
         if (s.L <= kSerialLights) {
             // Few lights: the warp-cooperative sweep would spend most of its instructions on broadcasts, scans and the
             // second pass (measured on the 16-light interior: 13 ms per 32-spp pass).  Each lane walks the whole table
-            // for its own vertex instead (all lanes read the same light: broadcast loads) and selects in the same pass
-            // by weighted reservoir sampling with ONE recycled uniform -- P(l) = w_l / weights_sum exactly.
-            int chosen = -1;
-            float wsum = 0.f, wch = 0.f;
+            // for ONE vertex instead (serial_pick below).  Only ~60 % of the entries of a chunk sample a light, so the
+            // sampling vertices are first collected in the warp's buffer and served 32 at a time, all lanes busy.
+            if (i < a.in_count && !need) a.sel4[i] = make_float4(__int_as_float(-1), 0.f, 0.f, 0.f);
+            const unsigned mneed = __ballot_sync(kFull, need);
             if (need) {
-                float uu = fminf(u, 0.99999994f);
-                for (int l = 0; l < s.L; l += 2) {
-                    // lights l and l + 1 in one packed evaluation (bit-identical to light_weight_fast), then the two
-                    // reservoir steps in table order
-                    const float2 w2 = light_weight_2lights(sm_lp + (l >> 1) * kLightPairFields, p, N);
-#pragma unroll
-                    for (int h = 0; h < 2; h++) {
-                        const float w = h ? w2.y : w2.x;
-                        if (w > 0.f && l + h < s.L) {
-                            wsum += w;
-                            const float pr = __fdividef(w, wsum);
-                            if (uu < pr) { chosen = l + h; wch = w; uu = __fdividef(uu, pr); }
-                            else uu = __fdividef(uu - pr, 1.f - pr);
-                            uu = fminf(fmaxf(uu, 0.f), 0.99999994f);
-                        }
-                    }
-                }
+                float4* e = wbuf + 2 * (q_n + __popc(mneed & ((1u << lane) - 1u)));
+                e[0] = make_float4(p.x, p.y, p.z, u);
+                e[1] = make_float4(N.x, N.y, N.z, __int_as_float(i));
             }
-            if (i < a.in_count) a.sel4[i] = make_float4(__int_as_float(chosen), wch, wsum, 0.f);
+            q_n += __popc(mneed);
+            __syncwarp();
+            if (q_n >= 32) {
+                q_n -= 32;
+                serial_pick(wbuf + 2 * (q_n + lane));
+                __syncwarp();
+            }
             continue;
         }
         if (i < a.in_count && !need) a.sel4[i] = make_float4(__int_as_float(-1), 0.f, 0.f, 0.f);
@@ -548,6 +568,7 @@ __global__ void __launch_bounds__(kBlk, MCPT_SEL_MINBLK) k_lightsel(const Bounce
         }
     }
     if (pend) sweep_pair(PX, PN, Pu, Pi, false, PX, PN, Pu, Pi);
+    if (lane < q_n) serial_pick(wbuf + 2 * lane);  // few lights: what is left in the warp's buffer
     if (lane == 0 && c_evals) atomicAdd(a.counters + CNT_EVALS, (unsigned long long)c_evals * 32);
 }
 
