@@ -253,14 +253,14 @@ def run_reference(args, wl_name, wl):
 
 
 def shade_flop_constants():
-    """FP32 flops per unit of work of the shading kernels, from the committed ncu capture (profiles/r2k_flops.json:
+    """FP32 flops per unit of work of the shading kernels, from the committed ncu capture (profiles/r3b_flops.json:
     thread-level SASS instruction counts by opcode from `ncu --set full --import-source on`, FFMA = 2 flops, FFMA2 = 4,
     FADD / FMUL = 1, FADD2 / FMUL2 = 2, MUFU = 1, divided by the units the captured launch processed).  Falls back to
     the hand count of lights.cuh (81 flops + 4 MUFU + ~5 min/max per light and vertex; ~320 per shaded vertex)."""
-    p = os.path.join(ROOT, "profiles", "r2k_flops.json")
+    p = os.path.join(ROOT, "profiles", "r3b_flops.json")
     try:
         j = json.load(open(p))
-        return float(j["flops_per_light_vertex"]), float(j["flops_per_shade_element"]), "ncu: profiles/r2k_flops.json"
+        return float(j["flops_per_light_vertex"]), float(j["flops_per_shade_element"]), "ncu: profiles/r3b_flops.json"
     except Exception:
         return 90.0, 320.0, "hand count (lights.cuh)"
 
