@@ -64,7 +64,10 @@ constexpr int kBvhStackDepth = 64;  // traversal stack entries; the builder fall
 // Refill thresholds of the ray-stream tracers (traverse.cuh): measured per layout, r2y -- the short traversals of the 4-wide
 // kernels want a low one (veach-mis trace side 25.2 -> 24.0 ms at 14 instead of 20, interior flat), the compressed 8-wide kernel
 // wants 20 on cornell-box and 29 on the 1 M-triangle soup (+6 %): the 8-wide value is settled per scene with the layout.
-constexpr int kRefill4 = 14, kRefill8 = 24, kRefill8Lo = 20, kRefill8Hi = 28;
+#ifndef MCPT_REFILL8_HI
+#define MCPT_REFILL8_HI 28
+#endif
+constexpr int kRefill4 = 14, kRefill8 = 24, kRefill8Lo = 20, kRefill8Hi = MCPT_REFILL8_HI;
 constexpr int kBvh8StackDepth = 32; // node-group entries of the 8-wide traversal: at most one pending group per level
 static_assert(kBvhMaxLeaf <= 6, "emit_wide8 splits a leaf into two slots of at most 3 triangles");
 

@@ -239,6 +239,14 @@ __device__ __forceinline__ HitD trace_exact(const float4* __restrict__ nodes, co
 //   load(idx, o, d, exclude, tmax, init_prim)   fetches ray idx
 //   store(idx, hit)                             consumes its result
 
+#ifndef MCPT_VOTE_A
+#define MCPT_VOTE_A 1
+#define MCPT_VOTE_B 1
+#endif
+#ifndef MCPT_VOTE8_A
+#define MCPT_VOTE8_A 1
+#define MCPT_VOTE8_B 4
+#endif
 template <bool ANY, class Load, class Store>
 __device__ __forceinline__ void trace_stream(const float4* __restrict__ nodes, const float4* __restrict__ tris, float tmin, int n,
                                              int* counter, int* stack_sm, int stack_stride, int refill, Load load, Store store)
@@ -291,7 +299,7 @@ __device__ __forceinline__ void trace_stream(const float4* __restrict__ nodes, c
             const bool at_inner = active && node >= 0, at_leaf = active && node < 0;
             const unsigned mi = __ballot_sync(full, at_inner), ml = __ballot_sync(full, at_leaf);
             bool done = false;
-            if (__popc(mi) >= __popc(ml)) {
+            if (MCPT_VOTE_A * __popc(mi) >= MCPT_VOTE_B * __popc(ml)) {
                 if (at_inner) {
                     // 4-wide node (bvh.h nodes4): seven 16-byte vectors, child k in component k.  The ray's direction
                     // signs pick the near and the far plane of every slab by ADDRESS (lo and hi planes are neighbouring
@@ -455,7 +463,7 @@ __device__ __forceinline__ void trace_stream8(const float4* __restrict__ nodes8,
             const bool at_leaf = active && T.y != 0u, at_inner = active && T.y == 0u;
             const unsigned mi = __ballot_sync(full, at_inner), ml = __ballot_sync(full, at_leaf);
             bool done = false;
-            if (__popc(mi) >= __popc(ml)) {
+            if (MCPT_VOTE8_A * __popc(mi) >= MCPT_VOTE8_B * __popc(ml)) {
                 if (at_inner) {
                     // nearest pending child of G in octant order = highest hit bit
                     const unsigned hits = G.y & 0xff000000u;
