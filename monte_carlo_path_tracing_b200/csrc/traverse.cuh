@@ -402,15 +402,17 @@ struct TStack8 {
 // byte i of w as a float.  MCPT_BYTE_MAGIC: one PRMT drops the byte into the mantissa of 2^23 and one FADD takes 2^23
 // off again (both full rate) instead of the I2F conversion.
 #ifndef MCPT_BYTE_MAGIC
-#define MCPT_BYTE_MAGIC 0
+#define MCPT_BYTE_MAGIC 2
 #endif
-__device__ __forceinline__ float byte_f(unsigned w, int i)
+__device__ __forceinline__ float byte_f_magic(unsigned w, int i) { return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7650u + (unsigned)i)) - 8388608.0f; }
+__device__ __forceinline__ float byte_f_cvt(unsigned w, int i) { return (float)((w >> (8 * i)) & 0xffu); }
+// MCPT_BYTE_MAGIC = how many of the six plane conversions of a child use PRMT + FADD instead of I2F, in the order far z, far y,
+// far x, near z, near y, near x (0 = all I2F, 6 = none): the 48 conversions of a visit keep the XU pipe 65 % busy, the magic form
+// moves some of them to the ALU / FMA pipes.
+template <int PLANE> __device__ __forceinline__ float byte_f(unsigned w, int i)
 {
-#if MCPT_BYTE_MAGIC
-    return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7650u + (unsigned)i)) - 8388608.0f;
-#else
-    return (float)((w >> (8 * i)) & 0xffu);
-#endif
+    if (PLANE < MCPT_BYTE_MAGIC) return byte_f_magic(w, i);
+    return byte_f_cvt(w, i);
 }
 
 template <bool ANY, class Load, class Store>
@@ -494,10 +496,10 @@ __device__ __forceinline__ void trace_stream8(const float4* __restrict__ nodes8,
                         const unsigned nz = (oct & 4u) ? qhz : qlz, fz = (oct & 4u) ? qlz : qhz;
 #pragma unroll
                         for (int i = 0; i < 4; i++) {
-                            const float tn = fmaxf(fmaxf(__fmaf_rn(byte_f(nx, i), sx, bx), __fmaf_rn(byte_f(ny, i), sy, by)),
-                                                   fmaxf(__fmaf_rn(byte_f(nz, i), sz, bz), 0.f));
-                            const float tf = fminf(fminf(__fmaf_rn(byte_f(fx, i), sx, bx), __fmaf_rn(byte_f(fy, i), sy, by)),
-                                                   fminf(__fmaf_rn(byte_f(fz, i), sz, bz), best.t));
+                            const float tn = fmaxf(fmaxf(__fmaf_rn(byte_f<5>(nx, i), sx, bx), __fmaf_rn(byte_f<4>(ny, i), sy, by)),
+                                                   fmaxf(__fmaf_rn(byte_f<3>(nz, i), sz, bz), 0.f));
+                            const float tf = fminf(fminf(__fmaf_rn(byte_f<2>(fx, i), sx, bx), __fmaf_rn(byte_f<1>(fy, i), sy, by)),
+                                                   fminf(__fmaf_rn(byte_f<0>(fz, i), sz, bz), best.t));
                             if (tn <= tf) hitmask |= ((cnt4 >> (8 * i)) & 0xffu) << ((bit4 >> (8 * i)) & 0xffu);
                         }
                     }
