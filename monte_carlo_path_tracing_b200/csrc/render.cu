@@ -8,8 +8,11 @@
 //   k_lightprep spherical strategies: the O(L) light-weight sweep of the first vertex, once per pixel PAIR, and the
 //               per-sample light draws from its CDF
 //   then per bounce, over the dense ray queue Q[0] and the hit records k_extend left for it:
-//   k_lightsel  spherical strategies, later vertices: warp-cooperative exact O(L) selection -> sel4[i]
-//               (k_lighttree instead with MCPT_LIGHT_TREE)
+//   k_lsel_classify / _offsets / _scatter + k_lightsel_sorted
+//               spherical strategies, later vertices, scenes with per-primitive survivor lists (light_lists.h: > 32
+//               lights): the sampling vertices grouped by list, packed sweeps of four vertices per list -> sel4[i]
+//   k_lightsel  the same selection without lists: warp-cooperative sweep of the whole table, or (<= 32 lights) one vertex
+//               per lane over the table in shared memory       (k_lighttree instead with MCPT_LIGHT_TREE)
 //   k_shade     shade prologue (main.cpp:273-288), Russian roulette, light and BRDF sampling, the MIS light-only ray;
 //               children are packed with __ballot_sync / popc prefix sums into the chunk's window of the staging
 //               queue Q[1], visibility rays with their pending contributions go to the shadow queue
