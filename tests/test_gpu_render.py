@@ -88,8 +88,13 @@ def test_full_size_properties(cornell_full):
     full, st = s.render(cam, api.NEE_UNIFORM, 16, **kw)
     again, _ = s.render(cam, api.NEE_UNIFORM, 16, **kw)
     assert np.array_equal(full, again)  # deterministic: counter-based RNG, atomic-free accumulation
-    small_batch, _ = s.render(cam, api.NEE_UNIFORM, 16, batch_spp=3, **kw)
+    small_batch, st_small = s.render(cam, api.NEE_UNIFORM, 16, batch_spp=3, **kw)
     assert np.array_equal(full, small_batch)  # the film adds its samples one by one in sample order, whatever the pass size
+    # the visibility-ray queue is filled through per-warp reservations whose unused tails are holes: they are counted and
+    # taken off, so the ray counters do not depend on how many passes (and reservations) a render was made of
+    for k in ("rays_shadow", "rays_closest", "vertices", "primary_hits"):
+        assert st[k] == st_small[k], (k, st[k], st_small[k])
+    assert 0 < st["rays_shadow"] <= st["vertices"]
     # spp sharding: samples [0,8) and [8,16) rendered separately, each normalised by the global 16
     lo, _ = s.render(cam, api.NEE_UNIFORM, 8, spp_offset=0, spp_total=16, **kw)
     hi, _ = s.render(cam, api.NEE_UNIFORM, 8, spp_offset=8, spp_total=16, **kw)
